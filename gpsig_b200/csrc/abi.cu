@@ -1,0 +1,305 @@
+// extern "C" entry points of libgpsig_b200.so (see include/gpsig_b200.h).
+#include <stdarg.h>
+#include <string.h>
+
+#include "pde_kernel.cuh"
+#include "tens_kernels.cuh"
+#include "trunc_kernel.cuh"
+
+namespace gpsig {
+
+static thread_local char g_err[512] = "";
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+// explicit instantiations live in trunc_inst.cu / tens_inst.cu (one object per T, OP, DP)
+#define GPSIG_DECL(T, OP, DP)                                                             \
+  extern template int launch_trunc<T, OP, DP>(const TruncParams&, cudaStream_t);          \
+  extern template int launch_tens_vs_seq<T, OP, DP>(const TensSeqParams&, int, cudaStream_t);
+#define GPSIG_DECL_T(T) \
+  GPSIG_DECL(T, 0, 4) GPSIG_DECL(T, 0, 8) GPSIG_DECL(T, 0, 16) \
+  GPSIG_DECL(T, 1, 4) GPSIG_DECL(T, 1, 8) GPSIG_DECL(T, 1, 16) \
+  GPSIG_DECL(T, 2, 4) GPSIG_DECL(T, 2, 8) GPSIG_DECL(T, 2, 16)
+GPSIG_DECL_T(float)
+GPSIG_DECL_T(double)
+
+static int op_of_base(int base) {
+  return base == GPSIG_BASE_LINEAR ? OP_LINEAR : (base == GPSIG_BASE_RBF ? OP_RBF : OP_GENERIC);
+}
+
+template <typename T>
+static int dispatch_trunc(const TruncParams& P, int base, int DP, cudaStream_t s) {
+  const int op = op_of_base(base);
+#define GPSIG_GO(OP) (DP == 4 ? launch_trunc<T, OP, 4>(P, s) : DP == 8 ? launch_trunc<T, OP, 8>(P, s) : launch_trunc<T, OP, 16>(P, s))
+  return op == OP_LINEAR ? GPSIG_GO(0) : (op == OP_RBF ? GPSIG_GO(1) : GPSIG_GO(2));
+#undef GPSIG_GO
+}
+template <typename T>
+static int dispatch_tens_seq(const TensSeqParams& P, int base, int DP, int m, cudaStream_t s) {
+  const int op = op_of_base(base);
+#define GPSIG_GO(OP) (DP == 4 ? launch_tens_vs_seq<T, OP, 4>(P, m, s) : DP == 8 ? launch_tens_vs_seq<T, OP, 8>(P, m, s) : launch_tens_vs_seq<T, OP, 16>(P, m, s))
+  return op == OP_LINEAR ? GPSIG_GO(0) : (op == OP_RBF ? GPSIG_GO(1) : GPSIG_GO(2));
+#undef GPSIG_GO
+}
+
+static int check_desc(const gpsig_trunc_desc* d) {
+  if (!d) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "desc is NULL");
+  if (d->base < GPSIG_BASE_LINEAR || d->base > GPSIG_BASE_MATERN52)
+    GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "unknown base kernel id %d", d->base);
+  if (d->num_levels < 1) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "num_levels must be >= 1 (got %d)", d->num_levels);
+  if (d->num_levels > 8) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "num_levels=%d > 8 is not supported", d->num_levels);
+  if (d->order != 1)
+    GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "order=%d: only the first-order recursion (order=1) is built into this library", d->order);
+  return GPSIG_OK;
+}
+
+template <typename T>
+static int pack(const T* X, int N, int L, int d, const T* ls, T* dst, cudaStream_t s) {
+  const size_t tot = (size_t)N * L;
+  if (tot == 0) return GPSIG_OK;
+  const int threads = 256;
+  const size_t blocks = (tot + threads - 1) / threads;
+  pack_sequences_kernel<T><<<(unsigned)blocks, threads, 0, s>>>(X, N, L, d, padded_dim(d), ls, dst, seq_block_elems(L, d, sizeof(T)));
+  GPSIG_LAUNCH_CHECK("pack_sequences_kernel");
+  return GPSIG_OK;
+}
+
+static size_t packed_bytes(int N, int L, int d, int elem) {
+  return align_up((size_t)N * seq_block_elems(L, d, elem) * elem, 128);
+}
+
+template <typename T>
+static int trunc_gram_impl(const gpsig_trunc_desc* desc, const T* X, int N, int L, const T* X2, int N2, int L2, int d,
+                           const T* ls, int row_begin, int row_end, const gpsig_epilogue* epi, T* out,
+                           void* ws, size_t ws_bytes, void* stream) {
+  if (int rc = check_desc(desc)) return rc;
+  const bool sym = X2 == nullptr;
+  if (sym) { N2 = N; L2 = L; }
+  if (!X || !out) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "X/out must not be NULL");
+  if (N < 0 || N2 < 0 || d < 1) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "bad sizes N=%d N2=%d d=%d", N, N2, d);
+  if (d > 16) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "state dimension d=%d > 16 is not supported", d);
+  const int minlen = desc->difference ? 2 : 1;
+  if (L < minlen || L2 < minlen) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "sequences too short (L=%d, L2=%d)", L, L2);
+  if (row_begin < 0 || row_end > N || row_begin > row_end)
+    GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "bad row range [%d, %d) for N=%d", row_begin, row_end, N);
+  if (epi && ((epi->norm_x == nullptr) != (epi->norm_x2 == nullptr)))
+    GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "norm_x and norm_x2 must be given together");
+  if (row_begin == row_end || N2 == 0) return GPSIG_OK;
+  const size_t need = gpsig_trunc_gram_workspace_bytes(N, L, sym ? 0 : N2, L2, d, sizeof(T));
+  if (!ws || ws_bytes < need || (reinterpret_cast<uintptr_t>(ws) & 15))
+    GPSIG_FAIL(GPSIG_ERR_WORKSPACE, "workspace too small or misaligned: need %zu bytes (16-byte aligned), got %zu", need, ws_bytes);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  T* xp = static_cast<T*>(ws);
+  T* yp = sym ? xp : reinterpret_cast<T*>(static_cast<char*>(ws) + packed_bytes(N, L, d, sizeof(T)));
+  if (int rc = pack<T>(X, N, L, d, ls, xp, s)) return rc;
+  if (!sym) if (int rc = pack<T>(X2, N2, L2, d, ls, yp, s)) return rc;
+
+  TruncParams P;
+  memset(&P, 0, sizeof(P));
+  P.xp = xp; P.yp = yp;
+  P.xblk = seq_block_elems(L, d, sizeof(T)); P.yblk = seq_block_elems(L2, d, sizeof(T));
+  P.N = N; P.N2 = N2; P.L = L; P.L2 = L2;
+  P.row_begin = row_begin; P.row_end = row_end;
+  P.m = desc->num_levels; P.difference = desc->difference;
+  P.symmetric = sym; P.diag = 0;
+  P.p0 = desc->base_params[0]; P.p1 = desc->base_params[1]; P.base = desc->base;
+  if (epi) {
+    P.norm_x = epi->norm_x; P.norm_x2 = epi->norm_x2; P.level_scale = epi->level_scale;
+    P.sym_jitter = epi->sym_jitter; P.return_levels = epi->return_levels;
+  } else P.return_levels = 1;
+  P.out = out;
+  return dispatch_trunc<T>(P, desc->base, padded_dim(d), s);
+}
+
+template <typename T>
+static int trunc_diag_impl(const gpsig_trunc_desc* desc, const T* X, int N, int L, int d, const T* ls, T* out,
+                           void* ws, size_t ws_bytes, void* stream) {
+  if (int rc = check_desc(desc)) return rc;
+  if (!X || !out) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "X/out must not be NULL");
+  if (d < 1 || d > 16) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "state dimension d=%d is not supported (1..16)", d);
+  if (L < (desc->difference ? 2 : 1)) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "sequences too short (L=%d)", L);
+  if (N == 0) return GPSIG_OK;
+  const size_t need = gpsig_trunc_diag_workspace_bytes(N, L, d, sizeof(T));
+  if (!ws || ws_bytes < need || (reinterpret_cast<uintptr_t>(ws) & 15))
+    GPSIG_FAIL(GPSIG_ERR_WORKSPACE, "workspace too small or misaligned: need %zu bytes, got %zu", need, ws_bytes);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  T* xp = static_cast<T*>(ws);
+  if (int rc = pack<T>(X, N, L, d, ls, xp, s)) return rc;
+  TruncParams P;
+  memset(&P, 0, sizeof(P));
+  P.xp = xp; P.yp = xp;
+  P.xblk = P.yblk = seq_block_elems(L, d, sizeof(T));
+  P.N = N; P.N2 = N; P.L = L; P.L2 = L;
+  P.row_begin = 0; P.row_end = N;
+  P.m = desc->num_levels; P.difference = desc->difference;
+  P.symmetric = 1; P.diag = 1; P.return_levels = 1;
+  P.p0 = desc->base_params[0]; P.p1 = desc->base_params[1]; P.base = desc->base;
+  P.out = out;
+  return dispatch_trunc<T>(P, desc->base, padded_dim(d), s);
+}
+
+template <typename T>
+static int tens_vs_seq_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, int increments, const T* X, int N, int L,
+                            int d, const T* ls, int col_begin, int col_end, const gpsig_epilogue* epi, T* out,
+                            void* ws, size_t ws_bytes, void* stream) {
+  if (int rc = check_desc(desc)) return rc;
+  if (!Z || !X || !out) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "Z/X/out must not be NULL");
+  if (d < 1 || d > 16) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "state dimension d=%d is not supported (1..16)", d);
+  if (L < (desc->difference ? 2 : 1)) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "sequences too short (L=%d)", L);
+  if (col_begin < 0 || col_end > N || col_begin > col_end)
+    GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "bad column range [%d, %d) for N=%d", col_begin, col_end, N);
+  if (col_begin == col_end || Mz == 0) return GPSIG_OK;
+  const int m = desc->num_levels, TT = m * (m + 1) / 2, zs = increments ? 2 : 1;
+  const size_t need = gpsig_tens_vs_seq_workspace_bytes(Mz, increments, N, L, d, m, sizeof(T));
+  if (!ws || ws_bytes < need || (reinterpret_cast<uintptr_t>(ws) & 15))
+    GPSIG_FAIL(GPSIG_ERR_WORKSPACE, "workspace too small or misaligned: need %zu bytes, got %zu", need, ws_bytes);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  T* zp = static_cast<T*>(ws);
+  T* xp = reinterpret_cast<T*>(static_cast<char*>(ws) + packed_bytes(TT * Mz, zs, d, sizeof(T)));
+  if (int rc = pack<T>(Z, TT * Mz, zs, d, ls, zp, s)) return rc;
+  if (int rc = pack<T>(X, N, L, d, ls, xp, s)) return rc;
+  TensSeqParams P;
+  memset(&P, 0, sizeof(P));
+  P.zp = zp; P.xp = xp;
+  P.zblk = seq_block_elems(zs, d, sizeof(T)); P.xblk = seq_block_elems(L, d, sizeof(T));
+  P.Mz = Mz; P.zs = zs; P.N = N; P.L = L; P.m = m; P.col_begin = col_begin; P.col_end = col_end;
+  P.difference = desc->difference;
+  P.p0 = desc->base_params[0]; P.p1 = desc->base_params[1]; P.base = desc->base;
+  if (epi) { P.norm_x = epi->norm_x2; P.level_scale = epi->level_scale; P.return_levels = epi->return_levels; }
+  else P.return_levels = 1;
+  P.out = out;
+  return dispatch_tens_seq<T>(P, desc->base, padded_dim(d), m, s);
+}
+
+template <typename T>
+static int tens_tens_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, int increments, int d, const T* ls,
+                          const gpsig_epilogue* epi, T* out, void* stream) {
+  if (int rc = check_desc(desc)) return rc;
+  if (!Z || !out) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "Z/out must not be NULL");
+  if (Mz == 0) return GPSIG_OK;
+  TensTensParams P;
+  memset(&P, 0, sizeof(P));
+  P.Z = Z; P.ls = ls; P.Mz = Mz; P.zs = increments ? 2 : 1; P.m = desc->num_levels; P.d = d;
+  P.p0 = desc->base_params[0]; P.p1 = desc->base_params[1]; P.base = desc->base;
+  if (epi) { P.level_scale = epi->level_scale; P.return_levels = epi->return_levels; } else P.return_levels = 1;
+  P.out = out;
+  dim3 grid((Mz + 127) / 128, Mz);
+  tens_tens_kernel<T><<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(P);
+  GPSIG_LAUNCH_CHECK("tens_tens_kernel");
+  return GPSIG_OK;
+}
+
+static int pde_impl(const double* X, int N, int L, const double* Y, int N2, int L2, int d, const double* ls,
+                    int order, int pair_mode, int row_begin, int row_end, double sigma, double* out,
+                    void* ws, size_t ws_bytes, void* stream) {
+  if (!X || !out) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "X/out must not be NULL");
+  const bool same = Y == nullptr;
+  if (same) { N2 = N; L2 = L; }
+  if (d < 1 || d > 16) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "state dimension d=%d is not supported (1..16)", d);
+  if (L < 2 || L2 < 2) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "sequences too short (L=%d, L2=%d)", L, L2);
+  if (order < 0 || order > 6) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "dyadic order %d is not supported (0..6)", order);
+  if (pair_mode != GPSIG_PDE_DIAG && pair_mode != GPSIG_PDE_GRAM) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "bad pair_mode %d", pair_mode);
+  if (pair_mode == GPSIG_PDE_DIAG && N2 != N) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "diagonal pairing needs N == N2 (%d vs %d)", N, N2);
+  if (row_begin < 0 || row_end > N || row_begin > row_end)
+    GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "bad row range [%d, %d) for N=%d", row_begin, row_end, N);
+  if (row_begin == row_end || N2 == 0) return GPSIG_OK;
+  const size_t need = gpsig_pde_workspace_bytes(N, L, same ? 0 : N2, L2, d, order, pair_mode);
+  if (!ws || ws_bytes < need || (reinterpret_cast<uintptr_t>(ws) & 15))
+    GPSIG_FAIL(GPSIG_ERR_WORKSPACE, "workspace too small or misaligned: need %zu bytes, got %zu", need, ws_bytes);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  double* xp = static_cast<double*>(ws);
+  double* yp = same ? xp : reinterpret_cast<double*>(static_cast<char*>(ws) + packed_bytes(N, L, d, 8));
+  if (int rc = pack<double>(X, N, L, d, ls, xp, s)) return rc;
+  if (!same) if (int rc = pack<double>(Y, N2, L2, d, ls, yp, s)) return rc;
+  PdeParams P;
+  memset(&P, 0, sizeof(P));
+  P.xp = xp; P.yp = yp; P.xblk = seq_block_elems(L, d, 8); P.yblk = seq_block_elems(L2, d, 8);
+  P.N = N; P.N2 = N2; P.L = L; P.L2 = L2; P.DP = padded_dim(d); P.order = order; P.pair_mode = pair_mode;
+  P.row_begin = row_begin; P.row_end = row_end; P.sigma = sigma; P.out = out;
+  const size_t smem = pde_smem_bytes(L, L2, P.DP, order);
+  if (smem > kMaxSmem)
+    GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "PDE grid too large for the on-chip plan: %zu bytes of shared memory (L=%d, L2=%d, order=%d)", smem, L, L2, order);
+  const size_t npairs = pair_mode == GPSIG_PDE_DIAG ? (size_t)(row_end - row_begin) : (size_t)(row_end - row_begin) * N2;
+  if (npairs > 0x7fffffffull) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "too many pairs in one call (%zu)", npairs);
+#define GPSIG_PDE_GO(DP_, O_) do { auto kern = pde_wavefront_kernel<DP_, O_>; \
+    GPSIG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    kern<<<(unsigned)npairs, 32, smem, s>>>(P); } while (0)
+#define GPSIG_PDE_DP(O_) do { if (P.DP == 4) GPSIG_PDE_GO(4, O_); else if (P.DP == 8) GPSIG_PDE_GO(8, O_); else GPSIG_PDE_GO(16, O_); } while (0)
+  switch (order) {
+    case 0: GPSIG_PDE_DP(0); break; case 1: GPSIG_PDE_DP(1); break; case 2: GPSIG_PDE_DP(2); break;
+    case 3: GPSIG_PDE_DP(3); break; case 4: GPSIG_PDE_DP(4); break; case 5: GPSIG_PDE_DP(5); break;
+    default: GPSIG_PDE_DP(6); break;
+  }
+  GPSIG_LAUNCH_CHECK("pde_wavefront_kernel");
+  return GPSIG_OK;
+}
+
+}  // namespace gpsig
+
+using namespace gpsig;
+
+extern "C" {
+
+const char* gpsig_last_error_string(void) { return g_err; }
+int gpsig_version(void) { return GPSIG_VERSION; }
+
+size_t gpsig_trunc_gram_workspace_bytes(int N, int L, int N2, int L2, int d, int elem) {
+  return packed_bytes(N, L, d, elem) + (N2 > 0 ? packed_bytes(N2, L2, d, elem) : 0);
+}
+size_t gpsig_trunc_diag_workspace_bytes(int N, int L, int d, int elem) { return packed_bytes(N, L, d, elem); }
+size_t gpsig_tens_vs_seq_workspace_bytes(int Mz, int increments, int N, int L, int d, int m, int elem) {
+  return packed_bytes(m * (m + 1) / 2 * Mz, increments ? 2 : 1, d, elem) + packed_bytes(N, L, d, elem);
+}
+
+int gpsig_trunc_gram_f64(const gpsig_trunc_desc* desc, const double* X, int N, int L, const double* X2, int N2, int L2,
+                         int d, const double* ls, int rb, int re, const gpsig_epilogue* epi, double* out,
+                         void* ws, size_t wsb, void* stream) {
+  return trunc_gram_impl<double>(desc, X, N, L, X2, N2, L2, d, ls, rb, re, epi, out, ws, wsb, stream);
+}
+int gpsig_trunc_gram_f32(const gpsig_trunc_desc* desc, const float* X, int N, int L, const float* X2, int N2, int L2,
+                         int d, const float* ls, int rb, int re, const gpsig_epilogue* epi, float* out,
+                         void* ws, size_t wsb, void* stream) {
+  return trunc_gram_impl<float>(desc, X, N, L, X2, N2, L2, d, ls, rb, re, epi, out, ws, wsb, stream);
+}
+int gpsig_trunc_diag_f64(const gpsig_trunc_desc* desc, const double* X, int N, int L, int d, const double* ls,
+                         double* out, void* ws, size_t wsb, void* stream) {
+  return trunc_diag_impl<double>(desc, X, N, L, d, ls, out, ws, wsb, stream);
+}
+int gpsig_trunc_diag_f32(const gpsig_trunc_desc* desc, const float* X, int N, int L, int d, const float* ls,
+                         float* out, void* ws, size_t wsb, void* stream) {
+  return trunc_diag_impl<float>(desc, X, N, L, d, ls, out, ws, wsb, stream);
+}
+int gpsig_tens_vs_seq_f64(const gpsig_trunc_desc* desc, const double* Z, int Mz, int inc, const double* X, int N, int L,
+                          int d, const double* ls, int cb, int ce, const gpsig_epilogue* epi, double* out,
+                          void* ws, size_t wsb, void* stream) {
+  return tens_vs_seq_impl<double>(desc, Z, Mz, inc, X, N, L, d, ls, cb, ce, epi, out, ws, wsb, stream);
+}
+int gpsig_tens_vs_seq_f32(const gpsig_trunc_desc* desc, const float* Z, int Mz, int inc, const float* X, int N, int L,
+                          int d, const float* ls, int cb, int ce, const gpsig_epilogue* epi, float* out,
+                          void* ws, size_t wsb, void* stream) {
+  return tens_vs_seq_impl<float>(desc, Z, Mz, inc, X, N, L, d, ls, cb, ce, epi, out, ws, wsb, stream);
+}
+
+int gpsig_tens_tens_f64(const gpsig_trunc_desc* desc, const double* Z, int Mz, int inc, int d, const double* ls,
+                        const gpsig_epilogue* epi, double* out, void* stream) {
+  return tens_tens_impl<double>(desc, Z, Mz, inc, d, ls, epi, out, stream);
+}
+int gpsig_tens_tens_f32(const gpsig_trunc_desc* desc, const float* Z, int Mz, int inc, int d, const float* ls,
+                        const gpsig_epilogue* epi, float* out, void* stream) {
+  return tens_tens_impl<float>(desc, Z, Mz, inc, d, ls, epi, out, stream);
+}
+
+size_t gpsig_pde_workspace_bytes(int N, int L, int N2, int L2, int d, int order, int pair_mode) {
+  (void)order; (void)pair_mode;
+  return packed_bytes(N, L, d, 8) + (N2 > 0 ? packed_bytes(N2, L2, d, 8) : 0);
+}
+int gpsig_pde_f64(const double* X, int N, int L, const double* Y, int N2, int L2, int d, const double* ls,
+                  int order, int pair_mode, int rb, int re, double sigma, double* out, void* ws, size_t wsb, void* stream) {
+  return pde_impl(X, N, L, Y, N2, L2, d, ls, order, pair_mode, rb, re, sigma, out, ws, wsb, stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,171 @@
+// Shared device/host helpers of the gpsig_b200 CUDA library (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <math.h>
+
+#include "../../include/gpsig_b200.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "gpsig_b200 is written for sm_100a (B200) only"
+#endif
+
+namespace gpsig {
+
+// ---------------------------------------------------------------------------
+// errors
+// ---------------------------------------------------------------------------
+void set_error(const char* fmt, ...);
+#define GPSIG_FAIL(code, ...) do { ::gpsig::set_error(__VA_ARGS__); return (code); } while (0)
+#define GPSIG_CUDA_CHECK(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) \
+    GPSIG_FAIL(GPSIG_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
+#define GPSIG_LAUNCH_CHECK(name) do { cudaError_t e_ = cudaGetLastError(); if (e_ != cudaSuccess) \
+    GPSIG_FAIL(GPSIG_ERR_CUDA, "launch of %s failed: %s", name, cudaGetErrorString(e_)); } while (0)
+
+// ---------------------------------------------------------------------------
+// packed sequence layout in HBM (produced by pack_sequences_kernel)
+//
+// One block per sequence, contiguous, a multiple of 16 bytes so that a whole
+// sequence is ONE 1-D TMA bulk copy (cp.async.bulk) into shared memory:
+//     T coords[L][DP]   scaled by 1/lengthscales (kernels.py:358-359), zero
+//                       padded from d to DP (zeros do not change dot products)
+//     T sqn[LP]         |x_p|^2 of the scaled point (kernels.py:948), LP = L
+//                       rounded up to 16 bytes
+// ---------------------------------------------------------------------------
+__host__ __device__ inline int padded_dim(int d) { return d <= 4 ? 4 : (d <= 8 ? 8 : 16); }
+__host__ __device__ inline int padded_len(int L, int elem) { int q = 16 / elem; return (L + q - 1) / q * q; }
+__host__ __device__ inline size_t seq_block_elems(int L, int d, int elem) {
+  return (size_t)L * padded_dim(d) + padded_len(L, elem);
+}
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+template <typename T>
+__global__ void pack_sequences_kernel(const T* __restrict__ X, int N, int L, int d, int DP,
+                                      const T* __restrict__ lengthscales, T* __restrict__ packed,
+                                      size_t block_elems) {
+  // one thread per point (n, p): reads d contiguous values, writes DP + 1
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (size_t)N * L) return;
+  int n = (int)(idx / L), p = (int)(idx % L);
+  const T* src = X + idx * d;
+  T* blk = packed + (size_t)n * block_elems;
+  T* dst = blk + (size_t)p * DP;
+  T s = 0;
+  for (int k = 0; k < DP; ++k) {
+    T v = 0;
+    if (k < d) { v = src[k]; if (lengthscales) v = v / lengthscales[k]; }
+    dst[k] = v;
+    s += v * v;              // tf.reduce_sum(tf.square(X), axis=-1), kernels.py:948
+  }
+  blk[(size_t)L * DP + p] = s;
+}
+
+// ---------------------------------------------------------------------------
+// base kernels as functors of (x.y, |x|^2, |y|^2) -- gpsig/kernels.py:946-1173
+// ---------------------------------------------------------------------------
+template <typename T> __device__ __forceinline__ T gexp(T x);
+template <> __device__ __forceinline__ double gexp<double>(double x) { return exp(x); }
+template <> __device__ __forceinline__ float gexp<float>(float x) { return expf(x); }
+template <typename T> __device__ __forceinline__ T gsqrt(T x);
+template <> __device__ __forceinline__ double gsqrt<double>(double x) { return sqrt(x); }
+template <> __device__ __forceinline__ float gsqrt<float>(float x) { return sqrtf(x); }
+template <typename T> __device__ __forceinline__ T gpow(T x, T y);
+template <> __device__ __forceinline__ double gpow<double>(double x, double y) { return pow(x, y); }
+template <> __device__ __forceinline__ float gpow<float>(float x, float y) { return powf(x, y); }
+template <typename T> __device__ __forceinline__ T gfma(T a, T b, T c);
+template <> __device__ __forceinline__ double gfma<double>(double a, double b, double c) { return fma(a, b, c); }
+template <> __device__ __forceinline__ float gfma<float>(float a, float b, float c) { return fmaf(a, b, c); }
+
+struct BaseParams { double p0, p1; int base; };
+
+// Generic evaluation (runtime switch; used for everything but the two hot
+// specialisations in the fused kernels and by the small tensor kernels).
+template <typename T>
+__device__ __forceinline__ T base_eval(int base, T p0, T p1, T dot, T xs, T ys) {
+  switch (base) {
+    case GPSIG_BASE_LINEAR: return dot;
+    case GPSIG_BASE_RBF: return gexp<T>(-((T(-2) * dot + xs) + ys) / T(2));
+    case GPSIG_BASE_COSINE: return dot / (gsqrt<T>(xs) * gsqrt<T>(ys));
+    case GPSIG_BASE_POLY: return gpow<T>(dot + p0, p1);
+    case GPSIG_BASE_MIX: { T ds = xs + ys - T(2) * dot; return p0 * gexp<T>(-ds / T(2)) + (T(1) - p0) * dot; }
+    default: {
+      T r2 = (T(-2) * dot + xs) + ys;
+      T r = gsqrt<T>(r2 > T(1e-40) ? r2 : T(1e-40));
+      if (base == GPSIG_BASE_MATERN12) return gexp<T>(-r);
+      if (base == GPSIG_BASE_MATERN32) { T s3 = T(1.7320508075688772); return (T(1) + s3 * r) * gexp<T>(-s3 * r); }
+      T s5 = T(2.23606797749979);
+      return (T(1) + s5 * r + T(5.0 / 3.0) * (r * r)) * gexp<T>(-s5 * r);
+    }
+  }
+}
+
+// ---- base-kernel specialisations on the fused path -------------------------
+enum { OP_LINEAR = 0, OP_RBF = 1, OP_GENERIC = 2 };
+
+template <typename T, int OP> struct BaseOp;
+template <typename T> struct BaseOp<T, OP_LINEAR> {
+  static __device__ __forceinline__ T col_const(T ysq) { return T(0); }
+  static __device__ __forceinline__ T row_const(T xsq) { return T(0); }
+  static __device__ __forceinline__ T init(T xc, T yc) { return T(0); }
+  static __device__ __forceinline__ T finish(T acc, T xc, T yc, int base, T p0, T p1) { return acc; }
+};
+template <typename T> struct BaseOp<T, OP_RBF> {
+  // exp(-(|x|^2 + |y|^2 - 2 x.y)/2) = exp(x.y - |x|^2/2 - |y|^2/2)   (kernels.py:1042-1044)
+  static __device__ __forceinline__ T col_const(T ysq) { return T(-0.5) * ysq; }
+  static __device__ __forceinline__ T row_const(T xsq) { return T(-0.5) * xsq; }
+  static __device__ __forceinline__ T init(T xc, T yc) { return xc + yc; }
+  static __device__ __forceinline__ T finish(T acc, T xc, T yc, int base, T p0, T p1) { return gexp<T>(acc); }
+};
+template <typename T> struct BaseOp<T, OP_GENERIC> {
+  static __device__ __forceinline__ T col_const(T ysq) { return ysq; }
+  static __device__ __forceinline__ T row_const(T xsq) { return xsq; }
+  static __device__ __forceinline__ T init(T xc, T yc) { return T(0); }
+  static __device__ __forceinline__ T finish(T acc, T xc, T yc, int base, T p0, T p1) {
+    return base_eval<T>(base, p0, p1, acc, xc, yc);
+  }
+};
+// out-of-line copy for kernels that evaluate the base kernel at many unrolled sites
+template <typename T>
+__device__ __noinline__ T base_eval_call(int base, T p0, T p1, T dot, T xs, T ys) {
+  return base_eval<T>(base, p0, p1, dot, xs, ys);
+}
+
+
+// ---------------------------------------------------------------------------
+// PTX: mbarrier + 1-D TMA bulk copy (SASS: UBLKCP / SYNCS)
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void fence_mbar_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// global -> shared bulk copy, completion signalled on an mbarrier (bytes % 16 == 0)
+__device__ __forceinline__ void tma_load_1d(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(smem_dst)), "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+template <typename T>
+__device__ __forceinline__ T warp_sum(T v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+}  // namespace gpsig

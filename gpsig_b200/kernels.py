@@ -1,0 +1,374 @@
+"""Truncated signature kernels -- drop-in for ``gpsig.kernels`` on B200.
+
+Same class names, constructor keywords, method names, argument meaning, result
+shapes and error behaviour as the reference (``gpsig/kernels.py``); the
+numbers come from the hand-written sm_100a kernels behind the C ABI
+(``include/gpsig_b200.h``) instead of a TensorFlow graph.  Inputs are torch
+CUDA tensors in GPflow's 2-D layout ``[N, L*d]`` (``compute_*`` methods take
+and return numpy, like the reference's autoflow wrappers).
+
+Differences that are deliberate:
+  * parameters are plain values (the constrained values GPflow's
+    ``params_as_tensors`` would hand to the methods), no TF variables;
+  * ``low_rank=True`` and ``num_lags > 0`` raise NotImplementedError (out of
+    the hot-path scope);
+  * ``order > 1`` (higher-order recursion) raises NotImplementedError from the
+    library until that kernel lands.
+"""
+import numpy as np
+import torch
+
+from . import ops, settings
+
+
+class SignatureKernel:
+    """gpsig/kernels.py:16-134 (constructor and validators)."""
+
+    _base = None          # name of the static kernel, set by the subclasses
+    _base_params = ()
+
+    def __init__(self, input_dim, num_features, num_levels, active_dims=None, variances=1, lengthscales=1, order=1,
+                 normalization=True, difference=True, num_lags=None, low_rank=False, num_components=50,
+                 rank_bound=None, sparsity='sqrt', name=None):
+        self.input_dim = int(input_dim)
+        self.name = name
+        if active_dims is None:                                     # gpflow Kernel.__init__
+            self.active_dims = slice(input_dim)
+        elif isinstance(active_dims, slice):
+            self.active_dims = active_dims
+        else:
+            self.active_dims = np.array(active_dims, dtype=np.int64)
+        self.num_features = num_features
+        self.num_levels = num_levels
+        self.len_examples = self._validate_number_of_features(input_dim, num_features)
+        self.order = num_levels if (order <= 0 or order >= num_levels) else order      # kernels.py:58
+
+        if self.order != 1 and low_rank:                            # kernels.py:60-61
+            raise NotImplementedError('Higher-order algorithms not compatible with low-rank mode (yet).')
+
+        self.normalization = normalization
+        self.difference = difference
+        self.variances = self._validate_signature_param("variances", variances, num_levels + 1)
+        self.sigma = 1.
+        self.low_rank, self.num_components, self.rank_bound, self.sparsity = \
+            self._validate_low_rank_params(low_rank, num_components, rank_bound, sparsity)
+        if self.low_rank:
+            raise NotImplementedError('gpsig_b200: the low-rank (Nystrom) mode is outside the B200 hot path.')
+
+        if num_lags is None:
+            self.num_lags = 0
+        else:
+            if not isinstance(num_lags, int) or num_lags < 0:       # kernels.py:75-76
+                raise ValueError('The variable num_lags most be a nonnegative integer or None.')
+            self.num_lags = int(num_lags)
+            if num_lags > 0:
+                raise NotImplementedError('gpsig_b200: num_lags > 0 is not implemented yet (SURVEY.md 8f-4).')
+
+        if lengthscales is not None:
+            self.lengthscales = self._validate_signature_param("lengthscales", lengthscales, self.num_features)
+        else:
+            self.lengthscales = None
+
+    # ---- validators (kernels.py:95-134) -------------------------------------
+    def _validate_number_of_features(self, input_dim, num_features):
+        if input_dim % num_features == 0:
+            return int(input_dim / num_features)
+        raise ValueError("The arguments num_features and input_dim are not consistent.")
+
+    def _validate_low_rank_params(self, low_rank, num_components, rank_bound, sparsity):
+        if low_rank is not None and low_rank == True:  # noqa: E712  (as the reference)
+            if not type(low_rank) == bool:
+                raise ValueError("Unknown low-rank argument: %s. It should be True of False." % low_rank)
+            if sparsity not in ['log', 'sqrt', 'lin']:
+                raise ValueError("Unknown sparsity argument %s. Possible values are 'sqrt', 'log', 'lin'" % sparsity)
+            if rank_bound is not None and rank_bound <= 0:
+                raise ValueError("The rank-bound in the low-rank algorithm must be either None or a positiv integer.")
+            if num_components is None or num_components <= 0:
+                raise ValueError("The number of components in the kernel approximation must be a positive integer.")
+            if rank_bound is None:
+                rank_bound = num_components
+        else:
+            low_rank = False
+        return low_rank, num_components, rank_bound, sparsity
+
+    def _validate_signature_param(self, name, value, length):
+        value = value * np.ones(length, dtype=np.float64)
+        correct_shape = () if length == 1 else (length,)
+        if np.asarray(value).squeeze().shape != correct_shape:
+            raise ValueError("shape of parameter {} is not what is expected ({})".format(name, length))
+        return value
+
+    # ---- helpers ---------------------------------------------------------------
+    def _slice(self, X, X2):
+        """gpflow 1.5 ``Kernel._slice``: keep the active input columns."""
+        def sl(A):
+            if A is None:
+                return None
+            if isinstance(self.active_dims, slice):
+                return A[:, self.active_dims]
+            return A[:, torch.as_tensor(self.active_dims, device=A.device)]
+        return sl(X), sl(X2)
+
+    def _seq(self, X):
+        """[N, L*d] -> contiguous [N, L, d]  (kernels.py:418-420)."""
+        if not torch.is_tensor(X):
+            raise TypeError("gpsig_b200 kernels take torch CUDA tensors (use compute_* for numpy)")
+        return X.reshape(X.shape[0], -1, self.num_features).contiguous()
+
+    def _param(self, value, like):
+        if value is None:
+            return None
+        return torch.as_tensor(np.asarray(value, dtype=np.float64), dtype=like.dtype, device=like.device).contiguous()
+
+    def _level_scale(self, like):
+        """sigma * variances  (kernels.py:472)."""
+        return self._param(float(self.sigma) * np.asarray(self.variances, dtype=np.float64).reshape(-1), like)
+
+    def _kw(self, like):
+        return dict(base=self._base, base_params=self._get_base_params(), order=self.order,
+                    difference=self.difference, lengthscales=self._param(self.lengthscales, like))
+
+    def _get_base_params(self):
+        return self._base_params
+
+    def _K_seq_diag(self, X):
+        """Raw per-level diagonals [m+1, N] of [N, L, d] sequences (kernels.py:190-207)."""
+        return ops.trunc_diag(X, self.num_levels, **self._kw(X))
+
+    # ---- public API ------------------------------------------------------------
+    def K(self, X, X2=None, presliced=False, return_levels=False, presliced_X=False, presliced_X2=False, rows=None):
+        """Signature kernel between sequences (kernels.py:401-477).
+
+        ``rows=(begin, end)`` (extension) restricts the computation to a row
+        block of the Gram -- the unit of multi-GPU sharding.
+        """
+        if presliced:
+            presliced_X = presliced_X2 = True
+        if not presliced_X and not presliced_X2:
+            X, X2 = self._slice(X, X2)
+        elif not presliced_X:
+            X, _ = self._slice(X, None)
+        elif not presliced_X2 and X2 is not None:
+            X2, _ = self._slice(X2, None)
+        Xs = self._seq(X)
+        jitter = settings.jitter
+        kw = self._kw(Xs)
+        if X2 is None:
+            norm = None
+            if self.normalization:                                   # kernels.py:431-434
+                norm = self._K_seq_diag(Xs) + jitter
+            return ops.trunc_gram(Xs, None, self.num_levels, norm_x=norm, norm_x2=norm,
+                                  level_scale=self._level_scale(Xs), sym_jitter=jitter if self.normalization else 0.0,
+                                  return_levels=return_levels, rows=rows, **kw)
+        X2s = self._seq(X2)
+        n1 = n2 = None
+        if self.normalization:                                       # kernels.py:456-470
+            n1 = self._K_seq_diag(Xs) + jitter
+            n2 = self._K_seq_diag(X2s) + jitter
+        return ops.trunc_gram(Xs, X2s, self.num_levels, norm_x=n1, norm_x2=n2, level_scale=self._level_scale(Xs),
+                              return_levels=return_levels, rows=rows, **kw)
+
+    def K_norms(self, X, presliced=False):
+        """kernels.py:480-506."""
+        if not presliced:
+            X, _ = self._slice(X, None)
+        Xs = self._seq(X)
+        const = torch.full((Xs.shape[0],), float(self.sigma) * float(np.sum(self.variances)), dtype=Xs.dtype, device=Xs.device)
+        return const, self._K_seq_diag(Xs)
+
+    def Kdiag(self, X, presliced=False, return_levels=False):
+        """kernels.py:509-541."""
+        N = X.shape[0]
+        if self.normalization:
+            sc = self._level_scale(X)
+            if return_levels:
+                return sc[:, None].repeat(1, N)
+            return torch.full((N,), float(self.sigma) * float(np.sum(self.variances)), dtype=X.dtype, device=X.device)
+        if not presliced:
+            X, _ = self._slice(X, None)
+        Xs = self._seq(X)
+        K = self._K_seq_diag(Xs) * self._level_scale(Xs)[:, None]
+        return K if return_levels else K.sum(dim=0)
+
+    def K_tens(self, Z, return_levels=False, increments=False):
+        """Square covariance of inducing tensors (kernels.py:543-567)."""
+        Z = Z.contiguous()
+        return ops.tens_tens(Z, self.num_levels, increments=increments, base=self._base,
+                             base_params=self._get_base_params(), lengthscales=self._param(self.lengthscales, Z),
+                             level_scale=self._level_scale(Z), return_levels=return_levels)
+
+    def K_tens_vs_seq(self, Z, X, return_levels=False, increments=False, presliced=False, cols=None):
+        """Inducing tensors vs sequences (kernels.py:570-620)."""
+        if not presliced:
+            X, _ = self._slice(X, None)
+        Xs = self._seq(X)
+        norm = self._K_seq_diag(Xs) + settings.jitter if self.normalization else None      # kernels.py:604-613
+        return ops.tens_vs_seq(Z.contiguous(), Xs, self.num_levels, increments=increments, norm_x=norm,
+                               level_scale=self._level_scale(Xs), return_levels=return_levels, cols=cols,
+                               **self._kw(Xs))
+
+    def K_tens_n_seq_covs(self, Z, X, full_X_cov=False, return_levels=False, increments=False, presliced=False):
+        """Kzz, Kzx, Kxx in one call (kernels.py:623-704)."""
+        if not presliced:
+            X, _ = self._slice(X, None)
+        Xs = self._seq(X)
+        Z = Z.contiguous()
+        N = Xs.shape[0]
+        jitter = settings.jitter
+        sc = self._level_scale(Xs)
+        kw = self._kw(Xs)
+        Kzz = ops.tens_tens(Z, self.num_levels, increments=increments, base=self._base,
+                            base_params=self._get_base_params(), lengthscales=kw['lengthscales'], level_scale=sc,
+                            return_levels=return_levels)
+        diag = self._K_seq_diag(Xs)
+        norm = diag + jitter if self.normalization else None
+        Kzx = ops.tens_vs_seq(Z, Xs, self.num_levels, increments=increments, norm_x=norm, level_scale=sc,
+                              return_levels=return_levels, **kw)
+        if full_X_cov:                                               # kernels.py:659-680
+            Kxx = ops.trunc_gram(Xs, None, self.num_levels, norm_x=norm, norm_x2=norm, level_scale=sc,
+                                 sym_jitter=jitter if self.normalization else 0.0, return_levels=return_levels, **kw)
+        else:                                                        # kernels.py:682-704
+            if self.normalization:
+                Kxx = sc[:, None].repeat(1, N)
+            else:
+                Kxx = diag * sc[:, None]
+            if not return_levels:
+                Kxx = Kxx.sum(dim=0)
+        return Kzz, Kzx, Kxx
+
+    def K_seq_n_seq_covs(self, X, X2, full_X2_cov=False, return_levels=False, presliced=False):
+        """Kxx, Kxx2, Kx2x2 for inducing sequences (kernels.py:706-794).
+
+        Follows the reference to the letter, including that (a) with
+        ``normalization`` and ``full_X2_cov=True`` it raises NameError
+        (kernels.py:756-761 use undefined names) and (b) with ``normalization``
+        and ``full_X2_cov=False`` the cross term is divided by sqrt(diag Kxx)
+        twice (kernels.py:746 and :783).
+        """
+        if not presliced:
+            X2, _ = self._slice(X2, None)
+        Xs, X2s = self._seq(X), self._seq(X2)
+        N2 = X2s.shape[0]
+        jitter = settings.jitter
+        sc = self._level_scale(Xs)
+        kw = self._kw(Xs)
+        if self.normalization and full_X2_cov:
+            raise NameError("name 'K_x2x2_lvls' is not defined")   # kernels.py:756
+        if self.normalization:
+            nx = self._K_seq_diag(Xs) + jitter
+            Kxx = ops.trunc_gram(Xs, None, self.num_levels, norm_x=nx, norm_x2=nx, level_scale=sc, sym_jitter=jitter,
+                                 return_levels=return_levels, **kw)
+            d2 = self._K_seq_diag(X2s) + jitter
+            # kernels.py:746 then :783 -> divided by sqrt(nx) twice and sqrt(d2) once
+            Kxx2 = ops.trunc_gram(Xs, X2s, self.num_levels, norm_x=nx, norm_x2=d2, level_scale=None,
+                                  return_levels=True, **kw)
+            Kxx2 = Kxx2 / torch.sqrt(nx)[:, :, None] * sc[:, None, None]
+            if not return_levels:
+                Kxx2 = Kxx2.sum(dim=0)
+            Kx2x2 = sc[:, None].repeat(1, N2)
+            if not return_levels:
+                Kx2x2 = Kx2x2.sum(dim=0)
+            return Kxx, Kxx2, Kx2x2
+        Kxx = ops.trunc_gram(Xs, None, self.num_levels, level_scale=sc, return_levels=return_levels, **kw)
+        Kxx2 = ops.trunc_gram(Xs, X2s, self.num_levels, level_scale=sc, return_levels=return_levels, **kw)
+        if full_X2_cov:
+            Kx2x2 = ops.trunc_gram(X2s, None, self.num_levels, level_scale=sc, return_levels=return_levels, **kw)
+        else:
+            Kx2x2 = self._K_seq_diag(X2s) * sc[:, None]
+            if not return_levels:
+                Kx2x2 = Kx2x2.sum(dim=0)
+        return Kxx, Kxx2, Kx2x2
+
+    # ---- numpy-in / numpy-out wrappers (the reference's autoflow methods, kernels.py:142-187)
+    @staticmethod
+    def _dev(A):
+        return torch.as_tensor(np.ascontiguousarray(A), dtype=settings.float_type, device=settings.device())
+
+    def compute_K(self, X, Y):
+        return self.K(self._dev(X), self._dev(Y)).cpu().numpy()
+
+    def compute_K_symm(self, X):
+        return self.K(self._dev(X)).cpu().numpy()
+
+    def compute_K_level_diags(self, X):
+        return self.Kdiag(self._dev(X), return_levels=True).cpu().numpy()
+
+    def compute_K_levels(self, X, X2):
+        return self.K(self._dev(X), self._dev(X2), return_levels=True).cpu().numpy()
+
+    def compute_Kdiag(self, X):
+        return self.Kdiag(self._dev(X)).cpu().numpy()
+
+    def compute_K_tens(self, Z):
+        return self.K_tens(self._dev(Z), return_levels=False).cpu().numpy()
+
+    def compute_K_tens_vs_seq(self, Z, X):
+        return self.K_tens_vs_seq(self._dev(Z), self._dev(X), return_levels=False).cpu().numpy()
+
+    def compute_K_incr_tens(self, Z):
+        return self.K_tens(self._dev(Z), increments=True, return_levels=False).cpu().numpy()
+
+    def compute_K_incr_tens_vs_seq(self, Z, X):
+        return self.K_tens_vs_seq(self._dev(Z), self._dev(X), increments=True, return_levels=False).cpu().numpy()
+
+
+class SignatureLinear(SignatureKernel):
+    """Identity state-space embedding (kernels.py:966-986)."""
+    _base = 'linear'
+
+
+class SignatureCosine(SignatureKernel):
+    """Cosine similarity (kernels.py:988-1008)."""
+    _base = 'cosine'
+
+
+class SignaturePoly(SignatureKernel):
+    """Polynomial kernel (kernels.py:1011-1028)."""
+    _base = 'poly'
+
+    def __init__(self, input_dim, num_features, num_levels, gamma=1, degree=3, **kwargs):
+        SignatureKernel.__init__(self, input_dim, num_features, num_levels, **kwargs)
+        self.gamma = float(gamma)
+        self.degree = float(degree)
+
+    def _get_base_params(self):
+        return (self.gamma, self.degree)
+
+
+class SignatureRBF(SignatureKernel):
+    """Gauss / RBF / squared-exponential (kernels.py:1030-1044)."""
+    _base = 'rbf'
+
+
+SignatureGauss = SignatureRBF
+
+
+class SignatureMix(SignatureKernel):
+    """Convex combination of RBF and identity (kernels.py:1050-1072)."""
+    _base = 'mix'
+
+    def __init__(self, input_dim, num_features, num_levels, **kwargs):
+        SignatureKernel.__init__(self, input_dim, num_features, num_levels, **kwargs)
+        self.mixing = 0.5
+
+    def _get_base_params(self):
+        return (float(self.mixing),)
+
+
+class SignatureMatern12(SignatureKernel):
+    """kernels.py:1124-1138."""
+    _base = 'matern12'
+
+
+SignatureLaplace = SignatureMatern12
+SignatureExponential = SignatureMatern12
+
+
+class SignatureMatern32(SignatureKernel):
+    """kernels.py:1144-1157."""
+    _base = 'matern32'
+
+
+class SignatureMatern52(SignatureKernel):
+    """kernels.py:1161-1173."""
+    _base = 'matern52'

@@ -1,0 +1,119 @@
+"""Untruncated (PDE) signature kernel -- drop-in for ``gpsig.kernels_pde``.
+
+``UntruncSignatureKernel.Kdiag`` (gpsig/kernels_pde.py:160-185) solves the
+Goursat PDE of each sequence against itself and keeps ``sigma * K[-1, -1]``.
+The reference does this either on the host through ``tf.py_func`` + Cython
+(``implementation='cython'``, gpsig/sigKer_fast.pyx) or with its TF custom op
+(``implementation='gpu_op'``, limited to 2^order (L-1) + 1 < 1024).  Here both
+spellings run the same sm_100a wavefront kernel (``csrc/pde_kernel.cuh``);
+the length limit does not apply.
+
+As in the reference, ``Kdiag`` never evaluates ``_base_kern`` (kernels_pde.py:177
+is commented out): the PDE path is linear-base-kernel only, so ``SignatureRBF``
+and ``SignatureLinear`` give the same ``Kdiag`` (SURVEY.md note N7).
+``K(X, X2)`` (extension; the reference declares ``compute_K`` but never defines
+``K``) returns the full untruncated Gram.
+"""
+import numpy as np
+import torch
+
+from . import ops, settings
+
+
+class UntruncSignatureKernel:
+    """gpsig/kernels_pde.py:28-101.  Keywords ``order=``, ``lengthscales=`` (SURVEY.md note N6)."""
+
+    def __init__(self, input_dim, num_features, lengthscales=1, order=0, num_lags=None, implementation='gpu_op',
+                 num_levels=None, active_dims=None, name=None):
+        self.input_dim = int(input_dim)
+        self.name = name
+        self.active_dims = slice(input_dim) if active_dims is None else active_dims
+        self.num_features = num_features
+        self.len_examples = self._validate_number_of_features(input_dim, num_features)
+        assert implementation in ['cython', 'gpu_op'], "implementation should be 'cython' or 'gpu_op'"
+        self.implementation = implementation
+        self.order = int(order)
+        if self.order < 0:
+            raise ValueError('order must be a nonnegative integer')
+        self.sigma = 1.
+        self.num_levels = num_levels
+        if num_lags is None:
+            self.num_lags = 0
+        else:
+            if not isinstance(num_lags, int) or num_lags < 0:
+                raise ValueError('The variable num_lags most be a nonnegative integer or None.')
+            self.num_lags = int(num_lags)
+            if num_lags > 0:
+                raise NotImplementedError('gpsig_b200: num_lags > 0 is not implemented yet (SURVEY.md 8f-4).')
+        if lengthscales is not None:
+            self.lengthscales = self._validate_signature_param("lengthscales", lengthscales, self.num_features)
+        else:
+            self.lengthscales = None
+
+    def _validate_number_of_features(self, input_dim, num_features):
+        if input_dim % num_features == 0:
+            return int(input_dim / num_features)
+        raise ValueError("The arguments num_features and input_dim are not consistent.")
+
+    def _validate_signature_param(self, name, value, length):
+        value = value * np.ones(length, dtype=np.float64)
+        correct_shape = () if length == 1 else (length,)
+        if np.asarray(value).squeeze().shape != correct_shape:
+            raise ValueError("shape of parameter {} is not what is expected ({})".format(name, length))
+        return value
+
+    def _slice(self, X):
+        if isinstance(self.active_dims, slice):
+            return X[:, self.active_dims]
+        return X[:, torch.as_tensor(np.asarray(self.active_dims), device=X.device)]
+
+    def _seq(self, X):
+        return X.reshape(X.shape[0], -1, self.num_features).contiguous()
+
+    def _ls(self, like):
+        if self.lengthscales is None:
+            return None
+        return torch.as_tensor(self.lengthscales, dtype=like.dtype, device=like.device)
+
+    def Kdiag(self, X, presliced=False, name=None, rows=None):
+        """sigma * k(x_i, x_i) for every sequence (kernels_pde.py:160-185)."""
+        if not presliced:
+            X = self._slice(X)
+        Xs = self._seq(X)
+        return ops.pde(Xs, None, dyadic_order=self.order, gram=False, lengthscales=self._ls(Xs),
+                       sigma=float(self.sigma), rows=rows)
+
+    def K(self, X, X2=None, presliced=False, rows=None):
+        """Full untruncated Gram sigma * k(x_i, y_j) (extension, see module docstring)."""
+        if not presliced:
+            X = self._slice(X)
+            X2 = None if X2 is None else self._slice(X2)
+        Xs = self._seq(X)
+        X2s = None if X2 is None else self._seq(X2)
+        return ops.pde(Xs, X2s, dyadic_order=self.order, gram=True, lengthscales=self._ls(Xs),
+                       sigma=float(self.sigma), rows=rows)
+
+    @staticmethod
+    def _dev(A):
+        return torch.as_tensor(np.ascontiguousarray(A), dtype=torch.float64, device=settings.device())
+
+    def compute_K(self, X, Y):
+        return self.K(self._dev(X), self._dev(Y)).cpu().numpy()
+
+    def compute_K_symm(self, X):
+        """The reference's ``compute_K_symm`` returns ``Kdiag`` (kernels_pde.py:110-112)."""
+        return self.Kdiag(self._dev(X)).cpu().numpy()
+
+
+class SignatureRBF(UntruncSignatureKernel):
+    """kernels_pde.py:404-417 (positional ``order, num_levels`` as in the reference's subclass)."""
+
+    def __init__(self, input_dim, num_features, order, num_levels, **kwargs):
+        UntruncSignatureKernel.__init__(self, input_dim, num_features, order=order, num_levels=num_levels, **kwargs)
+
+
+class SignatureLinear(UntruncSignatureKernel):
+    """kernels_pde.py:420-437."""
+
+    def __init__(self, input_dim, num_features, order, num_levels, **kwargs):
+        UntruncSignatureKernel.__init__(self, input_dim, num_features, order=order, num_levels=num_levels, **kwargs)

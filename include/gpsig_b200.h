@@ -1,0 +1,146 @@
+/* gpsig_b200 -- C ABI of the B200-native signature-kernel Gram library.
+ *
+ * This header is the drop-in boundary for the hot path of maudl3116/GPSig:
+ * everything below `gpsig.kernels` / `gpsig.kernels_pde` that touches numbers.
+ * Plain C: raw device pointers, sizes, a cudaStream_t passed as void*.  No
+ * torch / TensorFlow / C++ types cross it.  All functions
+ *   - return 0 (GPSIG_OK) or a negative GPSIG_ERR_* code; the message is
+ *     available (thread-local) from gpsig_last_error_string();
+ *   - launch asynchronously on the caller's stream and never synchronise;
+ *   - never allocate, free or retain device memory: the caller owns inputs,
+ *     outputs and the workspace (size from the matching *_workspace_bytes);
+ *   - treat every input as const.
+ * Sequences are dense row-major [N, L, d] (== the reference's 2-D GPflow
+ * layout [N, L*d], gpsig/kernels.py:418-420).  `lengthscales` is a DEVICE
+ * pointer to d values or NULL (gpsig/kernels.py:358-359: X /= lengthscales).
+ *
+ * Reference interface each entry point replaces (paths relative to the
+ * reference repository root):
+ *   gpsig_trunc_gram_*   gpsig/kernels.py:209-238  SignatureKernel._K_seq
+ *                        + gpsig/signature_algs.py:8-35 / :37-74, with the
+ *                        normalisation / variance epilogue of kernels.py:431-477
+ *   gpsig_trunc_diag_*   gpsig/kernels.py:190-207  SignatureKernel._K_seq_diag
+ *   gpsig_tens_vs_seq_*  gpsig/kernels.py:314-341  _K_tens_vs_seq
+ *                        + gpsig/signature_algs.py:101-127 / :129-160, epilogue kernels.py:604-620
+ *   gpsig_tens_tens_*    gpsig/kernels.py:264-284  _K_tens + signature_algs.py:76-99
+ *   gpsig_pde_*          gpsig/sigKer_fast.pyx:15-62 sig_kern_diag and the TF op
+ *                        gpsig/covariance_op/untrunc_cov_op_gpu.cc:43-50,61-102
+ *                        (UntruncCovKernelLauncher / UntruncCovOp::Compute)
+ */
+#ifndef GPSIG_B200_H_
+#define GPSIG_B200_H_
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GPSIG_VERSION 100
+
+/* status codes */
+#define GPSIG_OK 0
+#define GPSIG_ERR_INVALID_ARGUMENT (-1)
+#define GPSIG_ERR_UNSUPPORTED (-2)
+#define GPSIG_ERR_WORKSPACE (-3)
+#define GPSIG_ERR_CUDA (-4)
+
+/* static (base) kernels on R^d, gpsig/kernels.py:966-1173 */
+#define GPSIG_BASE_LINEAR 0   /* _lin      kernels.py:979  */
+#define GPSIG_BASE_RBF 1      /* _rbf      kernels.py:1042 */
+#define GPSIG_BASE_COSINE 2   /* _cos      kernels.py:1000 */
+#define GPSIG_BASE_POLY 3     /* _poly     kernels.py:1024  params: gamma, degree */
+#define GPSIG_BASE_MIX 4      /* _mix      kernels.py:1061  params: mixing */
+#define GPSIG_BASE_MATERN12 5 /* _Matern12 kernels.py:1135 */
+#define GPSIG_BASE_MATERN32 6 /* _Matern32 kernels.py:1154 */
+#define GPSIG_BASE_MATERN52 7 /* _Matern52 kernels.py:1171 */
+
+/* What the truncated kernel computes (constructor state of
+ * gpsig/kernels.py:19-89 that reaches the numerics). */
+typedef struct gpsig_trunc_desc {
+  int base;              /* GPSIG_BASE_* */
+  int num_levels;        /* m >= 1 (kernels.py:56) */
+  int order;             /* 1..m (kernels.py:58); 1 = first-order recursion */
+  int difference;        /* kernels.py:64; 1 = difference the lifted Gram */
+  double base_params[4]; /* POLY: {gamma, degree}; MIX: {mixing} */
+} gpsig_trunc_desc;
+
+/* How raw levels K_l become the returned matrix (kernels.py:431-434,456-477):
+ *   v_l = K_l (+ jitter if X2 == NULL and i == j)
+ *   v_l /= sqrt(norm_x[l, i]) * sqrt(norm_x2[l, j])      if norm_* != NULL
+ *   v_l *= level_scale[l]                                 if level_scale != NULL
+ *   out  = v_l per level (return_levels) or sum_l v_l
+ * norm_* hold the (jittered) per-level diagonals [m+1, N] / [m+1, N2] computed
+ * by gpsig_trunc_diag_*; level_scale = sigma * variances [m+1].  Device ptrs. */
+typedef struct gpsig_epilogue {
+  const void* norm_x;
+  const void* norm_x2;
+  const void* level_scale;
+  double sym_jitter;
+  int return_levels;
+} gpsig_epilogue;
+
+const char* gpsig_last_error_string(void);
+int gpsig_version(void);
+
+/* ---- truncated kernel: sequences vs sequences ------------------------------
+ * out: rows [row_begin, row_end) of the [N, N2] Gram, i.e. device array
+ *      [(m+1,)? row_end-row_begin, N2] (row-block sharding across GPUs).
+ * X2 == NULL: K(X, X) (then N2 = N, L2 = L are ignored). */
+size_t gpsig_trunc_gram_workspace_bytes(int N, int L, int N2, int L2, int d, int elem_size);
+int gpsig_trunc_gram_f64(const gpsig_trunc_desc* desc, const double* X, int N, int L,
+                         const double* X2, int N2, int L2, int d, const double* lengthscales,
+                         int row_begin, int row_end, const gpsig_epilogue* epi, double* out,
+                         void* workspace, size_t workspace_bytes, void* stream);
+int gpsig_trunc_gram_f32(const gpsig_trunc_desc* desc, const float* X, int N, int L,
+                         const float* X2, int N2, int L2, int d, const float* lengthscales,
+                         int row_begin, int row_end, const gpsig_epilogue* epi, float* out,
+                         void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- truncated kernel: diagonal k_l(x_i, x_i), raw levels out [m+1, N] ---- */
+size_t gpsig_trunc_diag_workspace_bytes(int N, int L, int d, int elem_size);
+int gpsig_trunc_diag_f64(const gpsig_trunc_desc* desc, const double* X, int N, int L, int d,
+                         const double* lengthscales, double* out,
+                         void* workspace, size_t workspace_bytes, void* stream);
+int gpsig_trunc_diag_f32(const gpsig_trunc_desc* desc, const float* X, int N, int L, int d,
+                         const float* lengthscales, float* out,
+                         void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- inducing tensors vs sequences (Kzx) -----------------------------------
+ * Z: [T, Mz, d] or, with increments, [T, Mz, 2, d]; T = m(m+1)/2.
+ * out: columns [col_begin, col_end) of [(m+1,)? Mz, N]  (sharded over N).
+ * epi->norm_x2 (if set) is the per-level diagonal of X [m+1, N]; norm_x unused. */
+size_t gpsig_tens_vs_seq_workspace_bytes(int Mz, int increments, int N, int L, int d, int num_levels, int elem_size);
+int gpsig_tens_vs_seq_f64(const gpsig_trunc_desc* desc, const double* Z, int Mz, int increments,
+                          const double* X, int N, int L, int d, const double* lengthscales,
+                          int col_begin, int col_end, const gpsig_epilogue* epi, double* out,
+                          void* workspace, size_t workspace_bytes, void* stream);
+int gpsig_tens_vs_seq_f32(const gpsig_trunc_desc* desc, const float* Z, int Mz, int increments,
+                          const float* X, int N, int L, int d, const float* lengthscales,
+                          int col_begin, int col_end, const gpsig_epilogue* epi, float* out,
+                          void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- inducing tensors vs inducing tensors (Kzz), out [(m+1,)? Mz, Mz] ------ */
+int gpsig_tens_tens_f64(const gpsig_trunc_desc* desc, const double* Z, int Mz, int increments, int d,
+                        const double* lengthscales, const gpsig_epilogue* epi, double* out, void* stream);
+int gpsig_tens_tens_f32(const gpsig_trunc_desc* desc, const float* Z, int Mz, int increments, int d,
+                        const float* lengthscales, const gpsig_epilogue* epi, float* out, void* stream);
+
+/* ---- untruncated (Goursat PDE) kernel ---------------------------------------
+ * Explicit 2nd-order stencil of sigKer_fast.pyx:48 on the 2^dyadic_order
+ * refined grid, linear base kernel (what the reference's Cython path solves).
+ * pair_mode GPSIG_PDE_DIAG: out[a] = sigma * k(x_a, y_a), a in [row_begin,row_end)
+ *           (Y == NULL -> y = x: the reference's Kdiag, kernels_pde.py:160-185);
+ * pair_mode GPSIG_PDE_GRAM: out[i - row_begin, j] = sigma * k(x_i, y_j). */
+#define GPSIG_PDE_DIAG 0
+#define GPSIG_PDE_GRAM 1
+size_t gpsig_pde_workspace_bytes(int N, int L, int N2, int L2, int d, int dyadic_order, int pair_mode);
+int gpsig_pde_f64(const double* X, int N, int L, const double* Y, int N2, int L2, int d,
+                  const double* lengthscales, int dyadic_order, int pair_mode,
+                  int row_begin, int row_end, double sigma, double* out,
+                  void* workspace, size_t workspace_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GPSIG_B200_H_ */

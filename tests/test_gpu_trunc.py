@@ -1,0 +1,137 @@
+"""GPU parity: fused truncated-Gram CUDA kernels (through the C ABI) vs the CPU oracle.
+
+Tolerances are the north star's: 1e-10 relative (to the Gram's scale) in
+float64, 1e-5 in float32.
+"""
+import numpy as np
+import pytest
+import torch
+
+from tests.util import brownian, rel_err
+
+pytestmark = pytest.mark.gpu
+TOL = {torch.float64: 1e-10, torch.float32: 1e-5}
+
+
+def _dev(a, dtype):
+    return torch.as_tensor(np.ascontiguousarray(a), dtype=dtype, device='cuda')
+
+
+BASES = [('linear', 'SignatureLinear', {}), ('rbf', 'SignatureRBF', {}), ('cosine', 'SignatureCosine', {}),
+         ('poly', 'SignaturePoly', dict(gamma=1.0, degree=3.0)), ('mix', 'SignatureMix', {}),
+         ('matern12', 'SignatureMatern12', {}), ('matern32', 'SignatureMatern32', {}),
+         ('matern52', 'SignatureMatern52', {})]
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("base,cls,bp", BASES)
+@pytest.mark.parametrize("normalization", [False, True])
+def test_gram_all_base_kernels(dtype, base, cls, bp, normalization):
+    from gpsig_b200 import kernels
+    from oracle.trunc_np import SignatureKernelOracle
+    N, N2, L, L2, d, m = 11, 9, 23, 17, 3, 4
+    X, Y = brownian(N, L, d, 0), brownian(N2, L2, d, 1)
+    ls = np.array([0.9, 1.3, 0.7])
+    k = getattr(kernels, cls)(L * d, d, m, lengthscales=ls, normalization=normalization, **bp)
+    k.sigma = 1.7
+    k.variances = np.linspace(0.5, 1.5, m + 1)
+    orc_kw = dict(bp)
+    if base == 'mix':
+        orc_kw = dict(mixing=0.5)
+    o = SignatureKernelOracle(L * d, d, m, base=base, lengthscales=ls, normalization=normalization, sigma=1.7,
+                              variances=np.linspace(0.5, 1.5, m + 1), **orc_kw)
+    for ret in (True, False):
+        G = k.K(_dev(X.reshape(N, -1), dtype), _dev(Y.reshape(N2, -1), dtype), return_levels=ret).cpu().numpy()
+        R = o.K(X.reshape(N, -1), Y.reshape(N2, -1), return_levels=ret)
+        assert G.shape == R.shape
+        assert rel_err(G, R) < TOL[dtype], (base, ret, rel_err(G, R))
+    Gs = k.K(_dev(X.reshape(N, -1), dtype), return_levels=True).cpu().numpy()
+    Rs = o.K(X.reshape(N, -1), return_levels=True)
+    assert rel_err(Gs, Rs) < TOL[dtype]
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("L,L2,d,m", [(2, 2, 1, 1), (3, 40, 2, 2), (50, 50, 3, 4), (33, 34, 5, 3), (65, 97, 8, 5),
+                                      (130, 161, 4, 6), (200, 200, 8, 5), (225, 256, 7, 8), (257, 300, 2, 4),
+                                      (100, 520, 9, 5), (40, 30, 16, 4)])
+def test_gram_shapes_raw_levels(dtype, L, L2, d, m):
+    """Every columns-per-lane shape, the column-chunked path (L2 > 256), all level counts, d padding."""
+    from gpsig_b200 import ops
+    from oracle import c_oracle
+    N, N2 = 5, 10
+    X, Y = brownian(N, L, d, 2), brownian(N2, L2, d, 3)
+    for base in ('linear', 'rbf'):
+        G = ops.trunc_gram(_dev(X, dtype), _dev(Y, dtype), m, base=base).cpu().numpy()
+        R = c_oracle.trunc_gram(X, Y, m, base)
+        scale = np.abs(R).max(axis=(1, 2), keepdims=True)
+        err = np.max(np.abs(G - R) / scale)
+        assert err < TOL[dtype], (base, L, L2, d, m, err)
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+def test_diag_matches_gram_diagonal_and_oracle(dtype):
+    from gpsig_b200 import ops
+    from oracle import c_oracle
+    N, L, d, m = 19, 45, 3, 5
+    X = brownian(N, L, d, 4)
+    Xd = _dev(X, dtype)
+    for base in ('linear', 'rbf', 'matern32'):
+        D = ops.trunc_diag(Xd, m, base=base)
+        G = ops.trunc_gram(Xd, None, m, base=base)
+        assert torch.equal(D, torch.diagonal(G, dim1=1, dim2=2)), "diag kernel and Gram kernel must agree bit for bit"
+        R = c_oracle.trunc_diag(X, m, base)
+        assert np.max(np.abs(D.cpu().numpy() - R) / np.abs(R).max(axis=1, keepdims=True)) < TOL[dtype]
+
+
+def test_no_difference_and_row_blocks():
+    from gpsig_b200 import ops
+    from oracle import c_oracle
+    N, N2, L, L2, d, m = 13, 7, 20, 31, 3, 3
+    X, Y = brownian(N, L, d, 5) * 0.3, brownian(N2, L2, d, 6) * 0.3
+    Xd, Yd = _dev(X, torch.float64), _dev(Y, torch.float64)
+    R = c_oracle.trunc_gram(X, Y, m, 'rbf', difference=False)
+    G = ops.trunc_gram(Xd, Yd, m, base='rbf', difference=False).cpu().numpy()
+    assert np.max(np.abs(G - R) / np.abs(R).max(axis=(1, 2), keepdims=True)) < 1e-10
+    # row-block sharding: blocks stitched together == the full matrix, bit for bit
+    full = ops.trunc_gram(Xd, Yd, m, base='rbf')
+    parts = [ops.trunc_gram(Xd, Yd, m, base='rbf', rows=(a, b)) for a, b in ((0, 4), (4, 4), (4, 13))]
+    assert torch.equal(torch.cat(parts, dim=1), full)
+
+
+def test_symmetric_gram_is_symmetric_and_unit_diagonal():
+    from gpsig_b200 import kernels
+    N, L, d, m = 40, 30, 4, 4
+    X = _dev(brownian(N, L, d, 7).reshape(N, -1), torch.float64)
+    k = kernels.SignatureRBF(L * d, d, m)
+    K = k.K(X, return_levels=True)
+    assert torch.allclose(K, K.transpose(1, 2), rtol=0, atol=1e-12)
+    assert torch.allclose(torch.diagonal(K, dim1=1, dim2=2), torch.ones(m + 1, N, dtype=K.dtype, device='cuda'), atol=1e-12)
+    assert torch.equal(k.Kdiag(X), torch.full((N,), float(m + 1), dtype=torch.float64, device='cuda'))
+
+
+def test_known_answer_level1_telescopes():
+    """Level 1 of the differenced kernel telescopes to 4 corner values of the base kernel."""
+    from gpsig_b200 import ops
+    X, Y = brownian(6, 200, 8, 8), brownian(4, 200, 8, 9)
+    G = ops.trunc_gram(_dev(X, torch.float64), _dev(Y, torch.float64), 2, base='linear').cpu().numpy()
+    ref = np.einsum('id,jd->ij', X[:, -1] - X[:, 0], Y[:, -1] - Y[:, 0])
+    assert np.allclose(G[0], 1.0) and np.max(np.abs(G[1] - ref)) < 1e-11
+
+
+def test_errors():
+    from gpsig_b200 import kernels, ops
+    with pytest.raises(ValueError):
+        kernels.SignatureLinear(10, 3, 2)
+    with pytest.raises(NotImplementedError):
+        kernels.SignatureLinear(12, 3, 2, order=2, low_rank=True)
+    with pytest.raises(ValueError):
+        kernels.SignatureLinear(12, 3, 2, num_lags=-1)
+    with pytest.raises(ValueError):
+        kernels.SignatureLinear(12, 3, 2, variances=np.ones(5))
+    X = torch.zeros(3, 1, 2, dtype=torch.float64, device='cuda')
+    with pytest.raises(ValueError):
+        ops.trunc_gram(X, None, 2)           # L=1 cannot be differenced
+    with pytest.raises(RuntimeError):
+        ops.trunc_gram(X.cpu(), None, 2)     # no CPU path
+    with pytest.raises(NotImplementedError):
+        ops.trunc_gram(torch.zeros(3, 4, 2, dtype=torch.float64, device='cuda'), None, 9)

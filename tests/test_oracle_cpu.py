@@ -1,0 +1,136 @@
+"""CPU tests of the oracle itself (no GPU): known-answer properties of the
+reference's notebooks, the committed golden vectors, and numpy <-> C port agreement."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import c_oracle, pde_np, sigs_np, trunc_np
+from tests.util import brownian, inducing_tensors, rel_err
+
+GOLD = os.path.join(os.path.dirname(__file__), 'golden')
+
+
+def test_higher_order_linear_equals_signature_inner_products():
+    """notebooks/signature_kernel.ipynb cells 11-13: SignatureLinear(order=num_levels,
+    normalization=False) == <S_k(x), S_k(y)> level by level."""
+    N, L, d, m = 6, 12, 3, 4
+    X, Y = brownian(N, L, d, 0), brownian(5, 9, d, 1)
+    o = trunc_np.SignatureKernelOracle(L * d, d, m, base='linear', order=m, normalization=False, lengthscales=None)
+    assert rel_err(o._K_seq(X), sigs_np.signature_gram_levels(X, None, m)) < 1e-13
+    assert rel_err(o._K_seq(X, Y), sigs_np.signature_gram_levels(X, Y, m)) < 1e-13
+
+
+def test_tens_vs_seq_equals_rank1_tensor_inner_products():
+    """notebooks/signature_kernel.ipynb cells 15-23 (higher order, linear, no increments)."""
+    N, L, d, m, Mz = 4, 10, 3, 3, 5
+    X = brownian(N, L, d, 2)
+    Z = inducing_tensors(X, m, Mz, False, 3)
+    o = trunc_np.SignatureKernelOracle(L * d, d, m, base='linear', order=m, normalization=False, lengthscales=None)
+    K = o._K_tens_vs_seq(Z, X)
+    S = [sigs_np.signature(x, m) for x in X]
+    k = 0
+    for lvl in range(1, m + 1):
+        for z in range(Mz):
+            t = sigs_np.rank1_tensor_levels(Z[k:k + lvl, z])
+            for n in range(N):
+                assert abs(K[lvl, z, n] - np.sum(t * S[n][lvl])) < 1e-12 * max(1, abs(K[lvl, z, n]))
+        k += lvl
+
+
+def test_tens_tens_equals_rank1_tensor_inner_products():
+    """notebooks/signature_kernel.ipynb cells 25-29."""
+    d, m, Mz = 3, 4, 6
+    Z = np.random.default_rng(4).standard_normal((m * (m + 1) // 2, Mz, d))
+    o = trunc_np.SignatureKernelOracle(30, d, m, base='linear', normalization=False, lengthscales=None)
+    K = o._K_tens(Z)
+    k = 0
+    for lvl in range(1, m + 1):
+        T = [sigs_np.rank1_tensor_levels(Z[k:k + lvl, z]) for z in range(Mz)]
+        ref = np.array([[np.sum(a * b) for b in T] for a in T])
+        assert rel_err(K[lvl], ref) < 1e-13
+        k += lvl
+
+
+def test_first_order_equals_higher_order_for_two_levels_only():
+    """order=1 is a different (cheaper) kernel: it agrees with the signature only up to level 1."""
+    X = brownian(5, 15, 2, 5)
+    o1 = trunc_np.SignatureKernelOracle(30, 2, 3, base='linear', order=1, normalization=False, lengthscales=None)
+    o3 = trunc_np.SignatureKernelOracle(30, 2, 3, base='linear', order=3, normalization=False, lengthscales=None)
+    A, B = o1._K_seq(X), o3._K_seq(X)
+    assert rel_err(A[:2], B[:2]) < 1e-13 and rel_err(A[2:], B[2:]) > 1e-3
+
+
+@pytest.mark.parametrize("base", sorted(c_oracle.BASE_IDS))
+def test_c_port_matches_numpy_restatement(base):
+    N, N2, L, L2, d, m = 7, 6, 13, 10, 3, 4
+    X, Y = brownian(N, L, d, 6), brownian(N2, L2, d, 7)
+    prm = {'poly': dict(gamma=1.0, degree=3.0), 'mix': dict(mixing=0.5)}.get(base, {})
+    o = trunc_np.SignatureKernelOracle(L * d, d, m, base=base, normalization=False, lengthscales=None, **prm)
+    tol = 1e-12
+    assert rel_err(c_oracle.trunc_gram(X, Y, m, base, list(prm.values())), o._K_seq(X, Y)) < tol
+    # Matern kernels take sqrt(max(r2, 1e-40)) of the CANCELLING expansion |x|^2+|y|^2-2x.y
+    # (kernels.py:959-961): at coincident points r = sqrt(rounding noise) ~ 1e-8, so the
+    # reference's own diagonal is only defined to ~1e-7 (it depends on the BLAS summation order).
+    dtol = 1e-6 if base.startswith('matern') else tol
+    assert rel_err(c_oracle.trunc_diag(X, m, base, list(prm.values())), o._K_seq_diag(X)) < dtol
+    for inc in (False, True):
+        Z = inducing_tensors(X, m, 5, inc, 8)
+        assert rel_err(c_oracle.tens_vs_seq(Z, X, m, inc, base, list(prm.values())), o._K_tens_vs_seq(Z, X, inc)) < tol
+
+
+def test_normalised_symmetric_gram_has_unit_diagonal():
+    X = brownian(8, 12, 3, 9).reshape(8, -1)
+    o = trunc_np.SignatureKernelOracle(36, 3, 4, base='rbf')
+    K = o.K(X, return_levels=True)
+    assert np.allclose(np.diagonal(K, axis1=1, axis2=2), 1.0, atol=1e-12)
+    assert np.allclose(o.Kdiag(X), 5.0)
+
+
+def test_trunc_golden_vectors():
+    g = np.load(os.path.join(GOLD, 'trunc_oracle.npz'))
+    X, Y, ls = g['X'], g['Y'], g['lengthscales']
+    N, L, d = X.shape
+    m = 4
+    for base in ('linear', 'rbf'):
+        for order in (1, 2, m):
+            for norm in (False, True):
+                o = trunc_np.SignatureKernelOracle(L * d, d, m, base=base, order=order, normalization=norm,
+                                                   lengthscales=ls, sigma=1.5, variances=np.linspace(0.5, 1.5, m + 1))
+                tag = '%s_o%d_n%d' % (base, order, norm)
+                assert rel_err(o.K(X.reshape(N, -1), Y.reshape(Y.shape[0], -1), return_levels=True), g['K_' + tag]) < 1e-13
+                assert rel_err(o.K(X.reshape(N, -1), return_levels=True), g['Ksym_' + tag]) < 1e-13
+
+
+def test_pde_numpy_and_c_match_reference_cython_golden():
+    """tests/golden/pde_ref.npz was produced by the reference's compiled sigKer_fast."""
+    g = np.load(os.path.join(GOLD, 'pde_ref.npz'))
+    X = g['X']
+    ix = np.arange(X.shape[0], dtype=np.int32)
+    for order in (0, 1, 2):
+        ref = g['kdiag_order%d' % order]
+        assert np.array_equal(pde_np.pde_kernel(X, None, order), ref)          # bit for bit
+        assert np.max(np.abs(c_oracle.pde_pairs(X, None, ix, ix, order) - ref) / np.abs(ref)) < 1e-14
+        assert np.array_equal(pde_np.pde_grid_rev(X, order)[:, -1, -1], g['krev_corner_order%d' % order])
+    for order in (0, 1):
+        G = pde_np.pde_grid(X[:2], None, order)
+        tril = np.tril(np.ones(G.shape[1:], bool))
+        assert np.array_equal(G[:, tril], g['grid_order%d' % order][:, tril])   # the reference fills the lower triangle only
+
+
+def test_pde_live_reference_module_if_built():
+    from oracle import build_ref
+    ref = build_ref.load()
+    if ref is None:
+        pytest.skip("oracle/_ref not built")
+    X = brownian(5, 17, 4, 10)
+    for order in (0, 2):
+        K, _ = ref.sig_kern_diag(X, order, 1)
+        assert np.array_equal(np.array(K)[:, -1, -1], pde_np.pde_kernel(X, None, order))
+
+
+def test_pde_rectangular_reduces_to_symmetric():
+    X = brownian(3, 9, 2, 11)
+    assert np.array_equal(pde_np.pde_kernel(X, X.copy(), 1), pde_np.pde_kernel(X, None, 1))
+    G = pde_np.pde_gram(X, None, 0)
+    assert np.allclose(G, G.T, rtol=1e-13)
