@@ -1,0 +1,305 @@
+#!/usr/bin/env python
+"""Headline benchmark: signature-kernel Gram pairs/sec (L=200, M=5).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--dtype f64|f32] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Workload (BASELINE.json configs[1], "c2"): SignatureRBF, num_levels=5, order=1,
+normalization=True, K(X, X2) with N = N2 = 2000 synthetic Brownian paths,
+L = 200, d = 8.  One step = one full K(X, X2) call = 4e6 ordered pairs.  With
+N GPUs every rank owns a 2000-row block of a (2000 N) x 2000 Gram (weak
+scaling, rows are independent: no data-path collective).
+
+Prints ONE JSON line (rank 0).  `value` = pairs/s with the inputs resident in
+HBM; `e2e` = the same through the numpy-in/numpy-out call (pinned host
+buffers, H2D + D2H inside the timed region); `roofline` = the fused Gram
+kernel against the measured CUDA-core FMA peak (it is compute bound -- see
+DESIGN.md); `cpu_baseline` = the C port of the reference algorithm
+(oracle/) on the host cores, bounded sample.
+"""
+import argparse
+import ctypes
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+CFG = dict(workload="c2: SignatureRBF m=5 order=1 normalization=True K(X,X2), N=N2=2000, L=200, d=8, Brownian paths",
+           N=2000, N2=2000, L=200, d=8, m=5)
+METRIC = "signature-kernel Gram pairs/sec (L=200,M=5)"
+UNIT = "pairs/s"
+
+
+def brownian(N, L, d, seed):
+    rng = np.random.default_rng(seed)
+    return np.cumsum(rng.standard_normal((N, L, d)) / np.sqrt(L), axis=1)
+
+
+def flops_per_pair(L, L2, d, m, rbf=True):
+    """2 d L L2 + c_k L L2 + 4 m (L-1)(L2-1); exp counted as part of c_k = 4."""
+    return 2 * d * L * L2 + (4 if rbf else 0) * L * L2 + 4 * m * (L - 1) * (L2 - 1)
+
+
+def bytes_per_pair(N, N2, L, L2, d, s, levels_out=1):
+    """s * [(N L d + N2 L2 d) / (N N2) + outputs]."""
+    return s * ((N * L * d + N2 * L2 * d) / (N * N2) + levels_out)
+
+
+# --------------------------------------------------------------------------------------
+# reference arm / CPU baseline: the C port of the reference algorithm (oracle/), all cores
+# --------------------------------------------------------------------------------------
+def cpu_pairs_per_sec(n_side, steps=1, warmup=0):
+    from oracle import c_oracle
+    c_oracle.build()
+    L, d, m = CFG['L'], CFG['d'], CFG['m']
+    X, Y = brownian(n_side, L, d, 0), brownian(n_side, L, d, 1)
+    for _ in range(warmup):
+        c_oracle.trunc_gram(X[:8], Y[:8], m, 'rbf')
+    times = []
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        # normalised K(X, X2) = Gram levels + the two diagonals (kernels.py:456-470)
+        c_oracle.trunc_gram(X, Y, m, 'rbf')
+        c_oracle.trunc_diag(X, m, 'rbf')
+        c_oracle.trunc_diag(Y, m, 'rbf')
+        times.append(time.perf_counter() - t0)
+    return n_side * n_side / statistics.mean(times), statistics.mean(times)
+
+
+def run_reference(args):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    cores = os.cpu_count()
+    # calibrate so that one step is a few seconds
+    cpu_pairs_per_sec(16)
+    v0, t0 = cpu_pairs_per_sec(32)
+    side = int(max(16, min(512, (v0 * 4.0) ** 0.5)))
+    v, t = cpu_pairs_per_sec(side, steps=args.steps, warmup=args.warmup)
+    line = {"metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * t, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic Brownian paths (seeded)", "impl": "reference", "config": dict(CFG, sample="%dx%d pairs per step" % (side, side)),
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                             "sample": "%dx%d sequence pairs of the c2 shape per step, C port of signature_algs.py:8-35 + kernels.py glue, OpenMP over pairs" % (side, side)},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+# --------------------------------------------------------------------------------------
+# ours
+# --------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown," \
+        "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, gpu_index):
+        self.f = tempfile.NamedTemporaryFile('w+', suffix='.csv', delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(['nvidia-smi', '-i', str(gpu_index), '--query-gpu=' + self.Q, '--format=csv,noheader,nounits',
+                                       '-lms', '100'], stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, smmax, reasons, power = [], [], set(), []
+        for ln in self.f.read().splitlines():
+            c = [x.strip() for x in ln.split(',')]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1])); smmax.append(float(c[2])); power.append(float(c[3]))
+            except ValueError:
+                continue
+            for name, val in zip(('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap'), c[5:9]):
+                if val.lower().startswith('active'):
+                    reasons.add(name)
+        try:
+            os.unlink(self.f.name)
+        except OSError:
+            pass
+        if sm:
+            out = {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(smmax), "reasons": sorted(reasons),
+                   "power_w_max": max(power), "samples": len(sm)}
+        return out
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(p):
+        return json.load(open(p)), "measured"
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}, "fallback"
+
+
+def fma_peak_tflops(torch, lib, esz):
+    """CUDA-core FMA peak measured with the library's FMA-chain microbenchmark."""
+    from gpsig_b200._lib import check, stream_handle
+    dev = torch.device('cuda', torch.cuda.current_device())
+    scratch = torch.zeros(64, dtype=torch.float64, device=dev)
+    blocks, iters = 148 * 16, 20000
+    best = 0.0
+    for rep in range(4):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        check(lib.gpsig_fma_peak(esz, blocks, iters, ctypes.c_void_p(scratch.data_ptr()), stream_handle(dev)))
+        e1.record()
+        e1.synchronize()
+        ms = e0.elapsed_time(e1)
+        if rep > 0:
+            best = max(best, 2.0 * blocks * 256 * 8 * iters / (ms * 1e-3) / 1e12)
+    return best
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get('RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; there is no CPU path (use --impl reference for the CPU baseline)")
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    from gpsig_b200 import kernels, ops, settings
+    from gpsig_b200._lib import lib
+    dtype = torch.float64 if args.dtype == 'f64' else torch.float32
+    esz = 8 if args.dtype == 'f64' else 4
+    settings.float_type = dtype
+    N, N2, L, d, m = CFG['N'], CFG['N2'], CFG['L'], CFG['d'], CFG['m']
+    # rank r owns rows [r N, (r+1) N) of the (world N) x N2 Gram: its own X block, shared X2
+    X_host = torch.from_numpy(brownian(N, L, d, 1000 + rank).reshape(N, L * d)).to(dtype).pin_memory()
+    X2_host = torch.from_numpy(brownian(N2, L, d, 1).reshape(N2, L * d)).to(dtype).pin_memory()
+    out_host = torch.empty((N, N2), dtype=dtype).pin_memory()
+    X, X2 = X_host.to(dev), X2_host.to(dev)
+    kern = kernels.SignatureRBF(L * d, d, m)
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)   # > 126 MB L2
+
+    def step_resident():
+        return kern.K(X, X2)
+
+    def step_e2e():
+        x = X_host.to(dev, non_blocking=True)
+        x2 = X2_host.to(dev, non_blocking=True)
+        K = kern.K(x, x2)
+        out_host.copy_(K, non_blocking=True)
+        return K
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup, profile_kernel=False):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        kms = []
+        n0 = lib.gpsig_launch_count()
+        lib.gpsig_profile_enable(1 if profile_kernel else 0)
+        for a, b in ev:
+            flush.fill_(1)                      # L2 flush between timed iterations (outside the events)
+            a.record()
+            fn()
+            b.record()
+            if profile_kernel:
+                kms.append(lib.gpsig_profile_last_kernel_ms())
+        barrier()
+        lib.gpsig_profile_enable(0)
+        launches = lib.gpsig_launch_count() - n0
+        tot_ms = sum(a.elapsed_time(b) for a, b in ev)
+        t = torch.tensor([tot_ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()), launches, kms
+
+    sampler = ClockSampler(local) if rank == 0 else None
+    tot_ms, launches, kms = timed(step_resident, args.steps, args.warmup, profile_kernel=True)
+    clocks = sampler.stop() if sampler else None
+    e2e_ms, _, _ = timed(step_e2e, args.steps, max(1, args.warmup // 2))
+    pairs_per_step = N * N2 * world
+    value = pairs_per_step * args.steps / (tot_ms * 1e-3)
+    e2e_value = pairs_per_step * args.steps / (e2e_ms * 1e-3)
+
+    if rank == 0:
+        peaks, how = measured_peaks()
+        fpeak = fma_peak_tflops(torch, lib, esz)
+        kern_ms = statistics.mean(kms) if kms else None
+        F = flops_per_pair(L, L, d, m)
+        achieved = N * N2 * F / (kern_ms * 1e-3) / 1e12 if kern_ms else None
+        Bp = bytes_per_pair(N, N2, L, L, d, esz)
+        nominal = 37.2 if esz == 8 else 74.4
+        roof = {"bound": "cuda-core-" + args.dtype, "achieved": achieved, "peak": fpeak, "unit": "TFLOP/s",
+                "frac": (achieved / fpeak) if (achieved and fpeak) else None, "traffic": None,
+                "peak_source": "FMA-chain microbenchmark in this run (gpsig_fma_peak); nominal %.1f TFLOP/s at 1965 MHz" % nominal,
+                "frac_of_nominal": achieved / nominal if achieved else None,
+                "kernel": "trunc_gram_kernel", "kernel_ms": kern_ms, "kernel_share_of_step": kern_ms * args.steps / tot_ms if kern_ms else None,
+                "flops_per_pair": F, "pairs_per_launch": N * N2,
+                "hbm": {"algorithmic_bytes_per_pair": Bp, "achieved_gbs": N * N2 * Bp / (kern_ms * 1e-3) / 1e9 if kern_ms else None,
+                        "peak_gbs": peaks.get("hbm_gbs"), "peak_source": how}}
+        # CPU baseline on a bounded sample
+        cpu_pairs_per_sec(16)
+        v0, _ = cpu_pairs_per_sec(32)
+        side = int(max(16, min(512, (v0 * 12.0) ** 0.5)))
+        cv, ct = cpu_pairs_per_sec(side)
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": tot_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": args.dtype, "data": "synthetic Brownian paths (seeded, SURVEY.md 8d)",
+                "config": dict(CFG, parallelism="rows x%d" % world, l2="flushed between timed iterations (256 MB write)",
+                               pairs_per_step=pairs_per_step),
+                "clocks": clocks,
+                "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms / args.steps,
+                        "h2d_bytes_per_step": int(X_host.numel() + X2_host.numel()) * esz,
+                        "d2h_bytes_per_step": int(out_host.numel()) * esz},
+                "gpu_launches": int(launches),
+                "roofline": roof,
+                "cpu_baseline": {"value": cv, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
+                                 "sample": "%dx%d pairs of the same shape in %.1f s (C port of the reference algorithm, OpenMP)" % (side, side, ct)}}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=5)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--dtype', choices=['f64', 'f32'], default='f64')
+    ap.add_argument('--impl', choices=['ours', 'reference'], default='ours')
+    args = ap.parse_args()
+    if args.impl == 'reference':
+        run_reference(args)
+    else:
+        world = int(os.environ.get('WORLD_SIZE', '1'))
+        if args.gpus > 1 and world == 1:
+            # convenience: relaunch under torchrun
+            cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', str(args.gpus),
+                   '--master-addr', '127.0.0.1', '--master-port', '29517', os.path.abspath(__file__)] + sys.argv[1:]
+            raise SystemExit(subprocess.call(cmd))
+        run_ours(args)
+
+
+if __name__ == '__main__':
+    main()

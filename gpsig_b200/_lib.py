@@ -34,7 +34,7 @@ class GpsigError(RuntimeError):
 def _load():
     if not os.path.exists(LIB_PATH):
         raise ImportError(
-            "gpsig_b200: %s is missing. Build it with `python -m gpsig_b200.build` "
+            "gpsig_b200: %s is missing. Build it with `python gpsig_b200/build.py` "
             "(there is no CPU or PyTorch fallback for the signature-kernel ops)." % LIB_PATH)
     lib = ctypes.CDLL(LIB_PATH)
     vp, i, sz, dbl = ctypes.c_void_p, ctypes.c_int, ctypes.c_size_t, ctypes.c_double
@@ -61,6 +61,12 @@ def _load():
         f = getattr(lib, 'gpsig_tens_tens_' + sfx)
         f.restype = i
         f.argtypes = [ctypes.POINTER(TruncDesc), vp, i, i, i, vp, ctypes.POINTER(Epilogue), vp, vp]
+    lib.gpsig_launch_count.restype = ctypes.c_ulonglong
+    lib.gpsig_profile_enable.argtypes = [i]
+    lib.gpsig_profile_enable.restype = None
+    lib.gpsig_profile_last_kernel_ms.restype = dbl
+    lib.gpsig_fma_peak.restype = i
+    lib.gpsig_fma_peak.argtypes = [i, i, i, vp, vp]
     lib.gpsig_pde_f64.restype = i
     lib.gpsig_pde_f64.argtypes = [vp, i, i, vp, i, i, i, vp, i, i, i, i, dbl, vp, vp, sz, vp]
     return lib

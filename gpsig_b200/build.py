@@ -1,6 +1,6 @@
 """Builds ``gpsig_b200/libgpsig_b200.so`` (sm_100a only) with nvcc, in-tree.
 
-    python -m gpsig_b200.build [--force] [--fast]
+    python gpsig_b200/build.py [--force] [--fast]     (run as a script: importing the package needs the built library)
 
 The library has no PyTorch dependency: it is a plain C-ABI shared object
 (``include/gpsig_b200.h``).  One object file per (dtype, base-kernel

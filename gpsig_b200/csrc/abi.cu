@@ -16,6 +16,40 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
+// ---- diagnostics ------------------------------------------------------------
+static unsigned long long g_launches = 0;
+void count_launch() { __atomic_add_fetch(&g_launches, 1ull, __ATOMIC_RELAXED); }
+
+static thread_local int g_prof_on = 0;
+static thread_local cudaEvent_t g_prof_ev[2] = {nullptr, nullptr};
+static thread_local int g_prof_valid = 0;
+void prof_begin(cudaStream_t s) {
+  if (!g_prof_on) return;
+  if (!g_prof_ev[0]) { cudaEventCreate(&g_prof_ev[0]); cudaEventCreate(&g_prof_ev[1]); }
+  cudaEventRecord(g_prof_ev[0], s);
+}
+void prof_end(cudaStream_t s) {
+  if (!g_prof_on) return;
+  cudaEventRecord(g_prof_ev[1], s);
+  g_prof_valid = 1;
+}
+
+// FMA-chain microbenchmark: 8 independent chains per thread, 2 flops per FMA.
+template <typename T>
+__global__ void __launch_bounds__(256) fma_peak_kernel(T* out, int iters, T a, T b) {
+  T v[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) v[k] = T(threadIdx.x + k);
+  for (int it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = gfma<T>(v[k], a, b);
+  }
+  T s = 0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s += v[k];
+  if (s == T(123.456)) out[0] = s;   // never true; keeps the chains alive
+}
+
 // explicit instantiations live in trunc_inst.cu / tens_inst.cu (one object per T, OP, DP)
 #define GPSIG_DECL(T, OP, DP)                                                             \
   extern template int launch_trunc<T, OP, DP>(const TruncParams&, cudaStream_t);          \
@@ -227,7 +261,7 @@ static int pde_impl(const double* X, int N, int L, const double* Y, int N2, int 
   if (npairs > 0x7fffffffull) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "too many pairs in one call (%zu)", npairs);
 #define GPSIG_PDE_GO(DP_, O_) do { auto kern = pde_wavefront_kernel<DP_, O_>; \
     GPSIG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-    kern<<<(unsigned)npairs, 32, smem, s>>>(P); } while (0)
+    prof_begin(s); kern<<<(unsigned)npairs, 32, smem, s>>>(P); prof_end(s); } while (0)
 #define GPSIG_PDE_DP(O_) do { if (P.DP == 4) GPSIG_PDE_GO(4, O_); else if (P.DP == 8) GPSIG_PDE_GO(8, O_); else GPSIG_PDE_GO(16, O_); } while (0)
   switch (order) {
     case 0: GPSIG_PDE_DP(0); break; case 1: GPSIG_PDE_DP(1); break; case 2: GPSIG_PDE_DP(2); break;
@@ -246,6 +280,25 @@ extern "C" {
 
 const char* gpsig_last_error_string(void) { return g_err; }
 int gpsig_version(void) { return GPSIG_VERSION; }
+
+unsigned long long gpsig_launch_count(void) { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
+void gpsig_profile_enable(int on) { g_prof_on = on; g_prof_valid = 0; }
+double gpsig_profile_last_kernel_ms(void) {
+  if (!g_prof_valid) return -1.0;
+  if (cudaEventSynchronize(g_prof_ev[1]) != cudaSuccess) return -1.0;
+  float ms = 0.f;
+  if (cudaEventElapsedTime(&ms, g_prof_ev[0], g_prof_ev[1]) != cudaSuccess) return -1.0;
+  return (double)ms;
+}
+int gpsig_fma_peak(int elem_size, int blocks, int iters, void* scratch, void* stream) {
+  if (!scratch || blocks < 1 || iters < 1) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "bad arguments to gpsig_fma_peak");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (elem_size == 8) fma_peak_kernel<double><<<blocks, 256, 0, s>>>(static_cast<double*>(scratch), iters, 0.999999, 1e-7);
+  else if (elem_size == 4) fma_peak_kernel<float><<<blocks, 256, 0, s>>>(static_cast<float*>(scratch), iters, 0.999999f, 1e-7f);
+  else GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "elem_size must be 4 or 8");
+  GPSIG_LAUNCH_CHECK("fma_peak_kernel");
+  return GPSIG_OK;
+}
 
 size_t gpsig_trunc_gram_workspace_bytes(int N, int L, int N2, int L2, int d, int elem) {
   return packed_bytes(N, L, d, elem) + (N2 > 0 ? packed_bytes(N2, L2, d, elem) : 0);

@@ -20,8 +20,18 @@ void set_error(const char* fmt, ...);
 #define GPSIG_FAIL(code, ...) do { ::gpsig::set_error(__VA_ARGS__); return (code); } while (0)
 #define GPSIG_CUDA_CHECK(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) \
     GPSIG_FAIL(GPSIG_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
-#define GPSIG_LAUNCH_CHECK(name) do { cudaError_t e_ = cudaGetLastError(); if (e_ != cudaSuccess) \
+#define GPSIG_LAUNCH_CHECK(name) do { ::gpsig::count_launch(); cudaError_t e_ = cudaGetLastError(); if (e_ != cudaSuccess) \
     GPSIG_FAIL(GPSIG_ERR_CUDA, "launch of %s failed: %s", name, cudaGetErrorString(e_)); } while (0)
+
+// ---------------------------------------------------------------------------
+// diagnostics (gpsig_profile_* / gpsig_launch_count in the C ABI)
+// ---------------------------------------------------------------------------
+void count_launch();                       // one per kernel launch of this library
+// When profiling is enabled, the launcher of each MAIN kernel (the fused Gram,
+// tensors-vs-sequences, PDE wavefront) brackets it with CUDA events on the
+// caller's stream; gpsig_profile_last_kernel_ms() reads them back.
+void prof_begin(cudaStream_t s);
+void prof_end(cudaStream_t s);
 
 // ---------------------------------------------------------------------------
 // packed sequence layout in HBM (produced by pack_sequences_kernel)

@@ -124,7 +124,9 @@ int launch_tens_vs_seq(const TensSeqParams& P, int m, cudaStream_t stream) {
   GPSIG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int ncols = P.col_end - P.col_begin;
   dim3 grid((ncols + 31) / 32, (P.Mz + kTensWarps - 1) / kTensWarps);
+  prof_begin(stream);
   kern<<<grid, kTensWarps * 32, smem, stream>>>(P);
+  prof_end(stream);
   GPSIG_LAUNCH_CHECK("tens_vs_seq_kernel");
   return GPSIG_OK;
 }

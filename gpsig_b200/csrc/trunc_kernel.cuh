@@ -320,7 +320,9 @@ int launch_trunc_inst(TruncParams P, cudaStream_t stream) {
     P.ichunk = ichunk;
     grid.y = (rows + ichunk - 1) / ichunk;
   }
+  if (!DIAG) prof_begin(stream);
   kern<<<grid, nwarps * 32, smem, stream>>>(P);
+  if (!DIAG) prof_end(stream);
   GPSIG_LAUNCH_CHECK("trunc_gram_kernel");
   return GPSIG_OK;
 }

@@ -140,6 +140,20 @@ int gpsig_pde_f64(const double* X, int N, int L, const double* Y, int N2, int L2
                   int row_begin, int row_end, double sigma, double* out,
                   void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- diagnostics (no reference counterpart; used by bench.py) ----------------
+ * gpsig_launch_count: kernels this library has launched since it was loaded.
+ * gpsig_profile_enable(1): from now on (this host thread) the launcher of each
+ *   MAIN kernel (fused Gram / tensors-vs-sequences / PDE wavefront) brackets it
+ *   with CUDA events on the caller's stream; gpsig_profile_last_kernel_ms()
+ *   waits for the most recent one and returns its duration (-1 if none).
+ * gpsig_fma_peak: FMA-chain microbenchmark (`blocks` CTAs x 256 threads x 8
+ *   chains x `iters` FMAs) -- the measured CUDA-core FP32/FP64 peak the
+ *   compute roofline is quoted against. */
+unsigned long long gpsig_launch_count(void);
+void gpsig_profile_enable(int on);
+double gpsig_profile_last_kernel_ms(void);
+int gpsig_fma_peak(int elem_size, int blocks, int iters, void* scratch, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
