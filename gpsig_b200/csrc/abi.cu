@@ -1,10 +1,12 @@
 // extern "C" entry points of libgpsig_b200.so (see include/gpsig_b200.h).
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "pde_kernel.cuh"
 #include "tens_kernels.cuh"
 #include "trunc_kernel.cuh"
+#include "trunc_skew_kernel.cuh"
 
 namespace gpsig {
 
@@ -53,6 +55,7 @@ __global__ void __launch_bounds__(256) fma_peak_kernel(T* out, int iters, T a, T
 // explicit instantiations live in trunc_inst.cu / tens_inst.cu (one object per T, OP, DP)
 #define GPSIG_DECL(T, OP, DP)                                                             \
   extern template int launch_trunc<T, OP, DP>(const TruncParams&, cudaStream_t);          \
+  extern template int launch_trunc_skew<T, OP, DP>(const TruncParams&, cudaStream_t);     \
   extern template int launch_tens_vs_seq<T, OP, DP>(const TensSeqParams&, int, cudaStream_t);
 #define GPSIG_DECL_T(T) \
   GPSIG_DECL(T, 0, 4) GPSIG_DECL(T, 0, 8) GPSIG_DECL(T, 0, 16) \
@@ -69,6 +72,13 @@ template <typename T>
 static int dispatch_trunc(const TruncParams& P, int base, int DP, cudaStream_t s) {
   const int op = op_of_base(base);
 #define GPSIG_GO(OP) (DP == 4 ? launch_trunc<T, OP, 4>(P, s) : DP == 8 ? launch_trunc<T, OP, 8>(P, s) : launch_trunc<T, OP, 16>(P, s))
+  return op == OP_LINEAR ? GPSIG_GO(0) : (op == OP_RBF ? GPSIG_GO(1) : GPSIG_GO(2));
+#undef GPSIG_GO
+}
+template <typename T>
+static int dispatch_skew(const TruncParams& P, int base, int DP, cudaStream_t s) {
+  const int op = op_of_base(base);
+#define GPSIG_GO(OP) (DP == 4 ? launch_trunc_skew<T, OP, 4>(P, s) : DP == 8 ? launch_trunc_skew<T, OP, 8>(P, s) : launch_trunc_skew<T, OP, 16>(P, s))
   return op == OP_LINEAR ? GPSIG_GO(0) : (op == OP_RBF ? GPSIG_GO(1) : GPSIG_GO(2));
 #undef GPSIG_GO
 }
@@ -92,18 +102,23 @@ static int check_desc(const gpsig_trunc_desc* d) {
 }
 
 template <typename T>
-static int pack(const T* X, int N, int L, int d, const T* ls, T* dst, cudaStream_t s) {
+static int pack(const T* X, int N, int L, int d, const T* ls, T* dst, cudaStream_t s, int RS = 0) {
   const size_t tot = (size_t)N * L;
   if (tot == 0) return GPSIG_OK;
+  if (RS == 0) RS = padded_dim(d);
   const int threads = 256;
   const size_t blocks = (tot + threads - 1) / threads;
-  pack_sequences_kernel<T><<<(unsigned)blocks, threads, 0, s>>>(X, N, L, d, padded_dim(d), ls, dst, seq_block_elems(L, d, sizeof(T)));
+  pack_sequences_kernel<T><<<(unsigned)blocks, threads, 0, s>>>(X, N, L, d, padded_dim(d), RS, ls, dst, seq_block_elems_rs(L, RS, sizeof(T)));
   GPSIG_LAUNCH_CHECK("pack_sequences_kernel");
   return GPSIG_OK;
 }
 
 static size_t packed_bytes(int N, int L, int d, int elem) {
   return align_up((size_t)N * seq_block_elems(L, d, elem) * elem, 128);
+}
+// with the padded row stride of the systolic Gram kernel (an upper bound of the plain layout)
+static size_t packed_bytes_padded(int N, int L, int d, int elem) {
+  return align_up((size_t)N * seq_block_elems_rs(L, skew_row_stride(d, elem), elem) * elem, 128);
 }
 
 template <typename T>
@@ -113,7 +128,6 @@ static int trunc_gram_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
   if (int rc = check_desc(desc)) return rc;
   const bool sym = X2 == nullptr;
   if (sym) { N2 = N; L2 = L; }
-  if (!X || !out) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "X/out must not be NULL");
   if (N < 0 || N2 < 0 || d < 1) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "bad sizes N=%d N2=%d d=%d", N, N2, d);
   if (d > 16) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "state dimension d=%d > 16 is not supported", d);
   const int minlen = desc->difference ? 2 : 1;
@@ -123,19 +137,24 @@ static int trunc_gram_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
   if (epi && ((epi->norm_x == nullptr) != (epi->norm_x2 == nullptr)))
     GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "norm_x and norm_x2 must be given together");
   if (row_begin == row_end || N2 == 0) return GPSIG_OK;
+  if (!X || !out) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "X/out must not be NULL");
   const size_t need = gpsig_trunc_gram_workspace_bytes(N, L, sym ? 0 : N2, L2, d, sizeof(T));
   if (!ws || ws_bytes < need || (reinterpret_cast<uintptr_t>(ws) & 15))
     GPSIG_FAIL(GPSIG_ERR_WORKSPACE, "workspace too small or misaligned: need %zu bytes (16-byte aligned), got %zu", need, ws_bytes);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
+  // the systolic kernel (padded rows) takes the throughput shapes, trunc_gram_kernel the rest
+  const bool skew = skew_eligible(L, L2, sizeof(T)) && getenv("GPSIG_NO_SKEW") == nullptr;
+  const int RS = skew ? skew_row_stride(d, sizeof(T)) : padded_dim(d);
   T* xp = static_cast<T*>(ws);
-  T* yp = sym ? xp : reinterpret_cast<T*>(static_cast<char*>(ws) + packed_bytes(N, L, d, sizeof(T)));
-  if (int rc = pack<T>(X, N, L, d, ls, xp, s)) return rc;
-  if (!sym) if (int rc = pack<T>(X2, N2, L2, d, ls, yp, s)) return rc;
+  T* yp = sym ? xp : reinterpret_cast<T*>(static_cast<char*>(ws) + packed_bytes_padded(N, L, d, sizeof(T)));
+  if (int rc = pack<T>(X, N, L, d, ls, xp, s, RS)) return rc;
+  if (!sym) if (int rc = pack<T>(X2, N2, L2, d, ls, yp, s, RS)) return rc;
 
   TruncParams P;
   memset(&P, 0, sizeof(P));
   P.xp = xp; P.yp = yp;
-  P.xblk = seq_block_elems(L, d, sizeof(T)); P.yblk = seq_block_elems(L2, d, sizeof(T));
+  P.xblk = seq_block_elems_rs(L, RS, sizeof(T)); P.yblk = seq_block_elems_rs(L2, RS, sizeof(T));
+  P.xrs = P.yrs = RS;
   P.N = N; P.N2 = N2; P.L = L; P.L2 = L2;
   P.row_begin = row_begin; P.row_end = row_end;
   P.m = desc->num_levels; P.difference = desc->difference;
@@ -146,6 +165,7 @@ static int trunc_gram_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
     P.sym_jitter = epi->sym_jitter; P.return_levels = epi->return_levels;
   } else P.return_levels = 1;
   P.out = out;
+  if (skew) return dispatch_skew<T>(P, desc->base, padded_dim(d), s);
   return dispatch_trunc<T>(P, desc->base, padded_dim(d), s);
 }
 
@@ -167,6 +187,7 @@ static int trunc_diag_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
   memset(&P, 0, sizeof(P));
   P.xp = xp; P.yp = xp;
   P.xblk = P.yblk = seq_block_elems(L, d, sizeof(T));
+  P.xrs = P.yrs = padded_dim(d);
   P.N = N; P.N2 = N; P.L = L; P.L2 = L;
   P.row_begin = 0; P.row_end = N;
   P.m = desc->num_levels; P.difference = desc->difference;
@@ -301,7 +322,7 @@ int gpsig_fma_peak(int elem_size, int blocks, int iters, void* scratch, void* st
 }
 
 size_t gpsig_trunc_gram_workspace_bytes(int N, int L, int N2, int L2, int d, int elem) {
-  return packed_bytes(N, L, d, elem) + (N2 > 0 ? packed_bytes(N2, L2, d, elem) : 0);
+  return packed_bytes_padded(N, L, d, elem) + (N2 > 0 ? packed_bytes_padded(N2, L2, d, elem) : 0);
 }
 size_t gpsig_trunc_diag_workspace_bytes(int N, int L, int d, int elem) { return packed_bytes(N, L, d, elem); }
 size_t gpsig_tens_vs_seq_workspace_bytes(int Mz, int increments, int N, int L, int d, int m, int elem) {

@@ -48,10 +48,14 @@ __host__ __device__ inline int padded_len(int L, int elem) { int q = 16 / elem; 
 __host__ __device__ inline size_t seq_block_elems(int L, int d, int elem) {
   return (size_t)L * padded_dim(d) + padded_len(L, elem);
 }
+__host__ __device__ inline size_t seq_block_elems_rs(int L, int RS, int elem) {
+  return (size_t)L * RS + padded_len(L, elem);
+}
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
+// RS = row stride of the packed rows in elements (>= DP; the pad is never read)
 template <typename T>
-__global__ void pack_sequences_kernel(const T* __restrict__ X, int N, int L, int d, int DP,
+__global__ void pack_sequences_kernel(const T* __restrict__ X, int N, int L, int d, int DP, int RS,
                                       const T* __restrict__ lengthscales, T* __restrict__ packed,
                                       size_t block_elems) {
   // one thread per point (n, p): reads d contiguous values, writes DP + 1
@@ -60,7 +64,7 @@ __global__ void pack_sequences_kernel(const T* __restrict__ X, int N, int L, int
   int n = (int)(idx / L), p = (int)(idx % L);
   const T* src = X + idx * d;
   T* blk = packed + (size_t)n * block_elems;
-  T* dst = blk + (size_t)p * DP;
+  T* dst = blk + (size_t)p * RS;
   T s = 0;
   for (int k = 0; k < DP; ++k) {
     T v = 0;
@@ -68,7 +72,7 @@ __global__ void pack_sequences_kernel(const T* __restrict__ X, int N, int L, int
     dst[k] = v;
     s += v * v;              // tf.reduce_sum(tf.square(X), axis=-1), kernels.py:948
   }
-  blk[(size_t)L * DP + p] = s;
+  blk[(size_t)L * RS + p] = s;
 }
 
 // ---------------------------------------------------------------------------

@@ -33,6 +33,7 @@ struct TruncParams {
   const void* xp;          // packed X  (see common.cuh)
   const void* yp;          // packed Y  (== xp for K(X, X) and for the diagonal)
   size_t xblk, yblk;       // packed block sizes in elements
+  int xrs, yrs;            // row strides of the packed blocks in elements (DP, or the padded stride of the systolic kernel)
   int N, N2, L, L2;
   int row_begin, row_end;  // rows of X this call covers
   int ichunk;              // rows per CTA

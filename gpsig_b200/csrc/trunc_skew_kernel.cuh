@@ -1,0 +1,393 @@
+// Fused truncated signature-kernel Gram for sm_100a -- systolic ("skewed") variant.
+//
+// Same contract as trunc_kernel.cuh (gpsig/kernels.py:209-238 + signature_algs.py:8-35
+// + epilogue kernels.py:431-477) for the shapes that carry the throughput:
+// K(X, X2) with 32 <= L and L2 <= 32*COLS (one warp pass over the columns).
+//
+// One WARP owns one column sequence y_j and streams the row sequences x_i of its
+// CTA's row chunk.  Lane t owns COLS consecutive columns q of the L x L2 base-kernel
+// tile and sweeps the rows; lane t runs ONE ROW-STEP BEHIND lane t-1:
+//
+//     step s:   lane t works on stream row (s - t)
+//
+// so everything lane t needs from the columns to its left at that row
+//   - the last first-difference U[p, q0-1] (for the 2-D increment D[p, q0-1]),
+//   - the row prefixes  e_l[p] = sum_{q' < q0} C_l[p, q'],  l = 0..m-2
+//     (C_l = running column sums of level l; signature_algs.py:32 re-associated),
+// was finished by lane t-1 one step earlier and arrives with ONE warp shuffle per
+// value -- there is no log-step prefix scan and no barrier in the recursion.  The
+// stream of rows continues across pairs: at the first row of the next x_i the same
+// shuffle chain carries the level totals K_l = sum_q C_l[L-1, q] to lane 31, which
+// applies the epilogue and stores.  The pipeline is filled once per CTA.
+//
+// x_i arrives in shared memory as one TMA bulk copy into a 3-deep ring shared by
+// the CTA's warps (full/empty mbarriers; lane 0 of warp 0 is the producer).  Rows
+// are padded to an odd number of 16-byte units so that the skewed row reads of a
+// quarter warp fall in distinct banks.
+#pragma once
+#include "trunc_kernel.cuh"
+
+namespace gpsig {
+
+constexpr int kSkewWarps = 8;
+constexpr int kSkewBufs = 3;
+
+// row stride (in elements) of the padded packed layout: an odd number of 16-byte units
+__host__ __device__ inline int skew_row_stride(int d, int elem) {
+  const int dp = padded_dim(d);
+  int u = dp * elem / 16;
+  if ((u & 1) == 0) ++u;
+  return u * 16 / elem;
+}
+
+// ---- exp for the RBF base kernel --------------------------------------------
+// float64: table-driven, 12 FP64-pipe instructions instead of ~22 for exp():
+//   x = (32 k + j) ln2/32 + r,  exp(x) = 2^k * 2^(j/32) * exp(r),  |r| <= ln2/64,
+// the 32-entry table 2^(j/32) lives one entry per lane and is read with a shuffle
+// (so the call must be warp-convergent), exp(r) is a degree-6 Taylor polynomial
+// (truncation 3.5e-18).  Accurate to ~1 ulp for x in [-700, 0].
+__device__ __forceinline__ double exp_tab32(double x, double tab_lane) {
+  x = fmax(x, -700.0);
+  const double s = fma(x, 46.16624130844683, 6755399441055744.0);
+  const int n = __double2loint(s);
+  const double nf = s - 6755399441055744.0;
+  double r = fma(nf, -0x1.62e42fee00000p-6, x);
+  r = fma(nf, -0x1.a39ef35793c76p-38, r);
+  const double tj = __shfl_sync(0xffffffffu, tab_lane, n & 31);
+  double q = fma(0.001388888888888889, r, 0.008333333333333333);
+  q = fma(q, r, 0.041666666666666664);
+  q = fma(q, r, 0.16666666666666666);
+  q = fma(q, r, 0.5);
+  q = fma(q, r, 1.0);
+  const double w = q * r;
+  const double res = fma(tj, w, tj);
+  return __hiloint2double(__double2hiint(res) + ((n >> 5) << 20), __double2loint(res));
+}
+
+template <typename T, int OP> struct SkewFinish {
+  static __device__ __forceinline__ T apply(T acc, T xc, T yc, int base, T p0, T p1, double tab) {
+    if (OP == OP_GENERIC) return base_eval_call<T>(base, p0, p1, acc, xc, yc);
+    return BaseOp<T, OP>::finish(acc, xc, yc, base, p0, p1);
+  }
+};
+template <> struct SkewFinish<double, OP_RBF> {
+  static __device__ __forceinline__ double apply(double acc, double, double, int, double, double, double tab) {
+    return exp_tab32(acc, tab);
+  }
+};
+
+template <typename T> struct SkewRows { static constexpr int R = sizeof(T) == 8 ? 2 : 1; };
+
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+template <typename T, int DP, int COLS, int MLEV, int OP>
+__global__ void __launch_bounds__(kSkewWarps * 32, 1) trunc_skew_kernel(const TruncParams P, const int RS) {
+  using V16 = typename Vec16<T>::type;
+  constexpr int V = Vec16<T>::V;
+  constexpr int KV = DP / V;
+  constexpr int R = SkewRows<T>::R;
+  constexpr bool YREG = YPolicy<T, DP, COLS>::kInRegs;
+  constexpr int NB = kSkewBufs;
+  using Op = BaseOp<T, OP>;
+
+  extern __shared__ __align__(128) unsigned char skew_smem[];
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(skew_smem);       // [NB]
+  uint64_t* empty_bar = full_bar + NB;                               // [NB]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int diff = P.difference ? 1 : 0;
+  const int L = P.L, L2 = P.L2;
+  const int ncols = L2 - diff;
+  const size_t xbytes = P.xblk * sizeof(T);
+  const size_t xslot = align_up_dev(xbytes);
+  unsigned char* xring = skew_smem + 128;
+  T* ysm = reinterpret_cast<T*>(xring + NB * xslot) + (size_t)warp * (COLS * 32 * DP);   // only if !YREG
+
+  const int i_lo = P.row_begin + blockIdx.y * P.ichunk;
+  const int i_hi = min(P.row_end, i_lo + P.ichunk);
+  const int npairs = i_hi - i_lo;
+  const T* xg = static_cast<const T*>(P.xp);
+
+  if (threadIdx.x == 0) {
+    for (int b = 0; b < NB; ++b) { mbar_init(&full_bar[b], 1); mbar_init(&empty_bar[b], kSkewWarps); }
+    fence_mbar_init();
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int it = 0; it < NB && it < npairs; ++it) {
+      mbar_expect_tx(&full_bar[it], (uint32_t)xbytes);
+      tma_load_1d(xring + it * xslot, xg + (size_t)(i_lo + it) * P.xblk, (uint32_t)xbytes, &full_bar[it]);
+    }
+  }
+
+  const int j = blockIdx.x * kSkewWarps + warp;
+  const bool active = j < P.N2;
+  const T* yblk = static_cast<const T*>(P.yp) + (size_t)(active ? j : P.N2 - 1) * P.yblk;
+  const T* ysqn = yblk + (size_t)L2 * P.yrs;
+
+  // ---- this lane's columns of y (fixed for the whole kernel) ---------------------
+  const int q0 = lane * COLS;
+  T yc[COLS];
+  V16 yreg[YREG ? COLS : 1][YREG ? KV : 1];
+  bool valid[COLS];
+#pragma unroll
+  for (int c = 0; c < COLS; ++c) {
+    const int q = min(q0 + c, L2 - 1);
+    yc[c] = Op::col_const(ysqn[q]);
+    const int dq = q0 + c - diff;                        // D column this slot produces
+    valid[c] = (dq >= 0) && (dq < ncols) && (q0 + c < L2);
+#pragma unroll
+    for (int kv = 0; kv < KV; ++kv) {
+      const V16 v = *reinterpret_cast<const V16*>(yblk + (size_t)q * P.yrs + kv * V);
+      if (YREG) yreg[YREG ? c : 0][YREG ? kv : 0] = v;
+      else *reinterpret_cast<V16*>(ysm + ((size_t)(c * KV + kv) * 32 + lane) * V) = v;
+    }
+  }
+  if (!YREG) __syncwarp();
+  double tab = 0.0;
+  if (OP == OP_RBF && sizeof(T) == 8) tab = exp2((double)lane * (1.0 / 32.0));
+
+  // ---- state ------------------------------------------------------------------------
+  T C[MLEV][COLS];
+#pragma unroll
+  for (int l = 0; l < MLEV; ++l)
+#pragma unroll
+    for (int c = 0; c < COLS; ++c) C[l][c] = T(0);
+  T Mprev[COLS];
+#pragma unroll
+  for (int c = 0; c < COLS; ++c) Mprev[c] = T(0);
+  T send[R][MLEV], sendU[R];
+#pragma unroll
+  for (int rr = 0; rr < R; ++rr) {
+    sendU[rr] = T(0);
+#pragma unroll
+    for (int l = 0; l < MLEV; ++l) send[rr][l] = T(0);
+  }
+
+  const int SPS = (L + R - 1) / R;                 // steps per pair
+  const int nsteps = npairs * SPS + 1 + 31;        // + finalisation step + pipeline drain
+  int seg = 0, rstep = 0, buf = 0;                 // this lane's position in the stream
+  const T p0 = T(P.p0), p1 = T(P.p1);
+  const size_t rows_out = (size_t)(P.row_end - P.row_begin);
+
+  for (int s = 0; s < nsteps; ++s) {
+    // ---- ring: wait for the pair lane 0 enters at this step; refill the slot lane 31 left ----
+    {
+      const int sseg = s / SPS;
+      if (s - sseg * SPS == 0 && sseg < npairs) mbar_wait(&full_bar[sseg % NB], (sseg / NB) & 1);
+      const int s31 = s - 32;                      // lane 31 finished pair (s31 / SPS) at step s - 1
+      if (s31 >= 0) {
+        const int dseg = s31 / SPS;
+        if (s31 - dseg * SPS == SPS - 1 && dseg < npairs) {
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&empty_bar[dseg % NB]);
+          const int nxt = dseg + NB;                // the pair that reuses this slot
+          if (threadIdx.x == 0 && nxt < npairs) {
+            mbar_wait(&empty_bar[dseg % NB], (dseg / NB) & 1);
+            mbar_expect_tx(&full_bar[nxt % NB], (uint32_t)xbytes);
+            tma_load_1d(xring + (nxt % NB) * xslot, xg + (size_t)(i_lo + nxt) * P.xblk, (uint32_t)xbytes, &full_bar[nxt % NB]);
+          }
+        }
+      }
+    }
+    // ---- chain values from the lane to the left (computed one step ago) -----------
+    T recv[R][MLEV], recvU[R];
+#pragma unroll
+    for (int rr = 0; rr < R; ++rr) {
+      recvU[rr] = __shfl_up_sync(0xffffffffu, sendU[rr], 1);
+#pragma unroll
+      for (int l = 0; l < MLEV; ++l) {
+        if (l < MLEV - 1 || rr == 0) recv[rr][l] = __shfl_up_sync(0xffffffffu, send[rr][l], 1);
+        else recv[rr][l] = T(0);
+      }
+      if (lane == 0) {
+        recvU[rr] = T(0);
+#pragma unroll
+        for (int l = 0; l < MLEV; ++l) recv[rr][l] = T(0);
+      }
+    }
+    const bool in_stream = (s >= lane) && (seg <= npairs);
+    const bool live = in_stream && (seg < npairs);            // rows of a real pair (else: finalisation only)
+    const T* xb = reinterpret_cast<const T*>(xring + (live ? buf : 0) * xslot);
+    const T* xsq = xb + (size_t)L * RS;
+    const int r0 = live ? rstep * R : 0;
+
+    // ---- base kernel on R rows x COLS columns -------------------------------------
+    T Mcur[R][COLS];
+    {
+      T xc[R];
+      T acc[R][COLS];
+#pragma unroll
+      for (int rr = 0; rr < R; ++rr) {
+        const int row = min(r0 + rr, L - 1);
+        xc[rr] = Op::row_const(xsq[row]);
+#pragma unroll
+        for (int c = 0; c < COLS; ++c) acc[rr][c] = Op::init(xc[rr], yc[c]);
+      }
+#pragma unroll
+      for (int kv = 0; kv < KV; ++kv) {
+        V16 xv[R];
+#pragma unroll
+        for (int rr = 0; rr < R; ++rr)
+          xv[rr] = *reinterpret_cast<const V16*>(xb + (size_t)min(r0 + rr, L - 1) * RS + kv * V);
+#pragma unroll
+        for (int c = 0; c < COLS; ++c) {
+          V16 yv;
+          if (YREG) yv = yreg[YREG ? c : 0][YREG ? kv : 0];
+          else yv = *reinterpret_cast<const V16*>(ysm + ((size_t)(c * KV + kv) * 32 + lane) * V);
+#pragma unroll
+          for (int rr = 0; rr < R; ++rr)
+#pragma unroll
+            for (int e = 0; e < V; ++e) acc[rr][c] = gfma<T>(vget(xv[rr], e), vget(yv, e), acc[rr][c]);
+        }
+      }
+#pragma unroll
+      for (int rr = 0; rr < R; ++rr)
+#pragma unroll
+        for (int c = 0; c < COLS; ++c)
+          Mcur[rr][c] = SkewFinish<T, OP>::apply(acc[rr][c], xc[rr], yc[c], P.base, p0, p1, tab);
+    }
+
+    // ---- recursion, row by row -----------------------------------------------------
+#pragma unroll
+    for (int rr = 0; rr < R; ++rr) {
+      const int row = r0 + rr;
+      const bool rowlive = live && (row < L);
+      T D[COLS];
+      if (diff) {
+        T U[COLS];
+#pragma unroll
+        for (int c = 0; c < COLS; ++c) { U[c] = Mcur[rr][c] - Mprev[c]; Mprev[c] = Mcur[rr][c]; }
+#pragma unroll
+        for (int c = 0; c < COLS; ++c) D[c] = U[c] - (c > 0 ? U[c - 1] : recvU[rr]);
+        sendU[rr] = U[COLS - 1];
+      } else {
+#pragma unroll
+        for (int c = 0; c < COLS; ++c) D[c] = Mcur[rr][c];
+      }
+      const bool drow = rowlive && (row >= diff);
+#pragma unroll
+      for (int c = 0; c < COLS; ++c) D[c] = (drow && valid[c]) ? D[c] : T(0);
+
+      if (rr == 0 && in_stream && rstep == 0) {
+        // first row of a pair: the chain carries the level totals of the pair just finished
+        T tot[MLEV];
+#pragma unroll
+        for (int l = 0; l < MLEV; ++l) {
+          T e = recv[0][l];
+#pragma unroll
+          for (int c = 0; c < COLS; ++c) e += C[l][c];
+          tot[l] = e;
+          send[0][l] = e;
+        }
+        if (lane == 31 && seg > 0 && active) {
+          // ---- epilogue: normalise, scale, store (kernels.py:431-477) ----
+          const int i = i_lo + seg - 1;
+          const size_t rc = (size_t)(i - P.row_begin) * P.N2 + j;
+          T sum = T(0);
+#pragma unroll
+          for (int lvl = 0; lvl <= MLEV; ++lvl) {
+            if (lvl <= P.m) {
+              T v = lvl == 0 ? T(1) : tot[lvl > 0 ? lvl - 1 : 0];
+              if (P.symmetric && i == j) v += T(P.sym_jitter);
+              if (P.norm_x) {
+                const T a = gsqrt<T>(static_cast<const T*>(P.norm_x)[(size_t)lvl * P.N + i]);
+                const T b = gsqrt<T>(static_cast<const T*>(P.norm_x2)[(size_t)lvl * P.N2 + j]);
+                v = v / (a * b);
+              }
+              if (P.level_scale) v *= static_cast<const T*>(P.level_scale)[lvl];
+              if (P.return_levels) static_cast<T*>(P.out)[(size_t)lvl * rows_out * P.N2 + rc] = v;
+              else sum += v;
+            }
+          }
+          if (!P.return_levels) static_cast<T*>(P.out)[rc] = sum;
+        }
+#pragma unroll
+        for (int l = 1; l < MLEV; ++l)
+#pragma unroll
+          for (int c = 0; c < COLS; ++c) C[l][c] = T(0);
+#pragma unroll
+        for (int c = 0; c < COLS; ++c) C[0][c] = D[c];
+      } else {
+        // C_{l+1}[q] += D[p, q] * sum_{q' < q} C_l[q'], highest level first (C_l is read before row p updates it)
+#pragma unroll
+        for (int l = MLEV - 2; l >= 0; --l) {
+          T e = recv[rr][l];
+#pragma unroll
+          for (int c = 0; c < COLS; ++c) {
+            const T t = e;
+            e += C[l][c];
+            C[l + 1][c] = gfma<T>(D[c], t, C[l + 1][c]);
+          }
+          send[rr][l] = e;
+        }
+#pragma unroll
+        for (int c = 0; c < COLS; ++c) C[0][c] += D[c];
+      }
+    }
+    if (in_stream) {
+      if (++rstep == SPS) { rstep = 0; ++seg; if (++buf == NB) buf = 0; }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------
+// Shapes this kernel takes (the rest runs trunc_gram_kernel): one column pass, rows long
+// enough (>= 32 steps per pair) that a lane-skewed warp touches at most two consecutive pairs.
+inline bool skew_eligible(int L, int L2, int elem) { return L >= 32 * (elem == 8 ? 2 : 1) + 1 && L2 <= 256; }
+
+template <typename T, int DP, int COLS, int MLEV, int OP>
+int launch_skew_inst(TruncParams P, cudaStream_t stream) {
+  const int RS = P.xrs;
+  const size_t xslot = align_up_dev(P.xblk * sizeof(T));
+  const size_t smem = 128 + kSkewBufs * xslot + (size_t)kSkewWarps * trunc_ywarp_bytes<T, DP, COLS>();
+  if (smem > kMaxSmem)
+    GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "sequence too long for the on-chip plan: needs %zu bytes of shared memory (L=%d)", smem, P.L);
+  auto kern = trunc_skew_kernel<T, DP, COLS, MLEV, OP>;
+  GPSIG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  dim3 grid;
+  grid.x = (P.N2 + kSkewWarps - 1) / kSkewWarps;
+  const int rows = P.row_end - P.row_begin;
+  // >= ~24 waves of CTAs over the 148 SMs, but >= 16 pairs per warp so the 31-step pipeline fill stays < 1 %
+  int want_y = (24 * 148 + (int)grid.x - 1) / (int)grid.x;
+  int ichunk = (rows + want_y - 1) / want_y;
+  if (ichunk < 16) ichunk = 16;
+  if (ichunk > rows) ichunk = rows;
+  P.ichunk = ichunk;
+  grid.y = (rows + ichunk - 1) / ichunk;
+  prof_begin(stream);
+  kern<<<grid, kSkewWarps * 32, smem, stream>>>(P, RS);
+  prof_end(stream);
+  GPSIG_LAUNCH_CHECK("trunc_skew_kernel");
+  return GPSIG_OK;
+}
+
+#ifdef GPSIG_FAST_BUILD
+#define GPSIG_SKEW_COLS(X) X(2) X(7)
+#define GPSIG_SKEW_MLEV(X) X(4) X(5)
+#else
+#define GPSIG_SKEW_COLS(X) X(2) X(4) X(6) X(7) X(8)
+#define GPSIG_SKEW_MLEV(X) X(4) X(5) X(8)
+#endif
+
+template <typename T, int OP, int DP, int COLS>
+int launch_skew_mlev(const TruncParams& P, cudaStream_t stream) {
+#define GPSIG_CASE(M_) if (P.m <= M_) return launch_skew_inst<T, DP, COLS, M_, OP>(P, stream);
+  GPSIG_SKEW_MLEV(GPSIG_CASE)
+#undef GPSIG_CASE
+  GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "num_levels=%d is not supported by this build", P.m);
+}
+
+template <typename T, int OP, int DP>
+int launch_trunc_skew(const TruncParams& P, cudaStream_t stream) {
+  const int need = (P.L2 + 31) / 32;
+#define GPSIG_CASE(C_) if (need <= C_) return launch_skew_mlev<T, OP, DP, C_>(P, stream);
+  GPSIG_SKEW_COLS(GPSIG_CASE)
+#undef GPSIG_CASE
+  GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "no systolic kernel shape for L2=%d", P.L2);
+}
+
+}  // namespace gpsig

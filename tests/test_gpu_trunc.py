@@ -40,14 +40,22 @@ def test_gram_all_base_kernels(dtype, base, cls, bp, normalization):
         orc_kw = dict(mixing=0.5)
     o = SignatureKernelOracle(L * d, d, m, base=base, lengthscales=ls, normalization=normalization, sigma=1.7,
                               variances=np.linspace(0.5, 1.5, m + 1), **orc_kw)
+    tol = TOL[dtype]
+    if base == 'matern12':
+        # exp(-r) is not differentiable at r = 0: on coincident points (the diagonal blocks of K(X, X))
+        # r = sqrt(max(|x|^2 + |y|^2 - 2 x.y, 1e-40)) is sqrt(rounding noise) ~ sqrt(eps), so ANY two
+        # evaluation orders (TF's matmul vs FMA chains) differ by ~sqrt(eps) there: the reference itself
+        # is only defined to that accuracy (kernels.py:959-961, 1135-1138).
+        # The normalised K(X, X2) inherits it through the diagonals k(x_i, x_i).
+        tol = {torch.float64: 1e-6, torch.float32: 1e-2}[dtype]
     for ret in (True, False):
         G = k.K(_dev(X.reshape(N, -1), dtype), _dev(Y.reshape(N2, -1), dtype), return_levels=ret).cpu().numpy()
         R = o.K(X.reshape(N, -1), Y.reshape(N2, -1), return_levels=ret)
         assert G.shape == R.shape
-        assert rel_err(G, R) < TOL[dtype], (base, ret, rel_err(G, R))
+        assert rel_err(G, R) < tol, (base, ret, rel_err(G, R))
     Gs = k.K(_dev(X.reshape(N, -1), dtype), return_levels=True).cpu().numpy()
     Rs = o.K(X.reshape(N, -1), return_levels=True)
-    assert rel_err(Gs, Rs) < TOL[dtype]
+    assert rel_err(Gs, Rs) < tol, (base, rel_err(Gs, Rs))
 
 
 @pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
@@ -78,7 +86,8 @@ def test_diag_matches_gram_diagonal_and_oracle(dtype):
     for base in ('linear', 'rbf', 'matern32'):
         D = ops.trunc_diag(Xd, m, base=base)
         G = ops.trunc_gram(Xd, None, m, base=base)
-        assert torch.equal(D, torch.diagonal(G, dim1=1, dim2=2)), "diag kernel and Gram kernel must agree bit for bit"
+        # the diagonal comes from trunc_gram_kernel, the Gram possibly from the systolic kernel (different summation order)
+        assert torch.allclose(D, torch.diagonal(G, dim1=1, dim2=2), rtol=10 * TOL[dtype], atol=0)
         R = c_oracle.trunc_diag(X, m, base)
         assert np.max(np.abs(D.cpu().numpy() - R) / np.abs(R).max(axis=1, keepdims=True)) < TOL[dtype]
 
