@@ -102,13 +102,13 @@ static int check_desc(const gpsig_trunc_desc* d) {
 }
 
 template <typename T>
-static int pack(const T* X, int N, int L, int d, const T* ls, T* dst, cudaStream_t s, int RS = 0) {
+static int pack(const T* X, int N, int L, int d, const T* ls, T* dst, cudaStream_t s, int RS = 0, double scale = 1.0) {
   const size_t tot = (size_t)N * L;
   if (tot == 0) return GPSIG_OK;
   if (RS == 0) RS = padded_dim(d);
   const int threads = 256;
   const size_t blocks = (tot + threads - 1) / threads;
-  pack_sequences_kernel<T><<<(unsigned)blocks, threads, 0, s>>>(X, N, L, d, padded_dim(d), RS, ls, dst, seq_block_elems_rs(L, RS, sizeof(T)));
+  pack_sequences_kernel<T><<<(unsigned)blocks, threads, 0, s>>>(X, N, L, d, padded_dim(d), RS, ls, dst, seq_block_elems_rs(L, RS, sizeof(T)), T(scale));
   GPSIG_LAUNCH_CHECK("pack_sequences_kernel");
   return GPSIG_OK;
 }
@@ -147,8 +147,11 @@ static int trunc_gram_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
   const int RS = skew ? skew_row_stride(d, sizeof(T)) : padded_dim(d);
   T* xp = static_cast<T*>(ws);
   T* yp = sym ? xp : reinterpret_cast<T*>(static_cast<char*>(ws) + packed_bytes_padded(N, L, d, sizeof(T)));
-  if (int rc = pack<T>(X, N, L, d, ls, xp, s, RS)) return rc;
-  if (!sym) if (int rc = pack<T>(X2, N2, L2, d, ls, yp, s, RS)) return rc;
+  // float32 RBF on the systolic kernel: coordinates pre-scaled by sqrt(log2 e) so that the exponent
+  // x.y - |x|^2/2 - |y|^2/2 comes out in base-2 units and exp() is one MUFU.EX2 (trunc_skew_kernel.cuh)
+  const double cscale = (skew && sizeof(T) == 4 && desc->base == GPSIG_BASE_RBF) ? 1.2011224087864498 : 1.0;
+  if (int rc = pack<T>(X, N, L, d, ls, xp, s, RS, cscale)) return rc;
+  if (!sym) if (int rc = pack<T>(X2, N2, L2, d, ls, yp, s, RS, cscale)) return rc;
 
   TruncParams P;
   memset(&P, 0, sizeof(P));

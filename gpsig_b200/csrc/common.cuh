@@ -57,7 +57,7 @@ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 template <typename T>
 __global__ void pack_sequences_kernel(const T* __restrict__ X, int N, int L, int d, int DP, int RS,
                                       const T* __restrict__ lengthscales, T* __restrict__ packed,
-                                      size_t block_elems) {
+                                      size_t block_elems, T scale) {
   // one thread per point (n, p): reads d contiguous values, writes DP + 1
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (size_t)N * L) return;
@@ -68,7 +68,7 @@ __global__ void pack_sequences_kernel(const T* __restrict__ X, int N, int L, int
   T s = 0;
   for (int k = 0; k < DP; ++k) {
     T v = 0;
-    if (k < d) { v = src[k]; if (lengthscales) v = v / lengthscales[k]; }
+    if (k < d) { v = src[k]; if (lengthscales) v = v / lengthscales[k]; if (scale != T(1)) v *= scale; }
     dst[k] = v;
     s += v * v;              // tf.reduce_sum(tf.square(X), axis=-1), kernels.py:948
   }

@@ -25,11 +25,12 @@
 // are padded to an odd number of 16-byte units so that the skewed row reads of a
 // quarter warp fall in distinct banks.
 #pragma once
+#include <type_traits>
+
 #include "trunc_kernel.cuh"
 
 namespace gpsig {
 
-constexpr int kSkewWarps = 8;
 constexpr int kSkewBufs = 3;
 
 // row stride (in elements) of the padded packed layout: an odd number of 16-byte units
@@ -45,9 +46,8 @@ __host__ __device__ inline int skew_row_stride(int d, int elem) {
 //   x = (32 k + j) ln2/32 + r,  exp(x) = 2^k * 2^(j/32) * exp(r),  |r| <= ln2/64,
 // the 32-entry table 2^(j/32) lives one entry per lane and is read with a shuffle
 // (so the call must be warp-convergent), exp(r) is a degree-6 Taylor polynomial
-// (truncation 3.5e-18).  Accurate to ~1 ulp for x in [-700, 0].
+// (truncation 3.5e-18).  Accurate to ~1 ulp for x <= 0 (for x < -693 it returns ~1e-301, i.e. 0 at any tolerance).
 __device__ __forceinline__ double exp_tab32(double x, double tab_lane) {
-  x = fmax(x, -700.0);
   const double s = fma(x, 46.16624130844683, 6755399441055744.0);
   const int n = __double2loint(s);
   const double nf = s - 6755399441055744.0;
@@ -61,7 +61,11 @@ __device__ __forceinline__ double exp_tab32(double x, double tab_lane) {
   q = fma(q, r, 1.0);
   const double w = q * r;
   const double res = fma(tj, w, tj);
-  return __hiloint2double(__double2hiint(res) + ((n >> 5) << 20), __double2loint(res));
+  // 2^k by an exponent-field add.  k is clamped at -1000 (the result is ~1e-301 instead of a
+  // denormal) and forced there for x <= -800, where n may have wrapped (integer test on the sign/exponent word).
+  int k = max(n >> 5, -1000);
+  if ((unsigned)__double2hiint(x) >= 0xC0890000u) k = -1000;
+  return __hiloint2double(__double2hiint(res) + (k << 20), __double2loint(res));
 }
 
 template <typename T, int OP> struct SkewFinish {
@@ -76,18 +80,31 @@ template <> struct SkewFinish<double, OP_RBF> {
   }
 };
 
-template <typename T> struct SkewRows { static constexpr int R = sizeof(T) == 8 ? 2 : 1; };
+template <typename T> struct SkewCfg;
+template <> struct SkewCfg<double> { static constexpr int R = 2; static constexpr int NW = 8; };   // rows per step, warps per CTA
+template <> struct SkewCfg<float> { static constexpr int R = 1; static constexpr int NW = 8; };
+
+// float32 RBF: the packed coordinates are pre-scaled by sqrt(log2 e) (abi.cu), so the exponent
+// arrives in base-2 units and exp() is a single MUFU.EX2
+template <> struct SkewFinish<float, OP_RBF> {
+  static __device__ __forceinline__ float apply(float acc, float, float, int, float, float, double) {
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(acc));
+    return r;
+  }
+};
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
 template <typename T, int DP, int COLS, int MLEV, int OP>
-__global__ void __launch_bounds__(kSkewWarps * 32, 1) trunc_skew_kernel(const TruncParams P, const int RS) {
+__global__ void __launch_bounds__(SkewCfg<T>::NW * 32, 1) trunc_skew_kernel(const TruncParams P, const int RS) {
   using V16 = typename Vec16<T>::type;
   constexpr int V = Vec16<T>::V;
   constexpr int KV = DP / V;
-  constexpr int R = SkewRows<T>::R;
+  constexpr int R = SkewCfg<T>::R;
+  constexpr int NW = SkewCfg<T>::NW;
   constexpr bool YREG = YPolicy<T, DP, COLS>::kInRegs;
   constexpr int NB = kSkewBufs;
   using Op = BaseOp<T, OP>;
@@ -96,9 +113,8 @@ __global__ void __launch_bounds__(kSkewWarps * 32, 1) trunc_skew_kernel(const Tr
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(skew_smem);       // [NB]
   uint64_t* empty_bar = full_bar + NB;                               // [NB]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int diff = P.difference ? 1 : 0;
+  const bool diff = P.difference != 0;
   const int L = P.L, L2 = P.L2;
-  const int ncols = L2 - diff;
   const size_t xbytes = P.xblk * sizeof(T);
   const size_t xslot = align_up_dev(xbytes);
   unsigned char* xring = skew_smem + 128;
@@ -110,7 +126,7 @@ __global__ void __launch_bounds__(kSkewWarps * 32, 1) trunc_skew_kernel(const Tr
   const T* xg = static_cast<const T*>(P.xp);
 
   if (threadIdx.x == 0) {
-    for (int b = 0; b < NB; ++b) { mbar_init(&full_bar[b], 1); mbar_init(&empty_bar[b], kSkewWarps); }
+    for (int b = 0; b < NB; ++b) { mbar_init(&full_bar[b], 1); mbar_init(&empty_bar[b], NW); }
     fence_mbar_init();
   }
   __syncthreads();
@@ -121,22 +137,21 @@ __global__ void __launch_bounds__(kSkewWarps * 32, 1) trunc_skew_kernel(const Tr
     }
   }
 
-  const int j = blockIdx.x * kSkewWarps + warp;
+  const int j = blockIdx.x * NW + warp;
   const bool active = j < P.N2;
   const T* yblk = static_cast<const T*>(P.yp) + (size_t)(active ? j : P.N2 - 1) * P.yblk;
   const T* ysqn = yblk + (size_t)L2 * P.yrs;
 
   // ---- this lane's columns of y (fixed for the whole kernel) ---------------------
+  // Slots past the last column repeat it: their first differences equal their left
+  // neighbour's, so their 2-D increments are exactly zero without any masking.
   const int q0 = lane * COLS;
   T yc[COLS];
   V16 yreg[YREG ? COLS : 1][YREG ? KV : 1];
-  bool valid[COLS];
 #pragma unroll
   for (int c = 0; c < COLS; ++c) {
     const int q = min(q0 + c, L2 - 1);
     yc[c] = Op::col_const(ysqn[q]);
-    const int dq = q0 + c - diff;                        // D column this slot produces
-    valid[c] = (dq >= 0) && (dq < ncols) && (q0 + c < L2);
 #pragma unroll
     for (int kv = 0; kv < KV; ++kv) {
       const V16 v = *reinterpret_cast<const V16*>(yblk + (size_t)q * P.yrs + kv * V);
@@ -154,9 +169,9 @@ __global__ void __launch_bounds__(kSkewWarps * 32, 1) trunc_skew_kernel(const Tr
   for (int l = 0; l < MLEV; ++l)
 #pragma unroll
     for (int c = 0; c < COLS; ++c) C[l][c] = T(0);
-  T Mprev[COLS];
+  T Mp[2][COLS];                                   // last base-kernel row, ping-pong over the step parity
 #pragma unroll
-  for (int c = 0; c < COLS; ++c) Mprev[c] = T(0);
+  for (int c = 0; c < COLS; ++c) Mp[0][c] = Mp[1][c] = T(0);
   T send[R][MLEV], sendU[R];
 #pragma unroll
   for (int rr = 0; rr < R; ++rr) {
@@ -165,30 +180,25 @@ __global__ void __launch_bounds__(kSkewWarps * 32, 1) trunc_skew_kernel(const Tr
     for (int l = 0; l < MLEV; ++l) send[rr][l] = T(0);
   }
 
-  const int SPS = (L + R - 1) / R;                 // steps per pair
-  const int nsteps = npairs * SPS + 1 + 31;        // + finalisation step + pipeline drain
-  int seg = 0, rstep = 0, buf = 0;                 // this lane's position in the stream
+  const int SPS = (L + R - 1) / R;                 // steps per pair (>= 32, see skew_eligible)
+  const int nsteps = npairs * SPS + 32;            // + finalisation step + pipeline drain
+  int kk = 0, sseg = 0, ubuf = 0, ubuf_prev = NB - 1;   // warp-uniform: step within pair, pair and ring slot of lane 0
   const T p0 = T(P.p0), p1 = T(P.p1);
   const size_t rows_out = (size_t)(P.row_end - P.row_begin);
 
-  for (int s = 0; s < nsteps; ++s) {
-    // ---- ring: wait for the pair lane 0 enters at this step; refill the slot lane 31 left ----
-    {
-      const int sseg = s / SPS;
-      if (s - sseg * SPS == 0 && sseg < npairs) mbar_wait(&full_bar[sseg % NB], (sseg / NB) & 1);
-      const int s31 = s - 32;                      // lane 31 finished pair (s31 / SPS) at step s - 1
-      if (s31 >= 0) {
-        const int dseg = s31 / SPS;
-        if (s31 - dseg * SPS == SPS - 1 && dseg < npairs) {
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&empty_bar[dseg % NB]);
-          const int nxt = dseg + NB;                // the pair that reuses this slot
-          if (threadIdx.x == 0 && nxt < npairs) {
-            mbar_wait(&empty_bar[dseg % NB], (dseg / NB) & 1);
-            mbar_expect_tx(&full_bar[nxt % NB], (uint32_t)xbytes);
-            tma_load_1d(xring + (nxt % NB) * xslot, xg + (size_t)(i_lo + nxt) * P.xblk, (uint32_t)xbytes, &full_bar[nxt % NB]);
-          }
-        }
+  auto step = [&](auto PAR, const int s) {
+    constexpr int par = decltype(PAR)::value;
+    // ---- ring: wait for the pair lane 0 enters now; hand back the slot lane 31 just left ----
+    if (kk == 0 && sseg < npairs) mbar_wait(&full_bar[ubuf], (sseg / NB) & 1);
+    if (kk == 31 && sseg >= 1) {
+      const int dseg = sseg - 1;
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty_bar[ubuf_prev]);
+      const int nxt = dseg + NB;                   // the pair that reuses this slot
+      if (threadIdx.x == 0 && nxt < npairs) {
+        mbar_wait(&empty_bar[ubuf_prev], (dseg / NB) & 1);
+        mbar_expect_tx(&full_bar[ubuf_prev], (uint32_t)xbytes);
+        tma_load_1d(xring + ubuf_prev * xslot, xg + (size_t)(i_lo + nxt) * P.xblk, (uint32_t)xbytes, &full_bar[ubuf_prev]);
       }
     }
     // ---- chain values from the lane to the left (computed one step ago) -----------
@@ -200,21 +210,21 @@ __global__ void __launch_bounds__(kSkewWarps * 32, 1) trunc_skew_kernel(const Tr
       for (int l = 0; l < MLEV; ++l) {
         if (l < MLEV - 1 || rr == 0) recv[rr][l] = __shfl_up_sync(0xffffffffu, send[rr][l], 1);
         else recv[rr][l] = T(0);
-      }
-      if (lane == 0) {
-        recvU[rr] = T(0);
-#pragma unroll
-        for (int l = 0; l < MLEV; ++l) recv[rr][l] = T(0);
+        if (lane == 0) recv[rr][l] = T(0);
       }
     }
-    const bool in_stream = (s >= lane) && (seg <= npairs);
-    const bool live = in_stream && (seg < npairs);            // rows of a real pair (else: finalisation only)
-    const T* xb = reinterpret_cast<const T*>(xring + (live ? buf : 0) * xslot);
+    // ---- this lane's place in the stream: one step behind the lane to its left ----
+    const bool behind = kk < lane;                            // still in the previous pair
+    const int seg = sseg - (behind ? 1 : 0);
+    const int rstep = kk - lane + (behind ? SPS : 0);
+    const bool started = s >= lane;
+    const bool live = started && seg < npairs;                // rows of a real pair (else: fill / finalisation / drain)
+    const T* xb = reinterpret_cast<const T*>(xring + (live ? (behind ? ubuf_prev : ubuf) : 0) * xslot);
     const T* xsq = xb + (size_t)L * RS;
     const int r0 = live ? rstep * R : 0;
 
     // ---- base kernel on R rows x COLS columns -------------------------------------
-    T Mcur[R][COLS];
+    T Mc[R][COLS];
     {
       T xc[R];
       T acc[R][COLS];
@@ -245,32 +255,40 @@ __global__ void __launch_bounds__(kSkewWarps * 32, 1) trunc_skew_kernel(const Tr
 #pragma unroll
       for (int rr = 0; rr < R; ++rr)
 #pragma unroll
-        for (int c = 0; c < COLS; ++c)
-          Mcur[rr][c] = SkewFinish<T, OP>::apply(acc[rr][c], xc[rr], yc[c], P.base, p0, p1, tab);
+        for (int c = 0; c < COLS; ++c) {
+          const T v = SkewFinish<T, OP>::apply(acc[rr][c], xc[rr], yc[c], P.base, p0, p1, tab);
+          if (rr == R - 1) Mp[par ^ 1][c] = v; else Mc[rr][c] = v;
+        }
     }
 
     // ---- recursion, row by row -----------------------------------------------------
 #pragma unroll
     for (int rr = 0; rr < R; ++rr) {
-      const int row = r0 + rr;
-      const bool rowlive = live && (row < L);
       T D[COLS];
       if (diff) {
+        // 2-D increment (signature_algs.py:26).  No masks: row 0 of a pair is consumed by the
+        // first-row branch below, padded rows/columns repeat their neighbour (increment 0).
         T U[COLS];
 #pragma unroll
-        for (int c = 0; c < COLS; ++c) { U[c] = Mcur[rr][c] - Mprev[c]; Mprev[c] = Mcur[rr][c]; }
+        for (int c = 0; c < COLS; ++c) {
+          const T cur = (rr == R - 1) ? Mp[par ^ 1][c] : Mc[rr][c];
+          const T prv = (rr == 0) ? Mp[par][c] : Mc[rr > 0 ? rr - 1 : 0][c];
+          U[c] = cur - prv;
+        }
+        const T left = lane == 0 ? U[0] : recvU[rr];          // column -1 does not exist: D = 0 there
 #pragma unroll
-        for (int c = 0; c < COLS; ++c) D[c] = U[c] - (c > 0 ? U[c - 1] : recvU[rr]);
+        for (int c = 0; c < COLS; ++c) D[c] = U[c] - (c > 0 ? U[c - 1] : left);
         sendU[rr] = U[COLS - 1];
       } else {
+        const bool rowok = live && (r0 + rr < L);
 #pragma unroll
-        for (int c = 0; c < COLS; ++c) D[c] = Mcur[rr][c];
+        for (int c = 0; c < COLS; ++c) {
+          const T cur = (rr == R - 1) ? Mp[par ^ 1][c] : Mc[rr][c];
+          D[c] = (rowok && q0 + c < L2) ? cur : T(0);
+        }
       }
-      const bool drow = rowlive && (row >= diff);
-#pragma unroll
-      for (int c = 0; c < COLS; ++c) D[c] = (drow && valid[c]) ? D[c] : T(0);
 
-      if (rr == 0 && in_stream && rstep == 0) {
+      if (rr == 0 && started && kk == lane) {
         // first row of a pair: the chain carries the level totals of the pair just finished
         T tot[MLEV];
 #pragma unroll
@@ -308,7 +326,7 @@ __global__ void __launch_bounds__(kSkewWarps * 32, 1) trunc_skew_kernel(const Tr
 #pragma unroll
           for (int c = 0; c < COLS; ++c) C[l][c] = T(0);
 #pragma unroll
-        for (int c = 0; c < COLS; ++c) C[0][c] = D[c];
+        for (int c = 0; c < COLS; ++c) C[0][c] = diff ? T(0) : D[c];
       } else {
         // C_{l+1}[q] += D[p, q] * sum_{q' < q} C_l[q'], highest level first (C_l is read before row p updates it)
 #pragma unroll
@@ -326,9 +344,12 @@ __global__ void __launch_bounds__(kSkewWarps * 32, 1) trunc_skew_kernel(const Tr
         for (int c = 0; c < COLS; ++c) C[0][c] += D[c];
       }
     }
-    if (in_stream) {
-      if (++rstep == SPS) { rstep = 0; ++seg; if (++buf == NB) buf = 0; }
-    }
+    if (++kk == SPS) { kk = 0; ++sseg; ubuf_prev = ubuf; if (++ubuf == NB) ubuf = 0; }
+  };
+
+  for (int s = 0; s < nsteps; s += 2) {
+    step(std::integral_constant<int, 0>{}, s);
+    step(std::integral_constant<int, 1>{}, s + 1);
   }
 }
 
@@ -343,13 +364,13 @@ template <typename T, int DP, int COLS, int MLEV, int OP>
 int launch_skew_inst(TruncParams P, cudaStream_t stream) {
   const int RS = P.xrs;
   const size_t xslot = align_up_dev(P.xblk * sizeof(T));
-  const size_t smem = 128 + kSkewBufs * xslot + (size_t)kSkewWarps * trunc_ywarp_bytes<T, DP, COLS>();
+  const size_t smem = 128 + kSkewBufs * xslot + (size_t)SkewCfg<T>::NW * trunc_ywarp_bytes<T, DP, COLS>();
   if (smem > kMaxSmem)
     GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "sequence too long for the on-chip plan: needs %zu bytes of shared memory (L=%d)", smem, P.L);
   auto kern = trunc_skew_kernel<T, DP, COLS, MLEV, OP>;
   GPSIG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid;
-  grid.x = (P.N2 + kSkewWarps - 1) / kSkewWarps;
+  grid.x = (P.N2 + SkewCfg<T>::NW - 1) / SkewCfg<T>::NW;
   const int rows = P.row_end - P.row_begin;
   // >= ~24 waves of CTAs over the 148 SMs, but >= 16 pairs per warp so the 31-step pipeline fill stays < 1 %
   int want_y = (24 * 148 + (int)grid.x - 1) / (int)grid.x;
@@ -359,7 +380,7 @@ int launch_skew_inst(TruncParams P, cudaStream_t stream) {
   P.ichunk = ichunk;
   grid.y = (rows + ichunk - 1) / ichunk;
   prof_begin(stream);
-  kern<<<grid, kSkewWarps * 32, smem, stream>>>(P, RS);
+  kern<<<grid, SkewCfg<T>::NW * 32, smem, stream>>>(P, RS);
   prof_end(stream);
   GPSIG_LAUNCH_CHECK("trunc_skew_kernel");
   return GPSIG_OK;
