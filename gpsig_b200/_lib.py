@@ -10,7 +10,7 @@ import os
 import torch
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, 'libgpsig_b200.so')
+LIB_PATH = os.path.join(HERE, os.environ.get('GPSIG_LIB_NAME', 'libgpsig_b200.so'))
 
 BASE_IDS = {'linear': 0, 'rbf': 1, 'cosine': 2, 'poly': 3, 'mix': 4,
             'matern12': 5, 'matern32': 6, 'matern52': 7}

@@ -16,8 +16,9 @@ from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
-OBJ = os.path.join(HERE, 'build')
-LIB = os.path.join(HERE, 'libgpsig_b200.so')
+LIB = os.path.join(HERE, os.environ.get('GPSIG_LIB_NAME', 'libgpsig_b200.so'))   # variants: developer experiments only
+EXTRA = os.environ.get('GPSIG_EXTRA_DEFS', '').split()
+OBJ = os.path.join(HERE, 'build', os.path.basename(LIB))
 NVCC = os.environ.get('NVCC', '/usr/local/cuda/bin/nvcc')
 ARCH = ['-gencode', 'arch=compute_100a,code=sm_100a']
 FLAGS = ARCH + ['-O3', '-std=c++17', '-lineinfo', '-Xcompiler', '-fPIC', 
@@ -33,12 +34,12 @@ def _stamp(extra):
     h = hashlib.sha1()
     for f in _deps():
         h.update(open(f, 'rb').read())
-    h.update(' '.join(FLAGS + extra).encode())
+    h.update(' '.join(FLAGS + extra + EXTRA + [LIB]).encode())
     return h.hexdigest()
 
 
 def _units(fast):
-    extra = ['-DGPSIG_FAST_BUILD'] if fast else []
+    extra = (['-DGPSIG_FAST_BUILD'] if fast else []) + EXTRA
     units = [('abi', os.path.join(CSRC, 'abi.cu'), extra)]
     for t in ('float', 'double'):
         for op in (0, 1, 2):

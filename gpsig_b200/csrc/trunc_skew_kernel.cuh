@@ -80,9 +80,24 @@ template <> struct SkewFinish<double, OP_RBF> {
   }
 };
 
+// rows per step (R) and warps per CTA (NW); tunables, overridable at build time for experiments.
+// Measured at c2 (tools/time_trunc.py): float32 R=1 14.1 M pairs/s, R=2 17.8 M; float64 R=1 6.6 M, R=2 7.1 M;
+// more warps per CTA (12) costs registers: float32 16.9 M at R=1, float64 spills (5.5 M).
+#ifndef GPSIG_SKEW_R_F64
+#define GPSIG_SKEW_R_F64 2
+#endif
+#ifndef GPSIG_SKEW_NW_F64
+#define GPSIG_SKEW_NW_F64 8
+#endif
+#ifndef GPSIG_SKEW_R_F32
+#define GPSIG_SKEW_R_F32 2
+#endif
+#ifndef GPSIG_SKEW_NW_F32
+#define GPSIG_SKEW_NW_F32 8
+#endif
 template <typename T> struct SkewCfg;
-template <> struct SkewCfg<double> { static constexpr int R = 2; static constexpr int NW = 8; };   // rows per step, warps per CTA
-template <> struct SkewCfg<float> { static constexpr int R = 1; static constexpr int NW = 8; };
+template <> struct SkewCfg<double> { static constexpr int R = GPSIG_SKEW_R_F64; static constexpr int NW = GPSIG_SKEW_NW_F64; };
+template <> struct SkewCfg<float> { static constexpr int R = GPSIG_SKEW_R_F32; static constexpr int NW = GPSIG_SKEW_NW_F32; };
 
 // float32 RBF: the packed coordinates are pre-scaled by sqrt(log2 e) (abi.cu), so the exponent
 // arrives in base-2 units and exp() is a single MUFU.EX2
@@ -358,7 +373,7 @@ __global__ void __launch_bounds__(SkewCfg<T>::NW * 32, 1) trunc_skew_kernel(cons
 // ---------------------------------------------------------------------------
 // Shapes this kernel takes (the rest runs trunc_gram_kernel): one column pass, rows long
 // enough (>= 32 steps per pair) that a lane-skewed warp touches at most two consecutive pairs.
-inline bool skew_eligible(int L, int L2, int elem) { return L >= 32 * (elem == 8 ? 2 : 1) + 1 && L2 <= 256; }
+inline bool skew_eligible(int L, int L2, int elem) { return L >= 32 * (elem == 8 ? GPSIG_SKEW_R_F64 : GPSIG_SKEW_R_F32) + 1 && L2 <= 256; }
 
 template <typename T, int DP, int COLS, int MLEV, int OP>
 int launch_skew_inst(TruncParams P, cudaStream_t stream) {
