@@ -278,14 +278,21 @@ static int pde_impl(const double* X, int N, int L, const double* Y, int N2, int 
   P.xp = xp; P.yp = yp; P.xblk = seq_block_elems(L, d, 8); P.yblk = seq_block_elems(L2, d, 8);
   P.N = N; P.N2 = N2; P.L = L; P.L2 = L2; P.DP = padded_dim(d); P.order = order; P.pair_mode = pair_mode;
   P.row_begin = row_begin; P.row_end = row_end; P.sigma = sigma; P.out = out;
-  const size_t smem = pde_smem_bytes(L, L2, P.DP, order);
-  if (smem > kMaxSmem)
-    GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "PDE grid too large for the on-chip plan: %zu bytes of shared memory (L=%d, L2=%d, order=%d)", smem, L, L2, order);
   const size_t npairs = pair_mode == GPSIG_PDE_DIAG ? (size_t)(row_end - row_begin) : (size_t)(row_end - row_begin) * N2;
   if (npairs > 0x7fffffffull) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "too many pairs in one call (%zu)", npairs);
-#define GPSIG_PDE_GO(DP_, O_) do { auto kern = pde_wavefront_kernel<DP_, O_>; \
+  // one warp per 32*kPdeW-column strip, all strips of a pair in flight (pde_pipe_kernel); pairs with more
+  // than kPdeMaxStrips strips run the strips one after the other on one warp (pde_wavefront_kernel)
+  const int Qf = (L2 - 1) << order;
+  const int nstrips = (Qf + 32 * kPdeW - 1) / (32 * kPdeW);
+  const bool pipe = nstrips <= kPdeMaxStrips && getenv("GPSIG_PDE_SEQ") == nullptr;
+  const size_t smem = pipe ? pde_pipe_smem_bytes(L, L2, P.DP, order, nstrips) : pde_smem_bytes(L, L2, P.DP, order);
+  if (smem > kMaxSmem)
+    GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "PDE grid too large for the on-chip plan: %zu bytes of shared memory (L=%d, L2=%d, order=%d)", smem, L, L2, order);
+#define GPSIG_PDE_GO(DP_, O_) do { if (pipe) { auto kern = pde_pipe_kernel<DP_, O_>; \
     GPSIG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-    prof_begin(s); kern<<<(unsigned)npairs, 32, smem, s>>>(P); prof_end(s); } while (0)
+    prof_begin(s); kern<<<(unsigned)npairs, 32 * nstrips, smem, s>>>(P); prof_end(s); } else { auto kern = pde_wavefront_kernel<DP_, O_>; \
+    GPSIG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    prof_begin(s); kern<<<(unsigned)npairs, 32, smem, s>>>(P); prof_end(s); } } while (0)
 #define GPSIG_PDE_DP(O_) do { if (P.DP == 4) GPSIG_PDE_GO(4, O_); else if (P.DP == 8) GPSIG_PDE_GO(8, O_); else GPSIG_PDE_GO(16, O_); } while (0)
   switch (order) {
     case 0: GPSIG_PDE_DP(0); break; case 1: GPSIG_PDE_DP(1); break; case 2: GPSIG_PDE_DP(2); break;

@@ -132,4 +132,195 @@ __global__ void __launch_bounds__(32) pde_wavefront_kernel(const PdeParams Pm) {
   }
 }
 
+
+// ---------------------------------------------------------------------------
+// Pipelined variant: one CTA per pair, one WARP PER STRIP.
+//
+// The sequential-strip kernel above leaves a pair's 2P-long dependency chain on
+// a single warp (c3: 8 strips x 2028 steps, 1000 pairs = 1000 warps on 148 SMs).
+// Here the strips of a pair run CONCURRENTLY as a second level of the same
+// systolic skew: warp w owns strip w and trails warp w-1 by one lane-pipeline
+// depth (32 steps) plus one hand-off window.  The right edge of strip w-1 flows
+// to warp w through a small shared-memory ring (kPdeRing rows) with two
+// monotonic progress counters per boundary (rows published / rows consumed),
+// exchanged every kPdeWin steps -- no block-wide barrier anywhere.  A pair's
+// critical path drops from strips*(P+32) to P + strips*(32+window) steps and
+// the CTA keeps `strips` warps busy, so the FP64 pipe, not latency, bounds it.
+// ---------------------------------------------------------------------------
+constexpr int kPdeRing = 128;   // ring rows per strip boundary (power of two, >= 2*kPdeWin + 32)
+constexpr int kPdeWin = 16;     // steps between progress exchanges
+constexpr int kPdeMaxStrips = 16;
+
+// dx rows are padded to an odd number of 16-byte units (skewed row reads of a quarter warp hit distinct
+// banks).  The dy coefficients a lane needs never change (its columns are fixed): they live in registers
+// when they fit (coarse columns per lane x DP <= 32 doubles), else in shared memory padded per lane.
+__host__ __device__ inline int pde_coarse_cols(int order) { return (kPdeW >> order) > 0 ? (kPdeW >> order) : 1; }
+__host__ __device__ inline bool pde_dy_in_regs(int DP, int order) { return pde_coarse_cols(order) * DP <= 32; }
+__host__ __device__ inline size_t pde_dy_smem_elems(int L2, int DP, int order) {
+  if (pde_dy_in_regs(DP, order)) return 0;
+  const int nc = pde_coarse_cols(order);
+  return (size_t)(L2 - 1) * DP + 2 * (size_t)((L2 - 1 + nc - 1) / nc) + 2;
+}
+inline size_t pde_pipe_smem_bytes(int L, int L2, int DP, int order, int nstrips) {
+  return ((size_t)(L - 1) * (DP + 2) + pde_dy_smem_elems(L2, DP, order) + (size_t)nstrips * kPdeRing) * sizeof(double) +
+         2 * kPdeMaxStrips * sizeof(int);
+}
+
+__device__ __forceinline__ int ld_volatile_shared(const int* p) {
+  int v;
+  asm volatile("ld.volatile.shared.s32 %0, [%1];" : "=r"(v) : "r"(smem_u32(p)) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_volatile_shared(int* p, int v) {
+  asm volatile("st.volatile.shared.s32 [%0], %1;" ::"r"(smem_u32(p)), "r"(v) : "memory");
+}
+
+template <int DP, int ORDER>
+__global__ void __launch_bounds__(kPdeMaxStrips * 32) pde_pipe_kernel(const PdeParams Pm) {
+  constexpr int W = kPdeW;
+  constexpr int NC = (W >> ORDER) > 0 ? (W >> ORDER) : 1;   // coarse columns per lane
+  constexpr int RB = kPdeRing, G = kPdeWin;
+  extern __shared__ __align__(128) unsigned char pde_smem[];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, NS = blockDim.x >> 5;
+  const int L = Pm.L, L2 = Pm.L2;
+  const int P = (L - 1) << ORDER, Q = (L2 - 1) << ORDER;
+  constexpr int XS = DP + 2;                                // padded dx row stride (doubles)
+  constexpr bool DYREG = NC * DP <= 32;
+  double* dx = reinterpret_cast<double*>(pde_smem);
+  double* dy = dx + (size_t)(L - 1) * XS;                  // only if !DYREG: element (J, k) at J*DP + k + 2*(J/NC)
+  double* ring = dy + pde_dy_smem_elems(L2, DP, ORDER);    // [NS][RB]: ring w = left boundary of strip w
+  int* prod = reinterpret_cast<int*>(ring + (size_t)NS * RB);   // prod[w]: rows of boundary w published by warp w-1
+  int* cons = prod + kPdeMaxStrips;                               // cons[w]: rows of boundary w consumed by warp w
+
+  int ix, iy;
+  if (Pm.pair_mode == GPSIG_PDE_DIAG) { ix = Pm.row_begin + blockIdx.x; iy = ix; }
+  else { ix = Pm.row_begin + blockIdx.x / Pm.N2; iy = blockIdx.x % Pm.N2; }
+  const double* x = static_cast<const double*>(Pm.xp) + (size_t)ix * Pm.xblk;
+  const double* y = static_cast<const double*>(Pm.yp) + (size_t)iy * Pm.yblk;
+
+  const double fscale = 1.0 / (double)(1 << (2 * ORDER));
+  for (int e = threadIdx.x; e < (L - 1) * DP; e += blockDim.x) {
+    const int I = e / DP, k = e - I * DP;
+    dx[I * XS + k] = (x[e + DP] - x[e]) * fscale;
+  }
+  if (!DYREG)
+    for (int e = threadIdx.x; e < (L2 - 1) * DP; e += blockDim.x) dy[e + 2 * ((e / DP) / NC)] = y[e + DP] - y[e];
+  if (threadIdx.x < kPdeMaxStrips) { prod[threadIdx.x] = 0; cons[threadIdx.x] = 0; }
+  __syncthreads();                                          // the only block-wide barrier
+
+  const int j0 = w * 32 * W + lane * W;                     // first fine column (cell index) of this lane
+  double2 dyreg[DYREG ? NC : 1][DYREG ? DP / 2 : 1];
+  if (DYREG) {
+#pragma unroll
+    for (int cc = 0; cc < NC; ++cc) {
+      const int J = min((j0 >> ORDER) + cc, L2 - 2);
+#pragma unroll
+      for (int k = 0; k < DP / 2; ++k)
+        dyreg[DYREG ? cc : 0][DYREG ? k : 0] = make_double2(y[(J + 1) * DP + 2 * k] - y[J * DP + 2 * k],
+                                                              y[(J + 1) * DP + 2 * k + 1] - y[J * DP + 2 * k + 1]);
+    }
+  }
+  const int ncell = max(0, min(W, Q - j0));
+  const int LL = min(31, (Q - w * 32 * W - 1) / W);         // last lane with cells in this strip
+  const bool has_left = w > 0, has_right = w + 1 < NS;
+  double* ring_in = ring + (size_t)w * RB;
+  double* ring_out = ring + (size_t)(w + 1) * RB;
+
+  double up[W];
+#pragma unroll
+  for (int c = 0; c < W; ++c) up[c] = 1.0;                  // K[0, .] = 1 (pyx:29-31)
+  double An[NC], Bn[NC];
+#pragma unroll
+  for (int cc = 0; cc < NC; ++cc) { An[cc] = 1.0; Bn[cc] = 1.0; }
+  double A[NC], B[NC];
+  double diag = 1.0, send = 1.0, result = 1.0;
+  const int nsteps = P + LL + 1;
+  for (int s = 0; s < nsteps; ++s) {
+    if ((s & (G - 1)) == 0) {
+      // ---- hand-off window: rows [s, s+G) ------------------------------------------
+      if (has_left) {                                       // lane 0 will read boundary rows s+1 .. s+G
+        const int need = min(s + G, P);
+        while (ld_volatile_shared(&prod[w]) < need) __nanosleep(64);
+      }
+      if (has_right) {                                      // lane LL will write boundary rows up to s+G-LL
+        const int top = min(s + G - LL, P);
+        while (top > ld_volatile_shared(&cons[w + 1]) + RB) __nanosleep(64);
+      }
+      __threadfence_block();
+    }
+    if ((s & ((1 << ORDER) - 1)) == 0 && ncell > 0) {
+      // Coefficients of the coarse row this lane enters during the next 2^ORDER steps, computed at a
+      // warp-uniform step (the lanes cross coarse rows at different steps because of the skew; doing
+      // this where they cross would run the divergent branch on every step).  pyx:41-48.
+      const int In = min(max((s - lane + (1 << ORDER) - 1) >> ORDER, 0), L - 2);
+      const double2* dxi = reinterpret_cast<const double2*>(dx + (size_t)In * XS);
+      double2 xv[DP / 2];
+#pragma unroll
+      for (int k = 0; k < DP / 2; ++k) xv[k] = dxi[k];
+#pragma unroll
+      for (int cc = 0; cc < NC; ++cc) {
+        double e = 0.0;
+        if (DYREG) {
+#pragma unroll
+          for (int k = 0; k < DP / 2; ++k) {
+            e = fma(xv[k].x, dyreg[DYREG ? cc : 0][DYREG ? k : 0].x, e);
+            e = fma(xv[k].y, dyreg[DYREG ? cc : 0][DYREG ? k : 0].y, e);
+          }
+        } else {
+          const int J = min((j0 >> ORDER) + cc, L2 - 2);
+          const double2* dyj = reinterpret_cast<const double2*>(dy + (size_t)J * DP + 2 * (J / NC));
+#pragma unroll
+          for (int k = 0; k < DP / 2; ++k) { const double2 yv = dyj[k]; e = fma(xv[k].x, yv.x, e); e = fma(xv[k].y, yv.y, e); }
+        }
+        const double e2 = e * e;
+        An[cc] = 1. + 0.5 * e + (1. / 12) * e2;             // pyx:48
+        Bn[cc] = 1. - (1. / 12) * e2;
+      }
+    }
+    const int i = s - lane;                                 // fine row of this lane at this step
+    double left = __shfl_up_sync(0xffffffffu, send, 1);     // K[i+1, j0] from lane-1 (computed last step)
+    const bool rowok = (i >= 0) && (i < P);
+    if (lane == 0) left = (rowok && has_left) ? ring_in[(i + 1) & (RB - 1)] : 1.0;
+    if (rowok && ncell > 0) {
+      if ((i & ((1 << ORDER) - 1)) == 0) {                  // entering a new coarse row
+#pragma unroll
+        for (int cc = 0; cc < NC; ++cc) { A[cc] = An[cc]; B[cc] = Bn[cc]; }
+      }
+      const double newdiag = left;
+      double dg = diag, lf = left;
+#pragma unroll
+      for (int c = 0; c < W; ++c) {
+        const int cc = (ORDER >= 3) ? 0 : (c >> ORDER);
+        const double wv = fma(up[c], A[cc], -(dg * B[cc]));  // off the dependency chain
+        const double v = fma(lf, A[cc], wv);                 // (k01 + k10) * A - k00 * B
+        dg = up[c];
+        if (c < ncell) { up[c] = v; lf = v; }
+      }
+      diag = newdiag;
+      send = lf;
+      if (lane == LL) {
+        if (has_right) ring_out[(i + 1) & (RB - 1)] = lf;    // right edge -> left boundary of strip w+1
+        else if (i == P - 1) result = lf;
+      }
+    }
+    if (((s + 1) & (G - 1)) == 0 || s + 1 == nsteps) {
+      // ---- publish progress ------------------------------------------------------------
+      __syncwarp();
+      if (has_right && lane == LL) {
+        __threadfence_block();
+        st_volatile_shared(&prod[w + 1], max(0, min(s - LL + 1, P)));
+      }
+      if (has_left && lane == 0) st_volatile_shared(&cons[w], min(s + 1, P));
+    }
+  }
+  if (w == NS - 1) {
+    result = __shfl_sync(0xffffffffu, result, LL);
+    if (lane == 0) {
+      const size_t o = Pm.pair_mode == GPSIG_PDE_DIAG ? (size_t)blockIdx.x
+                                                      : (size_t)(ix - Pm.row_begin) * Pm.N2 + iy;
+      Pm.out[o] = Pm.sigma * result;
+    }
+  }
+}
+
 }  // namespace gpsig
