@@ -166,6 +166,17 @@ inline size_t pde_pipe_smem_bytes(int L, int L2, int DP, int order, int nstrips)
          2 * kPdeMaxStrips * sizeof(int);
 }
 
+// keeps a loop-invariant value in a register (ptxas otherwise re-derives shared-window addresses at every use)
+__device__ __forceinline__ uint32_t opaque_u32(uint32_t v) {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %1;" : "=r"(r) : "r"(v));
+  return r;
+}
+__device__ __forceinline__ int ld_volatile_shared_u(uint32_t a) {
+  int v;
+  asm volatile("ld.volatile.shared.s32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
+  return v;
+}
 __device__ __forceinline__ int ld_volatile_shared(const int* p) {
   int v;
   asm volatile("ld.volatile.shared.s32 %0, [%1];" : "=r"(v) : "r"(smem_u32(p)) : "memory");
@@ -223,8 +234,11 @@ __global__ void __launch_bounds__(kPdeMaxStrips * 32) pde_pipe_kernel(const PdeP
   const int ncell = max(0, min(W, Q - j0));
   const int LL = min(31, (Q - w * 32 * W - 1) / W);         // last lane with cells in this strip
   const bool has_left = w > 0, has_right = w + 1 < NS;
-  double* ring_in = ring + (size_t)w * RB;
-  double* ring_out = ring + (size_t)(w + 1) * RB;
+  const uint32_t ring_in_s = opaque_u32(smem_u32(ring + (size_t)w * RB));          // shared-space addresses
+  const uint32_t ring_out_s = opaque_u32(smem_u32(ring + (size_t)(w + 1) * RB));
+  const uint32_t dx_s = opaque_u32(smem_u32(dx));
+  const uint32_t prod_in_s = opaque_u32(smem_u32(&prod[w]));
+  const uint32_t cons_out_s = opaque_u32(smem_u32(&cons[w + 1 < kPdeMaxStrips ? w + 1 : w]));
 
   double up[W];
 #pragma unroll
@@ -233,18 +247,18 @@ __global__ void __launch_bounds__(kPdeMaxStrips * 32) pde_pipe_kernel(const PdeP
 #pragma unroll
   for (int cc = 0; cc < NC; ++cc) { An[cc] = 1.0; Bn[cc] = 1.0; }
   double A[NC], B[NC];
-  double diag = 1.0, send = 1.0, result = 1.0;
+  double diag = 1.0, send = 1.0;
   const int nsteps = P + LL + 1;
   for (int s = 0; s < nsteps; ++s) {
     if ((s & (G - 1)) == 0) {
       // ---- hand-off window: rows [s, s+G) ------------------------------------------
       if (has_left) {                                       // lane 0 will read boundary rows s+1 .. s+G
         const int need = min(s + G, P);
-        while (ld_volatile_shared(&prod[w]) < need) __nanosleep(64);
+        while (ld_volatile_shared_u(prod_in_s) < need) __nanosleep(64);
       }
       if (has_right) {                                      // lane LL will write boundary rows up to s+G-LL
         const int top = min(s + G - LL, P);
-        while (top > ld_volatile_shared(&cons[w + 1]) + RB) __nanosleep(64);
+        while (top > ld_volatile_shared_u(cons_out_s) + RB) __nanosleep(64);
       }
       __threadfence_block();
     }
@@ -253,10 +267,11 @@ __global__ void __launch_bounds__(kPdeMaxStrips * 32) pde_pipe_kernel(const PdeP
       // warp-uniform step (the lanes cross coarse rows at different steps because of the skew; doing
       // this where they cross would run the divergent branch on every step).  pyx:41-48.
       const int In = min(max((s - lane + (1 << ORDER) - 1) >> ORDER, 0), L - 2);
-      const double2* dxi = reinterpret_cast<const double2*>(dx + (size_t)In * XS);
+      const uint32_t dxa = dx_s + (uint32_t)In * (uint32_t)(XS * 8);
       double2 xv[DP / 2];
 #pragma unroll
-      for (int k = 0; k < DP / 2; ++k) xv[k] = dxi[k];
+      for (int k = 0; k < DP / 2; ++k)
+        asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(xv[k].x), "=d"(xv[k].y) : "r"(dxa + 16u * k));
 #pragma unroll
       for (int cc = 0; cc < NC; ++cc) {
         double e = 0.0;
@@ -279,29 +294,37 @@ __global__ void __launch_bounds__(kPdeMaxStrips * 32) pde_pipe_kernel(const PdeP
     }
     const int i = s - lane;                                 // fine row of this lane at this step
     double left = __shfl_up_sync(0xffffffffu, send, 1);     // K[i+1, j0] from lane-1 (computed last step)
-    const bool rowok = (i >= 0) && (i < P);
-    if (lane == 0) left = (rowok && has_left) ? ring_in[(i + 1) & (RB - 1)] : 1.0;
-    if (rowok && ncell > 0) {
+    const bool rowok = (i >= 0) && (i < P) && (ncell > 0);
+    const uint32_t slot = (uint32_t)((i + 1) & (RB - 1)) * 8u;
+    if (lane == 0) {
+      left = 1.0;                                           // K[., 0] = 1 (pyx:29-31)
+      if (has_left && rowok) asm volatile("ld.shared.f64 %0, [%1];" : "=d"(left) : "r"(ring_in_s + slot) : "memory");
+    }
+    if (rowok) {
       if ((i & ((1 << ORDER) - 1)) == 0) {                  // entering a new coarse row
 #pragma unroll
         for (int cc = 0; cc < NC; ++cc) { A[cc] = An[cc]; B[cc] = Bn[cc]; }
       }
-      const double newdiag = left;
-      double dg = diag, lf = left;
+      // All W cells are computed, also the ones past column Q of the last lane (they feed nothing:
+      // the lane to their right has no cells, the result is picked from up[] at the end).
+      // (k01 + k10) * A - k00 * B, split into the part that only needs the previous row (wv, no
+      // dependency between cells) and the one FMA per cell on the left-to-right chain
+      double wv[W];
 #pragma unroll
       for (int c = 0; c < W; ++c) {
         const int cc = (ORDER >= 3) ? 0 : (c >> ORDER);
-        const double wv = fma(up[c], A[cc], -(dg * B[cc]));  // off the dependency chain
-        const double v = fma(lf, A[cc], wv);                 // (k01 + k10) * A - k00 * B
-        dg = up[c];
-        if (c < ncell) { up[c] = v; lf = v; }
+        wv[c] = fma(up[c], A[cc], -((c == 0 ? diag : up[c > 0 ? c - 1 : 0]) * B[cc]));
       }
-      diag = newdiag;
+      diag = left;
+      double lf = left;
+#pragma unroll
+      for (int c = 0; c < W; ++c) {
+        const int cc = (ORDER >= 3) ? 0 : (c >> ORDER);
+        lf = fma(lf, A[cc], wv[c]);
+        up[c] = lf;
+      }
       send = lf;
-      if (lane == LL) {
-        if (has_right) ring_out[(i + 1) & (RB - 1)] = lf;    // right edge -> left boundary of strip w+1
-        else if (i == P - 1) result = lf;
-      }
+      if (lane == 31 && has_right) asm volatile("st.shared.f64 [%0], %1;" ::"r"(ring_out_s + slot), "d"(lf) : "memory");
     }
     if (((s + 1) & (G - 1)) == 0 || s + 1 == nsteps) {
       // ---- publish progress ------------------------------------------------------------
@@ -314,6 +337,10 @@ __global__ void __launch_bounds__(kPdeMaxStrips * 32) pde_pipe_kernel(const PdeP
     }
   }
   if (w == NS - 1) {
+    // K[P, Q] = up[Q - 1 - j0] of the last lane with cells
+    double result = up[0];
+#pragma unroll
+    for (int c = 1; c < W; ++c) if (c == ncell - 1) result = up[c];
     result = __shfl_sync(0xffffffffu, result, LL);
     if (lane == 0) {
       const size_t o = Pm.pair_mode == GPSIG_PDE_DIAG ? (size_t)blockIdx.x
