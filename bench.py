@@ -80,6 +80,7 @@ def run_reference(args):
     if rank != 0:
         return
     cores = os.cpu_count()
+    os.environ['OMP_NUM_THREADS'] = str(cores)     # torchrun pins it to 1; the CPU arm uses every host core
     # calibrate so that one step is a few seconds
     cpu_pairs_per_sec(16)
     v0, t0 = cpu_pairs_per_sec(32)
@@ -167,6 +168,42 @@ def fma_peak_tflops(torch, lib, esz):
         if rep > 0:
             best = max(best, 2.0 * blocks * 256 * 8 * iters / (ms * 1e-3) / 1e12)
     return best
+
+
+def other_configs(torch, ops, lib):
+    """Secondary kernels of the path on their BASELINE configs (kernel time from the library's events), rank 0 only."""
+    out = {}
+
+    def timed(fn, reps=3):
+        fn()
+        lib.gpsig_profile_enable(1)
+        ms = []
+        for _ in range(reps):
+            fn()
+            ms.append(lib.gpsig_profile_last_kernel_ms())
+        lib.gpsig_profile_enable(0)
+        return sum(ms) / len(ms)
+
+    # c3: PDE, N=1000, L=500, d=4, dyadic order 2 (diagonal pairs, what the reference computes)
+    N, L, d, order = 1000, 500, 4, 2
+    X = torch.as_tensor(brownian(N, L, d, 0), dtype=torch.float64, device='cuda')
+    ms = timed(lambda: ops.pde(X, None, dyadic_order=order))
+    P = (L - 1) << order
+    cells = float(N) * P * P
+    out["c3_pde"] = {"workload": "kernels_pde Kdiag, N=1000, L=500, d=4, dyadic order 2 (P=1996)", "kernel": "pde_pipe_kernel",
+                     "kernel_ms": ms, "pairs_per_s": N / (ms * 1e-3), "cells_per_s": cells / (ms * 1e-3),
+                     "fp64_instr_per_cell": 3, "dtype": "f64"}
+    # c4: inducing tensors vs sequences, N=10k, L=100, d=8, m=4, Mz=500 (increments)
+    N, L, d, m, Mz = 10000, 100, 8, 4, 500
+    Xn = brownian(N, L, d, 0)
+    Zn = np.random.default_rng(2).standard_normal((m * (m + 1) // 2, Mz, 2, d)) * 0.5
+    for dt, nm in ((torch.float64, 'f64'), (torch.float32, 'f32')):
+        Xd = torch.as_tensor(Xn, dtype=dt, device='cuda')
+        Zd = torch.as_tensor(Zn, dtype=dt, device='cuda')
+        ms = timed(lambda: ops.tens_vs_seq(Zd, Xd, m, increments=True, base='rbf', return_levels=False))
+        out["c4_kzx_" + nm] = {"workload": "K_tens_vs_seq (increments), Mz=500, N=10000, L=100, d=8, m=4", "kernel": "tens_vs_seq_kernel",
+                               "kernel_ms": ms, "pairs_per_s": Mz * N / (ms * 1e-3), "flops_per_pair": 43574}
+    return out
 
 
 def run_ours(args):
@@ -258,11 +295,20 @@ def run_ours(args):
                 "flops_per_pair": F, "pairs_per_launch": N * N2,
                 "hbm": {"algorithmic_bytes_per_pair": Bp, "achieved_gbs": N * N2 * Bp / (kern_ms * 1e-3) / 1e9 if kern_ms else None,
                         "peak_gbs": peaks.get("hbm_gbs"), "peak_source": how}}
-        # CPU baseline on a bounded sample
-        cpu_pairs_per_sec(16)
-        v0, _ = cpu_pairs_per_sec(32)
-        side = int(max(16, min(512, (v0 * 12.0) ** 0.5)))
-        cv, ct = cpu_pairs_per_sec(side)
+        # CPU baseline on a bounded sample (N=1 only: under torchrun the host threads are pinned to 1 per rank)
+        cpu = None
+        if world == 1:
+            os.environ.setdefault('OMP_NUM_THREADS', str(os.cpu_count()))
+            cpu_pairs_per_sec(16)
+            v0, _ = cpu_pairs_per_sec(32)
+            side = int(max(16, min(512, (v0 * 12.0) ** 0.5)))
+            cv, ct = cpu_pairs_per_sec(side)
+            cpu = {"value": cv, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
+                   "sample": "%dx%d pairs of the same shape in %.1f s (C port of the reference algorithm, OpenMP)" % (side, side, ct)}
+        others = other_configs(torch, ops, lib) if world == 1 else None
+        if others and fpeak and esz == 8:
+            c3 = others["c3_pde"]
+            c3["frac_of_fp64_bound"] = c3["cells_per_s"] * 3 / (fpeak * 1e12 / 2)   # 3 FP64 instructions per cell vs measured DFMA rate
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": tot_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": args.dtype, "data": "synthetic Brownian paths (seeded, SURVEY.md 8d)",
@@ -274,8 +320,8 @@ def run_ours(args):
                         "d2h_bytes_per_step": int(out_host.numel()) * esz},
                 "gpu_launches": int(launches),
                 "roofline": roof,
-                "cpu_baseline": {"value": cv, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
-                                 "sample": "%dx%d pairs of the same shape in %.1f s (C port of the reference algorithm, OpenMP)" % (side, side, ct)}}
+                "other_configs": others,
+                "cpu_baseline": cpu}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
