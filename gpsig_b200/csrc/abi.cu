@@ -7,6 +7,7 @@
 #include "tens_kernels.cuh"
 #include "trunc_kernel.cuh"
 #include "trunc_skew_kernel.cuh"
+#include "generic_kernels.cuh"
 
 namespace gpsig {
 
@@ -96,8 +97,8 @@ static int check_desc(const gpsig_trunc_desc* d) {
     GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "unknown base kernel id %d", d->base);
   if (d->num_levels < 1) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "num_levels must be >= 1 (got %d)", d->num_levels);
   if (d->num_levels > 8) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "num_levels=%d > 8 is not supported", d->num_levels);
-  if (d->order != 1)
-    GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "order=%d: only the first-order recursion (order=1) is built into this library", d->order);
+  if (d->order < 1 || d->order > d->num_levels)
+    GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "order must be in 1..num_levels (got %d, num_levels=%d)", d->order, d->num_levels);
   return GPSIG_OK;
 }
 
@@ -142,8 +143,10 @@ static int trunc_gram_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
   if (!ws || ws_bytes < need || (reinterpret_cast<uintptr_t>(ws) & 15))
     GPSIG_FAIL(GPSIG_ERR_WORKSPACE, "workspace too small or misaligned: need %zu bytes (16-byte aligned), got %zu", need, ws_bytes);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  // the systolic kernel (padded rows) takes the throughput shapes, trunc_gram_kernel the rest
-  const bool skew = skew_eligible(L, L2, sizeof(T)) && getenv("GPSIG_NO_SKEW") == nullptr;
+  // order > 1: the general higher-order kernel; else the systolic kernel (padded rows) takes the
+  // throughput shapes and trunc_gram_kernel the rest
+  const bool generic = desc->order > 1;
+  const bool skew = !generic && skew_eligible(L, L2, sizeof(T)) && getenv("GPSIG_NO_SKEW") == nullptr;
   const int RS = skew ? skew_row_stride(d, sizeof(T)) : padded_dim(d);
   T* xp = static_cast<T*>(ws);
   T* yp = sym ? xp : reinterpret_cast<T*>(static_cast<char*>(ws) + packed_bytes_padded(N, L, d, sizeof(T)));
@@ -168,6 +171,16 @@ static int trunc_gram_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
     P.sym_jitter = epi->sym_jitter; P.return_levels = epi->return_levels;
   } else P.return_levels = 1;
   P.out = out;
+  if (generic) {
+    GenericParams G;
+    memset(&G, 0, sizeof(G));
+    G.xp = xp; G.yp = yp; G.xblk = P.xblk; G.yblk = P.yblk; G.N = N; G.N2 = N2; G.L = L; G.L2 = L2; G.DP = padded_dim(d);
+    G.row_begin = row_begin; G.row_end = row_end; G.m = desc->num_levels; G.order = desc->order; G.difference = desc->difference;
+    G.symmetric = sym; G.diag = 0; G.p0 = P.p0; G.p1 = P.p1; G.base = P.base;
+    G.norm_x = P.norm_x; G.norm_x2 = P.norm_x2; G.level_scale = P.level_scale; G.sym_jitter = P.sym_jitter;
+    G.return_levels = P.return_levels; G.out = out;
+    return launch_trunc_generic<T>(G, s);
+  }
   if (skew) return dispatch_skew<T>(P, desc->base, padded_dim(d), s);
   return dispatch_trunc<T>(P, desc->base, padded_dim(d), s);
 }
@@ -197,6 +210,14 @@ static int trunc_diag_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
   P.symmetric = 1; P.diag = 1; P.return_levels = 1;
   P.p0 = desc->base_params[0]; P.p1 = desc->base_params[1]; P.base = desc->base;
   P.out = out;
+  if (desc->order > 1) {
+    GenericParams G;
+    memset(&G, 0, sizeof(G));
+    G.xp = xp; G.yp = xp; G.xblk = G.yblk = P.xblk; G.N = N; G.N2 = N; G.L = L; G.L2 = L; G.DP = padded_dim(d);
+    G.row_begin = 0; G.row_end = N; G.m = desc->num_levels; G.order = desc->order; G.difference = desc->difference;
+    G.symmetric = 1; G.diag = 1; G.p0 = P.p0; G.p1 = P.p1; G.base = P.base; G.return_levels = 1; G.out = out;
+    return launch_trunc_generic<T>(G, s);
+  }
   return dispatch_trunc<T>(P, desc->base, padded_dim(d), s);
 }
 
@@ -230,6 +251,7 @@ static int tens_vs_seq_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, in
   if (epi) { P.norm_x = epi->norm_x2; P.level_scale = epi->level_scale; P.return_levels = epi->return_levels; }
   else P.return_levels = 1;
   P.out = out;
+  if (desc->order > 1) return launch_tens_seq_generic<T>(P, desc->order, padded_dim(d), s);
   return dispatch_tens_seq<T>(P, desc->base, padded_dim(d), m, s);
 }
 

@@ -12,8 +12,8 @@ Differences that are deliberate:
     ``params_as_tensors`` would hand to the methods), no TF variables;
   * ``low_rank=True`` and ``num_lags > 0`` raise NotImplementedError (out of
     the hot-path scope, SURVEY.md 2 C7/C8);
-  * ``order > 1`` (higher-order recursion) raises NotImplementedError from the
-    library until that kernel lands.
+  * ``order > 1`` (higher-order recursion, gpsig/signature_algs.py:37-74, 129-160)
+    runs the general kernels of ``csrc/generic_kernels.cuh`` (num_levels <= 8).
 """
 import numpy as np
 import torch
@@ -192,7 +192,7 @@ class SignatureKernel:
 
     def K_tens(self, Z, return_levels=False, increments=False):
         """Square covariance of inducing tensors (kernels.py:543-567)."""
-        Z = Z.contiguous()
+        Z = Z.contiguous()   # Kzz does not depend on `order` (signature_algs.py:76-99)
         return ops.tens_tens(Z, self.num_levels, increments=increments, base=self._base,
                              base_params=self._get_base_params(), lengthscales=self._param(self.lengthscales, Z),
                              level_scale=self._level_scale(Z), return_levels=return_levels)

@@ -45,9 +45,9 @@ def test_argument_validation_without_gpu():
     buf = (ctypes.c_double * 16)()
     rc = L.lib.gpsig_trunc_diag_f64(bad, buf, 1, 4, 2, None, buf, buf, 128, None)
     assert rc == -2 and b'num_levels' in L.lib.gpsig_last_error_string()
-    ho = L.make_desc('linear', 4, 2, True)
+    ho = L.make_desc('linear', 4, 5, True)
     rc = L.lib.gpsig_trunc_diag_f64(ho, buf, 1, 4, 2, None, buf, buf, 128, None)
-    assert rc == -2 and b'order' in L.lib.gpsig_last_error_string()
+    assert rc == -1 and b'order' in L.lib.gpsig_last_error_string()
     rc = L.lib.gpsig_trunc_diag_f64(desc, buf, 1, 4, 2, None, buf, buf, 8, None)
     assert rc == -3 and b'workspace' in L.lib.gpsig_last_error_string()
     rc = L.lib.gpsig_pde_f64(buf, 2, 1, None, 0, 0, 2, None, 0, 0, 0, 2, 1.0, buf, buf, 1024, None)

@@ -144,3 +144,5 @@ def test_errors():
         ops.trunc_gram(X.cpu(), None, 2)     # no CPU path
     with pytest.raises(NotImplementedError):
         ops.trunc_gram(torch.zeros(3, 4, 2, dtype=torch.float64, device='cuda'), None, 9)
+    with pytest.raises(ValueError):
+        ops.trunc_gram(torch.zeros(3, 4, 2, dtype=torch.float64, device='cuda'), None, 3, order=4)
