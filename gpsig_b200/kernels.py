@@ -10,14 +10,16 @@ and return numpy, like the reference's autoflow wrappers).
 Differences that are deliberate:
   * parameters are plain values (the constrained values GPflow's
     ``params_as_tensors`` would hand to the methods), no TF variables;
-  * ``low_rank=True`` and ``num_lags > 0`` raise NotImplementedError (out of
-    the hot-path scope, SURVEY.md 2 C7/C8);
+  * ``low_rank=True`` raises NotImplementedError (out of the hot-path scope,
+    SURVEY.md 2 C8); ``num_lags > 0`` is applied as torch preprocessing
+    (``gpsig_b200/lags.py``) before the CUDA kernels;
   * ``order > 1`` (higher-order recursion, gpsig/signature_algs.py:37-74, 129-160)
     runs the general kernels of ``csrc/generic_kernels.cuh`` (num_levels <= 8).
 """
 import numpy as np
 import torch
 
+from . import lags as _lags
 from . import ops, settings
 
 
@@ -61,8 +63,10 @@ class SignatureKernel:
             if not isinstance(num_lags, int) or num_lags < 0:       # kernels.py:75-76
                 raise ValueError('The variable num_lags most be a nonnegative integer or None.')
             self.num_lags = int(num_lags)
-            if num_lags > 0:
-                raise NotImplementedError('gpsig_b200: num_lags > 0 is not implemented yet (SURVEY.md 8f-4).')
+            if num_lags > 0:                                        # kernels.py:78-83
+                self.lags = 0.1 * np.asarray(range(1, num_lags + 1), dtype=np.float64)
+                gamma = 1. / np.asarray(range(1, self.num_lags + 2), dtype=np.float64)
+                self.gamma = gamma / np.sum(gamma)
 
         if lengthscales is not None:
             self.lengthscales = self._validate_signature_param("lengthscales", lengthscales, self.num_features)
@@ -110,10 +114,29 @@ class SignatureKernel:
         return sl(X), sl(X2)
 
     def _seq(self, X):
-        """[N, L*d] -> contiguous [N, L, d]  (kernels.py:418-420)."""
+        """[N, L*d] -> contiguous [N, L, d]  (kernels.py:418-420).  With lags: the scaled, lagged
+        sequences [N, L, d*(num_lags+1)] of ``_apply_scaling_and_lags_to_sequences`` (kernels.py:343-365)."""
         if not torch.is_tensor(X):
             raise TypeError("gpsig_b200 kernels take torch CUDA tensors (use compute_* for numpy)")
-        return X.reshape(X.shape[0], -1, self.num_features).contiguous()
+        X = X.reshape(X.shape[0], -1, self.num_features)
+        if self.num_lags > 0:
+            X = _lags.add_lags_to_sequences(X, self._param(self.lags, X))           # [N, L, num_lags+1, d]
+            if self.lengthscales is not None:
+                X = X / self._param(self.lengthscales, X)[None, None, None, :]
+            X = X * self._param(self.gamma, X)[None, None, :, None]
+            X = X.reshape(X.shape[0], X.shape[1], -1)
+        return X.contiguous()
+
+    def _tens(self, Z, increments):
+        """Inducing tensors as the CUDA kernels take them.  Without lags the lengthscales are applied
+        inside the library; with lags the scaling of kernels.py:367-399 is done here."""
+        Z = Z.contiguous()
+        if self.num_lags > 0 and self.lengthscales is not None:
+            shp = Z.shape
+            Zr = Z.reshape(shp[:-1] + (self.num_lags + 1, self.num_features))
+            Zr = Zr / self._param(self.lengthscales, Z) * self._param(self.gamma, Z)[:, None]
+            Z = Zr.reshape(shp).contiguous()
+        return Z
 
     def _param(self, value, like):
         if value is None:
@@ -125,8 +148,10 @@ class SignatureKernel:
         return self._param(float(self.sigma) * np.asarray(self.variances, dtype=np.float64).reshape(-1), like)
 
     def _kw(self, like):
+        # with lags the scaling has already been applied by _seq / _tens
         return dict(base=self._base, base_params=self._get_base_params(), order=self.order,
-                    difference=self.difference, lengthscales=self._param(self.lengthscales, like))
+                    difference=self.difference,
+                    lengthscales=None if self.num_lags > 0 else self._param(self.lengthscales, like))
 
     def _get_base_params(self):
         return self._base_params
@@ -192,9 +217,9 @@ class SignatureKernel:
 
     def K_tens(self, Z, return_levels=False, increments=False):
         """Square covariance of inducing tensors (kernels.py:543-567)."""
-        Z = Z.contiguous()   # Kzz does not depend on `order` (signature_algs.py:76-99)
+        Z = self._tens(Z, increments)   # Kzz does not depend on `order` (signature_algs.py:76-99)
         return ops.tens_tens(Z, self.num_levels, increments=increments, base=self._base,
-                             base_params=self._get_base_params(), lengthscales=self._param(self.lengthscales, Z),
+                             base_params=self._get_base_params(), lengthscales=self._kw(Z)['lengthscales'],
                              level_scale=self._level_scale(Z), return_levels=return_levels)
 
     def K_tens_vs_seq(self, Z, X, return_levels=False, increments=False, presliced=False, cols=None):
@@ -203,7 +228,7 @@ class SignatureKernel:
             X, _ = self._slice(X, None)
         Xs = self._seq(X)
         norm = self._K_seq_diag(Xs) + settings.jitter if self.normalization else None      # kernels.py:604-613
-        return ops.tens_vs_seq(Z.contiguous(), Xs, self.num_levels, increments=increments, norm_x=norm,
+        return ops.tens_vs_seq(self._tens(Z, increments), Xs, self.num_levels, increments=increments, norm_x=norm,
                                level_scale=self._level_scale(Xs), return_levels=return_levels, cols=cols,
                                **self._kw(Xs))
 
@@ -212,7 +237,7 @@ class SignatureKernel:
         if not presliced:
             X, _ = self._slice(X, None)
         Xs = self._seq(X)
-        Z = Z.contiguous()
+        Z = self._tens(Z, increments)
         N = Xs.shape[0]
         jitter = settings.jitter
         sc = self._level_scale(Xs)

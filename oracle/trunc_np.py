@@ -112,6 +112,27 @@ BASE_KERNELS = {
 
 
 # ----------------------------------------------------------------------------
+# lags -- gpsig/lags.py
+# ----------------------------------------------------------------------------
+def lin_interp(time, X, time_query, jitter=JITTER):
+    """gpsig/lags.py:7-38."""
+    pairwise = time[:, None, None] - time_query[None, :, :]
+    left_idx = np.argmax(np.where(pairwise > jitter, -np.inf, pairwise), axis=0)
+    right_idx = left_idx + 1
+    X_left, X_right = np.take(X, left_idx, axis=-2), np.take(X, np.minimum(right_idx, X.shape[-2] - 1), axis=-2)
+    t_left, t_right = time[left_idx], time[np.minimum(right_idx, time.shape[0] - 1)]
+    return X_left + (time_query[None, ..., None] - t_left[None, ..., None]) * (X_right - X_left) / (t_right[None, ..., None] - t_left[None, ..., None])
+
+
+def add_lags_to_sequences(X, lags):
+    """gpsig/lags.py:41-63.  [N, L, d] -> [N, L, num_lags+1, d]."""
+    L = X.shape[1]
+    time = np.arange(L, dtype=np.float64) / (L - 1)
+    time_lags = np.maximum(time[:, None] - lags[None, :], 0.)
+    return np.concatenate((X[:, :, None, :], lin_interp(time, X, time_lags)), axis=2)
+
+
+# ----------------------------------------------------------------------------
 # recursions -- gpsig/signature_algs.py
 # ----------------------------------------------------------------------------
 def _difference_2d(M):
@@ -229,7 +250,7 @@ class SignatureKernelOracle:
 
     def __init__(self, input_dim, num_features, num_levels, base='linear', variances=1, lengthscales=1,
                  order=1, normalization=True, difference=True, sigma=1.0, jitter=JITTER,
-                 block=16, dtype=np.float64, **base_params):
+                 block=16, dtype=np.float64, num_lags=0, **base_params):
         if input_dim % num_features != 0:  # kernels.py:95-103
             raise ValueError("The arguments num_features and input_dim are not consistent.")
         self.num_features = num_features
@@ -243,6 +264,11 @@ class SignatureKernelOracle:
         self.sigma = dtype(sigma)
         self.lengthscales = None if lengthscales is None else (lengthscales * np.ones(num_features)).astype(dtype)
         self.jitter = jitter
+        self.num_lags = int(num_lags or 0)
+        if self.num_lags > 0:                                        # kernels.py:78-83
+            self.lags = 0.1 * np.arange(1, self.num_lags + 1, dtype=np.float64)
+            gamma = 1. / np.arange(1, self.num_lags + 2, dtype=np.float64)
+            self.gamma = gamma / np.sum(gamma)
         self.block = block
         self.base = base
         self.base_params = base_params
@@ -254,6 +280,12 @@ class SignatureKernelOracle:
     def _seq(self, X):
         X = np.asarray(X, dtype=self.dtype)
         X = X.reshape(X.shape[0], -1, self.num_features)           # kernels.py:419
+        if self.num_lags > 0:                                        # kernels.py:343-365
+            X = add_lags_to_sequences(X, self.lags)
+            if self.lengthscales is not None:
+                X = X / self.lengthscales[None, None, None, :]
+            X = X * self.gamma[None, None, :, None]
+            return X.reshape(X.shape[0], X.shape[1], -1)
         if self.lengthscales is not None:                            # kernels.py:358-359
             X = X / self.lengthscales[None, None, :]
         return X
@@ -261,6 +293,10 @@ class SignatureKernelOracle:
     def _tens(self, Z, increments):
         Z = np.asarray(Z, dtype=self.dtype)                          # kernels.py:367-399
         if self.lengthscales is not None:
+            if self.num_lags > 0:
+                shp = Z.shape
+                Zr = Z.reshape(shp[:-1] + (self.num_lags + 1, self.num_features))
+                return (Zr / self.lengthscales * self.gamma[:, None]).reshape(shp)
             Z = Z / self.lengthscales
         return Z
 

@@ -113,3 +113,23 @@ def test_pde_gram_rectangular_and_rows():
     Ks = k.K(_dev(X.reshape(N, -1)))
     assert torch.allclose(Ks, Ks.T, rtol=1e-12, atol=0)
     assert torch.allclose(torch.diagonal(Ks), k.Kdiag(_dev(X.reshape(N, -1))), rtol=1e-12, atol=0)
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("num_lags", [1, 2])
+def test_lags_follow_reference(dtype, num_lags):
+    """num_lags > 0: lagged copies by linear interpolation (gpsig/lags.py), scaled by gamma (kernels.py:343-399)."""
+    from gpsig_b200 import kernels
+    from oracle.trunc_np import SignatureKernelOracle
+    N, L, d, m, Mz = 9, 40, 3, 3, 5
+    X = brownian(N, L, d, 11)
+    ls = np.array([1.2, 0.7, 0.9])
+    k = kernels.SignatureRBF(L * d, d, m, lengthscales=ls, num_lags=num_lags)
+    o = SignatureKernelOracle(L * d, d, m, base='rbf', lengthscales=ls, num_lags=num_lags)
+    Xd = _dev(X.reshape(N, -1), dtype)
+    assert rel_err(k.K(Xd, return_levels=True).cpu().numpy(), o.K(X.reshape(N, -1), return_levels=True)) < TOL[dtype]
+    Z = np.random.default_rng(12).standard_normal((m * (m + 1) // 2, Mz, 2, d * (num_lags + 1))) * 0.3
+    got = k.K_tens_n_seq_covs(_dev(Z, dtype), Xd, increments=True)
+    ref = o.K_tens_n_seq_covs(Z, X.reshape(N, -1), increments=True)
+    for g, r in zip(got, ref):
+        assert rel_err(g.cpu().numpy(), r) < TOL[dtype]
