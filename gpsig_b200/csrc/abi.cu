@@ -152,7 +152,8 @@ static int trunc_gram_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
   T* yp = sym ? xp : reinterpret_cast<T*>(static_cast<char*>(ws) + packed_bytes_padded(N, L, d, sizeof(T)));
   // float32 RBF on the systolic kernel: coordinates pre-scaled by sqrt(log2 e) so that the exponent
   // x.y - |x|^2/2 - |y|^2/2 comes out in base-2 units and exp() is one MUFU.EX2 (trunc_skew_kernel.cuh)
-  const double cscale = (skew && sizeof(T) == 4 && desc->base == GPSIG_BASE_RBF) ? 1.2011224087864498 : 1.0;
+  // (float64: same pre-scaling, the exponent feeds exp2_tab32)
+  const double cscale = (skew && (sizeof(T) == 4 || GPSIG_SKEW_EXP2) && desc->base == GPSIG_BASE_RBF) ? 1.2011224087864498 : 1.0;
   if (int rc = pack<T>(X, N, L, d, ls, xp, s, RS, cscale)) return rc;
   if (!sym) if (int rc = pack<T>(X2, N2, L2, d, ls, yp, s, RS, cscale)) return rc;
 

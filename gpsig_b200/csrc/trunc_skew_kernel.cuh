@@ -41,6 +41,59 @@ __host__ __device__ inline int skew_row_stride(int d, int elem) {
   return u * 16 / elem;
 }
 
+// float64: the lane's column tile of y (COLS x DP doubles) does not fit in registers next to the
+// recursion state.  It lives in TENSOR MEMORY instead: every lane owns one TMEM lane, writes its tile
+// once with tcgen05.st and re-reads it every step with tcgen05.ld (SASS STTM / LDTM).  TMEM is a
+// datapath of its own (measured 385 B/clk/SM at 8 warps, tools/microbench2.cu, against 127 B/clk/SM
+// for shared memory), so the tile no longer competes with the x-row loads and the warp shuffles of
+// the chain for the shared-memory pipe (which the lane-interleaved shared-memory tile kept 45 % busy).
+#ifndef GPSIG_SKEW_TMEM
+#define GPSIG_SKEW_TMEM 1
+#endif
+// float64 RBF: packed coordinates pre-scaled by sqrt(log2 e) (abi.cu) and exp2_tab32 below
+#ifndef GPSIG_SKEW_EXP2
+#define GPSIG_SKEW_EXP2 1
+#endif
+
+// ---- tensor memory as per-lane storage (PTX tcgen05.alloc / st / ld) ---------
+__device__ __forceinline__ uint32_t tmem_alloc(uint32_t* slot, int ncols) {    // whole CTA; warp 0 allocates
+  if ((threadIdx.x >> 5) == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot)), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  return *reinterpret_cast<volatile uint32_t*>(slot);
+}
+__device__ __forceinline__ void tmem_free(uint32_t base, int ncols) {           // whole CTA
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if ((threadIdx.x >> 5) == 0)
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(base), "r"(ncols) : "memory");
+}
+// 4 doubles (8 words) per lane
+__device__ __forceinline__ void tmem_st4(uint32_t addr, double a, double b, double c, double d) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+               ::"r"(addr), "r"(__double2loint(a)), "r"(__double2hiint(a)), "r"(__double2loint(b)), "r"(__double2hiint(b)),
+                 "r"(__double2loint(c)), "r"(__double2hiint(c)), "r"(__double2loint(d)), "r"(__double2hiint(d)) : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+struct TmemQuad { uint32_t w[8]; };
+__device__ __forceinline__ void tmem_ld4(TmemQuad& r, uint32_t addr) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(r.w[0]), "=r"(r.w[1]), "=r"(r.w[2]), "=r"(r.w[3]), "=r"(r.w[4]), "=r"(r.w[5]), "=r"(r.w[6]), "=r"(r.w[7])
+               : "r"(addr) : "memory");
+}
+// the loaded registers are tied to the wait so that no use can be scheduled above it
+__device__ __forceinline__ void tmem_ld_wait(TmemQuad& r) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(r.w[0]), "+r"(r.w[1]), "+r"(r.w[2]), "+r"(r.w[3]), "+r"(r.w[4]), "+r"(r.w[5]), "+r"(r.w[6]), "+r"(r.w[7])
+               :: "memory");
+}
+__device__ __forceinline__ double tmem_quad_get(const TmemQuad& r, int e) { return __hiloint2double((int)r.w[2 * e + 1], (int)r.w[2 * e]); }
+__host__ __device__ constexpr int tmem_cols_pow2(int n) { return n <= 32 ? 32 : n <= 64 ? 64 : n <= 128 ? 128 : n <= 256 ? 256 : 512; }
+
 // ---- exp for the RBF base kernel --------------------------------------------
 // float64: table-driven, 12 FP64-pipe instructions instead of ~22 for exp():
 //   x = (32 k + j) ln2/32 + r,  exp(x) = 2^k * 2^(j/32) * exp(r),  |r| <= ln2/64,
@@ -68,6 +121,27 @@ __device__ __forceinline__ double exp_tab32(double x, double tab_lane) {
   return __hiloint2double(__double2hiint(res) + (k << 20), __double2loint(res));
 }
 
+// float64, base-2 exponent t (coordinates pre-scaled by sqrt(log2 e)): 9 FP64-pipe instructions.
+//   t = n/32 + f, n = round(32 t) by the magic-number add (exact, |f| <= 1/64),
+//   2^t = 2^(n>>5) * 2^((n&31)/32) * 2^f, table as above, 2^f - 1 = f*(c1 + ... + c5 f^4) minimax
+//   (1.4e-16 relative).  t is clamped to >= -1021 by an integer min on its sign/exponent word, so the
+//   exponent-field add never leaves the normal range (the result there is ~1e-307, i.e. 0 at any tolerance).
+__device__ __forceinline__ double exp2_tab32(double t, double tab_lane) {
+  const unsigned hi = min((unsigned)__double2hiint(t), 0xC08FE800u);
+  t = __hiloint2double((int)hi, __double2loint(t));
+  const double s = t + 0x1.8p+47;
+  const int n = __double2loint(s);
+  const double f = t - (s - 0x1.8p+47);
+  const double tj = __shfl_sync(0xffffffffu, tab_lane, n & 31);
+  double q = fma(0x1.5d886e6d047f4p-10, f, 0x1.3b2b1bee89b8dp-7);
+  q = fma(q, f, 0x1.c6b08d70300ecp-5);
+  q = fma(q, f, 0x1.ebfbdff8131c3p-3);
+  q = fma(q, f, 0x1.62e42fefa39efp-1);
+  const double w = q * f;
+  const double res = fma(tj, w, tj);
+  return __hiloint2double(__double2hiint(res) + ((n >> 5) << 20), __double2loint(res));
+}
+
 template <typename T, int OP> struct SkewFinish {
   static __device__ __forceinline__ T apply(T acc, T xc, T yc, int base, T p0, T p1, double tab) {
     if (OP == OP_GENERIC) return base_eval_call<T>(base, p0, p1, acc, xc, yc);
@@ -76,7 +150,11 @@ template <typename T, int OP> struct SkewFinish {
 };
 template <> struct SkewFinish<double, OP_RBF> {
   static __device__ __forceinline__ double apply(double acc, double, double, int, double, double, double tab) {
+#if GPSIG_SKEW_EXP2
+    return exp2_tab32(acc, tab);
+#else
     return exp_tab32(acc, tab);
+#endif
   }
 };
 
@@ -98,6 +176,11 @@ template <> struct SkewFinish<double, OP_RBF> {
 template <typename T> struct SkewCfg;
 template <> struct SkewCfg<double> { static constexpr int R = GPSIG_SKEW_R_F64; static constexpr int NW = GPSIG_SKEW_NW_F64; };
 template <> struct SkewCfg<float> { static constexpr int R = GPSIG_SKEW_R_F32; static constexpr int NW = GPSIG_SKEW_NW_F32; };
+// y tile in tensor memory: float64 shapes whose tile does not fit in registers (and whose warps' tiles fit the 512 columns)
+template <typename T, int DP, int COLS> struct SkewYTmem {
+  static constexpr bool value = GPSIG_SKEW_TMEM && sizeof(T) == 8 && !YPolicy<T, DP, COLS>::kInRegs &&
+                                SkewCfg<T>::NW % 4 == 0 && (SkewCfg<T>::NW / 4) * COLS * DP * 2 <= 512;
+};
 
 // float32 RBF: the packed coordinates are pre-scaled by sqrt(log2 e) (abi.cu), so the exponent
 // arrives in base-2 units and exp() is a single MUFU.EX2
@@ -121,6 +204,11 @@ __global__ void __launch_bounds__(SkewCfg<T>::NW * 32, 1) trunc_skew_kernel(cons
   constexpr int R = SkewCfg<T>::R;
   constexpr int NW = SkewCfg<T>::NW;
   constexpr bool YREG = YPolicy<T, DP, COLS>::kInRegs;
+  constexpr bool YTM = SkewYTmem<T, DP, COLS>::value;      // y tile in tensor memory (float64)
+  constexpr int KC = DP / 4;                                // 4-double chunks per column
+  constexpr int TMW = COLS * DP * 2;                        // TMEM words (columns) per warp
+  constexpr int TMCOLS = tmem_cols_pow2((NW / 4) * TMW);
+  static_assert(!YTM || (NW % 4 == 0 && (NW / 4) * TMW <= 512), "tensor memory plan does not fit");
   constexpr int NB = kSkewBufs;
   using Op = BaseOp<T, OP>;
 
@@ -133,7 +221,7 @@ __global__ void __launch_bounds__(SkewCfg<T>::NW * 32, 1) trunc_skew_kernel(cons
   const size_t xbytes = P.xblk * sizeof(T);
   const size_t xslot = align_up_dev(xbytes);
   unsigned char* xring = skew_smem + 128;
-  T* ysm = reinterpret_cast<T*>(xring + NB * xslot) + (size_t)warp * (COLS * 32 * DP);   // only if !YREG
+  T* ysm = reinterpret_cast<T*>(xring + NB * xslot) + (size_t)warp * (COLS * 32 * DP);   // only if !YREG && !YTM
 
   const int i_lo = P.row_begin + blockIdx.y * P.ichunk;
   const int i_hi = min(P.row_end, i_lo + P.ichunk);
@@ -144,7 +232,11 @@ __global__ void __launch_bounds__(SkewCfg<T>::NW * 32, 1) trunc_skew_kernel(cons
     for (int b = 0; b < NB; ++b) { mbar_init(&full_bar[b], 1); mbar_init(&empty_bar[b], NW); }
     fence_mbar_init();
   }
-  __syncthreads();
+  uint32_t tbase = 0;
+  if (YTM) tbase = tmem_alloc(reinterpret_cast<uint32_t*>(skew_smem + 96), TMCOLS);   // includes the block barrier
+  else __syncthreads();
+  // this warp's tile: its lane quarter (warp % 4), column block (warp / 4)
+  const uint32_t ta = tbase + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)((warp >> 2) * TMW);
   if (threadIdx.x == 0) {
     for (int it = 0; it < NB && it < npairs; ++it) {
       mbar_expect_tx(&full_bar[it], (uint32_t)xbytes);
@@ -167,23 +259,35 @@ __global__ void __launch_bounds__(SkewCfg<T>::NW * 32, 1) trunc_skew_kernel(cons
   for (int c = 0; c < COLS; ++c) {
     const int q = min(q0 + c, L2 - 1);
     yc[c] = Op::col_const(ysqn[q]);
+    if constexpr (YTM) {
 #pragma unroll
-    for (int kv = 0; kv < KV; ++kv) {
-      const V16 v = *reinterpret_cast<const V16*>(yblk + (size_t)q * P.yrs + kv * V);
-      if (YREG) yreg[YREG ? c : 0][YREG ? kv : 0] = v;
-      else *reinterpret_cast<V16*>(ysm + ((size_t)(c * KV + kv) * 32 + lane) * V) = v;
+      for (int kc = 0; kc < KC; ++kc) {
+        const double2 a = *reinterpret_cast<const double2*>(yblk + (size_t)q * P.yrs + kc * 4);
+        const double2 b = *reinterpret_cast<const double2*>(yblk + (size_t)q * P.yrs + kc * 4 + 2);
+        tmem_st4(ta + (uint32_t)((kc * COLS + c) * 8), a.x, a.y, b.x, b.y);
+      }
+    } else {
+#pragma unroll
+      for (int kv = 0; kv < KV; ++kv) {
+        const V16 v = *reinterpret_cast<const V16*>(yblk + (size_t)q * P.yrs + kv * V);
+        if (YREG) yreg[YREG ? c : 0][YREG ? kv : 0] = v;
+        else *reinterpret_cast<V16*>(ysm + ((size_t)(c * KV + kv) * 32 + lane) * V) = v;
+      }
     }
   }
-  if (!YREG) __syncwarp();
+  if (YTM) tmem_st_wait();
+  else if (!YREG) __syncwarp();
   double tab = 0.0;
   if (OP == OP_RBF && sizeof(T) == 8) tab = exp2((double)lane * (1.0 / 32.0));
 
   // ---- state ------------------------------------------------------------------------
-  T C[MLEV][COLS];
+  // column sums C_l[q] of levels 0..MLEV-2; of the top level only the total is ever used: two partial sums
+  T C[MLEV - 1][COLS];
 #pragma unroll
-  for (int l = 0; l < MLEV; ++l)
+  for (int l = 0; l < MLEV - 1; ++l)
 #pragma unroll
     for (int c = 0; c < COLS; ++c) C[l][c] = T(0);
+  T Ct[2] = {T(0), T(0)};
   T Mp[2][COLS];                                   // last base-kernel row, ping-pong over the step parity
 #pragma unroll
   for (int c = 0; c < COLS; ++c) Mp[0][c] = Mp[1][c] = T(0);
@@ -240,6 +344,8 @@ __global__ void __launch_bounds__(SkewCfg<T>::NW * 32, 1) trunc_skew_kernel(cons
 
     // ---- base kernel on R rows x COLS columns -------------------------------------
     T Mc[R][COLS];
+    [[maybe_unused]] TmemQuad yq[2];
+    if constexpr (YTM) tmem_ld4(yq[0], ta);
     {
       T xc[R];
       T acc[R][COLS];
@@ -250,6 +356,35 @@ __global__ void __launch_bounds__(SkewCfg<T>::NW * 32, 1) trunc_skew_kernel(cons
 #pragma unroll
         for (int c = 0; c < COLS; ++c) acc[rr][c] = Op::init(xc[rr], yc[c]);
       }
+      if constexpr (YTM) {
+#pragma unroll
+        for (int kc = 0; kc < KC; ++kc) {
+          double2 xa[R], xq[R];
+#pragma unroll
+          for (int rr = 0; rr < R; ++rr) {
+            const T* xr = xb + (size_t)min(r0 + rr, L - 1) * RS + kc * 4;
+            xa[rr] = *reinterpret_cast<const double2*>(xr);
+            xq[rr] = *reinterpret_cast<const double2*>(xr + 2);
+          }
+#pragma unroll
+          for (int c = 0; c < COLS; ++c) {
+            const int idx = kc * COLS + c;
+            TmemQuad& cur = yq[idx & 1];
+            tmem_ld_wait(cur);
+            if (idx + 1 < KC * COLS) tmem_ld4(yq[(idx + 1) & 1], ta + (uint32_t)((idx + 1) * 8));
+            const double y0 = tmem_quad_get(cur, 0), y1 = tmem_quad_get(cur, 1), y2 = tmem_quad_get(cur, 2), y3 = tmem_quad_get(cur, 3);
+#pragma unroll
+            for (int rr = 0; rr < R; ++rr) {
+              T a = acc[rr][c];
+              a = gfma<T>(T(xa[rr].x), T(y0), a);
+              a = gfma<T>(T(xa[rr].y), T(y1), a);
+              a = gfma<T>(T(xq[rr].x), T(y2), a);
+              a = gfma<T>(T(xq[rr].y), T(y3), a);
+              acc[rr][c] = a;
+            }
+          }
+        }
+      } else {
 #pragma unroll
       for (int kv = 0; kv < KV; ++kv) {
         V16 xv[R];
@@ -266,6 +401,7 @@ __global__ void __launch_bounds__(SkewCfg<T>::NW * 32, 1) trunc_skew_kernel(cons
 #pragma unroll
             for (int e = 0; e < V; ++e) acc[rr][c] = gfma<T>(vget(xv[rr], e), vget(yv, e), acc[rr][c]);
         }
+      }
       }
 #pragma unroll
       for (int rr = 0; rr < R; ++rr)
@@ -309,8 +445,10 @@ __global__ void __launch_bounds__(SkewCfg<T>::NW * 32, 1) trunc_skew_kernel(cons
 #pragma unroll
         for (int l = 0; l < MLEV; ++l) {
           T e = recv[0][l];
+          if (l < MLEV - 1) {
 #pragma unroll
-          for (int c = 0; c < COLS; ++c) e += C[l][c];
+            for (int c = 0; c < COLS; ++c) e += C[l < MLEV - 1 ? l : 0][c];
+          } else e += Ct[0] + Ct[1];
           tot[l] = e;
           send[0][l] = e;
         }
@@ -337,9 +475,10 @@ __global__ void __launch_bounds__(SkewCfg<T>::NW * 32, 1) trunc_skew_kernel(cons
           if (!P.return_levels) static_cast<T*>(P.out)[rc] = sum;
         }
 #pragma unroll
-        for (int l = 1; l < MLEV; ++l)
+        for (int l = 1; l < MLEV - 1; ++l)
 #pragma unroll
           for (int c = 0; c < COLS; ++c) C[l][c] = T(0);
+        Ct[0] = Ct[1] = T(0);
 #pragma unroll
         for (int c = 0; c < COLS; ++c) C[0][c] = diff ? T(0) : D[c];
       } else {
@@ -351,7 +490,8 @@ __global__ void __launch_bounds__(SkewCfg<T>::NW * 32, 1) trunc_skew_kernel(cons
           for (int c = 0; c < COLS; ++c) {
             const T t = e;
             e += C[l][c];
-            C[l + 1][c] = gfma<T>(D[c], t, C[l + 1][c]);
+            if (l == MLEV - 2) Ct[c & 1] = gfma<T>(D[c], t, Ct[c & 1]);
+            else C[l + 1 < MLEV - 1 ? l + 1 : 0][c] = gfma<T>(D[c], t, C[l + 1 < MLEV - 1 ? l + 1 : 0][c]);
           }
           send[rr][l] = e;
         }
@@ -366,6 +506,7 @@ __global__ void __launch_bounds__(SkewCfg<T>::NW * 32, 1) trunc_skew_kernel(cons
     step(std::integral_constant<int, 0>{}, s);
     step(std::integral_constant<int, 1>{}, s + 1);
   }
+  if (YTM) tmem_free(tbase, TMCOLS);
 }
 
 // ---------------------------------------------------------------------------
@@ -373,13 +514,16 @@ __global__ void __launch_bounds__(SkewCfg<T>::NW * 32, 1) trunc_skew_kernel(cons
 // ---------------------------------------------------------------------------
 // Shapes this kernel takes (the rest runs trunc_gram_kernel): one column pass, rows long
 // enough (>= 32 steps per pair) that a lane-skewed warp touches at most two consecutive pairs.
+template <typename T, int DP, int COLS>
+constexpr size_t skew_ywarp_bytes() { return SkewYTmem<T, DP, COLS>::value ? 0 : trunc_ywarp_bytes<T, DP, COLS>(); }
+
 inline bool skew_eligible(int L, int L2, int elem) { return L >= 32 * (elem == 8 ? GPSIG_SKEW_R_F64 : GPSIG_SKEW_R_F32) + 1 && L2 <= 256; }
 
 template <typename T, int DP, int COLS, int MLEV, int OP>
 int launch_skew_inst(TruncParams P, cudaStream_t stream) {
   const int RS = P.xrs;
   const size_t xslot = align_up_dev(P.xblk * sizeof(T));
-  const size_t smem = 128 + kSkewBufs * xslot + (size_t)SkewCfg<T>::NW * trunc_ywarp_bytes<T, DP, COLS>();
+  const size_t smem = 128 + kSkewBufs * xslot + (size_t)SkewCfg<T>::NW * skew_ywarp_bytes<T, DP, COLS>();
   if (smem > kMaxSmem)
     GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "sequence too long for the on-chip plan: needs %zu bytes of shared memory (L=%d)", smem, P.L);
   auto kern = trunc_skew_kernel<T, DP, COLS, MLEV, OP>;
