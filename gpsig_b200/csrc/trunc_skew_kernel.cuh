@@ -51,6 +51,9 @@ __host__ __device__ inline int skew_row_stride(int d, int elem) {
 #define GPSIG_SKEW_TMEM 1
 #endif
 // float64 RBF: packed coordinates pre-scaled by sqrt(log2 e) (abi.cu) and exp2_tab32 below
+#ifndef GPSIG_TMEM_TIE
+#define GPSIG_TMEM_TIE 1
+#endif
 #ifndef GPSIG_SKEW_EXP2
 #define GPSIG_SKEW_EXP2 1
 #endif
@@ -83,13 +86,20 @@ struct TmemQuad { uint32_t w[8]; };
 __device__ __forceinline__ void tmem_ld4(TmemQuad& r, uint32_t addr) {
   asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                : "=r"(r.w[0]), "=r"(r.w[1]), "=r"(r.w[2]), "=r"(r.w[3]), "=r"(r.w[4]), "=r"(r.w[5]), "=r"(r.w[6]), "=r"(r.w[7])
-               : "r"(addr) : "memory");
+               : "r"(addr));
 }
-// the loaded registers are tied to the wait so that no use can be scheduled above it
-__device__ __forceinline__ void tmem_ld_wait(TmemQuad& r) {
-  asm volatile("tcgen05.wait::ld.sync.aligned;"
-               : "+r"(r.w[0]), "+r"(r.w[1]), "+r"(r.w[2]), "+r"(r.w[3]), "+r"(r.w[4]), "+r"(r.w[5]), "+r"(r.w[6]), "+r"(r.w[7])
-               :: "memory");
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// empty volatile asm that redefines the loaded registers after the wait: no use of them can be scheduled above it
+__device__ __forceinline__ void tmem_tie(TmemQuad& r) {
+  asm volatile("" : "+r"(r.w[0]), "+r"(r.w[1]), "+r"(r.w[2]), "+r"(r.w[3]), "+r"(r.w[4]), "+r"(r.w[5]), "+r"(r.w[6]), "+r"(r.w[7]));
+}
+// shuffle-up by one lane as a volatile asm: stays where it is written relative to the tensor-memory
+// loads / waits, i.e. in between the FMA groups of the contraction instead of in one burst at the step start
+__device__ __forceinline__ double shfl_up1_pinned(double v) {
+  int lo = __double2loint(v), hi = __double2hiint(v);
+  asm volatile("shfl.sync.up.b32 %0, %0, 1, 0, 0xffffffff;" : "+r"(lo));
+  asm volatile("shfl.sync.up.b32 %0, %0, 1, 0, 0xffffffff;" : "+r"(hi));
+  return __hiloint2double(hi, lo);
 }
 __device__ __forceinline__ double tmem_quad_get(const TmemQuad& r, int e) { return __hiloint2double((int)r.w[2 * e + 1], (int)r.w[2 * e]); }
 __host__ __device__ constexpr int tmem_cols_pow2(int n) { return n <= 32 ? 32 : n <= 64 ? 64 : n <= 128 ? 128 : n <= 256 ? 256 : 512; }
@@ -132,14 +142,19 @@ __device__ __forceinline__ double exp2_tab32(double t, double tab_lane) {
   const double s = t + 0x1.8p+47;
   const int n = __double2loint(s);
   const double f = t - (s - 0x1.8p+47);
-  const double tj = __shfl_sync(0xffffffffu, tab_lane, n & 31);
+  const double tj = __shfl_sync(0xffffffffu, tab_lane, n);          // source lane = n mod 32
   double q = fma(0x1.5d886e6d047f4p-10, f, 0x1.3b2b1bee89b8dp-7);
   q = fma(q, f, 0x1.c6b08d70300ecp-5);
   q = fma(q, f, 0x1.ebfbdff8131c3p-3);
   q = fma(q, f, 0x1.62e42fefa39efp-1);
   const double w = q * f;
   const double res = fma(tj, w, tj);
-  return __hiloint2double(__double2hiint(res) + ((n >> 5) << 20), __double2loint(res));
+  return __hiloint2double(__double2hiint(res) + (n & ~31) * 32768, __double2loint(res));   // + (n >> 5) << 20
+}
+
+template <int N, typename F, int I = 0>
+__device__ __forceinline__ void static_for(F&& f) {
+  if constexpr (I < N) { f(std::integral_constant<int, I>{}); static_for<N, F, I + 1>(static_cast<F&&>(f)); }
 }
 
 template <typename T, int OP> struct SkewFinish {
@@ -321,15 +336,18 @@ __global__ void __launch_bounds__(SkewCfg<T>::NW * 32, 1) trunc_skew_kernel(cons
       }
     }
     // ---- chain values from the lane to the left (computed one step ago) -----------
+    // (tensor-memory variant: the shuffles are issued inside the contraction below)
     T recv[R][MLEV], recvU[R];
+    if constexpr (!YTM) {
 #pragma unroll
-    for (int rr = 0; rr < R; ++rr) {
-      recvU[rr] = __shfl_up_sync(0xffffffffu, sendU[rr], 1);
+      for (int rr = 0; rr < R; ++rr) {
+        recvU[rr] = __shfl_up_sync(0xffffffffu, sendU[rr], 1);
 #pragma unroll
-      for (int l = 0; l < MLEV; ++l) {
-        if (l < MLEV - 1 || rr == 0) recv[rr][l] = __shfl_up_sync(0xffffffffu, send[rr][l], 1);
-        else recv[rr][l] = T(0);
-        if (lane == 0) recv[rr][l] = T(0);
+        for (int l = 0; l < MLEV; ++l) {
+          if (l < MLEV - 1 || rr == 0) recv[rr][l] = __shfl_up_sync(0xffffffffu, send[rr][l], 1);
+          else recv[rr][l] = T(0);
+          if (lane == 0) recv[rr][l] = T(0);
+        }
       }
     }
     // ---- this lane's place in the stream: one step behind the lane to its left ----
@@ -344,8 +362,29 @@ __global__ void __launch_bounds__(SkewCfg<T>::NW * 32, 1) trunc_skew_kernel(cons
 
     // ---- base kernel on R rows x COLS columns -------------------------------------
     T Mc[R][COLS];
-    [[maybe_unused]] TmemQuad yq[2];
-    if constexpr (YTM) tmem_ld4(yq[0], ta);
+    // tensor-memory variant: the tile arrives in groups of GS columns x 4 dimensions; group g+1 is
+    // requested before the FMAs of group g, its wait comes after them (wait::ld covers all loads in flight)
+    constexpr int GS = 4;
+    constexpr int NG = (COLS + GS - 1) / GS;          // groups per 4-dimension chunk
+    constexpr int NGT = NG * KC;
+    constexpr int NCH = R + R * (MLEV - 1) + 1;       // chain values per step
+    constexpr int CPG = (NCH + NGT - 1) / NGT;        // ... shuffled per group
+    [[maybe_unused]] TmemQuad yq[2][GS];
+    [[maybe_unused]] auto tm_issue = [&](auto G) {
+      constexpr int g = decltype(G)::value;
+      constexpr int kc = g / NG, c0 = (g % NG) * GS;
+#pragma unroll
+      for (int c = c0; c < c0 + GS && c < COLS; ++c) tmem_ld4(yq[g & 1][c - c0], ta + (uint32_t)((kc * COLS + c) * 8));
+    };
+    [[maybe_unused]] auto chain_slot = [&](auto K) {
+      constexpr int k = decltype(K)::value;
+      if constexpr (k < R) recvU[k] = shfl_up1_pinned(sendU[k]);
+      else if constexpr (k < R + R * (MLEV - 1)) {
+        constexpr int rr = (k - R) / (MLEV - 1), l = (k - R) % (MLEV - 1);
+        recv[rr][l] = shfl_up1_pinned(send[rr][l]);
+      } else if constexpr (k == NCH - 1) recv[0][MLEV - 1] = shfl_up1_pinned(send[0][MLEV - 1]);
+    };
+    if constexpr (YTM) tm_issue(std::integral_constant<int, 0>{});
     {
       T xc[R];
       T acc[R][COLS];
@@ -357,21 +396,29 @@ __global__ void __launch_bounds__(SkewCfg<T>::NW * 32, 1) trunc_skew_kernel(cons
         for (int c = 0; c < COLS; ++c) acc[rr][c] = Op::init(xc[rr], yc[c]);
       }
       if constexpr (YTM) {
+        double2 xa[R], xq[R];
+        static_for<NGT>([&](auto G) {
+          constexpr int g = decltype(G)::value;
+          constexpr int kc = g / NG, c0 = (g % NG) * GS;
+          if constexpr (g % NG == 0) {
 #pragma unroll
-        for (int kc = 0; kc < KC; ++kc) {
-          double2 xa[R], xq[R];
-#pragma unroll
-          for (int rr = 0; rr < R; ++rr) {
-            const T* xr = xb + (size_t)min(r0 + rr, L - 1) * RS + kc * 4;
-            xa[rr] = *reinterpret_cast<const double2*>(xr);
-            xq[rr] = *reinterpret_cast<const double2*>(xr + 2);
+            for (int rr = 0; rr < R; ++rr) {
+              const T* xr = xb + (size_t)min(r0 + rr, L - 1) * RS + kc * 4;
+              xa[rr] = *reinterpret_cast<const double2*>(xr);
+              xq[rr] = *reinterpret_cast<const double2*>(xr + 2);
+            }
           }
+          tmem_ld_wait();
 #pragma unroll
-          for (int c = 0; c < COLS; ++c) {
-            const int idx = kc * COLS + c;
-            TmemQuad& cur = yq[idx & 1];
-            tmem_ld_wait(cur);
-            if (idx + 1 < KC * COLS) tmem_ld4(yq[(idx + 1) & 1], ta + (uint32_t)((idx + 1) * 8));
+          for (int c = c0; c < c0 + GS && c < COLS; ++c) if (GPSIG_TMEM_TIE) tmem_tie(yq[g & 1][c - c0]);
+          if constexpr (g + 1 < NGT) tm_issue(std::integral_constant<int, g + 1>{});
+          static_for<CPG>([&](auto J) {
+            constexpr int k = g * CPG + decltype(J)::value;
+            if constexpr (k < NCH) chain_slot(std::integral_constant<int, k>{});
+          });
+#pragma unroll
+          for (int c = c0; c < c0 + GS && c < COLS; ++c) {
+            const TmemQuad& cur = yq[g & 1][c - c0];
             const double y0 = tmem_quad_get(cur, 0), y1 = tmem_quad_get(cur, 1), y2 = tmem_quad_get(cur, 2), y3 = tmem_quad_get(cur, 3);
 #pragma unroll
             for (int rr = 0; rr < R; ++rr) {
@@ -383,7 +430,14 @@ __global__ void __launch_bounds__(SkewCfg<T>::NW * 32, 1) trunc_skew_kernel(cons
               acc[rr][c] = a;
             }
           }
-        }
+        });
+#pragma unroll
+        for (int rr = 0; rr < R; ++rr)
+#pragma unroll
+          for (int l = 0; l < MLEV; ++l) {
+            if (!(l < MLEV - 1 || rr == 0)) recv[rr][l] = T(0);
+            if (lane == 0) recv[rr][l] = T(0);
+          }
       } else {
 #pragma unroll
       for (int kv = 0; kv < KV; ++kv) {
