@@ -311,7 +311,10 @@ static int pde_impl(const double* X, int N, int L, const double* Y, int N2, int 
   const size_t smem = pipe ? pde_pipe_smem_bytes(L, L2, P.DP, order, nstrips) : pde_smem_bytes(L, L2, P.DP, order);
   if (smem > kMaxSmem)
     GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "PDE grid too large for the on-chip plan: %zu bytes of shared memory (L=%d, L2=%d, order=%d)", smem, L, L2, order);
-#define GPSIG_PDE_GO(DP_, O_) do { if (pipe) { auto kern = pde_pipe_kernel<DP_, O_>; \
+  const bool rowstep = getenv("GPSIG_PDE_ROWSTEP") != nullptr;    // previous one-row-per-step kernel (A/B timing only)
+#define GPSIG_PDE_GO(DP_, O_) do { if (pipe && !rowstep) { auto kern = pde_block_kernel<DP_, O_>; \
+    GPSIG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    prof_begin(s); kern<<<(unsigned)npairs, 32 * nstrips, smem, s>>>(P); prof_end(s); } else if (pipe) { auto kern = pde_pipe_kernel<DP_, O_>; \
     GPSIG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
     prof_begin(s); kern<<<(unsigned)npairs, 32 * nstrips, smem, s>>>(P); prof_end(s); } else { auto kern = pde_wavefront_kernel<DP_, O_>; \
     GPSIG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \

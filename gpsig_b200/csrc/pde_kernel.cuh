@@ -350,4 +350,206 @@ __global__ void __launch_bounds__(kPdeMaxStrips * 32) pde_pipe_kernel(const PdeP
   }
 }
 
+// ---------------------------------------------------------------------------
+// Block-row variant of the pipelined kernel: a lane advances min(2^ORDER, 4) FINE ROWS per step
+// instead of one.  With the lanes skewed by whole coarse rows (ORDER <= 2) every lane enters a new
+// coarse row at every step, so the increment dot product and the stencil coefficients (pyx:41-48) are
+// computed straight into A/B at a warp-uniform point (no double buffer, no per-lane select), and the
+// fixed cost of a step (shuffles, ring hand-off, progress counters, loop control: ~70 instructions)
+// is spread over 4x the cells: ~4.7 issued instructions per cell instead of ~12, 3.5 of them FP64.
+// The 4 x 8 block of a step is itself a small wavefront (the compiler interleaves the four row chains).
+// Ring, counters and shared-memory layout are those of pde_pipe_kernel, counted in block rows.
+// ---------------------------------------------------------------------------
+template <int DP, int ORDER>
+__global__ void __launch_bounds__(kPdeMaxStrips * 32) pde_block_kernel(const PdeParams Pm) {
+  constexpr int W = kPdeW;
+  constexpr int NC = (W >> ORDER) > 0 ? (W >> ORDER) : 1;   // coarse columns per lane
+  constexpr int RS = (1 << ORDER) < 4 ? (1 << ORDER) : 4;   // fine rows per step
+  constexpr int CST = (1 << ORDER) / RS;                    // steps per coarse row (1 for ORDER <= 2)
+  constexpr int RB = kPdeRing;                              // ring rows (fine rows)
+  constexpr int RBb = RB / RS;                              // ... in block rows
+  constexpr int G = (16 / RS) > 4 ? (16 / RS) : 4;          // steps between progress exchanges (2G <= RBb)
+  extern __shared__ __align__(128) unsigned char pde_smem[];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, NS = blockDim.x >> 5;
+  const int L = Pm.L, L2 = Pm.L2;
+  const int P = (L - 1) << ORDER, Q = (L2 - 1) << ORDER;
+  const int PB = P / RS;                                    // block rows
+  constexpr int XS = DP + 2;                                // padded dx row stride (doubles)
+  constexpr bool DYREG = NC * DP <= 32;
+  double* dx = reinterpret_cast<double*>(pde_smem);
+  double* dy = dx + (size_t)(L - 1) * XS;
+  double* ring = dy + pde_dy_smem_elems(L2, DP, ORDER);
+  int* prod = reinterpret_cast<int*>(ring + (size_t)NS * RB);
+  int* cons = prod + kPdeMaxStrips;
+
+  int ix, iy;
+  if (Pm.pair_mode == GPSIG_PDE_DIAG) { ix = Pm.row_begin + blockIdx.x; iy = ix; }
+  else { ix = Pm.row_begin + blockIdx.x / Pm.N2; iy = blockIdx.x % Pm.N2; }
+  const double* x = static_cast<const double*>(Pm.xp) + (size_t)ix * Pm.xblk;
+  const double* y = static_cast<const double*>(Pm.yp) + (size_t)iy * Pm.yblk;
+
+  const double fscale = 1.0 / (double)(1 << (2 * ORDER));
+  for (int e = threadIdx.x; e < (L - 1) * DP; e += blockDim.x) {
+    const int I = e / DP, k = e - I * DP;
+    dx[I * XS + k] = (x[e + DP] - x[e]) * fscale;
+  }
+  if (!DYREG)
+    for (int e = threadIdx.x; e < (L2 - 1) * DP; e += blockDim.x) dy[e + 2 * ((e / DP) / NC)] = y[e + DP] - y[e];
+  if (threadIdx.x < kPdeMaxStrips) { prod[threadIdx.x] = 0; cons[threadIdx.x] = 0; }
+  __syncthreads();                                          // the only block-wide barrier
+
+  const int j0 = w * 32 * W + lane * W;
+  double2 dyreg[DYREG ? NC : 1][DYREG ? DP / 2 : 1];
+  if (DYREG) {
+#pragma unroll
+    for (int cc = 0; cc < NC; ++cc) {
+      const int J = min((j0 >> ORDER) + cc, L2 - 2);
+#pragma unroll
+      for (int k = 0; k < DP / 2; ++k)
+        dyreg[DYREG ? cc : 0][DYREG ? k : 0] = make_double2(y[(J + 1) * DP + 2 * k] - y[J * DP + 2 * k],
+                                                              y[(J + 1) * DP + 2 * k + 1] - y[J * DP + 2 * k + 1]);
+    }
+  }
+  const int ncell = max(0, min(W, Q - j0));
+  const int LL = min(31, (Q - w * 32 * W - 1) / W);         // last lane with cells in this strip
+  const bool has_left = w > 0, has_right = w + 1 < NS;
+  const uint32_t ring_in_s = opaque_u32(smem_u32(ring + (size_t)w * RB));
+  const uint32_t ring_out_s = opaque_u32(smem_u32(ring + (size_t)(w + 1) * RB));
+  const uint32_t dx_s = opaque_u32(smem_u32(dx));
+  const uint32_t prod_in_s = opaque_u32(smem_u32(&prod[w]));
+  const uint32_t cons_out_s = opaque_u32(smem_u32(&cons[w + 1 < kPdeMaxStrips ? w + 1 : w]));
+  const bool lane0 = lane == 0, lane_last = lane == 31;
+
+  double up[W];
+#pragma unroll
+  for (int c = 0; c < W; ++c) up[c] = 1.0;                  // K[0, .] = 1 (pyx:29-31)
+  double A[NC], B[NC], An[NC], Bn[NC];
+#pragma unroll
+  for (int cc = 0; cc < NC; ++cc) { A[cc] = B[cc] = An[cc] = Bn[cc] = 1.0; }
+  double send[RS];
+#pragma unroll
+  for (int r = 0; r < RS; ++r) send[r] = 1.0;
+  double dgl = 1.0;                                         // K[i, j0]
+  const int nsteps = PB + LL;
+  int b = -lane;                                            // block row of this lane at step s
+  for (int s = 0; s < nsteps; ++s, ++b) {
+    if ((s & (G - 1)) == 0) {
+      // ---- hand-off window: block rows [s, s+G) ------------------------------------
+      if (has_left) {
+        const int need = min(s + G, PB);
+        while (ld_volatile_shared_u(prod_in_s) < need) __nanosleep(32);
+      }
+      if (has_right) {
+        const int top = min(s + G - LL, PB);
+        while (top > ld_volatile_shared_u(cons_out_s) + RBb) __nanosleep(32);
+      }
+      __threadfence_block();
+    }
+    if ((CST == 1 || (s & (CST - 1)) == 0) && ncell > 0) {
+      // coefficients of the coarse row this lane enters within the next CST steps (pyx:41-48)
+      const int In = min(max(b + CST - 1, 0) / CST, L - 2);
+      const uint32_t dxa = dx_s + (uint32_t)In * (uint32_t)(XS * 8);
+      double2 xv[DP / 2];
+#pragma unroll
+      for (int k = 0; k < DP / 2; ++k)
+        asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(xv[k].x), "=d"(xv[k].y) : "r"(dxa + 16u * k));
+#pragma unroll
+      for (int cc = 0; cc < NC; ++cc) {
+        double e = 0.0;
+        if (DYREG) {
+#pragma unroll
+          for (int k = 0; k < DP / 2; ++k) {
+            e = fma(xv[k].x, dyreg[DYREG ? cc : 0][DYREG ? k : 0].x, e);
+            e = fma(xv[k].y, dyreg[DYREG ? cc : 0][DYREG ? k : 0].y, e);
+          }
+        } else {
+          const int J = min((j0 >> ORDER) + cc, L2 - 2);
+          const double2* dyj = reinterpret_cast<const double2*>(dy + (size_t)J * DP + 2 * (J / NC));
+#pragma unroll
+          for (int k = 0; k < DP / 2; ++k) { const double2 yv = dyj[k]; e = fma(xv[k].x, yv.x, e); e = fma(xv[k].y, yv.y, e); }
+        }
+        const double e2 = e * e;
+        An[cc] = 1. + 0.5 * e + (1. / 12) * e2;             // pyx:48
+        Bn[cc] = 1. - (1. / 12) * e2;
+      }
+    }
+    // K[i+1, j0] of this block row's RS fine rows, from the lane to the left (computed one step ago)
+    double recv[RS];
+#pragma unroll
+    for (int r = 0; r < RS; ++r) recv[r] = __shfl_up_sync(0xffffffffu, send[r], 1);
+    const bool rowok = (b >= 0) && (b < PB) && (ncell > 0);
+    const uint32_t slot = (uint32_t)((b * RS) & (RB - 1)) * 8u;
+    if (lane0) {
+#pragma unroll
+      for (int r = 0; r < RS; ++r) recv[r] = 1.0;           // K[., 0] = 1 (pyx:29-31)
+      if (has_left && rowok) {
+        if (RS == 4) {
+          asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(recv[0]), "=d"(recv[RS > 1 ? 1 : 0]) : "r"(ring_in_s + slot) : "memory");
+          asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(recv[RS > 2 ? 2 : 0]), "=d"(recv[RS > 3 ? 3 : 0]) : "r"(ring_in_s + slot + 16u) : "memory");
+        } else if (RS == 2) {
+          asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(recv[0]), "=d"(recv[RS > 1 ? 1 : 0]) : "r"(ring_in_s + slot) : "memory");
+        } else {
+          asm volatile("ld.shared.f64 %0, [%1];" : "=d"(recv[0]) : "r"(ring_in_s + slot) : "memory");
+        }
+      }
+    }
+    if (rowok) {
+      if (CST == 1 || (b & (CST - 1)) == 0) {               // entering a new coarse row
+#pragma unroll
+        for (int cc = 0; cc < NC; ++cc) { A[cc] = An[cc]; B[cc] = Bn[cc]; }
+      }
+      // (k01 + k10) * A - k00 * B per cell: wv needs only the previous row, one FMA per cell is on the
+      // left-to-right chain.  All W cells are computed, also those past column Q of the last lane.
+#pragma unroll
+      for (int r = 0; r < RS; ++r) {
+        double wv[W];
+#pragma unroll
+        for (int c = 0; c < W; ++c) {
+          const int cc = (ORDER >= 3) ? 0 : (c >> ORDER);
+          wv[c] = fma(up[c], A[cc], -((c == 0 ? dgl : up[c > 0 ? c - 1 : 0]) * B[cc]));
+        }
+        dgl = recv[r];
+        double lf = recv[r];
+#pragma unroll
+        for (int c = 0; c < W; ++c) {
+          const int cc = (ORDER >= 3) ? 0 : (c >> ORDER);
+          lf = fma(lf, A[cc], wv[c]);
+          up[c] = lf;
+        }
+        send[r] = lf;
+      }
+      if (lane_last && has_right) {
+        if (RS == 4) {
+          asm volatile("st.shared.v2.f64 [%0], {%1,%2};" ::"r"(ring_out_s + slot), "d"(send[0]), "d"(send[RS > 1 ? 1 : 0]) : "memory");
+          asm volatile("st.shared.v2.f64 [%0], {%1,%2};" ::"r"(ring_out_s + slot + 16u), "d"(send[RS > 2 ? 2 : 0]), "d"(send[RS > 3 ? 3 : 0]) : "memory");
+        } else if (RS == 2) {
+          asm volatile("st.shared.v2.f64 [%0], {%1,%2};" ::"r"(ring_out_s + slot), "d"(send[0]), "d"(send[RS > 1 ? 1 : 0]) : "memory");
+        } else {
+          asm volatile("st.shared.f64 [%0], %1;" ::"r"(ring_out_s + slot), "d"(send[0]) : "memory");
+        }
+      }
+    }
+    if (((s + 1) & (G - 1)) == 0 || s + 1 == nsteps) {
+      // ---- publish progress (block rows) ----------------------------------------------
+      __syncwarp();
+      if (has_right && lane == LL) {
+        __threadfence_block();
+        st_volatile_shared(&prod[w + 1], max(0, min(s - LL + 1, PB)));
+      }
+      if (has_left && lane0) st_volatile_shared(&cons[w], min(s + 1, PB));
+    }
+  }
+  if (w == NS - 1) {
+    double result = up[0];
+#pragma unroll
+    for (int c = 1; c < W; ++c) if (c == ncell - 1) result = up[c];
+    result = __shfl_sync(0xffffffffu, result, LL);
+    if (lane0) {
+      const size_t o = Pm.pair_mode == GPSIG_PDE_DIAG ? (size_t)blockIdx.x
+                                                      : (size_t)(ix - Pm.row_begin) * Pm.N2 + iy;
+      Pm.out[o] = Pm.sigma * result;
+    }
+  }
+}
+
 }  // namespace gpsig
