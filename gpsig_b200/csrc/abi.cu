@@ -303,18 +303,33 @@ static int pde_impl(const double* X, int N, int L, const double* Y, int N2, int 
   P.row_begin = row_begin; P.row_end = row_end; P.sigma = sigma; P.out = out;
   const size_t npairs = pair_mode == GPSIG_PDE_DIAG ? (size_t)(row_end - row_begin) : (size_t)(row_end - row_begin) * N2;
   if (npairs > 0x7fffffffull) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "too many pairs in one call (%zu)", npairs);
-  // one warp per 32*kPdeW-column strip, all strips of a pair in flight (pde_pipe_kernel); pairs with more
-  // than kPdeMaxStrips strips run the strips one after the other on one warp (pde_wavefront_kernel)
+  // one warp per 32*kPdeW-column strip, all strips of a pair in flight, persistent CTAs taking pairs from a
+  // ticket counter (pde_block_kernel); pairs with more than kPdeMaxStrips strips run the strips one after
+  // the other on one warp (pde_wavefront_kernel)
   const int Qf = (L2 - 1) << order;
   const int nstrips = (Qf + 32 * kPdeW - 1) / (32 * kPdeW);
   const bool pipe = nstrips <= kPdeMaxStrips && getenv("GPSIG_PDE_SEQ") == nullptr;
-  const size_t smem = pipe ? pde_pipe_smem_bytes(L, L2, P.DP, order, nstrips) : pde_smem_bytes(L, L2, P.DP, order);
+  // dyadic order 0 has one fine row per coarse row: the block-row kernel degenerates to the one-row-per-step
+  // kernel plus ticket overhead, so order 0 keeps pde_pipe_kernel (measured: 0.41 ms against 0.53 ms at N=1000, L=500)
+  const bool rowstep = order == 0 || getenv("GPSIG_PDE_ROWSTEP") != nullptr;
+  // persistent mode needs the dy coefficients in registers (they are per pair) and room for two dx buffers
+  bool persist = pipe && !rowstep && pde_dy_in_regs(P.DP, order) && getenv("GPSIG_PDE_NOPERSIST") == nullptr &&
+                 pde_block_smem_bytes(L, L2, P.DP, order, nstrips, true) <= kMaxSmem;
+  const size_t smem = !pipe ? pde_smem_bytes(L, L2, P.DP, order)
+                            : rowstep ? pde_pipe_smem_bytes(L, L2, P.DP, order, nstrips)
+                                      : pde_block_smem_bytes(L, L2, P.DP, order, nstrips, persist);
   if (smem > kMaxSmem)
     GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "PDE grid too large for the on-chip plan: %zu bytes of shared memory (L=%d, L2=%d, order=%d)", smem, L, L2, order);
-  const bool rowstep = getenv("GPSIG_PDE_ROWSTEP") != nullptr;    // previous one-row-per-step kernel (A/B timing only)
+  unsigned* ticket = reinterpret_cast<unsigned*>(static_cast<char*>(ws) + need - 128);
+  if (persist) GPSIG_CUDA_CHECK(cudaMemsetAsync(ticket, 0, sizeof(unsigned), s));
+  int sms = 148;
+  { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
 #define GPSIG_PDE_GO(DP_, O_) do { if (pipe && !rowstep) { auto kern = pde_block_kernel<DP_, O_>; \
     GPSIG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-    prof_begin(s); kern<<<(unsigned)npairs, 32 * nstrips, smem, s>>>(P); prof_end(s); } else if (pipe) { auto kern = pde_pipe_kernel<DP_, O_>; \
+    unsigned grid = (unsigned)npairs; \
+    if (persist) { int occ = 1; GPSIG_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 32 * nstrips, smem)); \
+      const size_t slots = (size_t)(occ > 0 ? occ : 1) * sms; if (npairs > slots) grid = (unsigned)slots; else persist = false; } \
+    prof_begin(s); kern<<<grid, 32 * nstrips, smem, s>>>(P, persist ? 1 : 0, ticket); prof_end(s); } else if (pipe) { auto kern = pde_pipe_kernel<DP_, O_>; \
     GPSIG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
     prof_begin(s); kern<<<(unsigned)npairs, 32 * nstrips, smem, s>>>(P); prof_end(s); } else { auto kern = pde_wavefront_kernel<DP_, O_>; \
     GPSIG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
@@ -405,7 +420,7 @@ int gpsig_tens_tens_f32(const gpsig_trunc_desc* desc, const float* Z, int Mz, in
 
 size_t gpsig_pde_workspace_bytes(int N, int L, int N2, int L2, int d, int order, int pair_mode) {
   (void)order; (void)pair_mode;
-  return packed_bytes(N, L, d, 8) + (N2 > 0 ? packed_bytes(N2, L2, d, 8) : 0);
+  return packed_bytes(N, L, d, 8) + (N2 > 0 ? packed_bytes(N2, L2, d, 8) : 0) + 128;   // + ticket counter of the persistent kernel
 }
 int gpsig_pde_f64(const double* X, int N, int L, const double* Y, int N2, int L2, int d, const double* ls,
                   int order, int pair_mode, int rb, int re, double sigma, double* out, void* ws, size_t wsb, void* stream) {

@@ -351,17 +351,38 @@ __global__ void __launch_bounds__(kPdeMaxStrips * 32) pde_pipe_kernel(const PdeP
 }
 
 // ---------------------------------------------------------------------------
-// Block-row variant of the pipelined kernel: a lane advances min(2^ORDER, 4) FINE ROWS per step
-// instead of one.  With the lanes skewed by whole coarse rows (ORDER <= 2) every lane enters a new
-// coarse row at every step, so the increment dot product and the stencil coefficients (pyx:41-48) are
-// computed straight into A/B at a warp-uniform point (no double buffer, no per-lane select), and the
-// fixed cost of a step (shuffles, ring hand-off, progress counters, loop control: ~70 instructions)
-// is spread over 4x the cells: ~4.7 issued instructions per cell instead of ~12, 3.5 of them FP64.
-// The 4 x 8 block of a step is itself a small wavefront (the compiler interleaves the four row chains).
-// Ring, counters and shared-memory layout are those of pde_pipe_kernel, counted in block rows.
+// Block-row, persistent variant of the pipelined kernel (the one the library launches).
+//
+// (1) A lane advances min(2^ORDER, 4) FINE ROWS per step instead of one.  With the lanes skewed by
+//     whole coarse rows (ORDER <= 2) every lane enters a new coarse row at every step, so the increment
+//     dot product and the stencil coefficients (pyx:41-48) are computed straight into A/B at a
+//     warp-uniform point (no double buffer, no per-lane select), and the fixed cost of a step
+//     (shuffles, ring hand-off, progress counters, loop control) is spread over 4x the cells:
+//     ~4.7 issued instructions per cell instead of ~12, 3.5 of them FP64.
+// (2) A CTA is PERSISTENT: it takes pair after pair from a global ticket counter, and warp w (strip w)
+//     moves on to the next pair as soon as its own strip is done.  The fill/drain bubble of the strip
+//     pipeline (warp w trails warp w-1 by ~36 steps: 32 % of a pair's warp-steps at c3) is paid once per
+//     CTA instead of once per pair.  dx is double buffered in shared memory (filled by warp 0), the ring
+//     and the progress counters run on cumulative block-row numbers, a 4-entry queue hands the ticket
+//     from warp 0 to the other warps.
+// Ring, counters and shared-memory layout otherwise as in pde_pipe_kernel.
 // ---------------------------------------------------------------------------
+// register cap: 80 = 3 CTAs of 8 strips per SM for the shapes with few coarse columns per lane; the
+// low dyadic orders keep 8 / 4 coefficient pairs and dy vectors per lane and need more
+__host__ __device__ constexpr int pde_block_maxreg(int DP, int ORDER) {
+  return ORDER <= 1 ? 128 : (ORDER == 2 ? (DP >= 16 ? 128 : (DP >= 8 ? 96 : 80)) : (DP >= 16 ? 96 : 80));
+}
+#ifndef GPSIG_PDE_SLEEP
+#define GPSIG_PDE_SLEEP 256
+#endif
+inline size_t pde_block_smem_bytes(int L, int L2, int DP, int order, int nstrips, bool persist) {
+  return ((size_t)(persist ? 2 : 1) * (L - 1) * (DP + 2) + pde_dy_smem_elems(L2, DP, order) + (size_t)nstrips * kPdeRing) * sizeof(double) +
+         (2 * kPdeMaxStrips + 8) * sizeof(int);
+}
+
 template <int DP, int ORDER>
-__global__ void __launch_bounds__(kPdeMaxStrips * 32) pde_block_kernel(const PdeParams Pm) {
+__global__ void __maxnreg__(pde_block_maxreg(DP, ORDER)) pde_block_kernel(const PdeParams Pm, const int persist,
+                                                                                      unsigned* __restrict__ ticket) {
   constexpr int W = kPdeW;
   constexpr int NC = (W >> ORDER) > 0 ? (W >> ORDER) : 1;   // coarse columns per lane
   constexpr int RS = (1 << ORDER) < 4 ? (1 << ORDER) : 4;   // fine rows per step
@@ -373,181 +394,238 @@ __global__ void __launch_bounds__(kPdeMaxStrips * 32) pde_block_kernel(const Pde
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, NS = blockDim.x >> 5;
   const int L = Pm.L, L2 = Pm.L2;
   const int P = (L - 1) << ORDER, Q = (L2 - 1) << ORDER;
-  const int PB = P / RS;                                    // block rows
+  const int PB = P / RS;                                    // block rows per pair
   constexpr int XS = DP + 2;                                // padded dx row stride (doubles)
   constexpr bool DYREG = NC * DP <= 32;
-  double* dx = reinterpret_cast<double*>(pde_smem);
-  double* dy = dx + (size_t)(L - 1) * XS;
+  const size_t dxsz = (size_t)(L - 1) * XS;
+  double* dx = reinterpret_cast<double*>(pde_smem);         // [persist ? 2 : 1][L-1][XS]
+  double* dy = dx + (persist ? 2 : 1) * dxsz;
   double* ring = dy + pde_dy_smem_elems(L2, DP, ORDER);
-  int* prod = reinterpret_cast<int*>(ring + (size_t)NS * RB);
-  int* cons = prod + kPdeMaxStrips;
+  int* prod = reinterpret_cast<int*>(ring + (size_t)NS * RB);   // cumulative block rows of boundary w published by warp w-1
+  int* cons = prod + kPdeMaxStrips;                               // ... consumed by warp w
+  int* pairq = cons + kPdeMaxStrips;                              // [4] ticket queue (pair index or -1)
+  int* npub = pairq + 4;                                          // tickets published by warp 0
+  int* fin = npub + 1;                                            // pairs finished by the last warp
 
-  int ix, iy;
-  if (Pm.pair_mode == GPSIG_PDE_DIAG) { ix = Pm.row_begin + blockIdx.x; iy = ix; }
-  else { ix = Pm.row_begin + blockIdx.x / Pm.N2; iy = blockIdx.x % Pm.N2; }
-  const double* x = static_cast<const double*>(Pm.xp) + (size_t)ix * Pm.xblk;
-  const double* y = static_cast<const double*>(Pm.yp) + (size_t)iy * Pm.yblk;
-
-  const double fscale = 1.0 / (double)(1 << (2 * ORDER));
-  for (int e = threadIdx.x; e < (L - 1) * DP; e += blockDim.x) {
-    const int I = e / DP, k = e - I * DP;
-    dx[I * XS + k] = (x[e + DP] - x[e]) * fscale;
-  }
-  if (!DYREG)
-    for (int e = threadIdx.x; e < (L2 - 1) * DP; e += blockDim.x) dy[e + 2 * ((e / DP) / NC)] = y[e + DP] - y[e];
   if (threadIdx.x < kPdeMaxStrips) { prod[threadIdx.x] = 0; cons[threadIdx.x] = 0; }
+  if (threadIdx.x == 0) { *npub = 0; *fin = 0; }
   __syncthreads();                                          // the only block-wide barrier
 
+  const size_t npairs = Pm.pair_mode == GPSIG_PDE_DIAG ? (size_t)(Pm.row_end - Pm.row_begin) : (size_t)(Pm.row_end - Pm.row_begin) * Pm.N2;
   const int j0 = w * 32 * W + lane * W;
-  double2 dyreg[DYREG ? NC : 1][DYREG ? DP / 2 : 1];
-  if (DYREG) {
-#pragma unroll
-    for (int cc = 0; cc < NC; ++cc) {
-      const int J = min((j0 >> ORDER) + cc, L2 - 2);
-#pragma unroll
-      for (int k = 0; k < DP / 2; ++k)
-        dyreg[DYREG ? cc : 0][DYREG ? k : 0] = make_double2(y[(J + 1) * DP + 2 * k] - y[J * DP + 2 * k],
-                                                              y[(J + 1) * DP + 2 * k + 1] - y[J * DP + 2 * k + 1]);
-    }
-  }
   const int ncell = max(0, min(W, Q - j0));
   const int LL = min(31, (Q - w * 32 * W - 1) / W);         // last lane with cells in this strip
   const bool has_left = w > 0, has_right = w + 1 < NS;
   const uint32_t ring_in_s = opaque_u32(smem_u32(ring + (size_t)w * RB));
   const uint32_t ring_out_s = opaque_u32(smem_u32(ring + (size_t)(w + 1) * RB));
-  const uint32_t dx_s = opaque_u32(smem_u32(dx));
   const uint32_t prod_in_s = opaque_u32(smem_u32(&prod[w]));
   const uint32_t cons_out_s = opaque_u32(smem_u32(&cons[w + 1 < kPdeMaxStrips ? w + 1 : w]));
+  const uint32_t npub_s = opaque_u32(smem_u32(npub)), fin_s = opaque_u32(smem_u32(fin));
   const bool lane0 = lane == 0, lane_last = lane == 31;
-
-  double up[W];
-#pragma unroll
-  for (int c = 0; c < W; ++c) up[c] = 1.0;                  // K[0, .] = 1 (pyx:29-31)
-  double A[NC], B[NC], An[NC], Bn[NC];
-#pragma unroll
-  for (int cc = 0; cc < NC; ++cc) { A[cc] = B[cc] = An[cc] = Bn[cc] = 1.0; }
-  double send[RS];
-#pragma unroll
-  for (int r = 0; r < RS; ++r) send[r] = 1.0;
-  double dgl = 1.0;                                         // K[i, j0]
+  const double fscale = 1.0 / (double)(1 << (2 * ORDER));
   const int nsteps = PB + LL;
-  int b = -lane;                                            // block row of this lane at step s
-  for (int s = 0; s < nsteps; ++s, ++b) {
-    if ((s & (G - 1)) == 0) {
-      // ---- hand-off window: block rows [s, s+G) ------------------------------------
-      if (has_left) {
-        const int need = min(s + G, PB);
-        while (ld_volatile_shared_u(prod_in_s) < need) __nanosleep(32);
-      }
-      if (has_right) {
-        const int top = min(s + G - LL, PB);
-        while (top > ld_volatile_shared_u(cons_out_s) + RBb) __nanosleep(32);
-      }
+
+  for (int n = 0;; ++n) {                                    // n-th pair of this CTA
+    const int base = n * PB;                                // cumulative block rows before this pair
+    // ---- ticket -------------------------------------------------------------------------------
+    if (w == 0) {
+      // dx buffer n&1 and queue slot n&3 are free once the last warp has finished pair n-2
+      while (ld_volatile_shared_u(fin_s) < n - 1) __nanosleep(GPSIG_PDE_SLEEP);
       __threadfence_block();
+      long long t = 0;
+      if (lane0) t = persist ? (long long)atomicAdd(ticket, 1u) : (n == 0 ? (long long)blockIdx.x : (long long)npairs);
+      t = __shfl_sync(0xffffffffu, t, 0);
+      const int pid = t < (long long)npairs ? (int)t : -1;
+      if (pid >= 0 && (!DYREG || true)) {
+        int ixn;
+        if (Pm.pair_mode == GPSIG_PDE_DIAG) ixn = Pm.row_begin + pid; else ixn = Pm.row_begin + pid / Pm.N2;
+        const double* xn = static_cast<const double*>(Pm.xp) + (size_t)ixn * Pm.xblk;
+        double* dxb = dx + (persist ? (size_t)(n & 1) * dxsz : 0);
+        for (int e = lane; e < (L - 1) * DP; e += 32) {
+          const int I = e / DP, k = e - I * DP;
+          dxb[I * XS + k] = (xn[e + DP] - xn[e]) * fscale;
+        }
+        if (!DYREG) {
+          const int iyn = Pm.pair_mode == GPSIG_PDE_DIAG ? ixn : pid % Pm.N2;
+          const double* yn = static_cast<const double*>(Pm.yp) + (size_t)iyn * Pm.yblk;
+          for (int e = lane; e < (L2 - 1) * DP; e += 32) dy[e + 2 * ((e / DP) / NC)] = yn[e + DP] - yn[e];
+        }
+      }
+      __syncwarp();
+      if (lane0) {
+        pairq[n & 3] = pid;
+        __threadfence_block();
+        st_volatile_shared(npub, n + 1);
+      }
+      __syncwarp();
     }
-    if ((CST == 1 || (s & (CST - 1)) == 0) && ncell > 0) {
-      // coefficients of the coarse row this lane enters within the next CST steps (pyx:41-48)
-      const int In = min(max(b + CST - 1, 0) / CST, L - 2);
-      const uint32_t dxa = dx_s + (uint32_t)In * (uint32_t)(XS * 8);
-      double2 xv[DP / 2];
-#pragma unroll
-      for (int k = 0; k < DP / 2; ++k)
-        asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(xv[k].x), "=d"(xv[k].y) : "r"(dxa + 16u * k));
+    while (ld_volatile_shared_u(npub_s) <= n) __nanosleep(GPSIG_PDE_SLEEP);
+    __threadfence_block();
+    const int pid = ld_volatile_shared(&pairq[n & 3]);
+    if (pid < 0) break;
+    int ix, iy;
+    if (Pm.pair_mode == GPSIG_PDE_DIAG) { ix = Pm.row_begin + pid; iy = ix; }
+    else { ix = Pm.row_begin + pid / Pm.N2; iy = pid % Pm.N2; }
+    const double* y = static_cast<const double*>(Pm.yp) + (size_t)iy * Pm.yblk;
+    const uint32_t dx_s = smem_u32(dx + (persist ? (size_t)(n & 1) * dxsz : 0));
+
+    double2 dyreg[DYREG ? NC : 1][DYREG ? DP / 2 : 1];
+    if (DYREG) {
 #pragma unroll
       for (int cc = 0; cc < NC; ++cc) {
-        double e = 0.0;
-        if (DYREG) {
+        const int J = min((j0 >> ORDER) + cc, L2 - 2);
 #pragma unroll
-          for (int k = 0; k < DP / 2; ++k) {
-            e = fma(xv[k].x, dyreg[DYREG ? cc : 0][DYREG ? k : 0].x, e);
-            e = fma(xv[k].y, dyreg[DYREG ? cc : 0][DYREG ? k : 0].y, e);
-          }
-        } else {
-          const int J = min((j0 >> ORDER) + cc, L2 - 2);
-          const double2* dyj = reinterpret_cast<const double2*>(dy + (size_t)J * DP + 2 * (J / NC));
-#pragma unroll
-          for (int k = 0; k < DP / 2; ++k) { const double2 yv = dyj[k]; e = fma(xv[k].x, yv.x, e); e = fma(xv[k].y, yv.y, e); }
-        }
-        const double e2 = e * e;
-        An[cc] = 1. + 0.5 * e + (1. / 12) * e2;             // pyx:48
-        Bn[cc] = 1. - (1. / 12) * e2;
+        for (int k = 0; k < DP / 2; ++k)
+          dyreg[DYREG ? cc : 0][DYREG ? k : 0] = make_double2(y[(J + 1) * DP + 2 * k] - y[J * DP + 2 * k],
+                                                                y[(J + 1) * DP + 2 * k + 1] - y[J * DP + 2 * k + 1]);
       }
     }
-    // K[i+1, j0] of this block row's RS fine rows, from the lane to the left (computed one step ago)
-    double recv[RS];
+    double up[W];
 #pragma unroll
-    for (int r = 0; r < RS; ++r) recv[r] = __shfl_up_sync(0xffffffffu, send[r], 1);
-    const bool rowok = (b >= 0) && (b < PB) && (ncell > 0);
-    const uint32_t slot = (uint32_t)((b * RS) & (RB - 1)) * 8u;
-    if (lane0) {
+    for (int c = 0; c < W; ++c) up[c] = 1.0;                // K[0, .] = 1 (pyx:29-31)
+    double A[NC], B[NC], An[NC], Bn[NC];
 #pragma unroll
-      for (int r = 0; r < RS; ++r) recv[r] = 1.0;           // K[., 0] = 1 (pyx:29-31)
-      if (has_left && rowok) {
-        if (RS == 4) {
-          asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(recv[0]), "=d"(recv[RS > 1 ? 1 : 0]) : "r"(ring_in_s + slot) : "memory");
-          asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(recv[RS > 2 ? 2 : 0]), "=d"(recv[RS > 3 ? 3 : 0]) : "r"(ring_in_s + slot + 16u) : "memory");
-        } else if (RS == 2) {
-          asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(recv[0]), "=d"(recv[RS > 1 ? 1 : 0]) : "r"(ring_in_s + slot) : "memory");
-        } else {
-          asm volatile("ld.shared.f64 %0, [%1];" : "=d"(recv[0]) : "r"(ring_in_s + slot) : "memory");
+    for (int cc = 0; cc < NC; ++cc) { A[cc] = B[cc] = An[cc] = Bn[cc] = 1.0; }
+    double send[RS];
+#pragma unroll
+    for (int r = 0; r < RS; ++r) send[r] = 1.0;
+    double dgl = 1.0;                                       // K[i, j0]
+    int b = -lane;                                          // block row of this lane at step s
+    for (int s = 0; s < nsteps; ++s, ++b) {
+      if ((s & (G - 1)) == 0) {
+        // ---- hand-off window: block rows [s, s+G) of this pair ----------------------------
+        if (has_left) {
+          const int need = base + min(s + G, PB);
+          while (ld_volatile_shared_u(prod_in_s) - need < 0) __nanosleep(GPSIG_PDE_SLEEP);
         }
-      }
-    }
-    if (rowok) {
-      if (CST == 1 || (b & (CST - 1)) == 0) {               // entering a new coarse row
-#pragma unroll
-        for (int cc = 0; cc < NC; ++cc) { A[cc] = An[cc]; B[cc] = Bn[cc]; }
-      }
-      // (k01 + k10) * A - k00 * B per cell: wv needs only the previous row, one FMA per cell is on the
-      // left-to-right chain.  All W cells are computed, also those past column Q of the last lane.
-#pragma unroll
-      for (int r = 0; r < RS; ++r) {
-        double wv[W];
-#pragma unroll
-        for (int c = 0; c < W; ++c) {
-          const int cc = (ORDER >= 3) ? 0 : (c >> ORDER);
-          wv[c] = fma(up[c], A[cc], -((c == 0 ? dgl : up[c > 0 ? c - 1 : 0]) * B[cc]));
+        if (has_right) {
+          const int top = base + min(s + G - LL, PB);
+          while (top - ld_volatile_shared_u(cons_out_s) > RBb) __nanosleep(GPSIG_PDE_SLEEP);
         }
-        dgl = recv[r];
-        double lf = recv[r];
-#pragma unroll
-        for (int c = 0; c < W; ++c) {
-          const int cc = (ORDER >= 3) ? 0 : (c >> ORDER);
-          lf = fma(lf, A[cc], wv[c]);
-          up[c] = lf;
-        }
-        send[r] = lf;
-      }
-      if (lane_last && has_right) {
-        if (RS == 4) {
-          asm volatile("st.shared.v2.f64 [%0], {%1,%2};" ::"r"(ring_out_s + slot), "d"(send[0]), "d"(send[RS > 1 ? 1 : 0]) : "memory");
-          asm volatile("st.shared.v2.f64 [%0], {%1,%2};" ::"r"(ring_out_s + slot + 16u), "d"(send[RS > 2 ? 2 : 0]), "d"(send[RS > 3 ? 3 : 0]) : "memory");
-        } else if (RS == 2) {
-          asm volatile("st.shared.v2.f64 [%0], {%1,%2};" ::"r"(ring_out_s + slot), "d"(send[0]), "d"(send[RS > 1 ? 1 : 0]) : "memory");
-        } else {
-          asm volatile("st.shared.f64 [%0], %1;" ::"r"(ring_out_s + slot), "d"(send[0]) : "memory");
-        }
-      }
-    }
-    if (((s + 1) & (G - 1)) == 0 || s + 1 == nsteps) {
-      // ---- publish progress (block rows) ----------------------------------------------
-      __syncwarp();
-      if (has_right && lane == LL) {
         __threadfence_block();
-        st_volatile_shared(&prod[w + 1], max(0, min(s - LL + 1, PB)));
       }
-      if (has_left && lane0) st_volatile_shared(&cons[w], min(s + 1, PB));
-    }
-  }
-  if (w == NS - 1) {
-    double result = up[0];
+      if ((CST == 1 || (s & (CST - 1)) == 0) && ncell > 0) {
+        // coefficients of the coarse row this lane enters within the next CST steps (pyx:41-48)
+        const int In = min(max(b + CST - 1, 0) / CST, L - 2);
+        const uint32_t dxa = dx_s + (uint32_t)In * (uint32_t)(XS * 8);
+        double2 xv[DP / 2];
 #pragma unroll
-    for (int c = 1; c < W; ++c) if (c == ncell - 1) result = up[c];
-    result = __shfl_sync(0xffffffffu, result, LL);
-    if (lane0) {
-      const size_t o = Pm.pair_mode == GPSIG_PDE_DIAG ? (size_t)blockIdx.x
-                                                      : (size_t)(ix - Pm.row_begin) * Pm.N2 + iy;
-      Pm.out[o] = Pm.sigma * result;
+        for (int k = 0; k < DP / 2; ++k)
+          asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(xv[k].x), "=d"(xv[k].y) : "r"(dxa + 16u * k));
+#pragma unroll
+        for (int cc = 0; cc < NC; ++cc) {
+          double e = 0.0;
+          if (DYREG) {
+#pragma unroll
+            for (int k = 0; k < DP / 2; ++k) {
+              e = fma(xv[k].x, dyreg[DYREG ? cc : 0][DYREG ? k : 0].x, e);
+              e = fma(xv[k].y, dyreg[DYREG ? cc : 0][DYREG ? k : 0].y, e);
+            }
+          } else {
+            const int J = min((j0 >> ORDER) + cc, L2 - 2);
+            const double2* dyj = reinterpret_cast<const double2*>(dy + (size_t)J * DP + 2 * (J / NC));
+#pragma unroll
+            for (int k = 0; k < DP / 2; ++k) { const double2 yv = dyj[k]; e = fma(xv[k].x, yv.x, e); e = fma(xv[k].y, yv.y, e); }
+          }
+          const double e2 = e * e;
+          An[cc] = 1. + 0.5 * e + (1. / 12) * e2;           // pyx:48
+          Bn[cc] = 1. - (1. / 12) * e2;
+        }
+      }
+      // K[i+1, j0] of this block row's RS fine rows, from the lane to the left (computed one step ago)
+      double recv[RS];
+#pragma unroll
+      for (int r = 0; r < RS; ++r) recv[r] = __shfl_up_sync(0xffffffffu, send[r], 1);
+      const bool rowok = (b >= 0) && (b < PB) && (ncell > 0);
+      const uint32_t slot = (uint32_t)(((base + b) * RS) & (RB - 1)) * 8u;
+      if (lane0) {
+#pragma unroll
+        for (int r = 0; r < RS; ++r) recv[r] = 1.0;         // K[., 0] = 1 (pyx:29-31)
+        if (has_left && rowok) {
+          if (RS == 4) {
+            asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(recv[0]), "=d"(recv[RS > 1 ? 1 : 0]) : "r"(ring_in_s + slot) : "memory");
+            asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(recv[RS > 2 ? 2 : 0]), "=d"(recv[RS > 3 ? 3 : 0]) : "r"(ring_in_s + slot + 16u) : "memory");
+          } else if (RS == 2) {
+            asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(recv[0]), "=d"(recv[RS > 1 ? 1 : 0]) : "r"(ring_in_s + slot) : "memory");
+          } else {
+            asm volatile("ld.shared.f64 %0, [%1];" : "=d"(recv[0]) : "r"(ring_in_s + slot) : "memory");
+          }
+        }
+      }
+      if (rowok) {
+        if (CST == 1 || (b & (CST - 1)) == 0) {             // entering a new coarse row
+#pragma unroll
+          for (int cc = 0; cc < NC; ++cc) { A[cc] = An[cc]; B[cc] = Bn[cc]; }
+        }
+        // (k01 + k10) * A - k00 * B per cell (pyx:48).  The RS x W block of this step is swept by
+        // ANTI-DIAGONALS, written out in that order: the up-to-RS cells of a diagonal are independent, each
+        // is DMUL -> DFMA (previous row only) -> DFMA (left neighbour, the chain), and a value is needed
+        // one diagonal (~12 FP64 instructions) after it was produced: no issue stalls on the 8.5-cycle
+        // DFMA latency.  (Row-by-row order left the warp waiting on every chain FMA.)  All W cells are
+        // computed, also those past column Q of the last lane.
+        double Kv[RS + 1][W + 1];                           // Kv[r+1][c+1] = cell (r, c); row 0 / column 0 = boundary
+        Kv[0][0] = dgl;
+#pragma unroll
+        for (int c = 0; c < W; ++c) Kv[0][c + 1] = up[c];
+#pragma unroll
+        for (int r = 0; r < RS; ++r) Kv[r + 1][0] = recv[r];
+#pragma unroll
+        for (int d = 0; d < RS + W - 1; ++d) {
+          double t0[RS], t1[RS];
+#pragma unroll
+          for (int r = 0; r < RS; ++r) {
+            const int c = d - r;
+            if (c >= 0 && c < W) t0[r] = Kv[r][c] * B[(ORDER >= 3) ? 0 : (c >> ORDER)];
+          }
+#pragma unroll
+          for (int r = 0; r < RS; ++r) {
+            const int c = d - r;
+            if (c >= 0 && c < W) t1[r] = fma(Kv[r][c + 1], A[(ORDER >= 3) ? 0 : (c >> ORDER)], -t0[r]);
+          }
+#pragma unroll
+          for (int r = 0; r < RS; ++r) {
+            const int c = d - r;
+            if (c >= 0 && c < W) Kv[r + 1][c + 1] = fma(Kv[r + 1][c], A[(ORDER >= 3) ? 0 : (c >> ORDER)], t1[r]);
+          }
+        }
+        dgl = recv[RS - 1];
+#pragma unroll
+        for (int c = 0; c < W; ++c) up[c] = Kv[RS][c + 1];
+#pragma unroll
+        for (int r = 0; r < RS; ++r) send[r] = Kv[r + 1][W];
+        if (lane_last && has_right) {
+          if (RS == 4) {
+            asm volatile("st.shared.v2.f64 [%0], {%1,%2};" ::"r"(ring_out_s + slot), "d"(send[0]), "d"(send[RS > 1 ? 1 : 0]) : "memory");
+            asm volatile("st.shared.v2.f64 [%0], {%1,%2};" ::"r"(ring_out_s + slot + 16u), "d"(send[RS > 2 ? 2 : 0]), "d"(send[RS > 3 ? 3 : 0]) : "memory");
+          } else if (RS == 2) {
+            asm volatile("st.shared.v2.f64 [%0], {%1,%2};" ::"r"(ring_out_s + slot), "d"(send[0]), "d"(send[RS > 1 ? 1 : 0]) : "memory");
+          } else {
+            asm volatile("st.shared.f64 [%0], %1;" ::"r"(ring_out_s + slot), "d"(send[0]) : "memory");
+          }
+        }
+      }
+      if (((s + 1) & (G - 1)) == 0 || s + 1 == nsteps) {
+        // ---- publish progress (cumulative block rows) -------------------------------------
+        __syncwarp();
+        if (has_right && lane == LL) {
+          __threadfence_block();
+          st_volatile_shared(&prod[w + 1], base + max(0, min(s - LL + 1, PB)));
+        }
+        if (has_left && lane0) st_volatile_shared(&cons[w], base + min(s + 1, PB));
+      }
+    }
+    if (w == NS - 1) {
+      double result = up[0];
+#pragma unroll
+      for (int c = 1; c < W; ++c) if (c == ncell - 1) result = up[c];
+      result = __shfl_sync(0xffffffffu, result, LL);
+      if (lane0) {
+        const size_t o = Pm.pair_mode == GPSIG_PDE_DIAG ? (size_t)pid : (size_t)(ix - Pm.row_begin) * Pm.N2 + iy;
+        Pm.out[o] = Pm.sigma * result;
+        __threadfence_block();
+        st_volatile_shared(fin, n + 1);
+      }
+      __syncwarp();
     }
   }
 }
