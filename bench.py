@@ -151,6 +151,12 @@ def measured_peaks():
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}, "fallback"
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the headline kernel at the bench shape (c2), from the
+# committed ncu --set full captures (algorithmic bytes: 83.2 MB f64 / 41.6 MB f32 per launch)
+NCU_TRAFFIC_BYTES = {"f64": 76.51e6 + 21.26e6, "f32": 41.83e6 + 0.67e6}
+NCU_TRAFFIC_SOURCE = "profiles/r01e_ncu_trunc_skew_f64.txt, profiles/r01f_ncu_trunc_skew_f32.txt (ncu --set full, N=N2=2000; the 16-32 MB output still sits in L2 when the kernel ends)"
+
+
 def fma_peak_tflops(torch, lib, esz):
     """CUDA-core FMA peak measured with the library's FMA-chain microbenchmark."""
     from gpsig_b200._lib import check, stream_handle
@@ -190,7 +196,7 @@ def other_configs(torch, ops, lib):
     ms = timed(lambda: ops.pde(X, None, dyadic_order=order))
     P = (L - 1) << order
     cells = float(N) * P * P
-    out["c3_pde"] = {"workload": "kernels_pde Kdiag, N=1000, L=500, d=4, dyadic order 2 (P=1996)", "kernel": "pde_pipe_kernel",
+    out["c3_pde"] = {"workload": "kernels_pde Kdiag, N=1000, L=500, d=4, dyadic order 2 (P=1996)", "kernel": "pde_block_kernel",
                      "kernel_ms": ms, "pairs_per_s": N / (ms * 1e-3), "cells_per_s": cells / (ms * 1e-3),
                      "fp64_instr_per_cell": 3, "dtype": "f64"}
     # c4: inducing tensors vs sequences, N=10k, L=100, d=8, m=4, Mz=500 (increments)
@@ -288,10 +294,11 @@ def run_ours(args):
         Bp = bytes_per_pair(N, N2, L, L, d, esz)
         nominal = 37.2 if esz == 8 else 74.4
         roof = {"bound": "cuda-core-" + args.dtype, "achieved": achieved, "peak": fpeak, "unit": "TFLOP/s",
-                "frac": (achieved / fpeak) if (achieved and fpeak) else None, "traffic": None,
+                "frac": (achieved / fpeak) if (achieved and fpeak) else None,
+                "traffic": NCU_TRAFFIC_BYTES.get(args.dtype), "traffic_source": NCU_TRAFFIC_SOURCE,
                 "peak_source": "FMA-chain microbenchmark in this run (gpsig_fma_peak); nominal %.1f TFLOP/s at 1965 MHz" % nominal,
                 "frac_of_nominal": achieved / nominal if achieved else None,
-                "kernel": "trunc_gram_kernel", "kernel_ms": kern_ms, "kernel_share_of_step": kern_ms * args.steps / tot_ms if kern_ms else None,
+                "kernel": "trunc_skew_kernel", "kernel_ms": kern_ms, "kernel_share_of_step": kern_ms * args.steps / tot_ms if kern_ms else None,
                 "flops_per_pair": F, "pairs_per_launch": N * N2,
                 "hbm": {"algorithmic_bytes_per_pair": Bp, "achieved_gbs": N * N2 * Bp / (kern_ms * 1e-3) / 1e9 if kern_ms else None,
                         "peak_gbs": peaks.get("hbm_gbs"), "peak_source": how}}

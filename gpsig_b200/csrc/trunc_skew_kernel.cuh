@@ -51,6 +51,12 @@ __host__ __device__ inline int skew_row_stride(int d, int elem) {
 #define GPSIG_SKEW_TMEM 1
 #endif
 // float64 RBF: packed coordinates pre-scaled by sqrt(log2 e) (abi.cu) and exp2_tab32 below
+#ifndef GPSIG_SKEW_TMEM_F32
+#define GPSIG_SKEW_TMEM_F32 0     // float32 tile in tensor memory as well (measured: no gain over registers at 12 warps, 20.4 vs 20.2 M pairs/s)
+#endif
+#ifndef GPSIG_SKEW_GS_F32
+#define GPSIG_SKEW_GS_F32 2
+#endif
 #ifndef GPSIG_TMEM_TIE
 #define GPSIG_TMEM_TIE 1
 #endif
@@ -81,6 +87,10 @@ __device__ __forceinline__ void tmem_st4(uint32_t addr, double a, double b, doub
                ::"r"(addr), "r"(__double2loint(a)), "r"(__double2hiint(a)), "r"(__double2loint(b)), "r"(__double2hiint(b)),
                  "r"(__double2loint(c)), "r"(__double2hiint(c)), "r"(__double2loint(d)), "r"(__double2hiint(d)) : "memory");
 }
+__device__ __forceinline__ void tmem_st8w(uint32_t addr, const uint32_t (&w)[8]) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+               ::"r"(addr), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7]) : "memory");
+}
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 struct TmemQuad { uint32_t w[8]; };
 __device__ __forceinline__ void tmem_ld4(TmemQuad& r, uint32_t addr) {
@@ -102,6 +112,14 @@ __device__ __forceinline__ double shfl_up1_pinned(double v) {
   return __hiloint2double(hi, lo);
 }
 __device__ __forceinline__ double tmem_quad_get(const TmemQuad& r, int e) { return __hiloint2double((int)r.w[2 * e + 1], (int)r.w[2 * e]); }
+template <typename T> __device__ __forceinline__ T tmem_get(const TmemQuad& r, int e);
+template <> __device__ __forceinline__ double tmem_get<double>(const TmemQuad& r, int e) { return tmem_quad_get(r, e); }
+template <> __device__ __forceinline__ float tmem_get<float>(const TmemQuad& r, int e) { return __uint_as_float(r.w[e]); }
+__device__ __forceinline__ float shfl_up1_pinned(float v) {
+  int x = __float_as_int(v);
+  asm volatile("shfl.sync.up.b32 %0, %0, 1, 0, 0xffffffff;" : "+r"(x));
+  return __int_as_float(x);
+}
 __host__ __device__ constexpr int tmem_cols_pow2(int n) { return n <= 32 ? 32 : n <= 64 ? 64 : n <= 128 ? 128 : n <= 256 ? 256 : 512; }
 
 // ---- exp for the RBF base kernel --------------------------------------------
@@ -174,8 +192,8 @@ template <> struct SkewFinish<double, OP_RBF> {
 };
 
 // rows per step (R) and warps per CTA (NW); tunables, overridable at build time for experiments.
-// Measured at c2 (tools/time_trunc.py): float32 R=1 14.1 M pairs/s, R=2 17.8 M; float64 R=1 6.6 M, R=2 7.1 M;
-// more warps per CTA (12) costs registers: float32 16.9 M at R=1, float64 spills (5.5 M).
+// Measured at c2 (tools/time_trunc.py): float32 R=2: 8 warps 17.5 M pairs/s, 12 warps 20.2 M (168 registers), 14: 14.4 M,
+// 16: 16.9 M; float64 (tile in tensor memory) R=2 x 8 warps 9.03 M, R=1 x 12 warps 8.87 M.
 #ifndef GPSIG_SKEW_R_F64
 #define GPSIG_SKEW_R_F64 2
 #endif
@@ -186,15 +204,20 @@ template <> struct SkewFinish<double, OP_RBF> {
 #define GPSIG_SKEW_R_F32 2
 #endif
 #ifndef GPSIG_SKEW_NW_F32
-#define GPSIG_SKEW_NW_F32 8
+#define GPSIG_SKEW_NW_F32 12
 #endif
 template <typename T> struct SkewCfg;
 template <> struct SkewCfg<double> { static constexpr int R = GPSIG_SKEW_R_F64; static constexpr int NW = GPSIG_SKEW_NW_F64; };
 template <> struct SkewCfg<float> { static constexpr int R = GPSIG_SKEW_R_F32; static constexpr int NW = GPSIG_SKEW_NW_F32; };
+// warps per CTA of one instantiation: float32 shapes whose y tile sits in shared memory keep 8 (12 tiles do not fit)
+template <typename T, int DP, int COLS> struct SkewNW {
+  static constexpr int value = (sizeof(T) == 4 && !YPolicy<T, DP, COLS>::kInRegs) ? 8 : SkewCfg<T>::NW;
+};
 // y tile in tensor memory: float64 shapes whose tile does not fit in registers (and whose warps' tiles fit the 512 columns)
 template <typename T, int DP, int COLS> struct SkewYTmem {
-  static constexpr bool value = GPSIG_SKEW_TMEM && sizeof(T) == 8 && !YPolicy<T, DP, COLS>::kInRegs &&
-                                SkewCfg<T>::NW % 4 == 0 && (SkewCfg<T>::NW / 4) * COLS * DP * 2 <= 512;
+  static constexpr bool value = GPSIG_SKEW_TMEM && (sizeof(T) == 8 ? !YPolicy<T, DP, COLS>::kInRegs : (GPSIG_SKEW_TMEM_F32 != 0)) &&
+                                DP * sizeof(T) >= 32 && SkewNW<T, DP, COLS>::value % 4 == 0 &&
+                                (SkewNW<T, DP, COLS>::value / 4) * COLS * DP * (sizeof(T) / 4) <= 512;
 };
 
 // float32 RBF: the packed coordinates are pre-scaled by sqrt(log2 e) (abi.cu), so the exponent
@@ -212,16 +235,17 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 }
 
 template <typename T, int DP, int COLS, int MLEV, int OP>
-__global__ void __launch_bounds__(SkewCfg<T>::NW * 32, 1) trunc_skew_kernel(const TruncParams P, const int RS) {
+__global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew_kernel(const TruncParams P, const int RS) {
   using V16 = typename Vec16<T>::type;
   constexpr int V = Vec16<T>::V;
   constexpr int KV = DP / V;
   constexpr int R = SkewCfg<T>::R;
-  constexpr int NW = SkewCfg<T>::NW;
+  constexpr int NW = SkewNW<T, DP, COLS>::value;
   constexpr bool YREG = YPolicy<T, DP, COLS>::kInRegs;
   constexpr bool YTM = SkewYTmem<T, DP, COLS>::value;      // y tile in tensor memory (float64)
-  constexpr int KC = DP / 4;                                // 4-double chunks per column
-  constexpr int TMW = COLS * DP * 2;                        // TMEM words (columns) per warp
+  constexpr int CE = 32 / sizeof(T);                        // elements per 8-word tensor-memory load (4 doubles / 8 floats)
+  constexpr int KC = DP / CE > 0 ? DP / CE : 1;             // chunks per column
+  constexpr int TMW = COLS * DP * (sizeof(T) / 4);          // TMEM words (columns) per warp
   constexpr int TMCOLS = tmem_cols_pow2((NW / 4) * TMW);
   static_assert(!YTM || (NW % 4 == 0 && (NW / 4) * TMW <= 512), "tensor memory plan does not fit");
   constexpr int NB = kSkewBufs;
@@ -277,9 +301,10 @@ __global__ void __launch_bounds__(SkewCfg<T>::NW * 32, 1) trunc_skew_kernel(cons
     if constexpr (YTM) {
 #pragma unroll
       for (int kc = 0; kc < KC; ++kc) {
-        const double2 a = *reinterpret_cast<const double2*>(yblk + (size_t)q * P.yrs + kc * 4);
-        const double2 b = *reinterpret_cast<const double2*>(yblk + (size_t)q * P.yrs + kc * 4 + 2);
-        tmem_st4(ta + (uint32_t)((kc * COLS + c) * 8), a.x, a.y, b.x, b.y);
+        union { V16 v[2]; uint32_t w[8]; } u;
+        u.v[0] = *reinterpret_cast<const V16*>(yblk + (size_t)q * P.yrs + kc * CE);
+        u.v[1] = *reinterpret_cast<const V16*>(yblk + (size_t)q * P.yrs + kc * CE + V);
+        tmem_st8w(ta + (uint32_t)((kc * COLS + c) * 8), u.w);
       }
     } else {
 #pragma unroll
@@ -296,13 +321,16 @@ __global__ void __launch_bounds__(SkewCfg<T>::NW * 32, 1) trunc_skew_kernel(cons
   if (OP == OP_RBF && sizeof(T) == 8) tab = exp2((double)lane * (1.0 / 32.0));
 
   // ---- state ------------------------------------------------------------------------
-  // column sums C_l[q] of levels 0..MLEV-2; of the top level only the total is ever used: two partial sums
+  // column sums C_l[q] of levels 0..MLEV-2; of the top level only the total is ever used: partial sums
   T C[MLEV - 1][COLS];
 #pragma unroll
   for (int l = 0; l < MLEV - 1; ++l)
 #pragma unroll
     for (int c = 0; c < COLS; ++c) C[l][c] = T(0);
-  T Ct[2] = {T(0), T(0)};
+  constexpr int NT = sizeof(T) == 8 ? 2 : COLS;            // float32: one per column (a 2-deep FFMA chain would stall on latency)
+  T Ct[NT];
+#pragma unroll
+  for (int k = 0; k < NT; ++k) Ct[k] = T(0);
   T Mp[2][COLS];                                   // last base-kernel row, ping-pong over the step parity
 #pragma unroll
   for (int c = 0; c < COLS; ++c) Mp[0][c] = Mp[1][c] = T(0);
@@ -364,7 +392,7 @@ __global__ void __launch_bounds__(SkewCfg<T>::NW * 32, 1) trunc_skew_kernel(cons
     T Mc[R][COLS];
     // tensor-memory variant: the tile arrives in groups of GS columns x 4 dimensions; group g+1 is
     // requested before the FMAs of group g, its wait comes after them (wait::ld covers all loads in flight)
-    constexpr int GS = 4;
+    constexpr int GS = sizeof(T) == 8 ? 4 : GPSIG_SKEW_GS_F32;
     constexpr int NG = (COLS + GS - 1) / GS;          // groups per 4-dimension chunk
     constexpr int NGT = NG * KC;
     constexpr int NCH = R + R * (MLEV - 1) + 1;       // chain values per step
@@ -396,16 +424,16 @@ __global__ void __launch_bounds__(SkewCfg<T>::NW * 32, 1) trunc_skew_kernel(cons
         for (int c = 0; c < COLS; ++c) acc[rr][c] = Op::init(xc[rr], yc[c]);
       }
       if constexpr (YTM) {
-        double2 xa[R], xq[R];
+        V16 xa[R], xq[R];
         static_for<NGT>([&](auto G) {
           constexpr int g = decltype(G)::value;
           constexpr int kc = g / NG, c0 = (g % NG) * GS;
           if constexpr (g % NG == 0) {
 #pragma unroll
             for (int rr = 0; rr < R; ++rr) {
-              const T* xr = xb + (size_t)min(r0 + rr, L - 1) * RS + kc * 4;
-              xa[rr] = *reinterpret_cast<const double2*>(xr);
-              xq[rr] = *reinterpret_cast<const double2*>(xr + 2);
+              const T* xr = xb + (size_t)min(r0 + rr, L - 1) * RS + kc * CE;
+              xa[rr] = *reinterpret_cast<const V16*>(xr);
+              xq[rr] = *reinterpret_cast<const V16*>(xr + V);
             }
           }
           tmem_ld_wait();
@@ -419,14 +447,13 @@ __global__ void __launch_bounds__(SkewCfg<T>::NW * 32, 1) trunc_skew_kernel(cons
 #pragma unroll
           for (int c = c0; c < c0 + GS && c < COLS; ++c) {
             const TmemQuad& cur = yq[g & 1][c - c0];
-            const double y0 = tmem_quad_get(cur, 0), y1 = tmem_quad_get(cur, 1), y2 = tmem_quad_get(cur, 2), y3 = tmem_quad_get(cur, 3);
 #pragma unroll
             for (int rr = 0; rr < R; ++rr) {
               T a = acc[rr][c];
-              a = gfma<T>(T(xa[rr].x), T(y0), a);
-              a = gfma<T>(T(xa[rr].y), T(y1), a);
-              a = gfma<T>(T(xq[rr].x), T(y2), a);
-              a = gfma<T>(T(xq[rr].y), T(y3), a);
+#pragma unroll
+              for (int e = 0; e < V; ++e) a = gfma<T>(vget(xa[rr], e), tmem_get<T>(cur, e), a);
+#pragma unroll
+              for (int e = 0; e < V; ++e) a = gfma<T>(vget(xq[rr], e), tmem_get<T>(cur, V + e), a);
               acc[rr][c] = a;
             }
           }
@@ -502,7 +529,10 @@ __global__ void __launch_bounds__(SkewCfg<T>::NW * 32, 1) trunc_skew_kernel(cons
           if (l < MLEV - 1) {
 #pragma unroll
             for (int c = 0; c < COLS; ++c) e += C[l < MLEV - 1 ? l : 0][c];
-          } else e += Ct[0] + Ct[1];
+          } else {
+#pragma unroll
+            for (int k = 0; k < NT; ++k) e += Ct[k];
+          }
           tot[l] = e;
           send[0][l] = e;
         }
@@ -532,7 +562,8 @@ __global__ void __launch_bounds__(SkewCfg<T>::NW * 32, 1) trunc_skew_kernel(cons
         for (int l = 1; l < MLEV - 1; ++l)
 #pragma unroll
           for (int c = 0; c < COLS; ++c) C[l][c] = T(0);
-        Ct[0] = Ct[1] = T(0);
+#pragma unroll
+        for (int k = 0; k < NT; ++k) Ct[k] = T(0);
 #pragma unroll
         for (int c = 0; c < COLS; ++c) C[0][c] = diff ? T(0) : D[c];
       } else {
@@ -544,7 +575,7 @@ __global__ void __launch_bounds__(SkewCfg<T>::NW * 32, 1) trunc_skew_kernel(cons
           for (int c = 0; c < COLS; ++c) {
             const T t = e;
             e += C[l][c];
-            if (l == MLEV - 2) Ct[c & 1] = gfma<T>(D[c], t, Ct[c & 1]);
+            if (l == MLEV - 2) Ct[c % NT] = gfma<T>(D[c], t, Ct[c % NT]);
             else C[l + 1 < MLEV - 1 ? l + 1 : 0][c] = gfma<T>(D[c], t, C[l + 1 < MLEV - 1 ? l + 1 : 0][c]);
           }
           send[rr][l] = e;
@@ -577,13 +608,14 @@ template <typename T, int DP, int COLS, int MLEV, int OP>
 int launch_skew_inst(TruncParams P, cudaStream_t stream) {
   const int RS = P.xrs;
   const size_t xslot = align_up_dev(P.xblk * sizeof(T));
-  const size_t smem = 128 + kSkewBufs * xslot + (size_t)SkewCfg<T>::NW * skew_ywarp_bytes<T, DP, COLS>();
+  const size_t smem = 128 + kSkewBufs * xslot + (size_t)SkewNW<T, DP, COLS>::value * skew_ywarp_bytes<T, DP, COLS>();
   if (smem > kMaxSmem)
     GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "sequence too long for the on-chip plan: needs %zu bytes of shared memory (L=%d)", smem, P.L);
   auto kern = trunc_skew_kernel<T, DP, COLS, MLEV, OP>;
   GPSIG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid;
-  grid.x = (P.N2 + SkewCfg<T>::NW - 1) / SkewCfg<T>::NW;
+  constexpr int NW = SkewNW<T, DP, COLS>::value;
+  grid.x = (P.N2 + NW - 1) / NW;
   const int rows = P.row_end - P.row_begin;
   // >= ~24 waves of CTAs over the 148 SMs, but >= 16 pairs per warp so the 31-step pipeline fill stays < 1 %
   int want_y = (24 * 148 + (int)grid.x - 1) / (int)grid.x;
@@ -593,7 +625,7 @@ int launch_skew_inst(TruncParams P, cudaStream_t stream) {
   P.ichunk = ichunk;
   grid.y = (rows + ichunk - 1) / ichunk;
   prof_begin(stream);
-  kern<<<grid, SkewCfg<T>::NW * 32, smem, stream>>>(P, RS);
+  kern<<<grid, NW * 32, smem, stream>>>(P, RS);
   prof_end(stream);
   GPSIG_LAUNCH_CHECK("trunc_skew_kernel");
   return GPSIG_OK;
