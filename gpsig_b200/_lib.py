@@ -61,6 +61,20 @@ def _load():
         f = getattr(lib, 'gpsig_tens_tens_' + sfx)
         f.restype = i
         f.argtypes = [ctypes.POINTER(TruncDesc), vp, i, i, i, vp, ctypes.POINTER(Epilogue), vp, vp]
+    lib.gpsig_trunc_vjp_workspace_bytes.restype = sz
+    lib.gpsig_trunc_vjp_workspace_bytes.argtypes = [i] * 6
+    lib.gpsig_tens_vs_seq_vjp_workspace_bytes.restype = sz
+    lib.gpsig_tens_vs_seq_vjp_workspace_bytes.argtypes = [i] * 5
+    for sfx in ('f32', 'f64'):
+        f = getattr(lib, 'gpsig_trunc_vjp_' + sfx)
+        f.restype = i
+        f.argtypes = [ctypes.POINTER(TruncDesc), vp, i, i, vp, i, i, i, i, i, i, vp, vp, vp, vp, sz, vp]
+        f = getattr(lib, 'gpsig_tens_vs_seq_vjp_' + sfx)
+        f.restype = i
+        f.argtypes = [ctypes.POINTER(TruncDesc), vp, i, i, vp, i, i, i, i, i, vp, vp, vp, vp, sz, vp]
+        f = getattr(lib, 'gpsig_tens_tens_vjp_' + sfx)
+        f.restype = i
+        f.argtypes = [ctypes.POINTER(TruncDesc), vp, i, i, i, vp, vp, vp]
     lib.gpsig_launch_count.restype = ctypes.c_ulonglong
     lib.gpsig_profile_enable.argtypes = [i]
     lib.gpsig_profile_enable.restype = None

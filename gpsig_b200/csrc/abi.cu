@@ -4,6 +4,7 @@
 #include <string.h>
 
 #include "pde_kernel.cuh"
+#include "vjp_kernels.cuh"
 #include "tens_kernels.cuh"
 #include "trunc_kernel.cuh"
 #include "trunc_skew_kernel.cuh"
@@ -344,6 +345,113 @@ static int pde_impl(const double* X, int N, int L, const double* Y, int N2, int 
   return GPSIG_OK;
 }
 
+
+// ---- reverse mode (vjp_kernels.cuh) ---------------------------------------------------------------
+extern "C" size_t gpsig_tens_vs_seq_vjp_workspace_bytes(int Mz, int ncols, int L, int m, int elem);
+static size_t trunc_vjp_ws(size_t npairs, int L, int L2, int m, int difference, int elem) {
+  const size_t PR = L - (difference ? 1 : 0), QC = L2 - (difference ? 1 : 0);
+  const size_t mm = m > 1 ? m - 1 : 0;
+  return align_up(npairs * (mm * PR * QC + mm * QC + PR * QC) * elem, 128);
+}
+
+template <typename T>
+static int trunc_vjp_impl(const gpsig_trunc_desc* desc, const T* X, int N, int L, const T* X2, int N2, int L2, int d,
+                          int pair_mode, int row_begin, int row_end, const T* grad_levels, T* gradX, T* gradX2,
+                          void* ws, size_t ws_bytes, void* stream) {
+  if (int rc = check_desc(desc)) return rc;
+  if (desc->order != 1) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "reverse mode is implemented for order == 1 only (got %d)", desc->order);
+  if (desc->num_levels > 8) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "reverse mode supports num_levels <= 8");
+  const bool sym = X2 == nullptr;
+  if (sym) { X2 = X; N2 = N; L2 = L; gradX2 = gradX; }
+  if (!X || !grad_levels || !gradX || !gradX2) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "X/grad_levels/gradX must not be NULL");
+  if (d < 1 || d > 16) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "state dimension d=%d is not supported (1..16)", d);
+  const int minlen = desc->difference ? 2 : 1;
+  if (L < minlen || L2 < minlen) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "sequences too short (L=%d, L2=%d)", L, L2);
+  if (row_begin < 0 || row_end > N || row_begin > row_end) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "bad row range [%d, %d) for N=%d", row_begin, row_end, N);
+  const bool diag = pair_mode == GPSIG_PDE_DIAG;
+  if (diag && (N2 != N || L2 != L)) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "diagonal pairing needs matching X and X2");
+  const size_t npairs = diag ? (size_t)(row_end - row_begin) : (size_t)(row_end - row_begin) * N2;
+  if (npairs == 0) return GPSIG_OK;
+  const size_t need = trunc_vjp_ws(npairs, L, L2, desc->num_levels, desc->difference, sizeof(T));
+  if (!ws || ws_bytes < need || (reinterpret_cast<uintptr_t>(ws) & 15))
+    GPSIG_FAIL(GPSIG_ERR_WORKSPACE, "workspace too small or misaligned: need %zu bytes, got %zu", need, ws_bytes);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  TruncVjpParams P;
+  memset(&P, 0, sizeof(P));
+  P.X = X; P.Y = X2; P.N = N; P.N2 = N2; P.L = L; P.L2 = L2; P.d = d; P.m = desc->num_levels;
+  P.diag = diag; P.row_begin = row_begin; P.row_end = row_end; P.difference = desc->difference;
+  P.p0 = desc->base_params[0]; P.p1 = desc->base_params[1]; P.base = desc->base;
+  P.g = grad_levels; P.gradX = gradX; P.gradY = gradX2; P.npairs = npairs;
+  const size_t PR = L - (desc->difference ? 1 : 0), QC = L2 - (desc->difference ? 1 : 0), mm = desc->num_levels - 1;
+  T* w = static_cast<T*>(ws);
+  P.F = w; w += npairs * mm * PR * QC;
+  P.C = w; w += npairs * mm * QC;
+  P.W = w;
+  const int threads = 128;
+  prof_begin(s);
+  trunc_vjp_tables_kernel<T><<<(unsigned)((npairs + threads - 1) / threads), threads, 0, s>>>(P);
+  prof_end(s);
+  GPSIG_LAUNCH_CHECK("trunc_vjp_tables_kernel");
+  const size_t tot = npairs * (size_t)(L + L2);
+  trunc_vjp_grad_kernel<T><<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(P);
+  GPSIG_LAUNCH_CHECK("trunc_vjp_grad_kernel");
+  return GPSIG_OK;
+}
+
+template <typename T>
+static int tens_seq_vjp_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, int increments, const T* X, int N, int L, int d,
+                             int col_begin, int col_end, const T* grad_levels, T* gradZ, T* gradX,
+                             void* ws, size_t ws_bytes, void* stream) {
+  if (int rc = check_desc(desc)) return rc;
+  if (desc->order != 1) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "reverse mode is implemented for order == 1 only (got %d)", desc->order);
+  if (desc->num_levels > 8) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "reverse mode supports num_levels <= 8");
+  if (!Z || !X || !grad_levels || !gradZ || !gradX) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "Z/X/grad_levels/gradZ/gradX must not be NULL");
+  if (d < 1 || d > 16) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "state dimension d=%d is not supported (1..16)", d);
+  if (L < (desc->difference ? 2 : 1)) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "sequences too short (L=%d)", L);
+  if (col_begin < 0 || col_end > N || col_begin > col_end) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "bad column range [%d, %d) for N=%d", col_begin, col_end, N);
+  const size_t npairs = (size_t)Mz * (col_end - col_begin);
+  if (npairs == 0) return GPSIG_OK;
+  const int m = desc->num_levels, TT = m * (m + 1) / 2, zs = increments ? 2 : 1;
+  const size_t need = gpsig_tens_vs_seq_vjp_workspace_bytes(Mz, col_end - col_begin, L, m, sizeof(T));
+  if (!ws || ws_bytes < need || (reinterpret_cast<uintptr_t>(ws) & 15))
+    GPSIG_FAIL(GPSIG_ERR_WORKSPACE, "workspace too small or misaligned: need %zu bytes, got %zu", need, ws_bytes);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  TensSeqVjpParams P;
+  memset(&P, 0, sizeof(P));
+  P.Z = Z; P.X = X; P.Mz = Mz; P.zs = zs; P.N = N; P.L = L; P.d = d; P.m = m;
+  P.col_begin = col_begin; P.col_end = col_end; P.difference = desc->difference;
+  P.p0 = desc->base_params[0]; P.p1 = desc->base_params[1]; P.base = desc->base;
+  P.g = grad_levels; P.gradZ = gradZ; P.gradX = gradX; P.S = ws; P.npairs = npairs;
+  const int gz = TT * zs * d, threads = 64;
+  const unsigned blocks = (unsigned)((npairs + threads - 1) / threads);
+  prof_begin(s);
+  if (gz <= 160) tens_seq_vjp_kernel<T, 160><<<blocks, threads, 0, s>>>(P);
+  else if (gz <= 480) tens_seq_vjp_kernel<T, 480><<<blocks, threads, 0, s>>>(P);
+  else tens_seq_vjp_kernel<T, 1152><<<blocks, threads, 0, s>>>(P);
+  prof_end(s);
+  GPSIG_LAUNCH_CHECK("tens_seq_vjp_kernel");
+  return GPSIG_OK;
+}
+
+template <typename T>
+static int tens_tens_vjp_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, int increments, int d, const T* grad_levels,
+                              T* gradZ, void* stream) {
+  if (int rc = check_desc(desc)) return rc;
+  if (!Z || !grad_levels || !gradZ) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "Z/grad_levels/gradZ must not be NULL");
+  if (d < 1 || d > 16) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "state dimension d=%d is not supported (1..16)", d);
+  if (Mz == 0) return GPSIG_OK;
+  TensTensVjpParams P;
+  memset(&P, 0, sizeof(P));
+  P.Z = Z; P.Mz = Mz; P.zs = increments ? 2 : 1; P.m = desc->num_levels; P.d = d;
+  P.p0 = desc->base_params[0]; P.p1 = desc->base_params[1]; P.base = desc->base;
+  P.g = grad_levels; P.gradZ = gradZ;
+  const int TT = P.m * (P.m + 1) / 2;
+  dim3 grid((Mz + 63) / 64, TT);
+  tens_tens_vjp_kernel<T><<<grid, 64, 0, static_cast<cudaStream_t>(stream)>>>(P);
+  GPSIG_LAUNCH_CHECK("tens_tens_vjp_kernel");
+  return GPSIG_OK;
+}
+
 }  // namespace gpsig
 
 using namespace gpsig;
@@ -407,6 +515,39 @@ int gpsig_tens_vs_seq_f32(const gpsig_trunc_desc* desc, const float* Z, int Mz, 
                           int d, const float* ls, int cb, int ce, const gpsig_epilogue* epi, float* out,
                           void* ws, size_t wsb, void* stream) {
   return tens_vs_seq_impl<float>(desc, Z, Mz, inc, X, N, L, d, ls, cb, ce, epi, out, ws, wsb, stream);
+}
+
+size_t gpsig_trunc_vjp_workspace_bytes(int npairs, int L, int L2, int m, int difference, int elem) {
+  return trunc_vjp_ws((size_t)npairs, L, L2, m, difference, elem);
+}
+size_t gpsig_tens_vs_seq_vjp_workspace_bytes(int Mz, int ncols, int L, int m, int elem) {
+  return align_up((size_t)Mz * ncols * (m * (m + 1) / 2) * L * elem, 128);
+}
+int gpsig_trunc_vjp_f64(const gpsig_trunc_desc* desc, const double* X, int N, int L, const double* X2, int N2, int L2, int d,
+                        int pair_mode, int rb, int re, const double* grad_levels, double* gradX, double* gradX2,
+                        void* ws, size_t wsb, void* stream) {
+  return trunc_vjp_impl<double>(desc, X, N, L, X2, N2, L2, d, pair_mode, rb, re, grad_levels, gradX, gradX2, ws, wsb, stream);
+}
+int gpsig_trunc_vjp_f32(const gpsig_trunc_desc* desc, const float* X, int N, int L, const float* X2, int N2, int L2, int d,
+                        int pair_mode, int rb, int re, const float* grad_levels, float* gradX, float* gradX2,
+                        void* ws, size_t wsb, void* stream) {
+  return trunc_vjp_impl<float>(desc, X, N, L, X2, N2, L2, d, pair_mode, rb, re, grad_levels, gradX, gradX2, ws, wsb, stream);
+}
+int gpsig_tens_vs_seq_vjp_f64(const gpsig_trunc_desc* desc, const double* Z, int Mz, int inc, const double* X, int N, int L, int d,
+                              int cb, int ce, const double* grad_levels, double* gradZ, double* gradX, void* ws, size_t wsb, void* stream) {
+  return tens_seq_vjp_impl<double>(desc, Z, Mz, inc, X, N, L, d, cb, ce, grad_levels, gradZ, gradX, ws, wsb, stream);
+}
+int gpsig_tens_vs_seq_vjp_f32(const gpsig_trunc_desc* desc, const float* Z, int Mz, int inc, const float* X, int N, int L, int d,
+                              int cb, int ce, const float* grad_levels, float* gradZ, float* gradX, void* ws, size_t wsb, void* stream) {
+  return tens_seq_vjp_impl<float>(desc, Z, Mz, inc, X, N, L, d, cb, ce, grad_levels, gradZ, gradX, ws, wsb, stream);
+}
+int gpsig_tens_tens_vjp_f64(const gpsig_trunc_desc* desc, const double* Z, int Mz, int inc, int d, const double* grad_levels,
+                            double* gradZ, void* stream) {
+  return tens_tens_vjp_impl<double>(desc, Z, Mz, inc, d, grad_levels, gradZ, stream);
+}
+int gpsig_tens_tens_vjp_f32(const gpsig_trunc_desc* desc, const float* Z, int Mz, int inc, int d, const float* grad_levels,
+                            float* gradZ, void* stream) {
+  return tens_tens_vjp_impl<float>(desc, Z, Mz, inc, d, grad_levels, gradZ, stream);
 }
 
 int gpsig_tens_tens_f64(const gpsig_trunc_desc* desc, const double* Z, int Mz, int inc, int d, const double* ls,

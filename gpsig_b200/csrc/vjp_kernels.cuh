@@ -1,0 +1,422 @@
+// Vector-Jacobian products (reverse mode) of the first-order truncated signature kernels for sm_100a.
+//
+// The reference gets these from TensorFlow's autodiff of gpsig/signature_algs.py:8-35, 76-127 (every
+// tf.cumsum / tf.reduce_sum / base-kernel op of the lifted tensor is differentiated and the lifted
+// tensor is kept alive for the backward pass).  Here each op has a hand-written adjoint:
+//
+//   trunc_vjp_*      raw levels K_l(x_i, y_j), l = 1..m  (Gram rows or diagonal pairs)   -> dL/dX, dL/dX2
+//   tens_seq_vjp_*   raw levels of inducing tensors vs sequences (signature_algs.py:101-127) -> dL/dZ, dL/dX
+//   tens_tens_vjp_*  raw levels of inducing tensors vs themselves (signature_algs.py:76-99)  -> dL/dZ
+//
+// Gradients are taken w.r.t. the coordinates the kernels are CALLED with (the host layer scales by the
+// lengthscales / applies lags with differentiable torch ops and chains the rest).
+//
+// Adjoint of the level recursion for one pair.  With D[p,q] the (differenced) base-kernel tile,
+//   F_a[p,q] = sum over a-tuples strictly inside [0,p) x [0,q)   (F_0 = 1; the forward 2-D exclusive prefix sums)
+//   G_b[p,q] = sum over b-tuples strictly inside (p,P) x (q,Q)   (G_0 = 1; the same recursion run backwards)
+//   K_l = sum_{p,q} D F_{l-1}           dK_l/dD[p,q] = sum_{a+b=l-1} F_a[p,q] G_b[p,q]
+// so  W[p,q] = dL/dD[p,q] = sum_a F_a[p,q] * (sum_b g_{a+b+1} G_b[p,q]).
+// One THREAD owns one pair: a forward sweep stores F_1..F_{m-1} in an HBM scratch table laid out with the
+// pair index fastest (coalesced across the threads of a warp), a backward sweep forms G on the fly and
+// stores W; a second kernel (one thread per (pair, point)) turns W into dL/dM by the adjoint of the 2-D
+// difference (signature_algs.py:26) and chains it through the base kernel's partial derivatives into the
+// coordinates, accumulating with atomics (several pairs share a sequence).
+// First version: parallel over pairs only, sized for the training shapes (minibatch x inducing points);
+// the large-Gram backward is chunked over rows by the host layer.  order == 1 only.
+#pragma once
+#include "common.cuh"
+
+namespace gpsig {
+
+// partial derivatives of the base kernel f(dot, xs, ys) (kernels.py:946-1173) w.r.t. x.y, |x|^2, |y|^2
+template <typename T>
+__device__ __forceinline__ void base_partials(int base, T p0, T p1, T dot, T xs, T ys, T& fd, T& fx, T& fy) {
+  fd = fx = fy = T(0);
+  switch (base) {
+    case GPSIG_BASE_LINEAR: fd = T(1); break;
+    case GPSIG_BASE_RBF: { const T f = gexp<T>(-((T(-2) * dot + xs) + ys) / T(2)); fd = f; fx = fy = T(-0.5) * f; break; }
+    case GPSIG_BASE_COSINE: {
+      const T sx = gsqrt<T>(xs), sy = gsqrt<T>(ys);
+      const T f = dot / (sx * sy);
+      fd = T(1) / (sx * sy); fx = T(-0.5) * f / xs; fy = T(-0.5) * f / ys; break;
+    }
+    case GPSIG_BASE_POLY: fd = p1 * gpow<T>(dot + p0, p1 - T(1)); break;
+    case GPSIG_BASE_MIX: {
+      const T e = gexp<T>(-(xs + ys - T(2) * dot) / T(2));
+      fd = p0 * e + (T(1) - p0); fx = fy = T(-0.5) * p0 * e; break;
+    }
+    default: {
+      const T r2 = (T(-2) * dot + xs) + ys;
+      if (!(r2 > T(1e-40))) break;                        // clamped: zero gradient, as tf.maximum in _euclid_dist (kernels.py:959-961)
+      const T r = gsqrt<T>(r2);
+      T dr2;                                              // df/d(r^2)
+      if (base == GPSIG_BASE_MATERN12) dr2 = -gexp<T>(-r) / (T(2) * r);
+      else if (base == GPSIG_BASE_MATERN32) dr2 = T(-1.5) * gexp<T>(-T(1.7320508075688772) * r);
+      else { const T s5 = T(2.23606797749979); dr2 = T(-5.0 / 6.0) * (T(1) + s5 * r) * gexp<T>(-s5 * r); }
+      fd = T(-2) * dr2; fx = fy = dr2;
+    }
+  }
+}
+
+template <typename T>
+__device__ __forceinline__ void dot3(const T* __restrict__ x, const T* __restrict__ y, int d, T& dot, T& xs, T& ys) {
+  dot = xs = ys = T(0);
+  for (int k = 0; k < d; ++k) { const T u = x[k], v = y[k]; dot = gfma<T>(u, v, dot); xs = gfma<T>(u, u, xs); ys = gfma<T>(v, v, ys); }
+}
+template <typename T>
+__device__ __forceinline__ T kappa_raw(const T* x, const T* y, int d, int base, T p0, T p1) {
+  T dot, xs, ys;
+  dot3(x, y, d, dot, xs, ys);
+  return base_eval<T>(base, p0, p1, dot, xs, ys);
+}
+
+template <typename T> __device__ __forceinline__ void atomic_add(T* p, T v) { atomicAdd(p, v); }
+
+struct TruncVjpParams {
+  const void* X; const void* Y;      // dense [N, L, d] / [N2, L2, d] (Y == X for the symmetric / diagonal case)
+  int N, N2, L, L2, d, m;
+  int diag;                          // pairs (i, i) instead of rows x N2
+  int row_begin, row_end;
+  int difference;
+  double p0, p1; int base;
+  const void* g;                     // upstream dL/dK_l: [m+1, R, N2] or [m+1, R] (diag)
+  void* gradX; void* gradY;          // [N, L, d] / [N2, L2, d], accumulated
+  void* F; void* C; void* W;         // scratch: F [(m-1), P, Q, npairs], C [(m-1), Q, npairs], W [P, Q, npairs]
+  size_t npairs;
+};
+
+// sweep 1+2: one thread per pair
+template <typename T>
+__global__ void trunc_vjp_tables_kernel(const TruncVjpParams P) {
+  const size_t pair = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (pair >= P.npairs) return;
+  const size_t np = P.npairs;
+  const int m = P.m, d = P.d, diff = P.difference ? 1 : 0;
+  const int PR = P.L - diff, QC = P.L2 - diff;                        // rows / columns of D
+  int i, j;
+  if (P.diag) { i = P.row_begin + (int)pair; j = i; }
+  else { i = P.row_begin + (int)(pair / P.N2); j = (int)(pair % P.N2); }
+  const T* x = static_cast<const T*>(P.X) + (size_t)i * P.L * d;
+  const T* y = static_cast<const T*>(P.Y) + (size_t)j * P.L2 * d;
+  const T p0 = T(P.p0), p1 = T(P.p1);
+  T* F = static_cast<T*>(P.F);
+  T* C = static_cast<T*>(P.C);
+  T* W = static_cast<T*>(P.W);
+  auto Fat = [&](int a, int p, int q) -> T& { return F[(((size_t)(a - 1) * PR + p) * QC + q) * np + pair]; };   // a = 1..m-1
+  auto Cat = [&](int a, int q) -> T& { return C[((size_t)(a - 1) * QC + q) * np + pair]; };
+  // upstream gradients of this pair
+  T g[9];
+  const size_t gstride = P.diag ? (size_t)(P.row_end - P.row_begin) : (size_t)(P.row_end - P.row_begin) * P.N2;
+  for (int l = 0; l <= m; ++l) g[l] = static_cast<const T*>(P.g)[(size_t)l * gstride + pair];
+
+  // D[p, q] from rolling base-kernel values: m00 = M[p, q], m01 = M[p, q+1], m10 = M[p+1, q], m11 = M[p+1, q+1]
+  auto Dcell = [&](int p, int q, T& m00, T& m10, bool fresh) -> T {
+    if (!diff) return kappa_raw<T>(x + (size_t)p * d, y + (size_t)q * d, d, P.base, p0, p1);
+    if (fresh) {
+      m00 = kappa_raw<T>(x + (size_t)p * d, y + (size_t)q * d, d, P.base, p0, p1);
+      m10 = kappa_raw<T>(x + (size_t)(p + 1) * d, y + (size_t)q * d, d, P.base, p0, p1);
+    }
+    const T m01 = kappa_raw<T>(x + (size_t)p * d, y + (size_t)(q + 1) * d, d, P.base, p0, p1);
+    const T m11 = kappa_raw<T>(x + (size_t)(p + 1) * d, y + (size_t)(q + 1) * d, d, P.base, p0, p1);
+    const T D = (m11 - m10) - (m01 - m00);                           // signature_algs.py:26
+    m00 = m01; m10 = m11;
+    return D;
+  };
+
+  // ---- forward sweep: F_a[p, q], a = 1..m-1 ----------------------------------------------------
+  for (int a = 1; a < m; ++a)
+    for (int q = 0; q < QC; ++q) Cat(a, q) = T(0);
+  for (int p = 0; p < PR; ++p) {
+    T E[8];
+    for (int a = 1; a < m; ++a) E[a] = T(0);
+    T m00 = T(0), m10 = T(0);
+    for (int q = 0; q < QC; ++q) {
+      const T D = Dcell(p, q, m00, m10, q == 0);
+      T Fprev = T(1);                                                // F_0
+      for (int a = 1; a < m; ++a) {
+        const T c = Cat(a, q);
+        const T Fa = E[a];                                           // rows < p, columns < q
+        Fat(a, p, q) = Fa;
+        E[a] += c;
+        Cat(a, q) = gfma<T>(D, Fprev, c);                            // column sum now includes row p
+        Fprev = Fa;
+      }
+    }
+  }
+  // ---- backward sweep: G_b on the fly, W = sum_a F_a H_a ------------------------------------------
+  for (int b = 1; b < m; ++b)
+    for (int q = 0; q < QC; ++q) Cat(b, q) = T(0);
+  for (int p = PR - 1; p >= 0; --p) {
+    T E[8];
+    for (int b = 1; b < m; ++b) E[b] = T(0);
+    // walk the columns right to left; rolling values mirrored: keep M[p, q+1], M[p+1, q+1] from the previous cell
+    T r01 = T(0), r11 = T(0);
+    for (int q = QC - 1; q >= 0; --q) {
+      T D;
+      if (!diff) D = kappa_raw<T>(x + (size_t)p * d, y + (size_t)q * d, d, P.base, p0, p1);
+      else {
+        if (q == QC - 1) {
+          r01 = kappa_raw<T>(x + (size_t)p * d, y + (size_t)(q + 1) * d, d, P.base, p0, p1);
+          r11 = kappa_raw<T>(x + (size_t)(p + 1) * d, y + (size_t)(q + 1) * d, d, P.base, p0, p1);
+        }
+        const T m00 = kappa_raw<T>(x + (size_t)p * d, y + (size_t)q * d, d, P.base, p0, p1);
+        const T m10 = kappa_raw<T>(x + (size_t)(p + 1) * d, y + (size_t)q * d, d, P.base, p0, p1);
+        D = (r11 - m10) - (r01 - m00);
+        r01 = m00; r11 = m10;
+      }
+      T G[8];
+      G[0] = T(1);
+      T Gprev = T(1);
+      for (int b = 1; b < m; ++b) {
+        const T c = Cat(b, q);
+        const T Gb = E[b];                                           // rows > p, columns > q
+        G[b] = Gb;
+        E[b] += c;
+        Cat(b, q) = gfma<T>(D, Gprev, c);
+        Gprev = Gb;
+      }
+      T w = T(0);
+      for (int a = 0; a < m; ++a) {
+        T H = T(0);
+        for (int b = 0; a + b + 1 <= m; ++b) H = gfma<T>(g[a + b + 1], G[b], H);
+        const T Fa = a == 0 ? T(1) : Fat(a, p, q);
+        w = gfma<T>(Fa, H, w);
+      }
+      W[((size_t)p * QC + q) * np + pair] = w;
+    }
+  }
+}
+
+// sweep 3: one thread per (pair, point): r < L -> point x_r of the pair, else point y_{r-L}
+template <typename T>
+__global__ void trunc_vjp_grad_kernel(const TruncVjpParams P) {
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t np = P.npairs;
+  const int LL = P.L + P.L2;
+  if (t >= np * LL) return;
+  const int r = (int)(t / np);
+  const size_t pair = t % np;
+  const int d = P.d, diff = P.difference ? 1 : 0;
+  const int PR = P.L - diff, QC = P.L2 - diff;
+  int i, j;
+  if (P.diag) { i = P.row_begin + (int)pair; j = i; }
+  else { i = P.row_begin + (int)(pair / P.N2); j = (int)(pair % P.N2); }
+  const T* x = static_cast<const T*>(P.X) + (size_t)i * P.L * d;
+  const T* y = static_cast<const T*>(P.Y) + (size_t)j * P.L2 * d;
+  const T* W = static_cast<const T*>(P.W);
+  const T p0 = T(P.p0), p1 = T(P.p1);
+  auto Wat = [&](int p, int q) -> T { return (p < 0 || q < 0 || p >= PR || q >= QC) ? T(0) : W[((size_t)p * QC + q) * np + pair]; };
+  // dL/dM[pp, qq]: adjoint of the 2-D difference
+  auto dM = [&](int pp, int qq) -> T {
+    if (!diff) return Wat(pp, qq);
+    return (Wat(pp - 1, qq - 1) - Wat(pp - 1, qq)) - (Wat(pp, qq - 1) - Wat(pp, qq));
+  };
+  T acc[16];
+  for (int k = 0; k < d; ++k) acc[k] = T(0);
+  if (r < P.L) {
+    const int pp = r;
+    const T* xp = x + (size_t)pp * d;
+    for (int qq = 0; qq < P.L2; ++qq) {
+      const T a = dM(pp, qq);
+      if (a == T(0)) continue;
+      const T* yq = y + (size_t)qq * d;
+      T dot, xs, ys, fd, fx, fy;
+      dot3(xp, yq, d, dot, xs, ys);
+      base_partials<T>(P.base, p0, p1, dot, xs, ys, fd, fx, fy);
+      for (int k = 0; k < d; ++k) acc[k] = gfma<T>(a, fd * yq[k] + T(2) * fx * xp[k], acc[k]);
+    }
+    T* gx = static_cast<T*>(P.gradX) + ((size_t)i * P.L + pp) * d;
+    for (int k = 0; k < d; ++k) atomic_add<T>(gx + k, acc[k]);
+  } else {
+    const int qq = r - P.L;
+    const T* yq = y + (size_t)qq * d;
+    for (int pp = 0; pp < P.L; ++pp) {
+      const T a = dM(pp, qq);
+      if (a == T(0)) continue;
+      const T* xp = x + (size_t)pp * d;
+      T dot, xs, ys, fd, fx, fy;
+      dot3(xp, yq, d, dot, xs, ys);
+      base_partials<T>(P.base, p0, p1, dot, xs, ys, fd, fx, fy);
+      for (int k = 0; k < d; ++k) acc[k] = gfma<T>(a, fd * xp[k] + T(2) * fy * yq[k], acc[k]);
+    }
+    T* gy = static_cast<T*>(P.gradY) + ((size_t)j * P.L2 + qq) * d;
+    for (int k = 0; k < d; ++k) atomic_add<T>(gy + k, acc[k]);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// inducing tensors vs sequences
+// ---------------------------------------------------------------------------
+struct TensSeqVjpParams {
+  const void* Z; const void* X;      // dense [T, Mz, zs, d], [N, L, d]
+  int Mz, zs, N, L, d, m;
+  int col_begin, col_end;
+  int difference;
+  double p0, p1; int base;
+  const void* g;                     // [m+1, Mz, C]
+  void* gradZ; void* gradX;
+  void* S;                           // scratch [T, L, npairs]: running sums S_k(l) of the forward recursion
+  size_t npairs;
+};
+
+// Forward (tens_level in tens_kernels.cuh): within level I, components jj = 0..I-1 (global index k),
+//   S_jj(l) = S_jj(l-1) + D_jj(l) * S_{jj-1}(l-1)   (S_{-1} = 1),  K_I = S_{I-1}(L-1).
+// Reverse: lam_jj(l-1) += lam_jj(l);  aD_jj(l) = lam_jj(l) * S_{jj-1}(l-1);  lam_{jj-1}(l-1) += lam_jj(l) * D_jj(l).
+template <typename T, int GZ>                         // GZ >= T * zs * d: per-thread accumulators of dL/dZ
+__global__ void tens_seq_vjp_kernel(const TensSeqVjpParams P) {
+  const size_t pair = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (pair >= P.npairs) return;
+  const size_t np = P.npairs;
+  const int ncols = P.col_end - P.col_begin;
+  const int z = (int)(pair / ncols), nl = (int)(pair % ncols), n = P.col_begin + nl;
+  const int m = P.m, d = P.d, zs = P.zs, L = P.L, TT = m * (m + 1) / 2;
+  const bool diff = P.difference != 0;
+  const T p0 = T(P.p0), p1 = T(P.p1);
+  const T* Z = static_cast<const T*>(P.Z);
+  const T* x = static_cast<const T*>(P.X) + (size_t)n * L * d;
+  T* S = static_cast<T*>(P.S);
+  auto zpt = [&](int k, int s) { return Z + (((size_t)k * P.Mz + z) * zs + s) * d; };
+  auto Mt = [&](int k, int l) -> T {
+    const T* xl = x + (size_t)l * d;
+    if (zs == 2) return kappa_raw<T>(zpt(k, 1), xl, d, P.base, p0, p1) - kappa_raw<T>(zpt(k, 0), xl, d, P.base, p0, p1);   // kernels.py:331
+    return kappa_raw<T>(zpt(k, 0), xl, d, P.base, p0, p1);
+  };
+  auto Sat = [&](int k, int l) -> T& { return S[((size_t)k * L + l) * np + pair]; };
+  const int l0 = diff ? 1 : 0;                                       // first time index that carries a D
+  // ---- forward: store S_k(l) -------------------------------------------------------------------
+  {
+    T Sv[36], Mprev[36];
+    for (int k = 0; k < TT; ++k) { Sv[k] = T(0); Mprev[k] = T(0); }
+    for (int l = 0; l < L; ++l) {
+      int k0 = 0;
+      for (int I = 1; I <= m; ++I) {
+        for (int jj = I - 1; jj >= 0; --jj) {
+          const int k = k0 + jj;
+          const T mt = Mt(k, l);
+          T D = mt;
+          if (diff) { D = mt - Mprev[k]; Mprev[k] = mt; }
+          if (l >= l0) Sv[k] = jj > 0 ? gfma<T>(D, Sv[k - 1], Sv[k]) : Sv[k] + D;
+        }
+        k0 += I;
+      }
+      for (int k = 0; k < TT; ++k) Sat(k, l) = Sv[k];
+    }
+  }
+  // ---- reverse -----------------------------------------------------------------------------------
+  T lam[36], aDnext[36], gz[GZ];
+  for (int k = 0; k < TT; ++k) { lam[k] = T(0); aDnext[k] = T(0); }
+  for (int e = 0; e < TT * zs * d; ++e) gz[e] = T(0);
+  {
+    int k0 = 0;
+    for (int I = 1; I <= m; ++I) { lam[k0 + I - 1] = static_cast<const T*>(P.g)[((size_t)I * P.Mz + z) * ncols + nl]; k0 += I; }
+  }
+  for (int l = L - 1; l >= 0; --l) {
+    const T* xl = x + (size_t)l * d;
+    T gx[16];
+    for (int q = 0; q < d; ++q) gx[q] = T(0);
+    int k0 = 0;
+    for (int I = 1; I <= m; ++I) {
+      for (int jj = 0; jj < I; ++jj) {
+        const int k = k0 + jj;
+        // adjoint of D_k(l) (zero where the forward skipped the update)
+        T aD = T(0);
+        if (l >= l0) {
+          const T Sprev = jj > 0 ? (l > 0 ? Sat(k - 1, l - 1) : T(0)) : T(1);
+          aD = lam[k] * Sprev;
+        }
+        // adjoint of Mt_k(l): D(l) = Mt(l) - Mt(l-1), D(l+1) = Mt(l+1) - Mt(l)
+        const T aM = diff ? aD - aDnext[k] : aD;
+        aDnext[k] = aD;
+        if (aM != T(0)) {
+          for (int s = 0; s < zs; ++s) {
+            const T sgn = (zs == 2 && s == 0) ? T(-1) : T(1);
+            const T* zp = zpt(k, s);
+            T dot, zsq, xsq, fd, fz, fx;
+            dot3(zp, xl, d, dot, zsq, xsq);
+            base_partials<T>(P.base, p0, p1, dot, zsq, xsq, fd, fz, fx);
+            const T w = sgn * aM;
+            for (int q = 0; q < d; ++q) {
+              gz[(k * zs + s) * d + q] = gfma<T>(w, fd * xl[q] + T(2) * fz * zp[q], gz[(k * zs + s) * d + q]);
+              gx[q] = gfma<T>(w, fd * zp[q] + T(2) * fx * xl[q], gx[q]);
+            }
+          }
+        }
+      }
+      k0 += I;
+    }
+    // propagate lam to time l-1 (needs D_k(l), highest component first within a level)
+    if (l >= l0) {
+      k0 = 0;
+      for (int I = 1; I <= m; ++I) {
+        for (int jj = 1; jj < I; ++jj) {
+          const int k = k0 + jj;
+          const T D = diff ? Mt(k, l) - Mt(k, l - 1) : Mt(k, l);
+          lam[k - 1] = gfma<T>(lam[k], D, lam[k - 1]);
+        }
+        k0 += I;
+      }
+    }
+    T* gxo = static_cast<T*>(P.gradX) + ((size_t)n * L + l) * d;
+    for (int q = 0; q < d; ++q) if (gx[q] != T(0)) atomic_add<T>(gxo + q, gx[q]);
+  }
+  for (int k = 0; k < TT; ++k)
+    for (int s = 0; s < zs; ++s) {
+      T* gzo = static_cast<T*>(P.gradZ) + (((size_t)k * P.Mz + z) * zs + s) * d;
+      for (int q = 0; q < d; ++q) atomic_add<T>(gzo + q, gz[(k * zs + s) * d + q]);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// inducing tensors vs themselves: one thread per (component k, row a); no atomics.
+//   R_i(a, b) = prod_{jj < i} Mt_{k_i + jj}(a, b),  Mt symmetric in (a, b)
+//   dL/dZ[k, a] = sum_b (g_i[a, b] + g_i[b, a]) * prod_{others} Mt * dMt_k(a, b)/dz_a
+// ---------------------------------------------------------------------------
+struct TensTensVjpParams {
+  const void* Z; int Mz, zs, m, d;
+  double p0, p1; int base;
+  const void* g;                     // [m+1, Mz, Mz]
+  void* gradZ;                       // [T, Mz, zs, d], overwritten
+};
+
+template <typename T>
+__global__ void tens_tens_vjp_kernel(const TensTensVjpParams P) {
+  const int a = blockIdx.x * blockDim.x + threadIdx.x;
+  const int k = blockIdx.y;                                          // global component index
+  if (a >= P.Mz) return;
+  const int d = P.d, zs = P.zs, Mz = P.Mz;
+  const T p0 = T(P.p0), p1 = T(P.p1);
+  const T* Z = static_cast<const T*>(P.Z);
+  int I = 1, k0 = 0;
+  while (k0 + I <= k) { k0 += I; ++I; }                               // level of component k, first component k0
+  auto zpt = [&](int kk, int zz, int s) { return Z + (((size_t)kk * Mz + zz) * zs + s) * d; };
+  auto Mt = [&](int kk, int b) -> T {
+    if (zs == 2)
+      return kappa_raw<T>(zpt(kk, a, 1), zpt(kk, b, 1), d, P.base, p0, p1) + kappa_raw<T>(zpt(kk, a, 0), zpt(kk, b, 0), d, P.base, p0, p1) -
+             kappa_raw<T>(zpt(kk, a, 1), zpt(kk, b, 0), d, P.base, p0, p1) - kappa_raw<T>(zpt(kk, a, 0), zpt(kk, b, 1), d, P.base, p0, p1);   // kernels.py:278
+    return kappa_raw<T>(zpt(kk, a, 0), zpt(kk, b, 0), d, P.base, p0, p1);
+  };
+  const T* g = static_cast<const T*>(P.g) + (size_t)I * Mz * Mz;
+  T acc[2][16];
+  for (int s = 0; s < zs; ++s) for (int q = 0; q < d; ++q) acc[s][q] = T(0);
+  for (int b = 0; b < Mz; ++b) {
+    T w = g[(size_t)a * Mz + b] + g[(size_t)b * Mz + a];
+    if (w == T(0)) continue;
+    for (int jj = 0; jj < I; ++jj) if (k0 + jj != k) w *= Mt(k0 + jj, b);
+    // d Mt_k(a, b) / d z_a^s: sum over the two kappas that contain z_a^s
+    for (int s = 0; s < zs; ++s) {
+      const T* za = zpt(k, a, s);
+      for (int s2 = 0; s2 < zs; ++s2) {
+        const T sgn = (zs == 2 && s != s2) ? T(-1) : T(1);
+        const T* zb = zpt(k, b, s2);
+        T dot, xs, ys, fd, fx, fy;
+        dot3(za, zb, d, dot, xs, ys);
+        base_partials<T>(P.base, p0, p1, dot, xs, ys, fd, fx, fy);
+        for (int q = 0; q < d; ++q) acc[s][q] = gfma<T>(sgn * w, fd * zb[q] + T(2) * fx * za[q], acc[s][q]);
+      }
+    }
+  }
+  for (int s = 0; s < zs; ++s)
+    for (int q = 0; q < d; ++q) static_cast<T*>(P.gradZ)[(((size_t)k * Mz + a) * zs + s) * d + q] = acc[s][q];
+}
+
+}  // namespace gpsig

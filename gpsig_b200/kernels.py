@@ -141,10 +141,14 @@ class SignatureKernel:
     def _param(self, value, like):
         if value is None:
             return None
+        if torch.is_tensor(value):                      # a trainable parameter used on the non-differentiable path
+            return value.detach().to(dtype=like.dtype, device=like.device).contiguous()
         return torch.as_tensor(np.asarray(value, dtype=np.float64), dtype=like.dtype, device=like.device).contiguous()
 
     def _level_scale(self, like):
         """sigma * variances  (kernels.py:472)."""
+        if torch.is_tensor(self.variances) or torch.is_tensor(self.sigma):
+            return (float(self.sigma) * self._param(self.variances, like).reshape(-1)).contiguous()
         return self._param(float(self.sigma) * np.asarray(self.variances, dtype=np.float64).reshape(-1), like)
 
     def _kw(self, like):
@@ -159,6 +163,101 @@ class SignatureKernel:
     def _K_seq_diag(self, X):
         """Raw per-level diagonals [m+1, N] of [N, L, d] sequences (kernels.py:190-207)."""
         return ops.trunc_diag(X, self.num_levels, **self._kw(X))
+
+    # ---- differentiable path (training) ------------------------------------------
+    # The reference trains lengthscales, variances, sigma and the inducing tensors through TensorFlow
+    # autodiff of these methods (training.py; inducing_variables.py:51-137).  Here: when any input or
+    # parameter is a torch tensor that requires grad, the methods below route through the CUDA ops'
+    # hand-written adjoints (gpsig_b200/autograd.py -> csrc/vjp_kernels.cuh); scaling, normalisation and
+    # the sigma * variances weighting are the same formulas written as differentiable torch expressions.
+    # order == 1 only (the adjoints of the higher-order recursion are not built).
+    def _wants_grad(self, *tensors):
+        if not torch.is_grad_enabled():
+            return False
+        return any(torch.is_tensor(t) and t.requires_grad
+                   for t in tensors + (self.variances, self.lengthscales, self.sigma))
+
+    def _tparam(self, value, like):
+        if torch.is_tensor(value):
+            return value.to(dtype=like.dtype, device=like.device)
+        return self._param(value, like)
+
+    def _d_check(self):
+        if self.order != 1:
+            raise NotImplementedError('gpsig_b200: gradients are implemented for order == 1 only')
+
+    def _d_seq(self, X):
+        X = X.reshape(X.shape[0], -1, self.num_features)
+        ls = None if self.lengthscales is None else self._tparam(self.lengthscales, X)
+        if self.num_lags > 0:
+            X = _lags.add_lags_to_sequences(X, self._param(self.lags, X))
+            if ls is not None:
+                X = X / ls[None, None, None, :]
+            X = X * self._param(self.gamma, X)[None, None, :, None]
+            return X.reshape(X.shape[0], X.shape[1], -1)
+        return X if ls is None else X / ls
+
+    def _d_tens(self, Z):
+        if self.lengthscales is None:
+            return Z
+        ls = self._tparam(self.lengthscales, Z)
+        if self.num_lags > 0:
+            shp = Z.shape
+            Zr = Z.reshape(shp[:-1] + (self.num_lags + 1, self.num_features))
+            return (Zr / ls * self._param(self.gamma, Z)[:, None]).reshape(shp)
+        return Z / ls
+
+    def _d_scale(self, like):
+        sigma = self.sigma if torch.is_tensor(self.sigma) else float(self.sigma)
+        return sigma * self._tparam(self.variances, like).reshape(-1)
+
+    def _d_bk(self):
+        return dict(base=self._base, base_params=self._get_base_params())
+
+    def _d_gram(self, Xs, X2s, return_levels):
+        """Differentiable K(X, X2) from scaled sequences (kernels.py:431-477)."""
+        from . import autograd as ag
+        sc = self._d_scale(Xs)
+        lv = ag.trunc_levels(Xs, X2s, self.num_levels, difference=self.difference, **self._d_bk())
+        if self.normalization:
+            jitter = settings.jitter
+            n1 = ag.trunc_diag_levels(Xs, self.num_levels, difference=self.difference, **self._d_bk()) + jitter
+            if X2s is None:
+                lv = lv + jitter * torch.eye(Xs.shape[0], dtype=Xs.dtype, device=Xs.device)[None]
+                n2 = n1
+            else:
+                n2 = ag.trunc_diag_levels(X2s, self.num_levels, difference=self.difference, **self._d_bk()) + jitter
+            lv = lv / (torch.sqrt(n1)[:, :, None] * torch.sqrt(n2)[:, None, :])
+        lv = lv * sc[:, None, None]
+        return lv if return_levels else lv.sum(dim=0)
+
+    def _d_tens_n_seq(self, Z, Xs, increments, full_X_cov, return_levels, want=('zz', 'zx', 'xx')):
+        from . import autograd as ag
+        self._d_check()
+        Zs = self._d_tens(Z)
+        sc = self._d_scale(Xs if Xs is not None else Zs)
+        m, jitter = self.num_levels, settings.jitter
+        out = {}
+        if 'zz' in want:
+            out['zz'] = ag.tens_tens_levels(Zs, m, increments=increments, **self._d_bk()) * sc[:, None, None]
+        diag = None
+        if Xs is not None and ('zx' in want or 'xx' in want) and (self.normalization or not full_X_cov):
+            diag = ag.trunc_diag_levels(Xs, m, difference=self.difference, **self._d_bk())
+        if 'zx' in want:
+            kzx = ag.tens_vs_seq_levels(Zs, Xs, m, increments=increments, difference=self.difference, **self._d_bk())
+            if self.normalization:
+                kzx = kzx / torch.sqrt(diag + jitter)[:, None, :]
+            out['zx'] = kzx * sc[:, None, None]
+        if 'xx' in want:
+            if full_X_cov:
+                out['xx'] = self._d_gram(Xs, None, True)
+            elif self.normalization:
+                out['xx'] = sc[:, None].repeat(1, Xs.shape[0])
+            else:
+                out['xx'] = diag * sc[:, None]
+        if not return_levels:
+            out = {k: v.sum(dim=0) for k, v in out.items()}
+        return out
 
     # ---- public API ------------------------------------------------------------
     def K(self, X, X2=None, presliced=False, return_levels=False, presliced_X=False, presliced_X2=False, rows=None):
@@ -175,6 +274,11 @@ class SignatureKernel:
             X, _ = self._slice(X, None)
         elif not presliced_X2 and X2 is not None:
             X2, _ = self._slice(X2, None)
+        if self._wants_grad(X, X2):
+            self._d_check()
+            if rows is not None:
+                raise NotImplementedError('gpsig_b200: rows= is not supported on the differentiable path')
+            return self._d_gram(self._d_seq(X), None if X2 is None else self._d_seq(X2), return_levels)
         Xs = self._seq(X)
         jitter = settings.jitter
         kw = self._kw(Xs)
@@ -204,6 +308,17 @@ class SignatureKernel:
     def Kdiag(self, X, presliced=False, return_levels=False):
         """kernels.py:509-541."""
         N = X.shape[0]
+        if self._wants_grad(X):
+            self._d_check()
+            if self.normalization:
+                K = self._d_scale(X)[:, None].repeat(1, N)
+            else:
+                from . import autograd as ag
+                if not presliced:
+                    X, _ = self._slice(X, None)
+                Xs = self._d_seq(X)
+                K = ag.trunc_diag_levels(Xs, self.num_levels, difference=self.difference, **self._d_bk()) * self._d_scale(Xs)[:, None]
+            return K if return_levels else K.sum(dim=0)
         if self.normalization:
             sc = self._level_scale(X)
             if return_levels:
@@ -217,6 +332,8 @@ class SignatureKernel:
 
     def K_tens(self, Z, return_levels=False, increments=False):
         """Square covariance of inducing tensors (kernels.py:543-567)."""
+        if self._wants_grad(Z):
+            return self._d_tens_n_seq(Z, None, increments, False, return_levels, want=('zz',))['zz']
         Z = self._tens(Z, increments)   # Kzz does not depend on `order` (signature_algs.py:76-99)
         return ops.tens_tens(Z, self.num_levels, increments=increments, base=self._base,
                              base_params=self._get_base_params(), lengthscales=self._kw(Z)['lengthscales'],
@@ -226,6 +343,10 @@ class SignatureKernel:
         """Inducing tensors vs sequences (kernels.py:570-620)."""
         if not presliced:
             X, _ = self._slice(X, None)
+        if self._wants_grad(Z, X):
+            if cols is not None:
+                raise NotImplementedError('gpsig_b200: cols= is not supported on the differentiable path')
+            return self._d_tens_n_seq(Z, self._d_seq(X), increments, False, return_levels, want=('zx',))['zx']
         Xs = self._seq(X)
         norm = self._K_seq_diag(Xs) + settings.jitter if self.normalization else None      # kernels.py:604-613
         return ops.tens_vs_seq(self._tens(Z, increments), Xs, self.num_levels, increments=increments, norm_x=norm,
@@ -236,6 +357,9 @@ class SignatureKernel:
         """Kzz, Kzx, Kxx in one call (kernels.py:623-704)."""
         if not presliced:
             X, _ = self._slice(X, None)
+        if self._wants_grad(Z, X):
+            o = self._d_tens_n_seq(Z, self._d_seq(X), increments, full_X_cov, return_levels)
+            return o['zz'], o['zx'], o['xx']
         Xs = self._seq(X)
         Z = self._tens(Z, increments)
         N = Xs.shape[0]

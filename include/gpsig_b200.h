@@ -126,6 +126,36 @@ int gpsig_tens_tens_f64(const gpsig_trunc_desc* desc, const double* Z, int Mz, i
 int gpsig_tens_tens_f32(const gpsig_trunc_desc* desc, const float* Z, int Mz, int increments, int d,
                         const float* lengthscales, const gpsig_epilogue* epi, float* out, void* stream);
 
+/* ---- reverse mode (vector-Jacobian products) of the first-order truncated kernels -------------
+ * The reference differentiates gpsig/signature_algs.py:8-35, 76-127 with TensorFlow autodiff (training.py
+ * optimises lengthscales, variances and the inducing tensors through Kzz / Kzx / Kxx_diag,
+ * inducing_variables.py:51-137).  These entry points are the hand-written adjoints of the RAW levels
+ * (no normalisation, no level scaling: the host layer chains those).  Inputs are the dense coordinates the
+ * forward kernels were called with, ALREADY divided by the lengthscales; gradients are w.r.t. those.
+ *   grad_levels: dL/dK_l, same shape as the forward's return_levels output (level 0 is ignored).
+ *   gradX / gradX2 / gradZ: same shapes as X / X2 / Z.  gradX, gradX2 are ACCUMULATED into (zero them first);
+ *   X2 == NULL: symmetric case, both roles accumulate into gradX.  gpsig_tens_tens_vjp overwrites gradZ.
+ * pair_mode: GPSIG_PDE_GRAM = rows [row_begin,row_end) x all N2 columns; GPSIG_PDE_DIAG = pairs (i, i).
+ * order must be 1; num_levels <= 8. */
+size_t gpsig_trunc_vjp_workspace_bytes(int npairs, int L, int L2, int num_levels, int difference, int elem_size);
+int gpsig_trunc_vjp_f64(const gpsig_trunc_desc* desc, const double* X, int N, int L, const double* X2, int N2, int L2,
+                        int d, int pair_mode, int row_begin, int row_end, const double* grad_levels,
+                        double* gradX, double* gradX2, void* workspace, size_t workspace_bytes, void* stream);
+int gpsig_trunc_vjp_f32(const gpsig_trunc_desc* desc, const float* X, int N, int L, const float* X2, int N2, int L2,
+                        int d, int pair_mode, int row_begin, int row_end, const float* grad_levels,
+                        float* gradX, float* gradX2, void* workspace, size_t workspace_bytes, void* stream);
+size_t gpsig_tens_vs_seq_vjp_workspace_bytes(int Mz, int ncols, int L, int num_levels, int elem_size);
+int gpsig_tens_vs_seq_vjp_f64(const gpsig_trunc_desc* desc, const double* Z, int Mz, int increments, const double* X,
+                              int N, int L, int d, int col_begin, int col_end, const double* grad_levels,
+                              double* gradZ, double* gradX, void* workspace, size_t workspace_bytes, void* stream);
+int gpsig_tens_vs_seq_vjp_f32(const gpsig_trunc_desc* desc, const float* Z, int Mz, int increments, const float* X,
+                              int N, int L, int d, int col_begin, int col_end, const float* grad_levels,
+                              float* gradZ, float* gradX, void* workspace, size_t workspace_bytes, void* stream);
+int gpsig_tens_tens_vjp_f64(const gpsig_trunc_desc* desc, const double* Z, int Mz, int increments, int d,
+                            const double* grad_levels, double* gradZ, void* stream);
+int gpsig_tens_tens_vjp_f32(const gpsig_trunc_desc* desc, const float* Z, int Mz, int increments, int d,
+                            const float* grad_levels, float* gradZ, void* stream);
+
 /* ---- untruncated (Goursat PDE) kernel ---------------------------------------
  * Explicit 2nd-order stencil of sigKer_fast.pyx:48 on the 2^dyadic_order
  * refined grid, linear base kernel (what the reference's Cython path solves).
