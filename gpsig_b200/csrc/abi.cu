@@ -241,8 +241,10 @@ static int tens_vs_seq_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, in
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   T* zp = static_cast<T*>(ws);
   T* xp = reinterpret_cast<T*>(static_cast<char*>(ws) + packed_bytes(TT * Mz, zs, d, sizeof(T)));
-  if (int rc = pack<T>(Z, TT * Mz, zs, d, ls, zp, s)) return rc;
-  if (int rc = pack<T>(X, N, L, d, ls, xp, s)) return rc;
+  // first-order RBF: coordinates pre-scaled by sqrt(log2 e), the exponent feeds exp2 (tens_kernels.cuh)
+  const double cscale = (desc->order == 1 && desc->base == GPSIG_BASE_RBF) ? 1.2011224087864498 : 1.0;
+  if (int rc = pack<T>(Z, TT * Mz, zs, d, ls, zp, s, 0, cscale)) return rc;
+  if (int rc = pack<T>(X, N, L, d, ls, xp, s, 0, cscale)) return rc;
   TensSeqParams P;
   memset(&P, 0, sizeof(P));
   P.zp = zp; P.xp = xp;

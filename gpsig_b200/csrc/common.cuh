@@ -114,6 +114,33 @@ __device__ __forceinline__ T base_eval(int base, T p0, T p1, T dot, T xs, T ys) 
   }
 }
 
+// float64, base-2 exponent t (coordinates pre-scaled by sqrt(log2 e)): 9 FP64-pipe instructions.
+//   t = n/32 + f, n = round(32 t) by the magic-number add (exact, |f| <= 1/64),
+//   2^t = 2^(n>>5) * 2^((n&31)/32) * 2^f, table as above, 2^f - 1 = f*(c1 + ... + c5 f^4) minimax
+//   (1.4e-16 relative).  t is clamped to >= -1021 by an integer min on its sign/exponent word, so the
+//   exponent-field add never leaves the normal range (the result there is ~1e-307, i.e. 0 at any tolerance).
+__device__ __forceinline__ double exp2_tab32(double t, double tab_lane) {
+  const unsigned hi = min((unsigned)__double2hiint(t), 0xC08FE800u);
+  t = __hiloint2double((int)hi, __double2loint(t));
+  const double s = t + 0x1.8p+47;
+  const int n = __double2loint(s);
+  const double f = t - (s - 0x1.8p+47);
+  const double tj = __shfl_sync(0xffffffffu, tab_lane, n);          // source lane = n mod 32
+  double q = fma(0x1.5d886e6d047f4p-10, f, 0x1.3b2b1bee89b8dp-7);
+  q = fma(q, f, 0x1.c6b08d70300ecp-5);
+  q = fma(q, f, 0x1.ebfbdff8131c3p-3);
+  q = fma(q, f, 0x1.62e42fefa39efp-1);
+  const double w = q * f;
+  const double res = fma(tj, w, tj);
+  return __hiloint2double(__double2hiint(res) + (n & ~31) * 32768, __double2loint(res));   // + (n >> 5) << 20
+}
+
+__device__ __forceinline__ float exp2_approx(float t) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(t));
+  return r;
+}
+
 // ---- base-kernel specialisations on the fused path -------------------------
 enum { OP_LINEAR = 0, OP_RBF = 1, OP_GENERIC = 2 };
 

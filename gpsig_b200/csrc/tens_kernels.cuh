@@ -37,9 +37,16 @@ struct TensSeqParams {
 
 // Level I of signature_algs.py:101-127 for one (z, x_n) pair: I running sums.
 // zc/zq point at this level's I (x zs) tensor components.
+// RBF: the packed coordinates are pre-scaled by sqrt(log2 e) (abi.cu), so the exponent is in base-2 units:
+// float64 exp2_tab32 (9 FP64 instructions, table lookup by warp shuffle -> the warp must be convergent),
+// float32 one MUFU.EX2.
+template <typename T> struct TensExp2;
+template <> struct TensExp2<double> { static __device__ __forceinline__ double ex(double t, double tab) { return exp2_tab32(t, tab); } };
+template <> struct TensExp2<float> { static __device__ __forceinline__ float ex(float t, double) { return exp2_approx(t); } };
+
 template <typename T, int DP, int OP, int I>
 __device__ __forceinline__ T tens_level(const T* zc, const T* zq, int zs, const T* xblk, const T* xsq, int L,
-                                        bool difference, int base, T p0, T p1) {
+                                        bool difference, int base, T p0, T p1, double tab) {
   using Op = BaseOp<T, OP>;
   T S[I], Mprev[I];
 #pragma unroll
@@ -54,6 +61,7 @@ __device__ __forceinline__ T tens_level(const T* zc, const T* zq, int zs, const 
 #pragma unroll
       for (int k = 0; k < DP; ++k) acc = gfma<T>(zc[e * DP + k], xv[k], acc);
       if (OP == OP_GENERIC) return base_eval_call<T>(base, p0, p1, acc, zq[e], xc);
+      if (OP == OP_RBF) return TensExp2<T>::ex(acc, tab);
       return Op::finish(acc, zq[e], xc, base, p0, p1);
     };
     const bool first = difference && l == 0;
@@ -92,8 +100,9 @@ __global__ void __launch_bounds__(kTensWarps * 32) tens_vs_seq_kernel(const Tens
   __syncwarp();
   const int ncols = P.col_end - P.col_begin;
   const int nl = blockIdx.x * 32 + lane;
-  if (nl >= ncols) return;
-  const int n = P.col_begin + nl;
+  const bool live = nl < ncols;                           // lanes past the last column compute on a clamped column (the warp stays convergent for the table shuffle)
+  const int n = P.col_begin + (live ? nl : ncols - 1);
+  const double tab = exp2((double)lane * (1.0 / 32.0));
   const T* xblk = static_cast<const T*>(P.xp) + (size_t)n * P.xblk;
   const T* xsq = xblk + (size_t)P.L * DP;
   const T p0 = T(P.p0), p1 = T(P.p1);
@@ -102,17 +111,18 @@ __global__ void __launch_bounds__(kTensWarps * 32) tens_vs_seq_kernel(const Tens
   // epilogue (kernels.py:604-620) applied level by level
   T acc = T(0);
   auto emit = [&](int lvl, T v) {
+    if (!live) return;
     if (P.norm_x) v = v / gsqrt<T>(static_cast<const T*>(P.norm_x)[(size_t)lvl * P.N + n]);
     if (P.level_scale) v *= static_cast<const T*>(P.level_scale)[lvl];
     if (P.return_levels) static_cast<T*>(P.out)[((size_t)lvl * P.Mz + z) * ncols + nl] = v; else acc += v;
   };
   emit(0, T(1));
 #define GPSIG_LEVEL(I_) if (m >= I_) { constexpr int k = I_ * (I_ - 1) / 2; \
-    emit(I_, tens_level<T, DP, OP, I_>(zc + (size_t)k * zs * DP, zq + k * zs, zs, xblk, xsq, P.L, diff, P.base, p0, p1)); }
+    const T v_ = tens_level<T, DP, OP, I_>(zc + (size_t)k * zs * DP, zq + k * zs, zs, xblk, xsq, P.L, diff, P.base, p0, p1, tab); emit(I_, v_); }
   GPSIG_LEVEL(1) GPSIG_LEVEL(2) GPSIG_LEVEL(3) GPSIG_LEVEL(4)
   GPSIG_LEVEL(5) GPSIG_LEVEL(6) GPSIG_LEVEL(7) GPSIG_LEVEL(8)
 #undef GPSIG_LEVEL
-  if (!P.return_levels) static_cast<T*>(P.out)[(size_t)z * ncols + nl] = acc;
+  if (!P.return_levels && live) static_cast<T*>(P.out)[(size_t)z * ncols + nl] = acc;
 }
 
 template <typename T, int OP, int DP>

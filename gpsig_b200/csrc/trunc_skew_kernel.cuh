@@ -54,6 +54,9 @@ __host__ __device__ inline int skew_row_stride(int d, int elem) {
 #ifndef GPSIG_SKEW_TMEM_F32
 #define GPSIG_SKEW_TMEM_F32 0     // float32 tile in tensor memory as well (measured: no gain over registers at 12 warps, 20.4 vs 20.2 M pairs/s)
 #endif
+#ifndef GPSIG_SKEW_GS_F64
+#define GPSIG_SKEW_GS_F64 2
+#endif
 #ifndef GPSIG_SKEW_GS_F32
 #define GPSIG_SKEW_GS_F32 2
 #endif
@@ -149,26 +152,7 @@ __device__ __forceinline__ double exp_tab32(double x, double tab_lane) {
   return __hiloint2double(__double2hiint(res) + (k << 20), __double2loint(res));
 }
 
-// float64, base-2 exponent t (coordinates pre-scaled by sqrt(log2 e)): 9 FP64-pipe instructions.
-//   t = n/32 + f, n = round(32 t) by the magic-number add (exact, |f| <= 1/64),
-//   2^t = 2^(n>>5) * 2^((n&31)/32) * 2^f, table as above, 2^f - 1 = f*(c1 + ... + c5 f^4) minimax
-//   (1.4e-16 relative).  t is clamped to >= -1021 by an integer min on its sign/exponent word, so the
-//   exponent-field add never leaves the normal range (the result there is ~1e-307, i.e. 0 at any tolerance).
-__device__ __forceinline__ double exp2_tab32(double t, double tab_lane) {
-  const unsigned hi = min((unsigned)__double2hiint(t), 0xC08FE800u);
-  t = __hiloint2double((int)hi, __double2loint(t));
-  const double s = t + 0x1.8p+47;
-  const int n = __double2loint(s);
-  const double f = t - (s - 0x1.8p+47);
-  const double tj = __shfl_sync(0xffffffffu, tab_lane, n);          // source lane = n mod 32
-  double q = fma(0x1.5d886e6d047f4p-10, f, 0x1.3b2b1bee89b8dp-7);
-  q = fma(q, f, 0x1.c6b08d70300ecp-5);
-  q = fma(q, f, 0x1.ebfbdff8131c3p-3);
-  q = fma(q, f, 0x1.62e42fefa39efp-1);
-  const double w = q * f;
-  const double res = fma(tj, w, tj);
-  return __hiloint2double(__double2hiint(res) + (n & ~31) * 32768, __double2loint(res));   // + (n >> 5) << 20
-}
+// exp2_tab32 (float64, base-2 exponent, 9 FP64-pipe instructions) lives in common.cuh
 
 template <int N, typename F, int I = 0>
 __device__ __forceinline__ void static_for(F&& f) {
@@ -392,7 +376,7 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
     T Mc[R][COLS];
     // tensor-memory variant: the tile arrives in groups of GS columns x 4 dimensions; group g+1 is
     // requested before the FMAs of group g, its wait comes after them (wait::ld covers all loads in flight)
-    constexpr int GS = sizeof(T) == 8 ? 4 : GPSIG_SKEW_GS_F32;
+    constexpr int GS = sizeof(T) == 8 ? GPSIG_SKEW_GS_F64 : GPSIG_SKEW_GS_F32;
     constexpr int NG = (COLS + GS - 1) / GS;          // groups per 4-dimension chunk
     constexpr int NGT = NG * KC;
     constexpr int NCH = R + R * (MLEV - 1) + 1;       // chain values per step
