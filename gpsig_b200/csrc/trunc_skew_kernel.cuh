@@ -154,6 +154,47 @@ __device__ __forceinline__ double exp_tab32(double x, double tab_lane) {
 
 // exp2_tab32 (float64, base-2 exponent, 9 FP64-pipe instructions) lives in common.cuh
 
+// ---- packed FP32 pairs (Blackwell FFMA2 / FADD2: two FP32 operations per lane and issue slot) ---------
+// The float32 kernel is bound by issue slots (75 % busy, profiles/r01f_ncu_trunc_skew_f32.txt); its FP32
+// work on ADJACENT COLUMNS (contraction, first differences, level updates) can be issued as packed pairs:
+// same flops, half the instructions (measured: FFMA2 at 1.9 warp-instr/clk/SM = the FFMA flop rate).
+// OFF by default: with the operands where they are today the pairs have to be assembled with MOVs every
+// step (x duplicated into a register pair, the y columns re-paired out of their float4 registers), which
+// costs more than the packing saves: 19.0 M pairs/s against 20.1 M at c2.  It needs the x rows stored
+// duplicated in shared memory and the y tile loaded as column pairs (next round).
+#ifndef GPSIG_SKEW_PACK_F32
+#define GPSIG_SKEW_PACK_F32 0
+#endif
+using u64 = unsigned long long;
+__device__ __forceinline__ u64 pk2(float lo, float hi) { u64 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void unpk2(u64 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+template <typename T> struct PairOps {          // generic: two scalar operations
+  static constexpr bool kPacked = false;
+  static __device__ __forceinline__ void fma(T& a0, T& a1, T x0, T x1, T y0, T y1) { a0 = gfma<T>(x0, y0, a0); a1 = gfma<T>(x1, y1, a1); }
+  static __device__ __forceinline__ void add(T& r0, T& r1, T a0, T a1, T b0, T b1) { r0 = a0 + b0; r1 = a1 + b1; }
+  static __device__ __forceinline__ void sub(T& r0, T& r1, T a0, T a1, T b0, T b1) { r0 = a0 - b0; r1 = a1 - b1; }
+};
+#if GPSIG_SKEW_PACK_F32
+template <> struct PairOps<float> {
+  static constexpr bool kPacked = true;
+  static __device__ __forceinline__ void fma(float& a0, float& a1, float x0, float x1, float y0, float y1) {
+    u64 a = pk2(a0, a1);
+    asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(a) : "l"(pk2(x0, x1)), "l"(pk2(y0, y1)));
+    unpk2(a, a0, a1);
+  }
+  static __device__ __forceinline__ void add(float& r0, float& r1, float a0, float a1, float b0, float b1) {
+    u64 r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk2(a0, a1)), "l"(pk2(b0, b1)));
+    unpk2(r, r0, r1);
+  }
+  static __device__ __forceinline__ void sub(float& r0, float& r1, float a0, float a1, float b0, float b1) {
+    u64 r;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk2(a0, a1)), "l"(pk2(b0, b1)));
+    unpk2(r, r0, r1);
+  }
+};
+#endif
+
 template <int N, typename F, int I = 0>
 __device__ __forceinline__ void static_for(F&& f) {
   if constexpr (I < N) { f(std::integral_constant<int, I>{}); static_for<N, F, I + 1>(static_cast<F&&>(f)); }
@@ -456,6 +497,25 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
 #pragma unroll
         for (int rr = 0; rr < R; ++rr)
           xv[rr] = *reinterpret_cast<const V16*>(xb + (size_t)min(r0 + rr, L - 1) * RS + kv * V);
+        if constexpr (PairOps<T>::kPacked && YREG) {
+          // adjacent columns as packed pairs (the y pairs are loop invariant: packed once by the compiler)
+#pragma unroll
+          for (int c = 0; c + 1 < COLS; c += 2) {
+            const V16 ya = yreg[YREG ? c : 0][YREG ? kv : 0], yb = yreg[YREG ? c + 1 : 0][YREG ? kv : 0];
+#pragma unroll
+            for (int rr = 0; rr < R; ++rr)
+#pragma unroll
+              for (int e = 0; e < V; ++e)
+                PairOps<T>::fma(acc[rr][c], acc[rr][c + 1], vget(xv[rr], e), vget(xv[rr], e), vget(ya, e), vget(yb, e));
+          }
+          if (COLS & 1) {
+            const V16 yv = yreg[YREG ? COLS - 1 : 0][YREG ? kv : 0];
+#pragma unroll
+            for (int rr = 0; rr < R; ++rr)
+#pragma unroll
+              for (int e = 0; e < V; ++e) acc[rr][COLS - 1] = gfma<T>(vget(xv[rr], e), vget(yv, e), acc[rr][COLS - 1]);
+          }
+        } else {
 #pragma unroll
         for (int c = 0; c < COLS; ++c) {
           V16 yv;
@@ -465,6 +525,7 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
           for (int rr = 0; rr < R; ++rr)
 #pragma unroll
             for (int e = 0; e < V; ++e) acc[rr][c] = gfma<T>(vget(xv[rr], e), vget(yv, e), acc[rr][c]);
+        }
         }
       }
       }
@@ -485,12 +546,11 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
         // 2-D increment (signature_algs.py:26).  No masks: row 0 of a pair is consumed by the
         // first-row branch below, padded rows/columns repeat their neighbour (increment 0).
         T U[COLS];
+        auto curv = [&](int c) -> T { return (rr == R - 1) ? Mp[par ^ 1][c] : Mc[rr][c]; };
+        auto prvv = [&](int c) -> T { return (rr == 0) ? Mp[par][c] : Mc[rr > 0 ? rr - 1 : 0][c]; };
 #pragma unroll
-        for (int c = 0; c < COLS; ++c) {
-          const T cur = (rr == R - 1) ? Mp[par ^ 1][c] : Mc[rr][c];
-          const T prv = (rr == 0) ? Mp[par][c] : Mc[rr > 0 ? rr - 1 : 0][c];
-          U[c] = cur - prv;
-        }
+        for (int c = 0; c + 1 < COLS; c += 2) PairOps<T>::sub(U[c], U[c + 1], curv(c), curv(c + 1), prvv(c), prvv(c + 1));
+        if (COLS & 1) U[COLS - 1] = curv(COLS - 1) - prvv(COLS - 1);
         const T left = lane == 0 ? U[0] : recvU[rr];          // column -1 does not exist: D = 0 there
 #pragma unroll
         for (int c = 0; c < COLS; ++c) D[c] = U[c] - (c > 0 ? U[c - 1] : left);
@@ -555,6 +615,21 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
 #pragma unroll
         for (int l = MLEV - 2; l >= 0; --l) {
           T e = recv[rr][l];
+          if constexpr (PairOps<T>::kPacked && NT == COLS) {
+            T t[COLS];
+#pragma unroll
+            for (int c = 0; c < COLS; ++c) { t[c] = e; e += C[l][c]; }
+            const int ln = l + 1 < MLEV - 1 ? l + 1 : 0;
+#pragma unroll
+            for (int c = 0; c + 1 < COLS; c += 2) {
+              if (l == MLEV - 2) PairOps<T>::fma(Ct[c], Ct[c + 1 < NT ? c + 1 : 0], D[c], D[c + 1], t[c], t[c + 1]);
+              else PairOps<T>::fma(C[ln][c], C[ln][c + 1], D[c], D[c + 1], t[c], t[c + 1]);
+            }
+            if (COLS & 1) {
+              if (l == MLEV - 2) Ct[(COLS - 1) % NT] = gfma<T>(D[COLS - 1], t[COLS - 1], Ct[(COLS - 1) % NT]);
+              else C[ln][COLS - 1] = gfma<T>(D[COLS - 1], t[COLS - 1], C[ln][COLS - 1]);
+            }
+          } else {
 #pragma unroll
           for (int c = 0; c < COLS; ++c) {
             const T t = e;
@@ -562,10 +637,12 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
             if (l == MLEV - 2) Ct[c % NT] = gfma<T>(D[c], t, Ct[c % NT]);
             else C[l + 1 < MLEV - 1 ? l + 1 : 0][c] = gfma<T>(D[c], t, C[l + 1 < MLEV - 1 ? l + 1 : 0][c]);
           }
+          }
           send[rr][l] = e;
         }
 #pragma unroll
-        for (int c = 0; c < COLS; ++c) C[0][c] += D[c];
+        for (int c = 0; c + 1 < COLS; c += 2) PairOps<T>::add(C[0][c], C[0][c + 1], C[0][c], C[0][c + 1], D[c], D[c + 1]);
+        if (COLS & 1) C[0][COLS - 1] += D[COLS - 1];
       }
     }
     if (++kk == SPS) { kk = 0; ++sseg; ubuf_prev = ubuf; if (++ubuf == NB) ubuf = 0; }
