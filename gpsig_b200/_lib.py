@@ -83,6 +83,10 @@ def _load():
     lib.gpsig_fma_peak.argtypes = [i, i, i, vp, vp]
     lib.gpsig_pde_f64.restype = i
     lib.gpsig_pde_f64.argtypes = [vp, i, i, vp, i, i, i, vp, i, i, i, i, dbl, vp, vp, sz, vp]
+    lib.gpsig_pde_kdiag_vjp_workspace_bytes.restype = sz
+    lib.gpsig_pde_kdiag_vjp_workspace_bytes.argtypes = [i, i, i]
+    lib.gpsig_pde_kdiag_vjp_f64.restype = i
+    lib.gpsig_pde_kdiag_vjp_f64.argtypes = [vp, i, i, i, i, i, i, i, vp, vp, vp, sz, vp]
     return lib
 
 

@@ -72,6 +72,29 @@ class _TensTensLevels(torch.autograd.Function):
             None, None, None, None
 
 
+class _PdeKdiag(torch.autograd.Function):
+    """k(x_i, x_i) of the untruncated kernel with the REFERENCE's gradient (``_KdiagGrad``,
+    gpsig/kernels_pde.py:465-509 / ``_untrunc_cov_grad.py:25-77``): a continuous-adjoint formula, not the
+    derivative of the stencil -- kept as is so that training follows the reference's trajectory."""
+
+    @staticmethod
+    def forward(ctx, X, dyadic_order, rev_solver):
+        ctx.save_for_backward(X)
+        ctx.cfg = (dyadic_order, rev_solver)
+        return ops.pde(X.detach().contiguous(), None, dyadic_order=dyadic_order, gram=False)
+
+    @staticmethod
+    def backward(ctx, g):
+        (X,) = ctx.saved_tensors
+        dyadic_order, rev_solver = ctx.cfg
+        return ops.pde_kdiag_vjp(X.detach().contiguous(), g.contiguous(), dyadic_order=dyadic_order,
+                                 rev_solver=rev_solver), None, None
+
+
+def pde_kdiag(X, dyadic_order=0, rev_solver=0):
+    return _PdeKdiag.apply(X, int(dyadic_order), int(rev_solver))
+
+
 def trunc_levels(X, X2, m, base='linear', base_params=(), difference=True):
     return _TruncLevels.apply(X, X2, int(m), base, tuple(base_params), bool(difference), False)
 

@@ -10,6 +10,7 @@ shapes of the BASELINE configs (developer iteration).
 """
 import hashlib
 import os
+import re
 import subprocess
 import sys
 from concurrent.futures import ThreadPoolExecutor
@@ -38,9 +39,34 @@ def _stamp(extra):
     return h.hexdigest()
 
 
+_INC = re.compile(r'^\s*#\s*include\s+"([^"]+)"', re.M)
+
+
+def _closure(src, seen=None):
+    """Transitive closure of the quoted includes of one translation unit."""
+    seen = set() if seen is None else seen
+    src = os.path.normpath(src)
+    if src in seen or not os.path.exists(src):
+        return seen
+    seen.add(src)
+    for inc in _INC.findall(open(src).read()):
+        _closure(os.path.join(os.path.dirname(src), inc), seen)
+    return seen
+
+
+def _unit_stamp(u):
+    name, src, extra = u
+    h = hashlib.sha1()
+    for f in sorted(_closure(src)):
+        h.update(open(f, 'rb').read())
+    h.update(' '.join(FLAGS + extra + [name]).encode())
+    return h.hexdigest()
+
+
 def _units(fast):
     extra = (['-DGPSIG_FAST_BUILD'] if fast else []) + EXTRA
-    units = [('abi', os.path.join(CSRC, 'abi.cu'), extra)]
+    units = [('abi', os.path.join(CSRC, 'abi.cu'), extra),
+             ('pde_vjp', os.path.join(CSRC, 'pde_vjp.cu'), extra)]
     for t in ('float', 'double'):
         for op in (0, 1, 2):
             for dp in (4, 8, 16):
@@ -62,12 +88,16 @@ def build(force=False, fast=None, verbose=False):
     def compile_one(u):
         name, src, extra = u
         obj = os.path.join(OBJ, name + '.o')
+        ustamp = _unit_stamp(u)
+        if not force and os.path.exists(obj) and os.path.exists(obj + '.stamp') and open(obj + '.stamp').read() == ustamp:
+            return obj
         cmd = [NVCC] + FLAGS + extra + ['-I', CSRC, '-c', src, '-o', obj]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError('nvcc failed for %s:\n%s\n%s' % (name, ' '.join(cmd), r.stderr))
         if verbose and r.stderr.strip():
             print(r.stderr)
+        open(obj + '.stamp', 'w').write(ustamp)
         return obj
 
     with ThreadPoolExecutor(max_workers=os.cpu_count() or 4) as ex:

@@ -17,7 +17,7 @@ and ``SignatureLinear`` give the same ``Kdiag`` (SURVEY.md note N7).
 import numpy as np
 import torch
 
-from . import ops, settings
+from . import autograd, ops, settings
 
 
 class UntruncSignatureKernel:
@@ -80,8 +80,23 @@ class UntruncSignatureKernel:
         if not presliced:
             X = self._slice(X)
         Xs = self._seq(X)
+        if torch.is_grad_enabled() and (Xs.requires_grad or any(torch.is_tensor(p) and p.requires_grad
+                                                                for p in (self.lengthscales, self.sigma))):
+            return self._Kdiag_differentiable(Xs, rows)
         return ops.pde(Xs, None, dyadic_order=self.order, gram=False, lengthscales=self._ls(Xs),
                        sigma=float(self.sigma), rows=rows)
+
+    def _Kdiag_differentiable(self, Xs, rows=None):
+        """Training path: the scaling by the lengthscales (kernels_pde.py:150-151) and ``sigma *`` (:185) are
+        torch expressions; the solve carries the reference's own backward (``autograd._PdeKdiag``):
+        1st-order reversed solve for ``implementation='cython'`` (sigKer_fast.pyx:50,61), 2nd-order for
+        ``'gpu_op'`` (_untrunc_cov_grad.py:44-49)."""
+        if rows is not None:
+            Xs = Xs[rows[0]:rows[1]]
+        if self.lengthscales is not None:
+            Xs = Xs / torch.as_tensor(self.lengthscales, dtype=Xs.dtype, device=Xs.device)[None, None, :]
+        rev_solver = 0 if self.implementation == 'cython' else 1
+        return self.sigma * autograd.pde_kdiag(Xs, self.order, rev_solver)
 
     def K(self, X, X2=None, presliced=False, rows=None):
         """Full untruncated Gram sigma * k(x_i, y_j) (extension, see module docstring)."""

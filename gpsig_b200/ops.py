@@ -210,3 +210,30 @@ def tens_tens_vjp(Z, grad_levels, num_levels, increments=False, base='linear', b
     with torch.cuda.device(Z.device):
         check(fn(desc, ptr(Z), Mz, int(increments), d, ptr(grad_levels.contiguous()), ptr(gradZ), stream_handle(Z.device)))
     return gradZ
+
+
+_PDE_VJP_WS_BYTES = 16 << 30   # grid scratch of one pde_kdiag_vjp call (8 P^2 bytes per sequence in flight)
+
+
+def pde_kdiag_vjp(X, grad_out, dyadic_order=0, rev_solver=0, rows=None):
+    """The reference's gradient of the PDE ``Kdiag`` w.r.t. the (scaled) sequences
+    (``_KdiagGrad``, gpsig/kernels_pde.py:465-509; ``rev_solver=1``: ``_untrunc_cov_grad.py:25-77``).
+    X ``[N, L, d]`` float64, grad_out ``[R]``; returns gradX ``[N, L, d]`` (zero outside ``rows``)."""
+    require_cuda(X, 'X')
+    if X.dtype != torch.float64:
+        raise TypeError("the PDE kernel is float64 only (as the reference: sigKer_fast.pyx:15)")
+    _same(grad_out, X, 'grad_out')
+    N, L, d = X.shape
+    rb, re = (0, N) if rows is None else rows
+    if grad_out.numel() != re - rb:
+        raise ValueError("grad_out must have one entry per row")
+    full = rb == 0 and re == N
+    gradX = torch.empty_like(X) if full else torch.zeros_like(X)
+    one = lib.gpsig_pde_kdiag_vjp_workspace_bytes(1, L, int(dyadic_order))
+    nseq = max(1, min(re - rb, _PDE_VJP_WS_BYTES // max(1, one)))
+    wsb = one * nseq
+    ws = workspace(wsb, X.device)
+    with torch.cuda.device(X.device):
+        check(lib.gpsig_pde_kdiag_vjp_f64(ptr(X), N, L, d, int(dyadic_order), int(rev_solver), rb, re, ptr(grad_out),
+                                          ptr(gradX), ptr(ws), wsb, stream_handle(X.device)))
+    return gradX

@@ -170,6 +170,23 @@ int gpsig_pde_f64(const double* X, int N, int L, const double* Y, int N2, int L2
                   int row_begin, int row_end, double sigma, double* out,
                   void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- reverse mode of the PDE kernel diagonal ----------------------------------
+ * The reference's hand-written gradient of Kdiag w.r.t. the sequences: `_KdiagGrad`
+ * (gpsig/kernels_pde.py:465-509, Cython path) / `_untrunc_cov_grad`
+ * (gpsig/covariance_op/_untrunc_cov_grad.py:25-77, TF op): the continuous adjoint
+ * sum_q K[p,q] K_rev[P-1-p,P-1-q] dx_q, NOT the derivative of the stencil.
+ *   X          [N, L, d] coordinates ALREADY divided by the lengthscales; gradients are w.r.t. those
+ *   rev_solver stencil of the reversed-path solve: 0 = 1st order (sigKer_fast.pyx:50,61, implementation
+ *              'cython'), 1 = 2nd order (the TF op re-runs `untrunc_cov`, implementation 'gpu_op')
+ *   grad_out   [row_end - row_begin] dL/dKdiag (fold sigma in)
+ *   gradX      [N, L, d]; rows [row_begin, row_end) are OVERWRITTEN
+ *   workspace  any multiple of gpsig_pde_kdiag_vjp_workspace_bytes(1, L, order) (8 P^2 bytes of grid scratch
+ *              per sequence in flight); the call runs the rows in chunks of what fits. */
+size_t gpsig_pde_kdiag_vjp_workspace_bytes(int nseq, int L, int dyadic_order);
+int gpsig_pde_kdiag_vjp_f64(const double* X, int N, int L, int d, int dyadic_order, int rev_solver,
+                            int row_begin, int row_end, const double* grad_out, double* gradX,
+                            void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- diagnostics (no reference counterpart; used by bench.py) ----------------
  * gpsig_launch_count: kernels this library has launched since it was loaded.
  * gpsig_profile_enable(1): from now on (this host thread) the launcher of each

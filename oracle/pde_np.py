@@ -75,3 +75,41 @@ def pde_gram(X, Y=None, n=0, solver=1, block=64):
             xb = np.broadcast_to(X[i][None], (yb.shape[0],) + X[i].shape)
             out[i, c:c + block] = pde_kernel(xb, yb, n, solver)
     return out
+
+
+def kdiag_grad_from_grids(x, K, K_rev, n=0):
+    """Transcription of the reference's hand-written gradient of ``Kdiag`` w.r.t. the (scaled) sequences,
+    given the two solution grids: ``_KdiagGrad`` (gpsig/kernels_pde.py:465-509, Cython path; the identical
+    tensor algebra is in ``covariance_op/_untrunc_cov_grad.py:52-77`` for the TF op).
+
+    x [A, L, d]; K, K_rev [A, P+1, P+1] FULL (already symmetrised, ``kernels_pde.py:481-486``) grids.
+    Returns ``grad_points`` [A, L, d] for an upstream gradient of 1 on every ``K[a, -1, -1]``.
+    """
+    x = np.asarray(x, dtype=np.float64)
+    A, M, D = x.shape
+    c = 2 ** n
+    inc_X = np.repeat((x[:, 1:, :] - x[:, :-1, :]) / float(c), c, axis=1)        # :489-490
+    K_rev_rev = K_rev[:, ::-1, ::-1]                                             # :493-494
+    KK = K[:, :-1, :-1] * K_rev_rev[:, 1:, 1:]                                   # :496
+    K_grad = (1. / c) * np.einsum('apq,aqd->apd', KK, inc_X)                     # :498-502
+    K_grad = K_grad.reshape(A, M - 1, c, D).sum(axis=2)                          # :504
+    z = np.zeros((A, 1, D))
+    return -2. * np.concatenate([K_grad, z], axis=1) + 2. * np.concatenate([z, K_grad], axis=1)   # :508
+
+
+def symmetrise_lower(K):
+    """``K += K^T - diag`` on a lower-triangular grid (kernels_pde.py:481-486)."""
+    K = np.array(K, dtype=np.float64)
+    d = np.einsum('aii->ai', K)
+    return K + K.transpose(0, 2, 1) - d[:, :, None] * np.eye(K.shape[1])[None]
+
+
+def pde_kdiag_grad(x, n=0, rev_solver=0):
+    """d Kdiag / d x as the reference computes it: forward grid from the 2nd-order stencil, reversed-path grid
+    from the 1st-order stencil (``rev_solver=0``: Cython path, pyx:50,61) or from the 2nd-order one
+    (``rev_solver=1``: the TF op solves the reversed increments with the same ``untrunc_cov`` kernel,
+    _untrunc_cov_grad.py:44-49)."""
+    x = np.asarray(x, dtype=np.float64)
+    K = pde_grid(x, None, n, solver=1)
+    K_rev = pde_grid(x[:, ::-1, :], None, n, solver=rev_solver)
+    return kdiag_grad_from_grids(x, K, K_rev, n)

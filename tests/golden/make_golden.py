@@ -4,7 +4,9 @@
     python tests/golden/make_golden.py
 
 * ``pde_ref.npz``    outputs of the REFERENCE's own compiled Cython solver
-                     (gpsig/sigKer_fast.pyx via oracle/build_ref.py) -- pins the PDE path.
+                     (gpsig/sigKer_fast.pyx via oracle/build_ref.py) -- pins the PDE path; the
+                     ``kdiag_grad_*`` entries are the reference's backward formula (a transcription of
+                     the TF algebra of ``_KdiagGrad``) evaluated on the reference's own two grids.
 * ``trunc_oracle.npz`` outputs of the numpy restatement of the TensorFlow path
                      (oracle/trunc_np.py) on seeded inputs -- pins later refactors of the
                      oracle and the CUDA path to today's numbers (the reference's TF-1.15
@@ -18,7 +20,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
 
-from oracle import build_ref, trunc_np  # noqa: E402
+from oracle import build_ref, pde_np, trunc_np  # noqa: E402
 from tests.util import brownian, inducing_tensors  # noqa: E402
 
 
@@ -34,6 +36,9 @@ def make_pde():
         K, K_rev = np.array(K), np.array(K_rev)
         out['kdiag_order%d' % order] = K[:, -1, -1]
         out['krev_corner_order%d' % order] = K_rev[:, -1, -1]
+        # the reference's hand-written backward (_KdiagGrad, kernels_pde.py:465-509) applied to ITS grids
+        out['kdiag_grad_order%d' % order] = pde_np.kdiag_grad_from_grids(
+            X, pde_np.symmetrise_lower(K), pde_np.symmetrise_lower(K_rev), order)
         if order < 2:
             out['grid_order%d' % order] = K[:2]
             out['grid_rev_order%d' % order] = K_rev[:2]

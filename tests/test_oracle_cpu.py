@@ -134,3 +134,12 @@ def test_pde_rectangular_reduces_to_symmetric():
     assert np.array_equal(pde_np.pde_kernel(X, X.copy(), 1), pde_np.pde_kernel(X, None, 1))
     G = pde_np.pde_gram(X, None, 0)
     assert np.allclose(G, G.T, rtol=1e-13)
+
+
+def test_pde_gradient_restatement_matches_reference_grids():
+    """The restated backward (oracle/pde_np.pde_kdiag_grad: grids from the numpy solver) against the same
+    formula evaluated on the grids of the reference's compiled Cython solver (golden)."""
+    g = np.load(os.path.join(GOLD, 'pde_ref.npz'))
+    for order in (0, 1, 2):
+        got = pde_np.pde_kdiag_grad(g['X'], order, rev_solver=0)
+        assert np.array_equal(got, g['kdiag_grad_order%d' % order])
