@@ -199,6 +199,21 @@ def other_configs(torch, ops, lib):
     out["c3_pde"] = {"workload": "kernels_pde Kdiag, N=1000, L=500, d=4, dyadic order 2 (P=1996)", "kernel": "pde_block_kernel",
                      "kernel_ms": ms, "pairs_per_s": N / (ms * 1e-3), "cells_per_s": cells / (ms * 1e-3),
                      "fp64_instr_per_cell": 3, "dtype": "f64"}
+    # c3 backward: the reference's _KdiagGrad formula (reversed grid through an HBM scratch, 16 P^2 bytes per sequence)
+    g = torch.ones(N, dtype=torch.float64, device='cuda')
+    ops.pde_kdiag_vjp(X, g, dyadic_order=order)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    ops.pde_kdiag_vjp(X, g, dyadic_order=order)
+    e1.record()
+    e1.synchronize()
+    ms = e0.elapsed_time(e1)
+    out["c3_pde_vjp"] = {"workload": "kernels_pde Kdiag backward (_KdiagGrad), N=1000, L=500, d=4, dyadic order 2", "kernel": "pde_vjp_sweep_kernel<0>+<1>",
+                         "ms": ms, "seqs_per_s": N / (ms * 1e-3), "cells_per_s": 2 * cells / (ms * 1e-3),
+                         "scratch_bytes_per_seq": 16.0 * P * P, "scratch_gbs": 16.0 * P * P * N / (ms * 1e-3) / 1e9, "dtype": "f64"}
+    del g
+    torch.cuda.empty_cache()
     # c4: inducing tensors vs sequences, N=10k, L=100, d=8, m=4, Mz=500 (increments)
     N, L, d, m, Mz = 10000, 100, 8, 4, 500
     Xn = brownian(N, L, d, 0)

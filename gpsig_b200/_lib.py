@@ -13,13 +13,15 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, os.environ.get('GPSIG_LIB_NAME', 'libgpsig_b200.so'))
 
 BASE_IDS = {'linear': 0, 'rbf': 1, 'cosine': 2, 'poly': 3, 'mix': 4,
-            'matern12': 5, 'matern32': 6, 'matern52': 7}
+            'matern12': 5, 'matern32': 6, 'matern52': 7, 'spectral': 8}
+SPECTRAL_FAMILIES = {'rbf': 0, 'exp': 1}
 PDE_DIAG, PDE_GRAM = 0, 1
 
 
 class TruncDesc(ctypes.Structure):
     _fields_ = [('base', ctypes.c_int), ('num_levels', ctypes.c_int), ('order', ctypes.c_int),
-                ('difference', ctypes.c_int), ('base_params', ctypes.c_double * 4)]
+                ('difference', ctypes.c_int), ('base_params', ctypes.c_double * 4),
+                ('spectral', ctypes.c_void_p), ('spectral_q', ctypes.c_int), ('spectral_family', ctypes.c_int)]
 
 
 class Epilogue(ctypes.Structure):
@@ -134,6 +136,16 @@ def make_desc(base, num_levels, order, difference, base_params=()):
     d.num_levels = int(num_levels)
     d.order = int(order)
     d.difference = int(bool(difference))
+    if base == 'spectral':
+        # base_params = (family, block): block = float64 CUDA tensor alpha[Q] ++ omega[Q, d] ++ gamma[Q, d], Q = block[0] size
+        family, q, block = base_params
+        if not (torch.is_tensor(block) and block.is_cuda and block.dtype == torch.float64 and block.is_contiguous()):
+            raise TypeError("gpsig_b200: the spectral parameter block must be a contiguous float64 CUDA tensor")
+        d.spectral = block.data_ptr()
+        d.spectral_q = int(q)
+        d.spectral_family = SPECTRAL_FAMILIES[family]
+        d._keep = block            # the descriptor only holds a raw pointer
+        base_params = ()
     bp = list(base_params) + [0.0] * 4
     for k in range(4):
         d.base_params[k] = float(bp[k])

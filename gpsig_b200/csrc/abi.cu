@@ -94,8 +94,14 @@ static int dispatch_tens_seq(const TensSeqParams& P, int base, int DP, int m, cu
 
 static int check_desc(const gpsig_trunc_desc* d) {
   if (!d) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "desc is NULL");
-  if (d->base < GPSIG_BASE_LINEAR || d->base > GPSIG_BASE_MATERN52)
+  if (d->base < GPSIG_BASE_LINEAR || d->base > GPSIG_BASE_SPECTRAL)
     GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "unknown base kernel id %d", d->base);
+  if (d->base == GPSIG_BASE_SPECTRAL) {
+    if (!d->spectral || d->spectral_q < 1 || d->spectral_q > 64)
+      GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "spectral base kernel needs its parameter block and 1 <= Q <= 64 (Q=%d)", d->spectral_q);
+    if (d->spectral_family != GPSIG_SPECTRAL_RBF && d->spectral_family != GPSIG_SPECTRAL_EXP)
+      GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "unknown spectral family %d", d->spectral_family);
+  }
   if (d->num_levels < 1) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "num_levels must be >= 1 (got %d)", d->num_levels);
   if (d->num_levels > 8) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "num_levels=%d > 8 is not supported", d->num_levels);
   if (d->order < 1 || d->order > d->num_levels)
@@ -146,7 +152,7 @@ static int trunc_gram_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   // order > 1: the general higher-order kernel; else the systolic kernel (padded rows) takes the
   // throughput shapes and trunc_gram_kernel the rest
-  const bool generic = desc->order > 1;
+  const bool generic = desc->order > 1 || desc->base == GPSIG_BASE_SPECTRAL;
   const bool skew = !generic && skew_eligible(L, L2, sizeof(T)) && getenv("GPSIG_NO_SKEW") == nullptr;
   const int RS = skew ? skew_row_stride(d, sizeof(T)) : padded_dim(d);
   T* xp = static_cast<T*>(ws);
@@ -179,6 +185,7 @@ static int trunc_gram_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
     G.xp = xp; G.yp = yp; G.xblk = P.xblk; G.yblk = P.yblk; G.N = N; G.N2 = N2; G.L = L; G.L2 = L2; G.DP = padded_dim(d);
     G.row_begin = row_begin; G.row_end = row_end; G.m = desc->num_levels; G.order = desc->order; G.difference = desc->difference;
     G.symmetric = sym; G.diag = 0; G.p0 = P.p0; G.p1 = P.p1; G.base = P.base;
+    G.sp.p = desc->spectral; G.sp.q = desc->spectral_q; G.sp.family = desc->spectral_family; G.d = d;
     G.norm_x = P.norm_x; G.norm_x2 = P.norm_x2; G.level_scale = P.level_scale; G.sym_jitter = P.sym_jitter;
     G.return_levels = P.return_levels; G.out = out;
     return launch_trunc_generic<T>(G, s);
@@ -212,12 +219,13 @@ static int trunc_diag_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
   P.symmetric = 1; P.diag = 1; P.return_levels = 1;
   P.p0 = desc->base_params[0]; P.p1 = desc->base_params[1]; P.base = desc->base;
   P.out = out;
-  if (desc->order > 1) {
+  if (desc->order > 1 || desc->base == GPSIG_BASE_SPECTRAL) {
     GenericParams G;
     memset(&G, 0, sizeof(G));
     G.xp = xp; G.yp = xp; G.xblk = G.yblk = P.xblk; G.N = N; G.N2 = N; G.L = L; G.L2 = L; G.DP = padded_dim(d);
     G.row_begin = 0; G.row_end = N; G.m = desc->num_levels; G.order = desc->order; G.difference = desc->difference;
     G.symmetric = 1; G.diag = 1; G.p0 = P.p0; G.p1 = P.p1; G.base = P.base; G.return_levels = 1; G.out = out;
+    G.sp.p = desc->spectral; G.sp.q = desc->spectral_q; G.sp.family = desc->spectral_family; G.d = d;
     return launch_trunc_generic<T>(G, s);
   }
   return dispatch_trunc<T>(P, desc->base, padded_dim(d), s);
@@ -255,7 +263,8 @@ static int tens_vs_seq_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, in
   if (epi) { P.norm_x = epi->norm_x2; P.level_scale = epi->level_scale; P.return_levels = epi->return_levels; }
   else P.return_levels = 1;
   P.out = out;
-  if (desc->order > 1) return launch_tens_seq_generic<T>(P, desc->order, padded_dim(d), s);
+  P.sp.p = desc->spectral; P.sp.q = desc->spectral_q; P.sp.family = desc->spectral_family; P.d = d;
+  if (desc->order > 1 || desc->base == GPSIG_BASE_SPECTRAL) return launch_tens_seq_generic<T>(P, desc->order, padded_dim(d), s);
   return dispatch_tens_seq<T>(P, desc->base, padded_dim(d), m, s);
 }
 
@@ -269,6 +278,8 @@ static int tens_tens_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, int 
   memset(&P, 0, sizeof(P));
   P.Z = Z; P.ls = ls; P.Mz = Mz; P.zs = increments ? 2 : 1; P.m = desc->num_levels; P.d = d;
   P.p0 = desc->base_params[0]; P.p1 = desc->base_params[1]; P.base = desc->base;
+  P.sp.p = desc->spectral; P.sp.q = desc->spectral_q; P.sp.family = desc->spectral_family;
+  if (d > 16) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "state dimension d=%d > 16 is not supported", d);
   if (epi) { P.level_scale = epi->level_scale; P.return_levels = epi->return_levels; } else P.return_levels = 1;
   P.out = out;
   dim3 grid((Mz + 127) / 128, Mz);
@@ -361,6 +372,7 @@ static int trunc_vjp_impl(const gpsig_trunc_desc* desc, const T* X, int N, int L
                           int pair_mode, int row_begin, int row_end, const T* grad_levels, T* gradX, T* gradX2,
                           void* ws, size_t ws_bytes, void* stream) {
   if (int rc = check_desc(desc)) return rc;
+  if (desc->base == GPSIG_BASE_SPECTRAL) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "reverse mode is not implemented for the spectral base kernel");
   if (desc->order != 1) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "reverse mode is implemented for order == 1 only (got %d)", desc->order);
   if (desc->num_levels > 8) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "reverse mode supports num_levels <= 8");
   const bool sym = X2 == nullptr;
@@ -405,6 +417,7 @@ static int tens_seq_vjp_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, i
                              int col_begin, int col_end, const T* grad_levels, T* gradZ, T* gradX,
                              void* ws, size_t ws_bytes, void* stream) {
   if (int rc = check_desc(desc)) return rc;
+  if (desc->base == GPSIG_BASE_SPECTRAL) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "reverse mode is not implemented for the spectral base kernel");
   if (desc->order != 1) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "reverse mode is implemented for order == 1 only (got %d)", desc->order);
   if (desc->num_levels > 8) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "reverse mode supports num_levels <= 8");
   if (!Z || !X || !grad_levels || !gradZ || !gradX) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "Z/X/grad_levels/gradZ/gradX must not be NULL");
@@ -439,6 +452,7 @@ template <typename T>
 static int tens_tens_vjp_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, int increments, int d, const T* grad_levels,
                               T* gradZ, void* stream) {
   if (int rc = check_desc(desc)) return rc;
+  if (desc->base == GPSIG_BASE_SPECTRAL) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "reverse mode is not implemented for the spectral base kernel");
   if (!Z || !grad_levels || !gradZ) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "Z/grad_levels/gradZ must not be NULL");
   if (d < 1 || d > 16) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "state dimension d=%d is not supported (1..16)", d);
   if (Mz == 0) return GPSIG_OK;

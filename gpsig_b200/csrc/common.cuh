@@ -114,6 +114,27 @@ __device__ __forceinline__ T base_eval(int base, T p0, T p1, T dot, T xs, T ys) 
   }
 }
 
+// Spectral mixture kernel on raw coordinates (kernels.py:1101-1122); x, y hold >= d values, parameters are doubles.
+struct SpectralParams { const double* p; int q, family; };
+template <typename T>
+__device__ __forceinline__ T spectral_eval(const SpectralParams& S, int d, const T* x, const T* y) {
+  const double* alpha = S.p; const double* omega = S.p + S.q; const double* gamma = omega + (size_t)S.q * d;
+  T tot = T(0);
+  for (int q = 0; q < S.q; ++q) {
+    T quad = T(0), ph = T(0);
+    for (int f = 0; f < d; ++f) {
+      const T df = x[f] - y[f];
+      const T t = df * T(gamma[q * d + f]);
+      quad += t * t;                                // reduce_sum(square(diff * gamma))
+      ph += df * T(omega[q * d + f]);               // reduce_sum(diff * omega)
+    }
+    const T kern = S.family == GPSIG_SPECTRAL_EXP ? gexp<T>(-gsqrt<T>(quad) / T(2)) : gexp<T>(-quad / T(2));
+    const T c = sizeof(T) == 8 ? T(cos(2. * 3.141592653589793 * (double)ph)) : T(cosf(2.f * 3.14159265358979f * (float)ph));
+    tot += kern * c * T(alpha[q]);
+  }
+  return tot;
+}
+
 // float64, base-2 exponent t (coordinates pre-scaled by sqrt(log2 e)): 9 FP64-pipe instructions.
 //   t = n/32 + f, n = round(32 t) by the magic-number add (exact, |f| <= 1/64),
 //   2^t = 2^(n>>5) * 2^((n&31)/32) * 2^f, table as above, 2^f - 1 = f*(c1 + ... + c5 f^4) minimax

@@ -29,6 +29,7 @@ struct GenericParams {
   int m, order, difference;
   int symmetric, diag;
   double p0, p1; int base;
+  SpectralParams sp; int d;             // GPSIG_BASE_SPECTRAL: parameter block and the true state dimension
   const void* norm_x; const void* norm_x2; const void* level_scale;
   double sym_jitter; int return_levels;
   void* out;
@@ -83,6 +84,7 @@ __global__ void __launch_bounds__(1024) trunc_generic_kernel(const GenericParams
 
   auto kappa = [&](int p, int qq) {
     const T* xr = x + (size_t)p * DP; const T* yr = y + (size_t)qq * DP;
+    if (P.base == GPSIG_BASE_SPECTRAL) return spectral_eval<T>(P.sp, P.d, xr, yr);
     T dot = T(0);
     for (int k = 0; k < DP; ++k) dot = gfma<T>(xr[k], yr[k], dot);
     return base_eval<T>(P.base, p0, p1, dot, xsq[p], ysq[qq]);
@@ -196,6 +198,7 @@ __global__ void __launch_bounds__(256) tens_seq_generic_kernel(const TensSeqPara
   auto kappa = [&](int t, int s, int l) {          // base kernel of tensor component (t, z, s) and x_n[l]
     const T* blk = static_cast<const T*>(P.zp) + ((size_t)t * P.Mz + z) * P.zblk;
     const T* zc = blk + s * DP; const T* xr = xblk + (size_t)l * DP;
+    if (P.base == GPSIG_BASE_SPECTRAL) return spectral_eval<T>(P.sp, P.d, zc, xr);
     T dot = T(0);
     for (int k = 0; k < DP; ++k) dot = gfma<T>(zc[k], xr[k], dot);
     return base_eval<T>(P.base, p0, p1, dot, blk[zs * DP + s], xsq[l]);

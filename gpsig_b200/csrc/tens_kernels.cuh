@@ -29,6 +29,7 @@ struct TensSeqParams {
   int col_begin, col_end;
   int difference;
   double p0, p1; int base;
+  SpectralParams sp; int d;   // GPSIG_BASE_SPECTRAL (general path only)
   const void* norm_x;  // [m+1, N] (already jittered) or NULL
   const void* level_scale;
   int return_levels;
@@ -149,6 +150,7 @@ struct TensTensParams {
   const void* ls;      // lengthscales [d] or NULL (kernels.py:367-399)
   int Mz, zs, m, d;
   double p0, p1; int base;
+  SpectralParams sp;
   const void* level_scale; int return_levels;
   void* out;           // [(m+1,)? Mz, Mz]
 };
@@ -165,6 +167,11 @@ __global__ void tens_tens_kernel(const TensTensParams P) {
   T* out = static_cast<T*>(P.out);
   const size_t MM = (size_t)P.Mz * P.Mz, ab = (size_t)a * P.Mz + b;
   auto kappa = [&](const T* za, const T* zb) {
+    if (P.base == GPSIG_BASE_SPECTRAL) {
+      T u[16], v[16];
+      for (int k = 0; k < d; ++k) { u[k] = za[k]; v[k] = zb[k]; if (len) { u[k] = u[k] / len[k]; v[k] = v[k] / len[k]; } }
+      return spectral_eval<T>(P.sp, d, u, v);
+    }
     T dot = T(0), xs = T(0), ys = T(0);
     for (int k = 0; k < d; ++k) {
       T u = za[k], v = zb[k];

@@ -153,11 +153,11 @@ class SignatureKernel:
 
     def _kw(self, like):
         # with lags the scaling has already been applied by _seq / _tens
-        return dict(base=self._base, base_params=self._get_base_params(), order=self.order,
+        return dict(base=self._base, base_params=self._get_base_params(like), order=self.order,
                     difference=self.difference,
                     lengthscales=None if self.num_lags > 0 else self._param(self.lengthscales, like))
 
-    def _get_base_params(self):
+    def _get_base_params(self, like=None):
         return self._base_params
 
     def _K_seq_diag(self, X):
@@ -336,7 +336,7 @@ class SignatureKernel:
             return self._d_tens_n_seq(Z, None, increments, False, return_levels, want=('zz',))['zz']
         Z = self._tens(Z, increments)   # Kzz does not depend on `order` (signature_algs.py:76-99)
         return ops.tens_tens(Z, self.num_levels, increments=increments, base=self._base,
-                             base_params=self._get_base_params(), lengthscales=self._kw(Z)['lengthscales'],
+                             base_params=self._get_base_params(Z), lengthscales=self._kw(Z)['lengthscales'],
                              level_scale=self._level_scale(Z), return_levels=return_levels)
 
     def K_tens_vs_seq(self, Z, X, return_levels=False, increments=False, presliced=False, cols=None):
@@ -367,7 +367,7 @@ class SignatureKernel:
         sc = self._level_scale(Xs)
         kw = self._kw(Xs)
         Kzz = ops.tens_tens(Z, self.num_levels, increments=increments, base=self._base,
-                            base_params=self._get_base_params(), lengthscales=kw['lengthscales'], level_scale=sc,
+                            base_params=self._get_base_params(Z), lengthscales=kw['lengthscales'], level_scale=sc,
                             return_levels=return_levels)
         diag = self._K_seq_diag(Xs)
         norm = diag + jitter if self.normalization else None
@@ -480,7 +480,7 @@ class SignaturePoly(SignatureKernel):
         self.gamma = float(gamma)
         self.degree = float(degree)
 
-    def _get_base_params(self):
+    def _get_base_params(self, like=None):
         return (self.gamma, self.degree)
 
 
@@ -500,8 +500,52 @@ class SignatureMix(SignatureKernel):
         SignatureKernel.__init__(self, input_dim, num_features, num_levels, **kwargs)
         self.mixing = 0.5
 
-    def _get_base_params(self):
+    def _get_base_params(self, like=None):
         return (float(self.mixing),)
+
+
+class SignatureSpectral(SignatureKernel):
+    """Spectral-mixture state-space embedding (kernels.py:1073-1122):
+    ``kappa(x, y) = sum_q alpha_q * k_q(gamma_q * (x - y)) * cos(2 pi omega_q . (x - y))`` with ``k_q`` Gaussian
+    (``family='gauss'|'gaussian'|'rbf'``) or exponential (``'exp'|'exponential'``).  As in the reference the
+    constructor passes ``lengthscales=None`` and draws ``alpha [Q]``, ``omega, gamma [Q, num_features]`` as
+    ``exp(randn)`` (:1092-1094).  Forward only, on the general (un-specialised) kernels.
+
+    Two reference defects are NOT reproduced: ``family='mixed'`` evaluates an undefined name ``Q`` (:1112) --
+    here it raises the same ``NameError`` when the kernel is evaluated; and ``_spectral`` broadcasts a batched
+    3-D input ``[N, L, d]`` as if it were 2-D (:1103, then ``tf.tile`` with 4 multiples on a 5-D tensor fails), so
+    in the reference ``Kdiag`` / ``normalization=True`` cannot be evaluated for this class -- here the batched
+    call means what it means for every other base kernel (each sequence against itself)."""
+    _base = 'spectral'
+
+    def __init__(self, input_dim, num_features, num_levels, family='gauss', Q=5, **kwargs):
+        SignatureKernel.__init__(self, input_dim, num_features, num_levels, lengthscales=None, **kwargs)
+        if family in ('exp', 'exponential'):
+            self.family = 'exp'
+        elif family in ('gauss', 'gaussian', 'rbf'):
+            self.family = 'rbf'
+        elif family in ('mixed', 'mix'):
+            self.family = 'mixed'
+        else:
+            raise ValueError("Unrecognized spectral family name.")
+        self.Q = Q
+        self.alpha = np.exp(np.random.randn(Q))
+        self.omega = np.exp(np.random.randn(Q, self.num_features))
+        self.gamma = np.exp(np.random.randn(Q, self.num_features))
+
+    def _get_base_params(self, like=None):
+        if self.family == 'mixed':
+            raise NameError("name 'Q' is not defined")           # kernels.py:1112
+        dev = settings.device() if like is None else like.device
+        d = self.num_features * (self.num_lags + 1)
+        omega, gamma = np.asarray(self.omega, dtype=np.float64), np.asarray(self.gamma, dtype=np.float64)
+        if omega.shape != (self.Q, d) or gamma.shape != (self.Q, d) or np.asarray(self.alpha).shape != (self.Q,):
+            raise ValueError("alpha / omega / gamma must have shapes [Q], [Q, d], [Q, d]")
+        block = np.concatenate([np.asarray(self.alpha, dtype=np.float64).ravel(), omega.ravel(), gamma.ravel()])
+        return (self.family, self.Q, torch.as_tensor(block, dtype=torch.float64, device=dev).contiguous())
+
+    def _d_check(self):
+        raise NotImplementedError('gpsig_b200: gradients are not implemented for the spectral base kernel')
 
 
 class SignatureMatern12(SignatureKernel):

@@ -54,6 +54,10 @@ extern "C" {
 #define GPSIG_BASE_MATERN12 5 /* _Matern12 kernels.py:1135 */
 #define GPSIG_BASE_MATERN32 6 /* _Matern32 kernels.py:1154 */
 #define GPSIG_BASE_MATERN52 7 /* _Matern52 kernels.py:1171 */
+#define GPSIG_BASE_SPECTRAL 8 /* _spectral kernels.py:1101-1122: sum_q alpha_q exp(-|gamma_q*(x-y)|^2 / 2) cos(2 pi omega_q.(x-y))
+                                 ('rbf' family) or exp(-|gamma_q*(x-y)| / 2) ('exp' family); forward only, general path */
+#define GPSIG_SPECTRAL_RBF 0
+#define GPSIG_SPECTRAL_EXP 1
 
 /* What the truncated kernel computes (constructor state of
  * gpsig/kernels.py:19-89 that reaches the numerics). */
@@ -63,6 +67,11 @@ typedef struct gpsig_trunc_desc {
   int order;             /* 1..m (kernels.py:58); 1 = first-order recursion */
   int difference;        /* kernels.py:64; 1 = difference the lifted Gram */
   double base_params[4]; /* POLY: {gamma, degree}; MIX: {mixing} */
+  /* SPECTRAL only: device array of DOUBLES (whatever the data type) alpha[Q], omega[Q, d], gamma[Q, d]
+   * (kernels.py:1092-1094), Q = spectral_q in 1..64, spectral_family = GPSIG_SPECTRAL_*. */
+  const double* spectral;
+  int spectral_q;
+  int spectral_family;
 } gpsig_trunc_desc;
 
 /* How raw levels K_l become the returned matrix (kernels.py:431-434,456-477):

@@ -104,7 +104,23 @@ def base_matern52(X, X2=None, **kw):
     return (1.0 + np.sqrt(5.) * r + 5. / 3. * np.square(r)) * np.exp(-np.sqrt(5.) * r)
 
 
+def base_spectral(X, X2=None, family='rbf', alpha=None, omega=None, gamma=None, **kw):
+    """gpsig/kernels.py:1101-1122 (``_spectral``), families 'rbf' and 'exp'; alpha [Q], omega/gamma [Q, d].
+    2-D inputs ``[n, d] x [n2, d]`` exactly as the reference broadcasts them (:1103-1105); a batched 3-D input
+    ``[N, L, d]`` is evaluated per batch entry (the reference's expression does not support it, see
+    gpsig_b200.kernels.SignatureSpectral)."""
+    Y = X if X2 is None else X2
+    diff = X[..., :, None, :] - Y[..., None, :, :]                                   # [..., n, n2, d]
+    out = np.zeros(diff.shape[:-1], dtype=X.dtype)
+    for q in range(len(alpha)):
+        quad = np.sum(np.square(diff * gamma[q]), axis=-1)
+        kern = np.exp(-np.sqrt(quad) / 2) if family == 'exp' else np.exp(-quad / 2)   # :1108, :1110
+        out = out + kern * np.cos(2. * np.pi * np.sum(diff * omega[q], axis=-1)) * alpha[q]   # :1117, :1122
+    return out
+
+
 BASE_KERNELS = {
+    'spectral': base_spectral,
     'linear': base_lin, 'cosine': base_cos, 'poly': base_poly, 'rbf': base_rbf,
     'mix': base_mix, 'matern12': base_matern12, 'matern32': base_matern32,
     'matern52': base_matern52,

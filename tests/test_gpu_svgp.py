@@ -1,0 +1,125 @@
+"""GPU parity of the SVGP glue around the hot path: ``Kuu`` / ``Kuf`` / ``Kuu_Kuf_Kff``
+(gpsig/inducing_variables.py:51-137) and the conditional of ``SVGP._build_predict`` (gpsig/models.py:109-131)."""
+import numpy as np
+import pytest
+import torch
+
+from tests.util import brownian, inducing_tensors, rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+def _dev(a, dtype=torch.float64):
+    return torch.as_tensor(np.ascontiguousarray(a), dtype=dtype, device='cuda')
+
+
+@pytest.mark.parametrize("increments", [False, True])
+@pytest.mark.parametrize("learn_weights", [False, True])
+def test_inducing_tensors_covariances(increments, learn_weights):
+    from gpsig_b200 import kernels
+    from gpsig_b200.inducing_variables import InducingTensors, Kuf, Kuu, Kuu_Kuf_Kff
+    from oracle import svgp_np
+    from oracle.trunc_np import SignatureKernelOracle
+    N, L, d, m, Mz = 23, 19, 3, 3, 6
+    X = brownian(N, L, d, 50)
+    Z = inducing_tensors(X, m, Mz, increments, 51)
+    ls = np.array([0.9, 1.1, 1.3])
+    k = kernels.SignatureRBF(L * d, d, m, lengthscales=ls)
+    o = SignatureKernelOracle(L * d, d, m, base='rbf', lengthscales=ls)
+    feat = InducingTensors(_dev(Z), m, increments=increments, learn_weights=learn_weights)
+    W = None
+    if learn_weights:
+        W = np.eye(Mz)[None] + 0.1 * np.random.default_rng(52).standard_normal((m, Mz, Mz))
+        feat.W = _dev(W)
+    Xd = _dev(X.reshape(N, -1))
+    rzz, rzx, rxx = svgp_np.Kuu_Kuf_Kff(o, Z, X.reshape(N, -1), increments=increments, W=W, jitter=1e-6)
+    Kzz, Kzx, Kxx = Kuu_Kuf_Kff(feat, k, Xd, jitter=1e-6)
+    for g, r in ((Kzz, rzz), (Kzx, rzx), (Kxx, rxx)):
+        assert rel_err(g.cpu().numpy(), r) < 1e-10
+    assert rel_err(Kuu(feat, k, jitter=1e-6).cpu().numpy(), rzz) < 1e-10
+    assert rel_err(Kuf(feat, k, Xd).cpu().numpy(), rzx) < 1e-10
+    with pytest.raises(NameError):      # the reference's own defect, inducing_variables.py:60
+        Kuu_Kuf_Kff(feat, k, Xd, jitter=1e-6, full_f_cov=True)
+
+
+@pytest.mark.parametrize("learn_weights", [False, True])
+def test_inducing_sequences_covariances(learn_weights):
+    from gpsig_b200 import kernels
+    from gpsig_b200.inducing_variables import InducingSequences, Kuf, Kuu, Kuu_Kuf_Kff
+    from oracle import svgp_np
+    from oracle.trunc_np import SignatureKernelOracle
+    N, L, Lz, d, m, Mz = 11, 16, 16, 2, 3, 5
+    X, Zs = brownian(N, L, d, 53), brownian(Mz, Lz, d, 54)
+    k = kernels.SignatureLinear(L * d, d, m)
+    o = SignatureKernelOracle(L * d, d, m, base='linear')
+    feat = InducingSequences(_dev(Zs), m, learn_weights=learn_weights)
+    W = None
+    if learn_weights:
+        W = np.eye(Mz)[None] + 0.1 * np.random.default_rng(55).standard_normal((m, Mz, Mz))
+        feat.W = _dev(W)
+    Xd = _dev(X.reshape(N, -1))
+    rzz, rzx, rxx = svgp_np.Kuu_Kuf_Kff(o, Zs.reshape(Mz, -1), X.reshape(N, -1), W=W, jitter=1e-6, sequences=True)
+    Kzz, Kzx, Kxx = Kuu_Kuf_Kff(feat, k, Xd, jitter=1e-6)
+    for g, r in ((Kzz, rzz), (Kzx, rzx), (Kxx, rxx)):
+        assert rel_err(g.cpu().numpy(), r) < 1e-10
+    # Kuu / Kuf go through ``kern.K`` (:101-121), which normalises once -- unlike K_seq_n_seq_covs, whose Kzx and
+    # Kzz the reference divides twice (kernels.py:746,783; kept as is)
+    Zf = Zs.reshape(Mz, -1)
+    if learn_weights:
+        ezz = svgp_np.mix_levels(W, Kzz=o.K(Zf, return_levels=True)) + 1e-6 * np.eye(Mz)
+        ezx = svgp_np.mix_levels(W, Kzx=o.K(Zf, X.reshape(N, -1), return_levels=True))
+    else:
+        ezz, ezx = o.K(Zf) + 1e-6 * np.eye(Mz), o.K(Zf, X.reshape(N, -1))
+    assert rel_err(Kuu(feat, k, jitter=1e-6).cpu().numpy(), ezz) < 1e-10
+    assert rel_err(Kuf(feat, k, Xd).cpu().numpy(), ezx) < 1e-10
+
+
+@pytest.mark.parametrize("whiten", [True, False])
+@pytest.mark.parametrize("q_diag", [False, True])
+def test_build_predict_matches_restated_conditional(whiten, q_diag):
+    """``SVGP._build_predict`` (models.py:109-131): covariances from the CUDA kernels + the conditional."""
+    from gpsig_b200 import conditionals, kernels, settings
+    from gpsig_b200.inducing_variables import InducingTensors
+    from oracle import svgp_np
+    from oracle.trunc_np import SignatureKernelOracle
+    N, L, d, m, Mz, R = 31, 25, 4, 4, 9, 3
+    X = brownian(N, L, d, 56)
+    Z = inducing_tensors(X, m, Mz, True, 57)
+    k = kernels.SignatureRBF(L * d, d, m)
+    o = SignatureKernelOracle(L * d, d, m, base='rbf')
+    rng = np.random.default_rng(58)
+    q_mu = rng.standard_normal((Mz, R))
+    q_sqrt = np.abs(rng.standard_normal((Mz, R))) if q_diag else np.tril(rng.standard_normal((R, Mz, Mz)))
+    feat = InducingTensors(_dev(Z), m, increments=True)
+    mean, var, Kzz = conditionals.build_predict(feat, k, _dev(X.reshape(N, -1)), _dev(q_mu), None, whiten=whiten, return_Kzz=True)
+    rzz, rzx, rxx = svgp_np.Kuu_Kuf_Kff(o, Z, X.reshape(N, -1), increments=True, jitter=settings.jitter)
+    rm, rv = svgp_np.base_conditional(rzx, rzz, rxx, q_mu, white=whiten)
+    assert rel_err(mean.cpu().numpy(), rm) < 1e-8 and rel_err(var.cpu().numpy(), rv) < 1e-8
+    mean, var = conditionals.base_conditional(_dev(rzx), _dev(rzz), _dev(rxx), _dev(q_mu), q_sqrt=_dev(q_sqrt), white=whiten)
+    rm, rv = svgp_np.base_conditional(rzx, rzz, rxx, q_mu, q_sqrt=q_sqrt, white=whiten)
+    assert rel_err(mean.cpu().numpy(), rm) < 1e-9 and rel_err(var.cpu().numpy(), rv) < 1e-9
+    if not q_diag:
+        mean, var = conditionals.base_conditional(_dev(rzx), _dev(rzz), _dev(o.K(X.reshape(N, -1))), _dev(q_mu), q_sqrt=_dev(q_sqrt),
+                                                  white=whiten, full_cov=True)
+        rm, rv = svgp_np.base_conditional(rzx, rzz, o.K(X.reshape(N, -1)), q_mu, q_sqrt=q_sqrt, white=whiten, full_cov=True)
+        assert rel_err(mean.cpu().numpy(), rm) < 1e-9 and rel_err(var.cpu().numpy(), rv) < 1e-9
+
+
+def test_elbo_style_gradients_flow_to_inducing_tensors():
+    """A training-style scalar of the predictive moments back-propagates to Z, W, lengthscales and q_mu
+    through the CUDA adjoints."""
+    from gpsig_b200 import conditionals, kernels
+    from gpsig_b200.inducing_variables import InducingTensors
+    N, L, d, m, Mz, R = 12, 14, 2, 3, 4, 1
+    X = brownian(N, L, d, 59)
+    Z = _dev(inducing_tensors(X, m, Mz, True, 60)).requires_grad_(True)
+    k = kernels.SignatureRBF(L * d, d, m)
+    k.lengthscales = _dev(np.ones(d)).requires_grad_(True)
+    feat = InducingTensors(Z, m, increments=True, learn_weights=True)
+    feat.W.requires_grad_(True)
+    q_mu = _dev(np.random.default_rng(61).standard_normal((Mz, R))).requires_grad_(True)
+    mean, var = conditionals.build_predict(feat, k, _dev(X.reshape(N, -1)), q_mu, None, whiten=True)
+    loss = (mean ** 2).sum() + var.sum()
+    loss.backward()
+    for t in (Z, feat.W, k.lengthscales, q_mu):
+        assert t.grad is not None and torch.isfinite(t.grad).all() and float(t.grad.abs().max()) > 0

@@ -146,3 +146,45 @@ def test_errors():
         ops.trunc_gram(torch.zeros(3, 4, 2, dtype=torch.float64, device='cuda'), None, 9)
     with pytest.raises(ValueError):
         ops.trunc_gram(torch.zeros(3, 4, 2, dtype=torch.float64, device='cuda'), None, 3, order=4)
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("family", ['rbf', 'exp'])
+def test_spectral_base_kernel(dtype, family):
+    """SignatureSpectral (kernels.py:1073-1122): K, Kdiag, inducing-tensor covariances vs the oracle."""
+    from gpsig_b200 import kernels
+    from oracle.trunc_np import SignatureKernelOracle
+    from tests.util import inducing_tensors
+    N, N2, L, L2, d, m, Mz, Q = 7, 5, 17, 12, 3, 3, 4, 4
+    X, Y = brownian(N, L, d, 31), brownian(N2, L2, d, 32)
+    rng = np.random.default_rng(33)
+    alpha, omega, gamma = np.exp(rng.standard_normal(Q)), np.exp(0.3 * rng.standard_normal((Q, d))), np.exp(rng.standard_normal((Q, d)))
+    tol = 1e-10 if dtype == torch.float64 else 2e-5
+    for normalization in (False, True):
+        k = kernels.SignatureSpectral(L * d, d, m, family=family, Q=Q, normalization=normalization)
+        assert k.lengthscales is None
+        k.alpha, k.omega, k.gamma = alpha, omega, gamma
+        o = SignatureKernelOracle(L * d, d, m, base='spectral', lengthscales=None, normalization=normalization,
+                                  family=family, alpha=alpha, omega=omega, gamma=gamma)
+        Xd, Yd = _dev(X.reshape(N, -1), dtype), _dev(Y.reshape(N2, -1), dtype)
+        k2 = kernels.SignatureSpectral(L2 * d, d, m, family=family, Q=Q, normalization=normalization)
+        assert rel_err(k.K(Xd, return_levels=True).cpu().numpy(), o.K(X.reshape(N, -1), return_levels=True)) < tol
+        assert rel_err(k.Kdiag(Xd, return_levels=True).cpu().numpy(), o.Kdiag(X.reshape(N, -1), return_levels=True)) < tol
+        for inc in (False, True):
+            Z = inducing_tensors(X, m, Mz, inc, 34)
+            got = k.K_tens_n_seq_covs(_dev(Z, dtype), Xd, increments=inc, return_levels=True)
+            ref = o.K_tens_n_seq_covs(Z, X.reshape(N, -1), increments=inc, return_levels=True)
+            for g, r in zip(got, ref):
+                assert rel_err(g.cpu().numpy(), r) < tol
+        del k2
+    # rectangular K(X, X2) needs equal L in the GPflow layout only per argument: raw op level
+    from gpsig_b200 import ops
+    blk = torch.as_tensor(np.concatenate([alpha, omega.ravel(), gamma.ravel()]), dtype=torch.float64, device='cuda')
+    got = ops.trunc_gram(_dev(X, dtype), _dev(Y, dtype), m, base='spectral', base_params=(family, Q, blk))
+    o = SignatureKernelOracle(L * d, d, m, base='spectral', lengthscales=None, normalization=False,
+                              family=family, alpha=alpha, omega=omega, gamma=gamma)
+    assert rel_err(got.cpu().numpy(), o._K_seq(X, Y)) < tol
+    with pytest.raises(NameError):
+        kernels.SignatureSpectral(L * d, d, m, family='mixed').K(_dev(X.reshape(N, -1), dtype))
+    with pytest.raises(ValueError):
+        kernels.SignatureSpectral(L * d, d, m, family='bogus')

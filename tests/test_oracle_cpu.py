@@ -143,3 +143,29 @@ def test_pde_gradient_restatement_matches_reference_grids():
     for order in (0, 1, 2):
         got = pde_np.pde_kdiag_grad(g['X'], order, rev_solver=0)
         assert np.array_equal(got, g['kdiag_grad_order%d' % order])
+
+
+def test_base_conditional_restatement_is_the_gaussian_conditional():
+    """oracle/svgp_np.base_conditional (GPflow 1.5.1 restated) against the closed form: for u ~ N(m, S),
+    f | u Gaussian => mean Knm Kmm^-1 m, cov Knn - Knm Kmm^-1 (Kmm - S) Kmm^-1 Kmn."""
+    from oracle import svgp_np
+    rng = np.random.default_rng(40)
+    M, N, R = 6, 9, 2
+    B = rng.standard_normal((M + N, M + N + 3))
+    Kall = B @ B.T
+    Kmm, Kmn, Knn = Kall[:M, :M], Kall[:M, M:], Kall[M:, M:]
+    f = rng.standard_normal((M, R))
+    q = np.tril(rng.standard_normal((R, M, M)))
+    mean, var = svgp_np.base_conditional(Kmn, Kmm, Knn, f, full_cov=True, q_sqrt=q, white=False)
+    Ki = np.linalg.inv(Kmm)
+    assert np.allclose(mean, Kmn.T @ Ki @ f, rtol=1e-9, atol=1e-9)
+    for r in range(R):
+        S = q[r] @ q[r].T
+        assert np.allclose(var[r], Knn - Kmn.T @ Ki @ (Kmm - S) @ Ki @ Kmn, rtol=1e-8, atol=1e-8)
+    md, vd = svgp_np.base_conditional(Kmn, Kmm, np.diag(Knn), f, full_cov=False, q_sqrt=q, white=False)
+    assert np.allclose(md, mean) and np.allclose(vd, np.stack([np.diag(v) for v in var], axis=1))
+    # whitened: u = Lm v, v ~ N(f, q q^T)
+    Lm = np.linalg.cholesky(Kmm)
+    mw, vw = svgp_np.base_conditional(Kmn, Kmm, np.diag(Knn), f, full_cov=False, q_sqrt=q, white=True)
+    mu, vu = svgp_np.base_conditional(Kmn, Kmm, np.diag(Knn), Lm @ f, full_cov=False, q_sqrt=np.matmul(Lm[None], q), white=False)
+    assert np.allclose(mw, mu) and np.allclose(vw, vu)
