@@ -212,7 +212,7 @@ def tens_tens_vjp(Z, grad_levels, num_levels, increments=False, base='linear', b
     return gradZ
 
 
-_PDE_VJP_WS_BYTES = 16 << 30   # grid scratch of one pde_kdiag_vjp call (8 P^2 bytes per sequence in flight)
+_PDE_VJP_WS_BYTES = 40 << 30   # cap on the grid scratch of one pde_kdiag_vjp call (8 P^2 bytes per sequence in flight)
 
 
 def pde_kdiag_vjp(X, grad_out, dyadic_order=0, rev_solver=0, rows=None):
@@ -230,7 +230,8 @@ def pde_kdiag_vjp(X, grad_out, dyadic_order=0, rev_solver=0, rows=None):
     full = rb == 0 and re == N
     gradX = torch.empty_like(X) if full else torch.zeros_like(X)
     one = lib.gpsig_pde_kdiag_vjp_workspace_bytes(1, L, int(dyadic_order))
-    nseq = max(1, min(re - rb, _PDE_VJP_WS_BYTES // max(1, one)))
+    budget = min(_PDE_VJP_WS_BYTES, torch.cuda.mem_get_info(X.device)[0] // 2)      # never more than half of what is free
+    nseq = max(1, min(re - rb, budget // max(1, one)))
     wsb = one * nseq
     ws = workspace(wsb, X.device)
     with torch.cuda.device(X.device):
