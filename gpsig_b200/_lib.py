@@ -26,7 +26,7 @@ class TruncDesc(ctypes.Structure):
 
 class Epilogue(ctypes.Structure):
     _fields_ = [('norm_x', ctypes.c_void_p), ('norm_x2', ctypes.c_void_p), ('level_scale', ctypes.c_void_p),
-                ('sym_jitter', ctypes.c_double), ('return_levels', ctypes.c_int)]
+                ('sym_jitter', ctypes.c_double), ('return_levels', ctypes.c_int), ('upper_only', ctypes.c_int)]
 
 
 class GpsigError(RuntimeError):
@@ -85,6 +85,10 @@ def _load():
     lib.gpsig_fma_peak.argtypes = [i, i, i, vp, vp]
     lib.gpsig_pde_f64.restype = i
     lib.gpsig_pde_f64.argtypes = [vp, i, i, vp, i, i, i, vp, i, i, i, i, dbl, vp, vp, sz, vp]
+    for sfx_ in ('f64', 'f32'):
+        fn = getattr(lib, 'gpsig_mirror_lower_' + sfx_)
+        fn.restype = i
+        fn.argtypes = [vp, i, i, vp]
     lib.gpsig_pde_kdiag_vjp_workspace_bytes.restype = sz
     lib.gpsig_pde_kdiag_vjp_workspace_bytes.argtypes = [i, i, i]
     lib.gpsig_pde_kdiag_vjp_f64.restype = i
@@ -152,11 +156,12 @@ def make_desc(base, num_levels, order, difference, base_params=()):
     return d
 
 
-def make_epilogue(norm_x=None, norm_x2=None, level_scale=None, sym_jitter=0.0, return_levels=True):
+def make_epilogue(norm_x=None, norm_x2=None, level_scale=None, sym_jitter=0.0, return_levels=True, upper_only=False):
     e = Epilogue()
     e.norm_x = None if norm_x is None else norm_x.data_ptr()
     e.norm_x2 = None if norm_x2 is None else norm_x2.data_ptr()
     e.level_scale = None if level_scale is None else level_scale.data_ptr()
     e.sym_jitter = float(sym_jitter)
     e.return_levels = int(bool(return_levels))
+    e.upper_only = int(bool(upper_only))
     return e

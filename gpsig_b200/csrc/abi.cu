@@ -66,6 +66,41 @@ __global__ void __launch_bounds__(256) fma_peak_kernel(T* out, int iters, T a, T
 GPSIG_DECL_T(float)
 GPSIG_DECL_T(double)
 
+// K(X, X) computed on and above the diagonal only: out[l, i, j] = out[l, j, i] for i > j (32 x 32 tiles through
+// shared memory, both sides coalesced).  Every i > j entry is overwritten, so the result is exactly symmetric.
+template <typename T>
+__global__ void __launch_bounds__(256) mirror_lower_kernel(T* out, int N, int nplanes) {
+  __shared__ T tile[32][33];
+  const int tj = blockIdx.x, ti = blockIdx.y;      // destination tile (rows ti, columns tj), ti >= tj
+  if (ti < tj) return;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int pl = blockIdx.z; pl < nplanes; pl += gridDim.z) {
+    T* o = out + (size_t)pl * N * N;
+    for (int r = ty; r < 32; r += 8) {             // source tile (rows tj, columns ti)
+      const int sr = tj * 32 + r, sc = ti * 32 + tx;
+      if (sr < N && sc < N) tile[r][tx] = o[(size_t)sr * N + sc];
+    }
+    __syncthreads();
+    for (int r = ty; r < 32; r += 8) {
+      const int dr = ti * 32 + r, dc = tj * 32 + tx;
+      if (dr < N && dc < N && dr > dc) o[(size_t)dr * N + dc] = tile[tx][r];
+    }
+    __syncthreads();
+  }
+}
+
+template <typename T>
+static int mirror_lower_impl(T* out, int N, int nplanes, void* stream) {
+  if (!out) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "out must not be NULL");
+  if (N < 0 || nplanes < 0) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "bad sizes N=%d nplanes=%d", N, nplanes);
+  if (N == 0 || nplanes == 0) return GPSIG_OK;
+  const int nt = (N + 31) / 32;
+  if (nt > 65535) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "matrix too large to mirror in one launch (N=%d)", N);
+  mirror_lower_kernel<T><<<dim3(nt, nt, nplanes < 64 ? nplanes : 64), 256, 0, static_cast<cudaStream_t>(stream)>>>(out, N, nplanes);
+  GPSIG_LAUNCH_CHECK("mirror_lower_kernel");
+  return GPSIG_OK;
+}
+
 static int op_of_base(int base) {
   return base == GPSIG_BASE_LINEAR ? OP_LINEAR : (base == GPSIG_BASE_RBF ? OP_RBF : OP_GENERIC);
 }
@@ -190,7 +225,17 @@ static int trunc_gram_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
     G.return_levels = P.return_levels; G.out = out;
     return launch_trunc_generic<T>(G, s);
   }
-  if (skew) return dispatch_skew<T>(P, desc->base, padded_dim(d), s);
+  if (skew) {
+    // the whole symmetric Gram in one call: compute the CTAs that touch i <= j, mirror the rest
+    const bool upper_only = sym && epi && epi->upper_only;
+    const bool auto_tri = sym && !upper_only && row_begin == 0 && row_end == N && N >= 64 && getenv("GPSIG_NO_TRI") == nullptr;
+    P.tri = upper_only || auto_tri;
+    if (int rc = dispatch_skew<T>(P, desc->base, padded_dim(d), s)) return rc;
+    if (auto_tri) {
+      if (int rc = mirror_lower_impl<T>(out, N, P.return_levels ? desc->num_levels + 1 : 1, stream)) return rc;
+    }
+    return GPSIG_OK;
+  }
   return dispatch_trunc<T>(P, desc->base, padded_dim(d), s);
 }
 
@@ -579,6 +624,8 @@ size_t gpsig_pde_workspace_bytes(int N, int L, int N2, int L2, int d, int order,
   (void)order; (void)pair_mode;
   return packed_bytes(N, L, d, 8) + (N2 > 0 ? packed_bytes(N2, L2, d, 8) : 0) + 128;   // + ticket counter of the persistent kernel
 }
+int gpsig_mirror_lower_f64(double* out, int N, int nplanes, void* stream) { return mirror_lower_impl<double>(out, N, nplanes, stream); }
+int gpsig_mirror_lower_f32(float* out, int N, int nplanes, void* stream) { return mirror_lower_impl<float>(out, N, nplanes, stream); }
 int gpsig_pde_f64(const double* X, int N, int L, const double* Y, int N2, int L2, int d, const double* ls,
                   int order, int pair_mode, int rb, int re, double sigma, double* out, void* ws, size_t wsb, void* stream) {
   return pde_impl(X, N, L, Y, N2, L2, d, ls, order, pair_mode, rb, re, sigma, out, ws, wsb, stream);

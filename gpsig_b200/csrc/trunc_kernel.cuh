@@ -42,6 +42,7 @@ struct TruncParams {
   int nchunks;             // column chunks of 32*COLS-1
   int x_in_smem;           // stage x_i with TMA (else broadcast loads from L1/L2)
   int symmetric;           // X2 == NULL
+  int tri;                 // symmetric Gram over all rows: CTAs strictly below the diagonal exit, mirror_lower_kernel fills them in
   int diag;                // pairs (i, i) only: one pair per warp, x rows read through L1
   double p0, p1; int base; // base-kernel parameters
   const void* norm_x; const void* norm_x2; const void* level_scale;

@@ -291,6 +291,8 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
   const int i_hi = min(P.row_end, i_lo + P.ichunk);
   const int npairs = i_hi - i_lo;
   const T* xg = static_cast<const T*>(P.xp);
+  // K(X, X): every pair of this CTA has i > j -> its mirror image (j, i) is computed elsewhere (whole CTA exits)
+  if (P.tri && i_lo >= (int)(blockIdx.x + 1) * NW) return;
 
   if (threadIdx.x == 0) {
     for (int b = 0; b < NB; ++b) { mbar_init(&full_bar[b], 1); mbar_init(&empty_bar[b], NW); }
@@ -680,6 +682,7 @@ int launch_skew_inst(TruncParams P, cudaStream_t stream) {
   const int rows = P.row_end - P.row_begin;
   // >= ~24 waves of CTAs over the 148 SMs, but >= 16 pairs per warp so the 31-step pipeline fill stays < 1 %
   int want_y = (24 * 148 + (int)grid.x - 1) / (int)grid.x;
+  if (P.tri) want_y *= 2;                         // half of the CTAs exit at once; smaller chunks also waste less along the diagonal
   int ichunk = (rows + want_y - 1) / want_y;
   if (ichunk < 16) ichunk = 16;
   if (ichunk > rows) ichunk = rows;

@@ -260,11 +260,13 @@ class SignatureKernel:
         return out
 
     # ---- public API ------------------------------------------------------------
-    def K(self, X, X2=None, presliced=False, return_levels=False, presliced_X=False, presliced_X2=False, rows=None):
+    def K(self, X, X2=None, presliced=False, return_levels=False, presliced_X=False, presliced_X2=False, rows=None,
+          upper_only=False):
         """Signature kernel between sequences (kernels.py:401-477).
 
         ``rows=(begin, end)`` (extension) restricts the computation to a row
-        block of the Gram -- the unit of multi-GPU sharding.
+        block of the Gram -- the unit of multi-GPU sharding.  ``upper_only`` (with ``X2=None``): the caller only
+        needs the entries on and above the diagonal of its rows (``sharding.sharded_gram`` mirrors the rest).
         """
         if presliced:
             presliced_X = presliced_X2 = True
@@ -288,7 +290,7 @@ class SignatureKernel:
                 norm = self._K_seq_diag(Xs) + jitter
             return ops.trunc_gram(Xs, None, self.num_levels, norm_x=norm, norm_x2=norm,
                                   level_scale=self._level_scale(Xs), sym_jitter=jitter if self.normalization else 0.0,
-                                  return_levels=return_levels, rows=rows, **kw)
+                                  return_levels=return_levels, rows=rows, upper_only=upper_only, **kw)
         X2s = self._seq(X2)
         n1 = n2 = None
         if self.normalization:                                       # kernels.py:456-470

@@ -22,11 +22,13 @@ def _same(t, ref, name):
 
 
 def trunc_gram(X, X2, num_levels, base='linear', base_params=(), order=1, difference=True, lengthscales=None,
-               norm_x=None, norm_x2=None, level_scale=None, sym_jitter=0.0, return_levels=True, rows=None):
+               norm_x=None, norm_x2=None, level_scale=None, sym_jitter=0.0, return_levels=True, rows=None,
+               upper_only=False):
     """Rows ``rows=(begin, end)`` (default all) of the truncated signature Gram.
 
     Replaces ``SignatureKernel._K_seq`` + epilogue (gpsig/kernels.py:209-238, 431-477).
-    Returns ``[m+1, R, N2]`` (``return_levels``) or ``[R, N2]``.
+    Returns ``[m+1, R, N2]`` (``return_levels``) or ``[R, N2]``.  ``upper_only`` (K(X, X), row-sharded callers):
+    entries below the diagonal may be left unwritten; complete the assembled matrix with ``mirror_lower``.
     """
     require_cuda(X, 'X')
     for t, n in ((X2, 'X2'), (lengthscales, 'lengthscales'), (norm_x, 'norm_x'), (norm_x2, 'norm_x2'),
@@ -41,7 +43,7 @@ def trunc_gram(X, X2, num_levels, base='linear', base_params=(), order=1, differ
     shape = (m + 1, re - rb, N2) if return_levels else (re - rb, N2)
     out = torch.empty(shape, dtype=X.dtype, device=X.device)
     desc = make_desc(base, m, order, difference, base_params)
-    epi = make_epilogue(norm_x, norm_x2, level_scale, sym_jitter, return_levels)
+    epi = make_epilogue(norm_x, norm_x2, level_scale, sym_jitter, return_levels, upper_only and X2 is None)
     esz = X.element_size()
     wsb = lib.gpsig_trunc_gram_workspace_bytes(N, L, 0 if X2 is None else N2, L2, d, esz)
     ws = workspace(wsb, X.device)
@@ -50,6 +52,17 @@ def trunc_gram(X, X2, num_levels, base='linear', base_params=(), order=1, differ
         check(fn(desc, ptr(X), N, L, ptr(X2), N2, L2, d, ptr(lengthscales), rb, re, epi, ptr(out), ptr(ws), wsb,
                  stream_handle(X.device)))
     return out
+
+
+def mirror_lower(K):
+    """In place ``K[..., i, j] = K[..., j, i]`` for i > j on a contiguous ``[N, N]`` or ``[P, N, N]`` CUDA tensor."""
+    require_cuda(K, 'K')
+    if K.dim() not in (2, 3) or K.shape[-1] != K.shape[-2]:
+        raise ValueError("mirror_lower needs [N, N] or [P, N, N]")
+    fn = getattr(lib, 'gpsig_mirror_lower_' + sfx(K.dtype))
+    with torch.cuda.device(K.device):
+        check(fn(ptr(K), K.shape[-1], 1 if K.dim() == 2 else K.shape[0], stream_handle(K.device)))
+    return K
 
 
 def trunc_diag(X, num_levels, base='linear', base_params=(), order=1, difference=True, lengthscales=None):

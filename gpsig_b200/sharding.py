@@ -58,10 +58,77 @@ def all_gather_rows(block, n_rows, group=None, row_dim=0):
     return out.movedim(0, row_dim)
 
 
-def sharded_gram(kernel, X, X2=None, return_levels=False, gather=True, group=None):
-    """``kernel.K(X, X2)`` with the rows split over the ranks; ``gather=True`` returns the full matrix on every rank."""
+def sym_row_ranges(n_rows, world_size, rank):
+    """K(X, X) with only the entries i <= j computed: row i costs N - i pairs, so rank r takes blocks r and
+    2G-1-r of a partition into 2G blocks -- every rank gets the same number of pairs."""
+    blocks = all_row_ranges(n_rows, 2 * world_size)
+    return [blocks[rank], blocks[2 * world_size - 1 - rank]]
+
+
+def _gather_into(full, blk, ranges, group, handles):
+    """All-gather one row block per rank (``ranges[r]`` = rows of rank r, uneven allowed) into ``full`` (rows on
+    dim 0).  Asynchronous: appends (work, finish) to ``handles``; ``finish()`` places the pieces."""
+    world = len(ranges)
+    maxr = max(e - b for b, e in ranges)
+    if maxr == 0:
+        return
+    pad = blk
+    if blk.shape[0] != maxr:
+        pad = blk.new_zeros((maxr,) + tuple(blk.shape[1:]))
+        pad[:blk.shape[0]] = blk
+    buf = blk.new_empty((world * maxr,) + tuple(blk.shape[1:]))
+    work = dist.all_gather_into_tensor(buf, pad.contiguous(), group=group, async_op=True)
+
+    def finish():
+        for r, (b, e) in enumerate(ranges):
+            full[b:e] = buf[r * maxr:r * maxr + (e - b)]
+    handles.append((work, finish))
+
+
+def sharded_gram(kernel, X, X2=None, return_levels=False, gather=True, group=None, tiles=1, mirror=None):
+    """``kernel.K(X, X2)`` with the rows split over the ranks; ``gather=True`` returns the full matrix on every rank.
+
+    * ``tiles > 1``: the rank's rows are computed in ``tiles`` pieces and the all-gather of a finished piece
+      (NCCL, its own stream) runs while the next piece is computed -- the collective hides behind the kernel.
+    * ``X2 is None`` and ``gather``: only the entries on and above the diagonal are computed
+      (``kernel.K(..., upper_only=True)`` on the mirrored row blocks of ``sym_row_ranges``), the assembled matrix
+      is completed by ``mirror`` (default ``gpsig_b200.ops.mirror_lower``): half the pairs, every rank the same share.
+    """
     n = X.shape[0]
-    blk, _ = sharded_rows(lambda b, e: kernel.K(X, X2, return_levels=return_levels, rows=(b, e)), n, group)
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    if world == 1:
+        return kernel.K(X, X2, return_levels=return_levels)
     if not gather:
-        return blk
-    return all_gather_rows(blk, n, group=group, row_dim=1 if return_levels else 0)
+        b, e = row_range(n, world, rank)
+        return kernel.K(X, X2, return_levels=return_levels, rows=(b, e))
+    sym = X2 is None
+    if sym:
+        per_rank = [sym_row_ranges(n, world, r) for r in range(world)]           # two blocks per rank
+    else:
+        per_rank = [[row_range(n, world, r)] for r in range(world)]
+    # split every block into `tiles` pieces (same piece count on every rank)
+    pieces = []                                                                    # [piece][rank] -> (b, e)
+    for k in range(len(per_rank[0])):
+        for t in range(max(1, int(tiles))):
+            pieces.append([tuple(bb + x for x in row_range(ee - bb, max(1, int(tiles)), t)) for bb, ee in (pr[k] for pr in per_rank)])
+    full = None
+    handles = []
+    for ranges in pieces:
+        b, e = ranges[rank]
+        kw = dict(upper_only=True) if sym else {}
+        blk = kernel.K(X, X2, return_levels=return_levels, rows=(b, e), **kw)
+        blk = blk.movedim(1, 0) if return_levels else blk                          # rows first
+        if full is None:
+            full = blk.new_empty((n,) + tuple(blk.shape[1:]))
+        _gather_into(full, blk, ranges, group, handles)
+    for work, finish in handles:
+        work.wait()
+        finish()
+    full = full.movedim(0, 1).contiguous() if return_levels else full
+    if sym:
+        if mirror is None:
+            from . import ops
+            mirror = ops.mirror_lower
+        full = mirror(full)
+    return full

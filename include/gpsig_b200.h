@@ -87,6 +87,10 @@ typedef struct gpsig_epilogue {
   const void* level_scale;
   double sym_jitter;
   int return_levels;
+  /* K(X, X) only, row-sharded callers: entries with i > j MAY be left unwritten (the fused kernel skips the CTAs
+   * that lie strictly below the diagonal); after assembling all rows complete the matrix with
+   * gpsig_mirror_lower_*.  A single call that covers all rows of K(X, X) does both by itself. */
+  int upper_only;
 } gpsig_epilogue;
 
 const char* gpsig_last_error_string(void);
@@ -105,6 +109,10 @@ int gpsig_trunc_gram_f32(const gpsig_trunc_desc* desc, const float* X, int N, in
                          const float* X2, int N2, int L2, int d, const float* lengthscales,
                          int row_begin, int row_end, const gpsig_epilogue* epi, float* out,
                          void* workspace, size_t workspace_bytes, void* stream);
+
+/* out[p, i, j] = out[p, j, i] for i > j on `nplanes` [N, N] planes (see gpsig_epilogue.upper_only). */
+int gpsig_mirror_lower_f64(double* out, int N, int nplanes, void* stream);
+int gpsig_mirror_lower_f32(float* out, int N, int nplanes, void* stream);
 
 /* ---- truncated kernel: diagonal k_l(x_i, x_i), raw levels out [m+1, N] ---- */
 size_t gpsig_trunc_diag_workspace_bytes(int N, int L, int d, int elem_size);

@@ -188,3 +188,33 @@ def test_spectral_base_kernel(dtype, family):
         kernels.SignatureSpectral(L * d, d, m, family='mixed').K(_dev(X.reshape(N, -1), dtype))
     with pytest.raises(ValueError):
         kernels.SignatureSpectral(L * d, d, m, family='bogus')
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("N,L", [(64, 70), (131, 80), (300, 66)])
+def test_symmetric_gram_triangular_mode(dtype, N, L):
+    """K(X, X) on the systolic kernel computes the CTAs touching i <= j and mirrors the rest: exactly symmetric,
+    equal (to tolerance) to K(X, X2 = X) and to the oracle on a sub-block, for levels and for the sum."""
+    from gpsig_b200 import kernels, ops
+    from oracle.trunc_np import SignatureKernelOracle
+    d, m = 3, 4
+    Xn = brownian(N, L, d, 70)
+    X = _dev(Xn.reshape(N, -1), dtype)
+    k = kernels.SignatureRBF(L * d, d, m)
+    for ret in (True, False):
+        Ks, Kf = k.K(X, return_levels=ret), k.K(X, X.clone(), return_levels=ret)
+        assert torch.equal(Ks, Ks.transpose(-1, -2))
+        # the jitter on the diagonal exists only in the symmetric call (kernels.py:432)
+        off = 1.0 - torch.eye(N, dtype=dtype, device='cuda')
+        scale = float(Kf.abs().max())
+        assert float(((Ks - Kf) * off).abs().max()) / scale < 10 * TOL[dtype]
+    raw = ops.trunc_gram(X.reshape(N, L, d), None, m, base='rbf')
+    assert torch.equal(raw, raw.transpose(1, 2))
+    o = SignatureKernelOracle(L * d, d, m, base='rbf', normalization=False)
+    sub = np.r_[0:5, N - 6:N]
+    ref = o._K_seq(Xn[sub], Xn[sub])
+    got = raw[:, sub][:, :, sub].cpu().numpy()
+    assert rel_err(got, ref) < TOL[dtype]
+    # row-sharded symmetric calls still work and agree to tolerance with the mirrored full matrix
+    parts = torch.cat([ops.trunc_gram(X.reshape(N, L, d), None, m, base='rbf', rows=r) for r in ((0, N // 3), (N // 3, N))], dim=1)
+    assert float((parts - raw).abs().max()) / float(raw.abs().max()) < TOL[dtype]

@@ -25,6 +25,22 @@ def _sharding():
     return mod
 
 
+def test_sym_row_ranges_balance_the_upper_triangle():
+    sh = _sharding()
+    for n in (8, 2000, 50001):
+        for w in (1, 2, 4, 8):
+            seen = np.zeros(n, dtype=int)
+            work = []
+            for r in range(w):
+                tot = 0
+                for b, e in sh.sym_row_ranges(n, w, r):
+                    seen[b:e] += 1
+                    tot += sum(n - i for i in range(b, e)) if n < 5000 else (e - b) * (2 * n - b - e + 1) // 2
+                work.append(tot)
+            assert (seen == 1).all()
+            assert max(work) - min(work) <= 2 * n + 4          # equal shares up to one row per block
+
+
 def test_row_ranges_partition():
     sh = _sharding()
     for n in (0, 1, 7, 8, 2000, 50001):
@@ -62,14 +78,43 @@ def _worker(rank, world, port, n, return_levels, q):
     class K:  # same call signature as gpsig_b200.kernels.SignatureKernel.K(..., rows=)
         @staticmethod
         def K(X_, X2_, return_levels=False, rows=None):
-            b, e = rows
+            b, e = rows if rows is not None else (0, n)
             full = o.K(X.reshape(n, -1)[b:e], Y.reshape(5, -1), return_levels=return_levels) if e > b else \
                 np.zeros(((m + 1, 0, 5) if return_levels else (0, 5)))
             return torch.from_numpy(np.ascontiguousarray(full))
 
-    out = sh.sharded_gram(K, torch.from_numpy(X.reshape(n, -1)), None, return_levels=return_levels, gather=True)
+    Yt = torch.from_numpy(Y.reshape(5, -1))
+    out = sh.sharded_gram(K, torch.from_numpy(X.reshape(n, -1)), Yt, return_levels=return_levels, gather=True)
     ref = o.K(X.reshape(n, -1), Y.reshape(5, -1), return_levels=return_levels)
     ok = out.shape == ref.shape and bool(np.array_equal(out.numpy(), ref))
+    # tiled (collective overlapped with the next tile's compute): same matrix
+    out2 = sh.sharded_gram(K, torch.from_numpy(X.reshape(n, -1)), Yt, return_levels=return_levels, gather=True, tiles=2)
+    ok = ok and bool(np.array_equal(out2.numpy(), ref))
+
+    class KS:  # symmetric: honours upper_only by POISONING the entries below the diagonal of its rows
+        @staticmethod
+        def K(X_, X2_, return_levels=False, rows=None, upper_only=False):
+            assert X2_ is None
+            b, e = rows if rows is not None else (0, n)
+            full = o.K(X.reshape(n, -1), return_levels=return_levels)
+            blk = np.array(full[..., b:e, :])
+            if upper_only:
+                for i in range(b, e):
+                    blk[..., i - b, :i] = np.nan
+            return torch.from_numpy(np.ascontiguousarray(blk))
+
+    def mirror(full):
+        a = full.numpy()
+        iu = np.triu_indices(n, 1)
+        a[..., iu[1], iu[0]] = a[..., iu[0], iu[1]]
+        return full
+
+    refs = o.K(X.reshape(n, -1), return_levels=return_levels)
+    refs = np.triu(refs) + np.swapaxes(np.triu(refs, 1), -1, -2)
+    for t in (1, 2):
+        outs = sh.sharded_gram(KS, torch.from_numpy(X.reshape(n, -1)), None, return_levels=return_levels, gather=True,
+                               tiles=t, mirror=mirror)
+        ok = ok and outs.shape == refs.shape and bool(np.array_equal(outs.numpy(), refs))
     q.put((rank, ok))
     dist.barrier()
     dist.destroy_process_group()
