@@ -90,7 +90,7 @@ def _load():
         fn.restype = i
         fn.argtypes = [vp, i, i, vp]
     lib.gpsig_pde_kdiag_vjp_workspace_bytes.restype = sz
-    lib.gpsig_pde_kdiag_vjp_workspace_bytes.argtypes = [i, i, i]
+    lib.gpsig_pde_kdiag_vjp_workspace_bytes.argtypes = [i, i, i, i]
     lib.gpsig_pde_kdiag_vjp_f64.restype = i
     lib.gpsig_pde_kdiag_vjp_f64.argtypes = [vp, i, i, i, i, i, i, i, vp, vp, vp, sz, vp]
     return lib

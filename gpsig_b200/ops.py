@@ -225,7 +225,7 @@ def tens_tens_vjp(Z, grad_levels, num_levels, increments=False, base='linear', b
     return gradZ
 
 
-_PDE_VJP_WS_BYTES = 40 << 30   # cap on the grid scratch of one pde_kdiag_vjp call (8 P^2 bytes per sequence in flight)
+_PDE_VJP_WS_BYTES = 96 << 30   # cap on the grid scratch of one pde_kdiag_vjp call (8 P^2 bytes per sequence in flight)
 
 
 def pde_kdiag_vjp(X, grad_out, dyadic_order=0, rev_solver=0, rows=None):
@@ -242,7 +242,7 @@ def pde_kdiag_vjp(X, grad_out, dyadic_order=0, rev_solver=0, rows=None):
         raise ValueError("grad_out must have one entry per row")
     full = rb == 0 and re == N
     gradX = torch.empty_like(X) if full else torch.zeros_like(X)
-    one = lib.gpsig_pde_kdiag_vjp_workspace_bytes(1, L, int(dyadic_order))
+    one = lib.gpsig_pde_kdiag_vjp_workspace_bytes(1, L, d, int(dyadic_order))
     budget = min(_PDE_VJP_WS_BYTES, torch.cuda.mem_get_info(X.device)[0] // 2)      # never more than half of what is free
     nseq = max(1, min(re - rb, budget // max(1, one)))
     wsb = one * nseq

@@ -197,9 +197,9 @@ int gpsig_pde_f64(const double* X, int N, int L, const double* Y, int N2, int L2
  *              'cython'), 1 = 2nd order (the TF op re-runs `untrunc_cov`, implementation 'gpu_op')
  *   grad_out   [row_end - row_begin] dL/dKdiag (fold sigma in)
  *   gradX      [N, L, d]; rows [row_begin, row_end) are OVERWRITTEN
- *   workspace  any multiple of gpsig_pde_kdiag_vjp_workspace_bytes(1, L, order) (8 P^2 bytes of grid scratch
+ *   workspace  any multiple of gpsig_pde_kdiag_vjp_workspace_bytes(1, L, d, order) (8 P^2 bytes of grid scratch
  *              per sequence in flight); the call runs the rows in chunks of what fits. */
-size_t gpsig_pde_kdiag_vjp_workspace_bytes(int nseq, int L, int dyadic_order);
+size_t gpsig_pde_kdiag_vjp_workspace_bytes(int nseq, int L, int d, int dyadic_order);
 int gpsig_pde_kdiag_vjp_f64(const double* X, int N, int L, int d, int dyadic_order, int rev_solver,
                             int row_begin, int row_end, const double* grad_out, double* gradX,
                             void* workspace, size_t workspace_bytes, void* stream);

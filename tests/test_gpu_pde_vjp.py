@@ -53,7 +53,7 @@ def test_pde_kdiag_vjp_rows_and_chunks():
     assert float(part[:2].abs().max()) == 0. and float(part[5:].abs().max()) == 0.
     old = ops._PDE_VJP_WS_BYTES
     try:
-        ops._PDE_VJP_WS_BYTES = 2 * ops.lib.gpsig_pde_kdiag_vjp_workspace_bytes(1, L, order)
+        ops._PDE_VJP_WS_BYTES = 2 * ops.lib.gpsig_pde_kdiag_vjp_workspace_bytes(1, L, d, order)
         chunked = ops.pde_kdiag_vjp(X, g, dyadic_order=order)
     finally:
         ops._PDE_VJP_WS_BYTES = old

@@ -2,6 +2,7 @@
 
     python tools/prof_case.py trunc f64 1000      # K(X, X2) raw levels, N=N2=1000, L=200, d=8, m=5
     python tools/prof_case.py pde 256 500 2       # PDE Kdiag, N=256, L=500, dyadic order 2
+    python tools/prof_case.py pde_vjp 296 500 2   # PDE Kdiag backward (two sweeps)
     python tools/prof_case.py tens f64 2000       # Kzx, N=2000, L=100, d=8, m=4, Mz=500
 """
 import os
@@ -34,6 +35,14 @@ elif what == 'pde':
     X = torch.as_tensor(brownian(N, L, 4, 0), dtype=torch.float64, device='cuda')
     for _ in range(2):
         K = ops.pde(X, None, dyadic_order=order)
+    torch.cuda.synchronize()
+    print(float(K.sum()))
+elif what == 'pde_vjp':
+    N, L, order = int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4])
+    X = torch.as_tensor(brownian(N, L, 4, 0), dtype=torch.float64, device='cuda')
+    g = torch.ones(N, dtype=torch.float64, device='cuda')
+    for _ in range(2):
+        K = ops.pde_kdiag_vjp(X, g, dyadic_order=order)
     torch.cuda.synchronize()
     print(float(K.sum()))
 elif what == 'tens':
