@@ -24,7 +24,6 @@ struct PdeVjpParams {
   const double* X;        // [N, L, d] coordinates (already divided by the lengthscales)
   const double* gout;     // [row_end - row_begin] upstream gradient (sigma folded in by the caller)
   double* gradX;          // [N, L, d]
-  double* E;              // [chunk, L-1, L-1] coarse increments <dx_I, dx_J> / 4^n
   double* DX;             // [chunk, L-1, d] dx_J
   double* grid;           // [chunk, bands, P/CS + 31, CS, 32] reversed-path grid (node columns 1..P) in sweep order
   double* rowbuf;         // [chunk, kVjpWarps, 32 * bands]
@@ -34,137 +33,172 @@ struct PdeVjpParams {
   int rev_solver;
 };
 
-// E[I][J] in the accumulation order of sigKer_fast.pyx:41-43 (inc += dx*dy/factor, k ascending); row I = L-1 of the
-// launch writes DX[J][k] = x[J+1][k] - x[J][k] instead
-__global__ void __launch_bounds__(256) pde_vjp_inc_kernel(const PdeVjpParams P) {
+// DX[a][J][k] = x[J+1][k] - x[J][k]
+__global__ void __launch_bounds__(256) pde_vjp_dx_kernel(const PdeVjpParams P) {
   const int Lm = P.L - 1;
-  const size_t per = (size_t)Lm * Lm;
+  const size_t per = (size_t)Lm * P.d;
   const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= per * P.npairs) return;
   const int a = (int)(idx / per);
-  const int I = (int)((idx % per) / Lm), J = (int)(idx % Lm);
+  const size_t e = idx % per;
   const double* x = P.X + (size_t)(P.pair0 + a) * P.L * P.d;
-  const double factor = (double)(1u << (2 * P.order));
-  double inc = 0.;
-  for (int k = 0; k < P.d; ++k)
-    inc = inc + (x[(I + 1) * P.d + k] - x[I * P.d + k]) * (x[(J + 1) * P.d + k] - x[J * P.d + k]) / factor;
-  P.E[idx] = inc;
-  if (I == 0)
-    for (int k = 0; k < P.d; ++k) P.DX[((size_t)a * Lm + J) * P.d + k] = x[(J + 1) * P.d + k] - x[J * P.d + k];
+  P.DX[idx] = x[e + P.d] - x[e];
 }
 
 __device__ __forceinline__ double shfl_up1(double v) { return __shfl_up_sync(0xffffffffu, v, 1); }
 
 constexpr int kVjpWarps = 8;      // warps per CTA = bands of one sequence in flight
-constexpr int kVjpUnroll = 2;     // steps per prefetch group of the stored grid
 
 __host__ __device__ inline int vjp_cs(int order) { return order >= 2 ? 4 : (1 << order); }   // node columns per step
 __host__ __device__ inline size_t vjp_bands(size_t Pf) { return (Pf + 31) / 32; }
 __host__ __device__ inline size_t vjp_steps(size_t Pf, int cs) { return Pf / cs + 31; }      // steps of one band
 __host__ __device__ inline size_t vjp_grid_elems(size_t Pf, int cs) { return vjp_bands(Pf) * vjp_steps(Pf, cs) * cs * 32; }
 __host__ __device__ inline size_t vjp_rowbuf_elems(size_t Pf) { return (size_t)kVjpWarps * vjp_bands(Pf) * 32; }
+// dynamic shared memory: progress counters [bands] (padded to 16 B) + the sequence's dx [L-1][d] when it fits
+__host__ __device__ inline size_t vjp_prog_bytes(size_t Pf) { return (vjp_bands(Pf) * sizeof(int) + 15) & ~(size_t)15; }
+constexpr size_t kVjpDxSmemMax = 48 * 1024;
+
+template <int CS> struct VjpVec;
+template <> struct VjpVec<1> { double v[1]; };
+template <> struct __align__(16) VjpVec<2> { double v[2]; };
+template <> struct __align__(16) VjpVec<4> { double v[4]; };
+template <int CS> __device__ __forceinline__ void vjp_load(double (&o)[CS], const double* p) {
+  if constexpr (CS == 1) o[0] = __ldg(p);
+  else {
+#pragma unroll
+    for (int h = 0; h < CS / 2; ++h) { const double2 t = __ldg(reinterpret_cast<const double2*>(p) + h); o[2 * h] = t.x; o[2 * h + 1] = t.y; }
+  }
+}
+template <int CS> __device__ __forceinline__ void vjp_store(double* p, const double (&o)[CS]) {
+  if constexpr (CS == 1) p[0] = o[0];
+  else {
+#pragma unroll
+    for (int h = 0; h < CS / 2; ++h) reinterpret_cast<double2*>(p)[h] = make_double2(o[2 * h], o[2 * h + 1]);
+  }
+}
 
 // One CTA per sequence, kVjpWarps warps; warp w sweeps the 32-row bands w, w + W, ... of the grid.  Lane = one
 // node row r (0 = the boundary row of ones); a STEP advances a lane by CS node columns (CS = 2^order up to 4: one
-// coarse column of cells, so the stencil coefficients, the increment load and the flush of the q-reduction happen
-// at the same step for every lane: no divergence), lanes skewed by one step: lane t is at column group s - t.
+// coarse column of cells, so the stencil coefficients and the flush of the q-reduction happen at the same step
+// for every lane: no divergence), lanes skewed by one step: lane t is at column group s - t.
 // `up` (the CS values of the row above) comes from the lane above by shuffles; the last row of band b reaches band
 // b+1 (the next warp) through a row buffer in global memory, published in blocks of 32 columns through a per-band
-// progress counter in shared memory, so all bands of a sequence run as a pipeline.
+// progress counter in shared memory, so all bands of a sequence run as a pipeline.  The increments
+// <dx_I, dx_J> / 4^n are formed on the fly from the sequence's dx, staged once per CTA in shared memory.
 // Node columns 1..P are swept (group g = nodes g CS + 1 .. g CS + CS = cells g CS .. g CS + CS - 1); column 0 is 1.
 // MODE 0 solves the grid of the time-reversed path and stores it; MODE 1 solves the forward grid, multiplies
 // each value by the stored reversed value of the mirrored node and reduces.  The scratch is laid out in the
-// ORDER THE SWEEP PRODUCES IT, [band][step][k][lane]: every value moves in coalesced 256-byte rows.  The two
-// sweeps meet when MODE 1 aligns its bands to the END of the grid (rows r = 32 band + lane - pad): the value it
-// needs at (band, step s, lane t) was written by MODE 0's (NB-1-band, ~NG+30-s, 31-t).
-template <int MODE, int CS, int DA>
-__global__ void __launch_bounds__(32 * kVjpWarps) pde_vjp_sweep_kernel(const PdeVjpParams P) {
-  extern __shared__ int prog[];                            // [NB] row-buffer entries of band b published so far
+// ORDER THE SWEEP PRODUCES IT, [band][step][lane][CS]: a step is one coalesced 32 CS x 8-byte store / load
+// (128-bit per lane).  The two sweeps meet when MODE 1 aligns its bands to the END of the grid (rows r = 32 band
+// + lane - pad): what it needs at (band, step s, lane t) was written by MODE 0's (NB-1-band, ~NG+30-s, 31-t).
+template <int MODE, int CS, int DA, bool AL>
+__global__ void __launch_bounds__(32 * kVjpWarps, MODE == 0 ? (DA <= 4 ? 3 : (DA <= 8 ? 2 : 1)) : (DA <= 4 ? 2 : 1))
+pde_vjp_sweep_kernel(const PdeVjpParams P, const int dx_in_smem) {
+  extern __shared__ __align__(16) unsigned char vjp_smem[];
+  int* prog = reinterpret_cast<int*>(vjp_smem);            // [NB] row-buffer entries of band b published so far
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int a = blockIdx.x;
-  const int n = P.order, c = 1 << n, Pf = P.P, Lm = P.L - 1, d = P.d;
-  constexpr int LCS = CS == 4 ? 2 : (CS == 2 ? 1 : 0);
+  // AL: a step is exactly one coarse column of cells (order <= 2, CS = 2^order): n and c are compile-time
+  const int n = AL ? (CS == 4 ? 2 : (CS == 2 ? 1 : 0)) : P.order, c = AL ? CS : (1 << n);
+  const int Pf = P.P, Lm = P.L - 1, d = P.d;
   const int NB = (int)vjp_bands(Pf), NG = Pf / CS, NS = NG + 31;
+  const double* dxs = P.DX + (size_t)a * Lm * d;
   for (int i = threadIdx.x; i < NB; i += blockDim.x) prog[i] = 0;
+  if (dx_in_smem) {
+    double* sdx = reinterpret_cast<double*>(vjp_smem + vjp_prog_bytes(Pf));
+    for (int i = threadIdx.x; i < Lm * d; i += blockDim.x) sdx[i] = dxs[i];
+    dxs = sdx;
+  }
   __syncthreads();
   volatile int* vprog = prog;
-  const double* E = P.E + (size_t)a * Lm * Lm;
-  const double* DX = P.DX + (size_t)a * Lm * d;
   double* S = P.grid + (size_t)a * vjp_grid_elems(Pf, CS);
   double* rowbufs = P.rowbuf + (size_t)a * vjp_rowbuf_elems(Pf);
   const size_t Pfp = (size_t)NB * 32;
   const bool second = MODE == 1 || P.rev_solver == 1;
   const int roff = MODE == 1 ? NB * 32 - Pf : 0;
+  const double fscale = 1.0 / (double)(1u << (2 * n));
+  constexpr bool aligned = AL;
+  const int jstep = (MODE == 0 ? -1 : 1) * d;              // MODE 0: inc_rev[I][J] = inc[L-2-I][L-2-J] (pyx:43)
 
   for (int band = warp; band < NB; band += kVjpWarps) {
     const int r = band * 32 + lane - roff;
     const bool row_ok = r >= 0 && r < Pf;
     const int rc = min(max(r, 0), Pf - 1);
-    // coarse row of the cells (r-1, .) this lane solves; MODE 0 indexes the reversed increments
-    // inc_rev[I][J] = inc[L-2-I][L-2-J] (pyx:43)
-    const int Ic = rc > 0 ? ((rc - 1) >> n) : 0;
-    const double* Erow = E + (size_t)(MODE == 0 ? (Lm - 1 - Ic) : Ic) * Lm;
+    const int Ic = rc > 0 ? ((rc - 1) >> n) : 0;           // coarse row of the cells (r-1, .) this lane solves
+    double dxI[DA];                                        // ... its dx, pre-scaled by 1/4^n (exact)
+#pragma unroll
+    for (int k = 0; k < DA; ++k) dxI[k] = k < d ? dxs[(size_t)(MODE == 0 ? Lm - 1 - Ic : Ic) * d + k] * fscale : 0.;
     const double* rb_in = rowbufs + (size_t)((band + kVjpWarps - 1) % kVjpWarps) * Pfp;
     double* rb_out = rowbufs + (size_t)(band % kVjpWarps) * Pfp;
-    double* Sw = S + (size_t)band * NS * (CS * 32) + lane;                       // MODE 0: + (s CS + k) 32
-    const double* Sr = S + (size_t)(NB - 1 - band) * NS * (CS * 32) + (31 - lane);
-    // MODE 1: stored value of the mirrored node of node column q of this lane's row (1 on its boundary, 0 outside)
-    auto rev_at = [&](int q) -> double {
-      const int b = Pf - 1 - q;                            // node column of the reversed grid
-      if (b <= 0) return b == 0 ? 1. : 0.;
-      const int gp = (b - 1) >> LCS, kp = (b - 1) & (CS - 1);
-      return __ldg(Sr + ((size_t)(gp + 31 - lane) * CS + kp) * 32);
+    // scratch in units of one lane-step (CS doubles): MODE 0 writes unit (band NS + s) 32 + lane.  MODE 1 needs, for
+    // node q = g CS + 1 + k of its row, the reversed grid's node b = P - 1 - q of row P - 1 - r, which MODE 0 wrote
+    // from lane 31 - t of band NB-1-band as element (b-1) % CS of its group (b-1) / CS.  b - 1 = (NG-1-g) CS +
+    // (CS-3-k): the reader's group g straddles writer groups h(g) = NG-1-g and h(g+1) (CS = 4), or is h(g+1)
+    // (CS = 2) or h(g+2) (CS = 1), reversed inside -- a window that slides by one unit per step.
+    double* pW = S + ((size_t)band * NS * 32 + lane) * CS;
+    auto unit_ptr = [&](int gp) -> const double* {         // writer group gp of writer lane 31 - t
+      return S + (((size_t)(NB - 1 - band) * NS + (size_t)(gp + 31 - lane)) * 32 + (31 - lane)) * CS;
     };
+    auto fetch = [&](double (&o)[CS], int gg) {            // writer group h(gg) (zeros outside the grid)
+      const int gp = NG - 1 - gg;
+#pragma unroll
+      for (int k = 0; k < CS; ++k) o[k] = 0.;
+      if (row_ok && gp >= 0 && gp < NG) vjp_load<CS>(o, unit_ptr(gp));
+    };
+    double gq[4][CS];                                      // ring: gq[(u + j) & 3] = h(g + j) at unrolled step u
+    if (MODE == 1) {
+#pragma unroll
+      for (int jj = 0; jj < 4; ++jj) fetch(gq[jj], -lane + jj);
+    }
     double acc[DA];
 #pragma unroll
     for (int k = 0; k < DA; ++k) acc[k] = 0.;
     double sJ = 0.;
-    if (MODE == 1 && row_ok) sJ = rev_at(0);               // node column 0: K = 1
+    // MODE 1, node column 0: K = 1 times the reversed grid's node column P - 1
+    if (MODE == 1 && row_ok) sJ = Pf == 1 ? 1. : __ldg(unit_ptr((Pf - 2) / CS) + (Pf - 2) % CS);
     double cur = 1., upl = 1.;                             // left neighbour (r, q-1); up-left (r-1, q-1)
     double vs[CS];
 #pragma unroll
     for (int k = 0; k < CS; ++k) vs[k] = 1.;
     double A = 1., B = 1.;
-    double e_next = Erow[MODE == 0 ? (Lm - 1) : 0];
+    const double* pJ = dxs + (size_t)(MODE == 0 ? Lm - 1 : 0) * d;    // dx of the next coarse column to enter
+    double dxJ[DA], dxJn[DA];
+#pragma unroll
+    for (int k = 0; k < DA; ++k) { dxJ[k] = 0.; dxJn[k] = k < d ? pJ[k] : 0.; }
     double rbcur = 1., rbnext = 1.;
     if (band > 0) {
-      while (vprog[band - 1] < min(32, Pf)) { }
+      while (vprog[band - 1] < min(32, Pf)) __nanosleep(100);
       __threadfence_block();
       rbnext = __ldcg(rb_in + lane);
     }
-    double gcur[kVjpUnroll][CS], gnext[kVjpUnroll][CS];
-    if (MODE == 1) {
+    const double* pRB = rb_in + 32 + lane;                 // next block of the row above
+    double* pRO = rb_out - (size_t)lane * CS;              // lane 31: rb_out + g CS
+    int g = -lane;                                         // column group of this lane at step s
+    for (int s0 = 0; s0 < NS; s0 += 4) {
 #pragma unroll
-      for (int u = 0; u < kVjpUnroll; ++u)
-#pragma unroll
-        for (int k = 0; k < CS; ++k) {
-          const int g2 = u - lane;
-          gnext[u][k] = (row_ok && g2 >= 0 && g2 < NG) ? rev_at(g2 * CS + 1 + k) : 0.;
-          gcur[u][k] = 0.;
-        }
-    }
-    for (int s0 = 0; s0 < NS; s0 += kVjpUnroll) {
-      if (MODE == 1) {
-#pragma unroll
-        for (int u = 0; u < kVjpUnroll; ++u)
-#pragma unroll
-          for (int k = 0; k < CS; ++k) {
-            gcur[u][k] = gnext[u][k];
-            const int g2 = s0 + kVjpUnroll + u - lane;
-            gnext[u][k] = (row_ok && g2 >= 0 && g2 < NG) ? rev_at(g2 * CS + 1 + k) : 0.;
-          }
-      }
-#pragma unroll
-      for (int u = 0; u < kVjpUnroll; ++u) {
+      for (int u = 0; u < 4; ++u, ++g) {
         const int s = s0 + u;
-        const int g = s - lane;                            // column group of this lane
         if (((s * CS) & 31) == 0 && band > 0) {            // next 32 entries of the row above this band
           rbcur = rbnext;
           if (s * CS + 32 < Pf) {
             const int need = min(s * CS + 64, Pf);
-            while (vprog[band - 1] < need) { }
+            while (vprog[band - 1] < need) __nanosleep(100);
             __threadfence_block();
-            rbnext = __ldcg(rb_in + s * CS + 32 + lane);
+            rbnext = __ldcg(pRB);
+            pRB += 32;
+          }
+        }
+        double gv[CS];
+        if (MODE == 1) {                                   // stored values of this step; refill the ring slot 4 steps ahead
+          if (CS == 4) { gv[0] = gq[u][1]; gv[1] = gq[u][0]; gv[CS > 2 ? 2 : 0] = gq[(u + 1) & 3][CS > 3 ? 3 : 0]; gv[CS > 3 ? 3 : 0] = gq[(u + 1) & 3][CS > 2 ? 2 : 0]; }
+          if (CS == 2) { gv[0] = gq[(u + 1) & 3][CS > 1 ? 1 : 0]; gv[CS > 1 ? 1 : 0] = gq[(u + 1) & 3][0]; }
+          if (CS == 1) gv[0] = gq[(u + 2) & 3][0];
+          fetch(gq[u], g + 4);
+#pragma unroll
+          for (int k = 0; k < CS; ++k) {
+            const int b = Pf - 2 - g * CS - k;             // = P - 1 - q: 0 = the reversed grid's boundary column, < 0 outside
+            if (b == 0) gv[k] = 1.;
+            if (b < 0) gv[k] = 0.;
           }
         }
         double up[CS];
@@ -174,43 +208,49 @@ __global__ void __launch_bounds__(32 * kVjpWarps) pde_vjp_sweep_kernel(const Pde
           const double u0 = __shfl_sync(0xffffffffu, rbcur, (s * CS + k) & 31);
           if (lane == 0) up[k] = band > 0 ? u0 : 1.;
         }
-        const bool active = row_ok && g >= 0 && g < NG;
+        const bool active = row_ok && (unsigned)g < (unsigned)NG;
         if (active) {
-          if (((g * CS) & (c - 1)) == 0) {                 // cells of a new coarse column J = (g CS) >> n
-            const double e = e_next;
-            const int Jn = ((g * CS) >> n) + 1;
-            if (Jn < Lm) e_next = Erow[MODE == 0 ? (Lm - 1 - Jn) : Jn];
+          if (aligned || ((g * CS) & (c - 1)) == 0) {      // cells of a new coarse column J = (g CS) >> n
+            double e = 0.;
+#pragma unroll
+            for (int k = 0; k < DA; ++k) { dxJ[k] = dxJn[k]; e = fma(dxI[k], dxJ[k], e); }
+            pJ += jstep;
+            if (((g * CS) >> n) + 1 < Lm) {
+#pragma unroll
+              for (int k = 0; k < DA; ++k) if (k < d) dxJn[k] = pJ[k];
+            }
             if (second) { const double e2 = e * e * (1. / 12); A = 1. + 0.5 * e + e2; B = 1. - e2; }
             else { A = 1.; B = 1. - e; }
+            if (r == 0) { A = 0.; B = -1.; }               // boundary row: v = up-left = 1
           }
           double ul = upl, left = cur;
 #pragma unroll
           for (int k = 0; k < CS; ++k) {
-            const double v = r == 0 ? 1. : fma(left, A, fma(up[k], A, -(ul * B)));   // (k01 + k10) A - k00 B
+            const double v = fma(left, A, fma(up[k], A, -(ul * B)));   // (k01 + k10) A - k00 B
             vs[k] = v; left = v; ul = up[k];
-            if (MODE == 0) Sw[(size_t)(s * CS + k) * 32] = v;
           }
           cur = left; upl = ul;
+          if (MODE == 0) vjp_store<CS>(pW, vs);
           if (MODE == 1) {
             // q-reduction: node q multiplies dx[q >> n]; the group's last node may open the next coarse column
 #pragma unroll
-            for (int k = 0; k < CS - 1; ++k) sJ = fma(vs[k], gcur[u][k], sJ);
-            const double last = vs[CS - 1] * gcur[u][CS - 1];
-            if (((g * CS + CS) & (c - 1)) == 0) {
-              const double* dxa = DX + (size_t)((g * CS + CS - 1) >> n) * d;
+            for (int k = 0; k < CS - 1; ++k) sJ = fma(vs[k], gv[k], sJ);
+            const double last = vs[CS - 1] * gv[CS - 1];
+            if (aligned || ((g * CS + CS) & (c - 1)) == 0) {
 #pragma unroll
-              for (int k = 0; k < DA; ++k)
-                if (k < d) acc[k] = fma(sJ, __ldg(dxa + k), acc[k]);
+              for (int k = 0; k < DA; ++k) acc[k] = fma(sJ, dxJ[k], acc[k]);
               sJ = last;
             } else sJ += last;
           }
           if (lane == 31) {                                // top row of the next band
 #pragma unroll
-            for (int k = 0; k < CS; ++k) __stcg(rb_out + g * CS + k, vs[k]);
+            for (int k = 0; k < CS; ++k) __stcg(pRO + k, vs[k]);
             const int done = g * CS + CS;
             if ((done & 31) == 0 || done == Pf) { __threadfence_block(); vprog[band] = done; }
           }
         }
+        pW += CS * 32;
+        pRO += CS;
       }
     }
     if (MODE == 1 && row_ok) {
@@ -227,26 +267,26 @@ __global__ void __launch_bounds__(32 * kVjpWarps) pde_vjp_sweep_kernel(const Pde
 
 static size_t pde_vjp_pair_bytes(int L, int d, int order) {
   const size_t Pf = (size_t)(L - 1) << order;
-  return (vjp_grid_elems(Pf, vjp_cs(order)) + (size_t)(L - 1) * (L - 1) + (size_t)(L - 1) * d + vjp_rowbuf_elems(Pf)) * sizeof(double);
+  return (vjp_grid_elems(Pf, vjp_cs(order)) + (size_t)(L - 1) * d + vjp_rowbuf_elems(Pf)) * sizeof(double);
 }
 
-template <int MODE, int CS, int DA>
-static int launch_vjp_sweep(const PdeVjpParams& P, size_t smem, cudaStream_t s) {
-  auto kern = pde_vjp_sweep_kernel<MODE, CS, DA>;
+template <int MODE, int CS, int DA, bool AL>
+static int launch_vjp_sweep(const PdeVjpParams& P, cudaStream_t s) {
+  auto kern = pde_vjp_sweep_kernel<MODE, CS, DA, AL>;
+  const size_t dxb = (size_t)(P.L - 1) * P.d * sizeof(double);
+  const int dx_in_smem = dxb <= kVjpDxSmemMax;
+  const size_t smem = vjp_prog_bytes((size_t)P.P) + (dx_in_smem ? dxb : 0);
   if (smem > 48 * 1024) GPSIG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  kern<<<(unsigned)P.npairs, 32 * kVjpWarps, smem, s>>>(P);
+  kern<<<(unsigned)P.npairs, 32 * kVjpWarps, smem, s>>>(P, dx_in_smem);
   GPSIG_LAUNCH_CHECK("pde_vjp_sweep_kernel");
   return GPSIG_OK;
 }
 template <int MODE>
-static int dispatch_vjp_sweep(const PdeVjpParams& P, size_t smem, cudaStream_t s) {
+static int dispatch_vjp_sweep(const PdeVjpParams& P, cudaStream_t s) {
   const int cs = vjp_cs(P.order);
-#define GPSIG_VJP_GO(CS_) (P.d <= 4 ? launch_vjp_sweep<MODE, CS_, 4>(P, smem, s) : P.d <= 8 ? launch_vjp_sweep<MODE, CS_, 8>(P, smem, s) \
-                                                                                         : launch_vjp_sweep<MODE, CS_, 16>(P, smem, s))
-  if constexpr (MODE == 0)
-    return cs == 1 ? launch_vjp_sweep<0, 1, 4>(P, smem, s) : cs == 2 ? launch_vjp_sweep<0, 2, 4>(P, smem, s) : launch_vjp_sweep<0, 4, 4>(P, smem, s);
-  else
-    return cs == 1 ? GPSIG_VJP_GO(1) : cs == 2 ? GPSIG_VJP_GO(2) : GPSIG_VJP_GO(4);
+#define GPSIG_VJP_GO(CS_, AL_) (P.d <= 4 ? launch_vjp_sweep<MODE, CS_, 4, AL_>(P, s) : P.d <= 8 ? launch_vjp_sweep<MODE, CS_, 8, AL_>(P, s) \
+                                                                                             : launch_vjp_sweep<MODE, CS_, 16, AL_>(P, s))
+  return cs == 1 ? GPSIG_VJP_GO(1, true) : cs == 2 ? GPSIG_VJP_GO(2, true) : (P.order == 2 ? GPSIG_VJP_GO(4, true) : GPSIG_VJP_GO(4, false));
 #undef GPSIG_VJP_GO
 }
 
@@ -264,8 +304,7 @@ static int pde_kdiag_vjp_impl(const double* X, int N, int L, int d, int order, i
   if (rows == 0) return GPSIG_OK;
   const size_t Pf = (size_t)(L - 1) << order;
   const int cs = vjp_cs(order);
-  const size_t smem = vjp_bands(Pf) * sizeof(int);
-  if (smem > 200 * 1024) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "grid too long for the PDE backward (P=%zu)", Pf);
+  if (vjp_prog_bytes(Pf) > 128 * 1024) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "grid too long for the PDE backward (P=%zu)", Pf);
   GPSIG_CUDA_CHECK(cudaMemsetAsync(gradX + (size_t)row_begin * L * d, 0, (size_t)rows * L * d * sizeof(double), s));
   const size_t per = pde_vjp_pair_bytes(L, d, order);
   if (!ws || ws_bytes < per || (reinterpret_cast<uintptr_t>(ws) & 15))
@@ -275,18 +314,17 @@ static int pde_kdiag_vjp_impl(const double* X, int N, int L, int d, int order, i
   memset(&P, 0, sizeof(P));
   P.X = X; P.gout = gout; P.gradX = gradX;
   P.grid = static_cast<double*>(ws);
-  P.E = P.grid + (size_t)chunk * vjp_grid_elems(Pf, cs);
-  P.DX = P.E + (size_t)chunk * (L - 1) * (L - 1);
+  P.DX = P.grid + (size_t)chunk * vjp_grid_elems(Pf, cs);
   P.rowbuf = P.DX + (size_t)chunk * (L - 1) * d;
   P.L = L; P.d = d; P.order = order; P.P = (int)Pf; P.row_begin = row_begin; P.rev_solver = rev_solver;
   for (int p0 = row_begin; p0 < row_end; p0 += chunk) {
     P.pair0 = p0; P.npairs = min(chunk, row_end - p0);
-    const size_t ninc = (size_t)P.npairs * (L - 1) * (L - 1);
-    pde_vjp_inc_kernel<<<(unsigned)((ninc + 255) / 256), 256, 0, s>>>(P);
-    GPSIG_LAUNCH_CHECK("pde_vjp_inc_kernel");
+    const size_t ndx = (size_t)P.npairs * (L - 1) * d;
+    pde_vjp_dx_kernel<<<(unsigned)((ndx + 255) / 256), 256, 0, s>>>(P);
+    GPSIG_LAUNCH_CHECK("pde_vjp_dx_kernel");
     prof_begin(s);
-    if (int rc = dispatch_vjp_sweep<0>(P, smem, s)) return rc;
-    if (int rc = dispatch_vjp_sweep<1>(P, smem, s)) return rc;
+    if (int rc = dispatch_vjp_sweep<0>(P, s)) return rc;
+    if (int rc = dispatch_vjp_sweep<1>(P, s)) return rc;
     prof_end(s);
   }
   return GPSIG_OK;
