@@ -57,6 +57,7 @@ __host__ __device__ inline size_t vjp_rowbuf_elems(size_t Pf) { return (size_t)k
 // dynamic shared memory: progress counters [bands] (padded to 16 B) + the sequence's dx [L-1][d] when it fits
 __host__ __device__ inline size_t vjp_prog_bytes(size_t Pf) { return (vjp_bands(Pf) * sizeof(int) + 15) & ~(size_t)15; }
 constexpr size_t kVjpDxSmemMax = 48 * 1024;
+constexpr size_t kVjpRbsBytes = (size_t)kVjpWarps * 2 * 32 * sizeof(double);   // per-warp double-buffered 32-entry window of the row above
 
 template <int CS> struct VjpVec;
 template <> struct VjpVec<1> { double v[1]; };
@@ -104,8 +105,9 @@ pde_vjp_sweep_kernel(const PdeVjpParams P, const int dx_in_smem) {
   const int NB = (int)vjp_bands(Pf), NG = Pf / CS, NS = NG + 31;
   const double* dxs = P.DX + (size_t)a * Lm * d;
   for (int i = threadIdx.x; i < NB; i += blockDim.x) prog[i] = 0;
+  double* rbs = reinterpret_cast<double*>(vjp_smem + vjp_prog_bytes(Pf)) + (size_t)warp * 64;
   if (dx_in_smem) {
-    double* sdx = reinterpret_cast<double*>(vjp_smem + vjp_prog_bytes(Pf));
+    double* sdx = reinterpret_cast<double*>(vjp_smem + vjp_prog_bytes(Pf) + kVjpRbsBytes);
     for (int i = threadIdx.x; i < Lm * d; i += blockDim.x) sdx[i] = dxs[i];
     dxs = sdx;
   }
@@ -165,7 +167,7 @@ pde_vjp_sweep_kernel(const PdeVjpParams P, const int dx_in_smem) {
     double dxJ[DA], dxJn[DA];
 #pragma unroll
     for (int k = 0; k < DA; ++k) { dxJ[k] = 0.; dxJn[k] = k < d ? pJ[k] : 0.; }
-    double rbcur = 1., rbnext = 1.;
+    double rbnext = 1.;
     if (band > 0) {
       while (vprog[band - 1] < min(32, Pf)) __nanosleep(100);
       __threadfence_block();
@@ -178,8 +180,10 @@ pde_vjp_sweep_kernel(const PdeVjpParams P, const int dx_in_smem) {
 #pragma unroll
       for (int u = 0; u < 4; ++u, ++g) {
         const int s = s0 + u;
-        if (((s * CS) & 31) == 0 && band > 0) {            // next 32 entries of the row above this band
-          rbcur = rbnext;
+        if (((s * CS) & 31) == 0 && band > 0) {            // next 32 entries of the row above this band -> this warp's window
+          __syncwarp();
+          rbs[(((s * CS) >> 5) & 1) * 32 + lane] = rbnext;
+          __syncwarp();
           if (s * CS + 32 < Pf) {
             const int need = min(s * CS + 64, Pf);
             while (vprog[band - 1] < need) __nanosleep(100);
@@ -203,10 +207,19 @@ pde_vjp_sweep_kernel(const PdeVjpParams P, const int dx_in_smem) {
         }
         double up[CS];
 #pragma unroll
-        for (int k = 0; k < CS; ++k) {
-          up[k] = shfl_up1(vs[k]);                         // (r-1, q_k): finished by lane-1 one step ago
-          const double u0 = __shfl_sync(0xffffffffu, rbcur, (s * CS + k) & 31);
-          if (lane == 0) up[k] = band > 0 ? u0 : 1.;
+        for (int k = 0; k < CS; ++k) up[k] = shfl_up1(vs[k]);   // (r-1, q_k): finished by lane-1 one step ago
+        if (lane == 0) {                                   // first row of the band: from the band above (or the boundary)
+          if (band > 0) {
+            const double* w = rbs + ((s * CS) & 63);
+            if constexpr (CS == 1) up[0] = w[0];
+            else {
+#pragma unroll
+              for (int h = 0; h < CS / 2; ++h) { const double2 t = reinterpret_cast<const double2*>(w)[h]; up[2 * h] = t.x; up[2 * h + 1] = t.y; }
+            }
+          } else {
+#pragma unroll
+            for (int k = 0; k < CS; ++k) up[k] = 1.;
+          }
         }
         const bool active = row_ok && (unsigned)g < (unsigned)NG;
         if (active) {
@@ -275,7 +288,7 @@ static int launch_vjp_sweep(const PdeVjpParams& P, cudaStream_t s) {
   auto kern = pde_vjp_sweep_kernel<MODE, CS, DA, AL>;
   const size_t dxb = (size_t)(P.L - 1) * P.d * sizeof(double);
   const int dx_in_smem = dxb <= kVjpDxSmemMax;
-  const size_t smem = vjp_prog_bytes((size_t)P.P) + (dx_in_smem ? dxb : 0);
+  const size_t smem = vjp_prog_bytes((size_t)P.P) + kVjpRbsBytes + (dx_in_smem ? dxb : 0);
   if (smem > 48 * 1024) GPSIG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   kern<<<(unsigned)P.npairs, 32 * kVjpWarps, smem, s>>>(P, dx_in_smem);
   GPSIG_LAUNCH_CHECK("pde_vjp_sweep_kernel");

@@ -243,7 +243,9 @@ def pde_kdiag_vjp(X, grad_out, dyadic_order=0, rev_solver=0, rows=None):
     full = rb == 0 and re == N
     gradX = torch.empty_like(X) if full else torch.zeros_like(X)
     one = lib.gpsig_pde_kdiag_vjp_workspace_bytes(1, L, d, int(dyadic_order))
-    budget = min(_PDE_VJP_WS_BYTES, torch.cuda.mem_get_info(X.device)[0] // 2)      # never more than half of what is free
+    # at most half of the device memory (a function of the device, not of what is free now: the same call must ask
+    # the caching allocator for the same block every time)
+    budget = min(_PDE_VJP_WS_BYTES, torch.cuda.get_device_properties(X.device).total_memory // 2)
     nseq = max(1, min(re - rb, budget // max(1, one)))
     wsb = one * nseq
     ws = workspace(wsb, X.device)
