@@ -214,6 +214,8 @@ static int trunc_gram_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
     P.sym_jitter = epi->sym_jitter; P.return_levels = epi->return_levels;
   } else P.return_levels = 1;
   P.out = out;
+  const bool upper_only = sym && epi && epi->upper_only;
+  const bool whole_sym = sym && !upper_only && row_begin == 0 && row_end == N && N >= 2;
   if (generic) {
     GenericParams G;
     memset(&G, 0, sizeof(G));
@@ -223,20 +225,17 @@ static int trunc_gram_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
     G.sp.p = desc->spectral; G.sp.q = desc->spectral_q; G.sp.family = desc->spectral_family; G.d = d;
     G.norm_x = P.norm_x; G.norm_x2 = P.norm_x2; G.level_scale = P.level_scale; G.sym_jitter = P.sym_jitter;
     G.return_levels = P.return_levels; G.out = out;
-    return launch_trunc_generic<T>(G, s);
-  }
-  if (skew) {
-    // the whole symmetric Gram in one call: compute the CTAs that touch i <= j, mirror the rest
-    const bool upper_only = sym && epi && epi->upper_only;
-    const bool auto_tri = sym && !upper_only && row_begin == 0 && row_end == N && N >= 64 && getenv("GPSIG_NO_TRI") == nullptr;
-    P.tri = upper_only || auto_tri;
+    if (int rc = launch_trunc_generic<T>(G, s)) return rc;
+  } else if (skew) {
+    // the whole symmetric Gram in one call: compute only the CTAs that touch i <= j
+    P.tri = upper_only || (whole_sym && N >= 64 && getenv("GPSIG_NO_TRI") == nullptr);
     if (int rc = dispatch_skew<T>(P, desc->base, padded_dim(d), s)) return rc;
-    if (auto_tri) {
-      if (int rc = mirror_lower_impl<T>(out, N, P.return_levels ? desc->num_levels + 1 : 1, stream)) return rc;
-    }
-    return GPSIG_OK;
+  } else {
+    if (int rc = dispatch_trunc<T>(P, desc->base, padded_dim(d), s)) return rc;
   }
-  return dispatch_trunc<T>(P, desc->base, padded_dim(d), s);
+  // K(X, X) over all rows is returned EXACTLY symmetric whichever kernel ran: the upper triangle is mirrored down
+  if (whole_sym) return mirror_lower_impl<T>(out, N, P.return_levels ? desc->num_levels + 1 : 1, stream);
+  return GPSIG_OK;
 }
 
 template <typename T>
