@@ -209,11 +209,25 @@ def other_configs(torch, ops, lib):
     e1.record()
     e1.synchronize()
     ms = e0.elapsed_time(e1)
+    hbm_peak = measured_peaks()[0].get("hbm_gbs")
+    gbs = 16.0 * P * P * N / (ms * 1e-3) / 1e9
     out["c3_pde_vjp"] = {"workload": "kernels_pde Kdiag backward (_KdiagGrad), N=1000, L=500, d=4, dyadic order 2", "kernel": "pde_vjp_sweep_kernel<0>+<1>",
                          "ms": ms, "seqs_per_s": N / (ms * 1e-3), "cells_per_s": 2 * cells / (ms * 1e-3),
-                         "scratch_bytes_per_seq": 16.0 * P * P, "scratch_gbs": 16.0 * P * P * N / (ms * 1e-3) / 1e9, "dtype": "f64"}
+                         "bound": "hbm", "algorithmic_bytes_per_seq": 16.0 * P * P, "achieved_gbs": gbs, "peak_gbs": hbm_peak,
+                         "frac": (gbs / hbm_peak) if hbm_peak else None, "dtype": "f64"}
     del g
     torch.cuda.empty_cache()
+    # c5 (symmetric sweep) on a 4000-row block: K(X, X) computes the CTAs touching i <= j and mirrors the rest;
+    # delivered = N^2 ordered pairs in the output, computed = what the kernel evaluated
+    Ns = 4000
+    Xs = brownian(Ns, 200, 8, 0)
+    for dt, nm in ((torch.float64, 'f64'), (torch.float32, 'f32')):
+        Xd = torch.as_tensor(Xs, dtype=dt, device='cuda')
+        ms = timed(lambda: ops.trunc_gram(Xd, None, 5, base='rbf', return_levels=False))
+        out["c5_sym_block_" + nm] = {"workload": "SignatureRBF m=5 K(X, X) raw, N=4000 of the 50k rows, L=200, d=8 (upper triangle + mirror)",
+                                     "kernel": "trunc_skew_kernel (tri) + mirror_lower_kernel", "kernel_ms": ms,
+                                     "delivered_pairs_per_s": Ns * Ns / (ms * 1e-3)}
+        del Xd
     # c4: inducing tensors vs sequences, N=10k, L=100, d=8, m=4, Mz=500 (increments)
     N, L, d, m, Mz = 10000, 100, 8, 4, 500
     Xn = brownian(N, L, d, 0)
