@@ -18,6 +18,7 @@ import numpy as np
 import torch
 
 from . import autograd, ops, settings
+from . import lags as _lags
 
 
 class UntruncSignatureKernel:
@@ -43,8 +44,10 @@ class UntruncSignatureKernel:
             if not isinstance(num_lags, int) or num_lags < 0:
                 raise ValueError('The variable num_lags most be a nonnegative integer or None.')
             self.num_lags = int(num_lags)
-            if num_lags > 0:
-                raise NotImplementedError('gpsig_b200: num_lags > 0 is not implemented yet (SURVEY.md 8f-4).')
+            if num_lags > 0:                                            # kernels_pde.py:64-69
+                self.lags = 0.1 * np.asarray(range(1, num_lags + 1), dtype=np.float64)
+                gamma = 1. / np.asarray(range(1, self.num_lags + 2), dtype=np.float64)
+                self.gamma = gamma / np.sum(gamma)
         if lengthscales is not None:
             self.lengthscales = self._validate_signature_param("lengthscales", lengthscales, self.num_features)
         else:
@@ -70,6 +73,21 @@ class UntruncSignatureKernel:
     def _seq(self, X):
         return X.reshape(X.shape[0], -1, self.num_features).contiguous()
 
+    def _t(self, v, like):
+        return v.to(dtype=like.dtype, device=like.device) if torch.is_tensor(v) else \
+            torch.as_tensor(np.asarray(v, dtype=np.float64), dtype=like.dtype, device=like.device)
+
+    def _apply_scaling_and_lags_to_sequences(self, Xs):
+        """kernels_pde.py:135-157: lagged copies by linear interpolation, division by the lengthscales, ``gamma``
+        weights; [N, L, d] -> [N, L, d (num_lags + 1)].  Torch preprocessing on the device (differentiable)."""
+        N, L, _ = Xs.shape
+        X = _lags.add_lags_to_sequences(Xs, self._t(self.lags, Xs)) if self.num_lags > 0 else Xs[:, :, None, :]
+        if self.lengthscales is not None:
+            X = X / self._t(self.lengthscales, Xs)[None, None, None, :]
+        if self.num_lags > 0:
+            X = X * self._t(self.gamma, Xs)[None, None, :, None]
+        return X.reshape(N, L, -1).contiguous()
+
     def _ls(self, like):
         if self.lengthscales is None:
             return None
@@ -80,9 +98,12 @@ class UntruncSignatureKernel:
         if not presliced:
             X = self._slice(X)
         Xs = self._seq(X)
-        if torch.is_grad_enabled() and (Xs.requires_grad or any(torch.is_tensor(p) and p.requires_grad
-                                                                for p in (self.lengthscales, self.sigma))):
+        params = (self.lengthscales, self.sigma) + ((self.lags, self.gamma) if self.num_lags > 0 else ())
+        if torch.is_grad_enabled() and (Xs.requires_grad or any(torch.is_tensor(p) and p.requires_grad for p in params)):
             return self._Kdiag_differentiable(Xs, rows)
+        if self.num_lags > 0:
+            return ops.pde(self._apply_scaling_and_lags_to_sequences(Xs), None, dyadic_order=self.order, gram=False,
+                           sigma=float(self.sigma), rows=rows)
         return ops.pde(Xs, None, dyadic_order=self.order, gram=False, lengthscales=self._ls(Xs),
                        sigma=float(self.sigma), rows=rows)
 
@@ -93,8 +114,7 @@ class UntruncSignatureKernel:
         ``'gpu_op'`` (_untrunc_cov_grad.py:44-49)."""
         if rows is not None:
             Xs = Xs[rows[0]:rows[1]]
-        if self.lengthscales is not None:
-            Xs = Xs / torch.as_tensor(self.lengthscales, dtype=Xs.dtype, device=Xs.device)[None, None, :]
+        Xs = self._apply_scaling_and_lags_to_sequences(Xs)
         rev_solver = 0 if self.implementation == 'cython' else 1
         return self.sigma * autograd.pde_kdiag(Xs, self.order, rev_solver)
 
@@ -105,6 +125,10 @@ class UntruncSignatureKernel:
             X2 = None if X2 is None else self._slice(X2)
         Xs = self._seq(X)
         X2s = None if X2 is None else self._seq(X2)
+        if self.num_lags > 0:
+            Xs = self._apply_scaling_and_lags_to_sequences(Xs)
+            X2s = None if X2s is None else self._apply_scaling_and_lags_to_sequences(X2s)
+            return ops.pde(Xs, X2s, dyadic_order=self.order, gram=True, sigma=float(self.sigma), rows=rows)
         return ops.pde(Xs, X2s, dyadic_order=self.order, gram=True, lengthscales=self._ls(Xs),
                        sigma=float(self.sigma), rows=rows)
 

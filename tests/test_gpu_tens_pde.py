@@ -133,3 +133,30 @@ def test_lags_follow_reference(dtype, num_lags):
     ref = o.K_tens_n_seq_covs(Z, X.reshape(N, -1), increments=True)
     for g, r in zip(got, ref):
         assert rel_err(g.cpu().numpy(), r) < TOL[dtype]
+
+
+@pytest.mark.parametrize("num_lags", [1, 2])
+def test_pde_lags_follow_reference(num_lags):
+    """kernels_pde.py:135-157: lagged copies + lengthscales + gamma before the solve (oracle: trunc_np's restatement of
+    gpsig/lags.py applied in the same order, then the restated solver)."""
+    from gpsig_b200 import kernels_pde
+    from oracle import pde_np, trunc_np
+    N, L, d, order = 5, 30, 2, 1
+    X = brownian(N, L, d, 13)
+    ls = np.array([1.3, 0.8])
+    k = kernels_pde.UntruncSignatureKernel(L * d, d, lengthscales=ls, order=order, num_lags=num_lags, implementation='cython')
+    got = k.Kdiag(_dev(X.reshape(N, -1))).cpu().numpy()
+    Xl = trunc_np.add_lags_to_sequences(X, k.lags) / ls[None, None, None, :] * k.gamma[None, None, :, None]
+    ref = pde_np.pde_kernel(Xl.reshape(N, L, -1), None, order)
+    assert np.max(np.abs(got - ref) / np.abs(ref)) < 1e-10
+    # and under autograd (the reference's backward chained through the interpolation)
+    Xt = _dev(X.reshape(N, -1)).requires_grad_(True)
+    out = k.Kdiag(Xt)
+    out.sum().backward()
+    assert np.max(np.abs(out.detach().cpu().numpy() - ref) / np.abs(ref)) < 1e-10
+    gs = pde_np.pde_kdiag_grad(Xl.reshape(N, L, -1), order, 0)                     # d / d(lagged, scaled coordinates)
+    eps = 1e-6                                                                     # chain through the linear map numerically
+    Xp = X.copy(); Xp[2, 7, 1] += eps
+    Xlp = trunc_np.add_lags_to_sequences(Xp, k.lags) / ls[None, None, None, :] * k.gamma[None, None, :, None]
+    want = float(np.sum(gs * (Xlp.reshape(N, L, -1) - Xl.reshape(N, L, -1)) / eps))
+    assert abs(float(Xt.grad.reshape(N, L, d)[2, 7, 1]) - want) < 1e-6 * max(1.0, abs(want))
