@@ -10,6 +10,6 @@ been built (``python gpsig_b200/build.py``).
 from . import settings  # noqa: F401
 from . import _lib  # noqa: F401  (raises if libgpsig_b200.so is missing)
 from . import ops, kernels, kernels_pde  # noqa: F401
-from . import inducing_variables, conditionals  # noqa: F401
+from . import inducing_variables, conditionals, preprocessing  # noqa: F401
 
 __version__ = '0.1.0'
