@@ -59,10 +59,6 @@ __host__ __device__ inline size_t vjp_prog_bytes(size_t Pf) { return (vjp_bands(
 constexpr size_t kVjpDxSmemMax = 48 * 1024;
 constexpr size_t kVjpRbsBytes = (size_t)kVjpWarps * 2 * 32 * sizeof(double);   // per-warp double-buffered 32-entry window of the row above
 
-template <int CS> struct VjpVec;
-template <> struct VjpVec<1> { double v[1]; };
-template <> struct __align__(16) VjpVec<2> { double v[2]; };
-template <> struct __align__(16) VjpVec<4> { double v[4]; };
 template <int CS> __device__ __forceinline__ void vjp_load(double (&o)[CS], const double* p) {
   if constexpr (CS == 1) o[0] = __ldg(p);
   else {
