@@ -14,6 +14,8 @@
 // Lanes of a warp are 32 consecutive sequences (coalesced output); the 8 warps
 // of a CTA are 8 inducing tensors sharing those sequences' rows through L1.
 #pragma once
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace gpsig {
@@ -126,9 +128,196 @@ __global__ void __launch_bounds__(kTensWarps * 32) tens_vs_seq_kernel(const Tens
   if (!P.return_levels && live) static_cast<T*>(P.out)[(size_t)z * ncols + nl] = acc;
 }
 
+// ---------------------------------------------------------------------------
+// Kzx, register-resident tensors (the variant the library launches for the common shapes).
+//
+// tens_vs_seq_kernel above keeps z in shared memory and gives every lane its own sequence: every FMA of the
+// contraction reads a z operand through the shared-memory pipe (1 LDS per 2-4 FMAs) and every lane streams its own
+// x rows through L1 -- ncu: issue slots 26-31 % busy, stalled on the MIO queue / short scoreboard.  Here the roles
+// are swapped: LANE = inducing tensor (its I x zs x DP coordinates of the current level live in REGISTERS), the
+// CTA's warps share one sequence x_n at a time, brought by one TMA bulk copy into a double-buffered shared-memory
+// slot and read as warp-uniform broadcasts (DP/2 + 1 loads per time step against I zs (DP + exp) FMAs).
+// Levels are the outer loop (z registers are loaded once per level and CTA), the CH sequences of the CTA's chunk
+// the inner loop; results are collected in a shared-memory tile [CH][ZB+1] and written out transposed, so the
+// stores are coalesced along the sequence index.
+// ---------------------------------------------------------------------------
+template <typename T> struct TensVec;   // 16-byte vector of T
+template <> struct TensVec<double> { static constexpr int V = 2; using type = double2;
+  static __device__ __forceinline__ double get(const double2& v, int e) { return e == 0 ? v.x : v.y; } };
+template <> struct TensVec<float> { static constexpr int V = 4; using type = float4;
+  static __device__ __forceinline__ float get(const float4& v, int e) { return e == 0 ? v.x : (e == 1 ? v.y : (e == 2 ? v.z : v.w)); } };
+constexpr size_t kTens2MaxSmem = 200 * 1024;
+constexpr int kTens2Warps = 4;      // 128 tensors per CTA
+constexpr int kTens2Chunk = 16;     // sequences per CTA
+
+template <typename T, int DP, int OP, int ZS, int I>
+__device__ __forceinline__ T tens2_level(const T (&zr)[I * ZS * DP], const T (&zq)[I * ZS], const T* xs, const T* xsq, int L,
+                                         bool difference, int base, T p0, T p1, double tab) {
+  using Op = BaseOp<T, OP>;
+  T S[I], Mprev[I];
+#pragma unroll
+  for (int t = 0; t < I; ++t) { S[t] = T(0); Mprev[t] = T(0); }
+  for (int l = 0; l < L; ++l) {
+    T xv[DP];
+    using V16 = typename TensVec<T>::type;
+    constexpr int V = TensVec<T>::V;
+#pragma unroll
+    for (int kv = 0; kv < DP / V; ++kv) {
+      const V16 v = *reinterpret_cast<const V16*>(xs + (size_t)l * DP + kv * V);      // warp-uniform: broadcast
+#pragma unroll
+      for (int e = 0; e < V; ++e) xv[kv * V + e] = TensVec<T>::get(v, e);
+    }
+    const T xc = Op::col_const(xsq[l]);
+    auto kappa = [&](int e) {
+      T acc = Op::init(zq[e], xc);
+#pragma unroll
+      for (int k = 0; k < DP; ++k) acc = gfma<T>(zr[e * DP + k], xv[k], acc);
+      if (OP == OP_GENERIC) return base_eval_call<T>(base, p0, p1, acc, zq[e], xc);
+      if (OP == OP_RBF) return TensExp2<T>::ex(acc, tab);
+      return Op::finish(acc, zq[e], xc, base, p0, p1);
+    };
+    const bool first = difference && l == 0;
+#pragma unroll
+    for (int jj = I - 1; jj >= 0; --jj) {
+      T Mt = ZS == 2 ? kappa(2 * jj + 1) - kappa(2 * jj) : kappa(jj);       // kernels.py:331
+      T D = Mt;
+      if (difference) { D = Mt - Mprev[jj]; Mprev[jj] = Mt; }               // signature_algs.py:114
+      if (!first) {
+        if (jj > 0) S[jj] = gfma<T>(D, S[jj - 1], S[jj]);                     // signature_algs.py:123
+        else S[jj] += D;
+      }
+    }
+  }
+  return S[I - 1];                                                           // signature_algs.py:125
+}
+
+// registers the z tile of the top level needs (32-bit units); the kernel is used when this fits
+template <typename T> constexpr int tens2_zregs(int m, int zs, int DP) { return m * zs * (DP + 1) * (int)(sizeof(T) / 4); }
+
+template <typename T, int DP, int OP, int ZS, int MMAX>
+__global__ void __launch_bounds__(kTens2Warps * 32) tens_vs_seq_kernel2(const TensSeqParams P) {
+  using Op = BaseOp<T, OP>;
+  constexpr int ZB = kTens2Warps * 32, CH = kTens2Chunk;
+  extern __shared__ __align__(128) unsigned char tens_smem[];
+  uint64_t* full = reinterpret_cast<uint64_t*>(tens_smem);                     // [2]
+  const size_t xbytes = P.xblk * sizeof(T);
+  const size_t xslot = (xbytes + 127) / 128 * 128;
+  unsigned char* xbuf = tens_smem + 128;                                       // [2][xslot]
+  T* tile = reinterpret_cast<T*>(xbuf + 2 * xslot);                            // [CH][ZB + 1]
+  const int lane = threadIdx.x & 31;
+  const int m = P.m;
+  const int ncols = P.col_end - P.col_begin;
+  const int c0 = blockIdx.x * CH, nseq = min(CH, ncols - c0);                  // this CTA's sequences (local column indices)
+  const int zraw = blockIdx.y * ZB + threadIdx.x;
+  const bool zlive = zraw < P.Mz;
+  const int z = zlive ? zraw : P.Mz - 1;                                       // clamped: the warp stays convergent (table shuffle)
+  const double tab = exp2((double)lane * (1.0 / 32.0));
+  const T p0 = T(P.p0), p1 = T(P.p1);
+  const bool diff = P.difference != 0;
+  const T* xg = static_cast<const T*>(P.xp) + (size_t)(P.col_begin + c0) * P.xblk;
+
+  if (threadIdx.x == 0) { mbar_init(&full[0], 1); mbar_init(&full[1], 1); fence_mbar_init(); }
+  __syncthreads();
+  const int nitems = m * nseq;                                                 // (level, sequence) items, level-major
+  if (threadIdx.x == 0 && nitems > 0) { mbar_expect_tx(&full[0], (uint32_t)xbytes); tma_load_1d(xbuf, xg, (uint32_t)xbytes, &full[0]); }
+  // level 0 is the constant 1 (signature_algs.py:110)
+  T l0 = T(1);
+  if (P.level_scale) l0 *= static_cast<const T*>(P.level_scale)[0];
+  for (int j = 0; j < nseq; ++j) {
+    T v = T(1);
+    if (P.norm_x) v = v / gsqrt<T>(static_cast<const T*>(P.norm_x)[(size_t)P.col_begin + c0 + j]);
+    if (P.level_scale) v *= static_cast<const T*>(P.level_scale)[0];
+    tile[j * (ZB + 1) + threadIdx.x] = v;
+  }
+  (void)l0;
+  auto flush = [&](int lvl) {                                                  // tile -> out[(lvl,) z, c0 + j], coalesced along j
+    __syncthreads();
+    for (int e = threadIdx.x; e < ZB * CH; e += ZB) {
+      const int zz = e / CH, j = e % CH;
+      const int zo = blockIdx.y * ZB + zz;
+      if (zo < P.Mz && j < nseq) {
+        T* o = static_cast<T*>(P.out) + (P.return_levels ? (size_t)lvl * P.Mz * ncols : 0) + (size_t)zo * ncols + c0 + j;
+        *o = tile[j * (ZB + 1) + zz];
+      }
+    }
+    __syncthreads();
+  };
+  if (P.return_levels) flush(0);
+
+  int it = 0;
+  auto run_level = [&](auto IC) {
+    constexpr int I = decltype(IC)::value;
+    if (I > m) return;
+    constexpr int k0 = I * (I - 1) / 2;
+    T zr[I * ZS * DP], zq[I * ZS];
+#pragma unroll
+    for (int t = 0; t < I; ++t) {
+      const T* blk = static_cast<const T*>(P.zp) + ((size_t)(k0 + t) * P.Mz + z) * P.zblk;
+#pragma unroll
+      for (int s = 0; s < ZS; ++s) {
+#pragma unroll
+        for (int k = 0; k < DP; ++k) zr[(t * ZS + s) * DP + k] = blk[s * DP + k];
+        zq[t * ZS + s] = Op::row_const(blk[ZS * DP + s]);
+      }
+    }
+    T ls = T(1);
+    if (P.level_scale) ls = static_cast<const T*>(P.level_scale)[I];
+    for (int j = 0; j < nseq; ++j, ++it) {
+      const int b = it & 1;
+      // the other slot was released by the barrier that ended the previous item
+      if (threadIdx.x == 0 && it + 1 < nitems) {
+        const int jn = (j + 1 < nseq) ? j + 1 : 0;
+        mbar_expect_tx(&full[b ^ 1], (uint32_t)xbytes);
+        tma_load_1d(xbuf + (size_t)(b ^ 1) * xslot, xg + (size_t)jn * P.xblk, (uint32_t)xbytes, &full[b ^ 1]);
+      }
+      mbar_wait(&full[b], (it >> 1) & 1);
+      const T* xs = reinterpret_cast<const T*>(xbuf + (size_t)b * xslot);
+      T v = tens2_level<T, DP, OP, ZS, I>(zr, zq, xs, xs + (size_t)P.L * DP, P.L, diff, P.base, p0, p1, tab);
+      if (P.norm_x) v = v / gsqrt<T>(static_cast<const T*>(P.norm_x)[(size_t)I * P.N + P.col_begin + c0 + j]);   // kernels.py:610-614
+      v *= ls;
+      T* tl = tile + j * (ZB + 1) + threadIdx.x;
+      if (P.return_levels) *tl = v; else *tl += v;
+      __syncthreads();
+    }
+    if (P.return_levels) flush(I);
+  };
+#define GPSIG_L2(I_) if constexpr (MMAX >= I_) run_level(std::integral_constant<int, I_>{});
+  GPSIG_L2(1) GPSIG_L2(2) GPSIG_L2(3) GPSIG_L2(4) GPSIG_L2(5) GPSIG_L2(6) GPSIG_L2(7) GPSIG_L2(8)
+#undef GPSIG_L2
+  if (!P.return_levels) flush(0);
+}
+
+template <typename T, int OP, int DP, int ZS, int MMAX>
+int launch_tens2(const TensSeqParams& P, cudaStream_t stream) {
+  const size_t xslot = (P.xblk * sizeof(T) + 127) / 128 * 128;
+  const size_t smem = 128 + 2 * xslot + (size_t)kTens2Chunk * (kTens2Warps * 32 + 1) * sizeof(T);
+  if (smem > kTens2MaxSmem) return -100;                                           // caller falls back to tens_vs_seq_kernel
+  auto kern = tens_vs_seq_kernel2<T, DP, OP, ZS, MMAX>;
+  GPSIG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int ncols = P.col_end - P.col_begin;
+  dim3 grid((ncols + kTens2Chunk - 1) / kTens2Chunk, (P.Mz + kTens2Warps * 32 - 1) / (kTens2Warps * 32));
+  prof_begin(stream);
+  kern<<<grid, kTens2Warps * 32, smem, stream>>>(P);
+  prof_end(stream);
+  GPSIG_LAUNCH_CHECK("tens_vs_seq_kernel2");
+  return GPSIG_OK;
+}
+
 template <typename T, int OP, int DP>
 int launch_tens_vs_seq(const TensSeqParams& P, int m, cudaStream_t stream) {
   if (m < 1 || m > 8) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "num_levels=%d is not supported (1..8)", m);
+  // register-resident tensors when the top level's z tile fits in <= 144 registers (C4: m=4, zs=2, DP=8: 72 f32 / 144 f64)
+  if (getenv("GPSIG_TENS_OLD") == nullptr) {
+    const int mm = m <= 2 ? 2 : (m <= 4 ? 4 : 8);
+    if (tens2_zregs<T>(mm, P.zs, DP) <= 144) {
+      int rc = -100;
+#define GPSIG_T2(ZS_, MM_) rc = launch_tens2<T, OP, DP, ZS_, MM_>(P, stream)
+      if (P.zs == 2) { if (mm == 2) GPSIG_T2(2, 2); else if (mm == 4) GPSIG_T2(2, 4); else GPSIG_T2(2, 8); }
+      else { if (mm == 2) GPSIG_T2(1, 2); else if (mm == 4) GPSIG_T2(1, 4); else GPSIG_T2(1, 8); }
+#undef GPSIG_T2
+      if (rc != -100) return rc;
+    }
+  }
   const int TT = m * (m + 1) / 2;
   const size_t smem = (size_t)kTensWarps * TT * 2 * (DP + 1) * sizeof(T);
   auto kern = tens_vs_seq_kernel<T, DP, OP>;
