@@ -447,7 +447,9 @@ static int trunc_vjp_impl(const gpsig_trunc_desc* desc, const T* X, int N, int L
   P.W = w;
   const int threads = 128;
   prof_begin(s);
-  trunc_vjp_tables_kernel<T><<<(unsigned)((npairs + threads - 1) / threads), threads, 0, s>>>(P);
+  // few pairs (training shapes): one warp per pair; many pairs: one thread per pair fills the machine
+  const bool warp_per_pair = npairs < 32768 && getenv("GPSIG_VJP_THREAD") == nullptr && launch_trunc_vjp_tables_warp<T>(P, s);
+  if (!warp_per_pair) trunc_vjp_tables_kernel<T><<<(unsigned)((npairs + threads - 1) / threads), threads, 0, s>>>(P);
   prof_end(s);
   GPSIG_LAUNCH_CHECK("trunc_vjp_tables_kernel");
   const size_t tot = npairs * (size_t)(L + L2);

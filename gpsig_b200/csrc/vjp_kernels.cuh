@@ -187,6 +187,159 @@ __global__ void trunc_vjp_tables_kernel(const TruncVjpParams P) {
   }
 }
 
+// sweep 1+2, one WARP per pair (training shapes: few pairs, e.g. the 50 diagonal pairs of a minibatch -- with one
+// thread per pair the sweeps are a single serial chain per pair: 60 ms for 50 pairs of L = 100).  Lane t owns the
+// CW consecutive columns [t CW, (t+1) CW) of D; rows are swept one at a time.  The column sums C_a[q] live in
+// registers; the exclusive prefix over q that turns them into F_a[p, .] (G_b[p, .] on the way back: suffix) is a
+// lane-local scan plus one warp scan of the lane totals per level (the levels of a row are independent).  Same
+// scratch tables and layout as the thread-per-pair kernel (the grad kernel reads W from it).
+template <typename T, int CW, int MLV>
+__global__ void __launch_bounds__(128) trunc_vjp_tables_warp_kernel(const TruncVjpParams P) {
+  const size_t pair = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (pair >= P.npairs) return;
+  const int lane = threadIdx.x & 31;
+  const size_t np = P.npairs;
+  const int m = P.m, d = P.d, diff = P.difference ? 1 : 0;
+  const int PR = P.L - diff, QC = P.L2 - diff;
+  int i, j;
+  if (P.diag) { i = P.row_begin + (int)pair; j = i; }
+  else { i = P.row_begin + (int)(pair / P.N2); j = (int)(pair % P.N2); }
+  const T* x = static_cast<const T*>(P.X) + (size_t)i * P.L * d;
+  const T* y = static_cast<const T*>(P.Y) + (size_t)j * P.L2 * d;
+  const T p0 = T(P.p0), p1 = T(P.p1);
+  T* F = static_cast<T*>(P.F);
+  T* W = static_cast<T*>(P.W);
+  auto Fat = [&](int a, int p, int q) -> T& { return F[(((size_t)(a - 1) * PR + p) * QC + q) * np + pair]; };   // a = 1..m-1
+  T g[9];
+  const size_t gstride = P.diag ? (size_t)(P.row_end - P.row_begin) : (size_t)(P.row_end - P.row_begin) * P.N2;
+  for (int l = 0; l <= m; ++l) g[l] = static_cast<const T*>(P.g)[(size_t)l * gstride + pair];
+  const int q0 = lane * CW;
+  // base-kernel row r on this lane's columns q0 .. q0 + CW (one more than it owns: the difference needs q + 1)
+  auto Mrow = [&](int r, T (&o)[CW + 1]) {
+#pragma unroll
+    for (int c = 0; c <= CW; ++c) {
+      const int q = min(q0 + c, P.L2 - 1);
+      o[c] = kappa_raw<T>(x + (size_t)r * d, y + (size_t)q * d, d, P.base, p0, p1);
+    }
+  };
+  auto Drow = [&](const T (&lo)[CW + 1], const T (&hi)[CW + 1], T (&D)[CW]) {   // rows p (lo) and p+1 (hi)
+#pragma unroll
+    for (int c = 0; c < CW; ++c) {
+      const T v = diff ? (hi[c + 1] - hi[c]) - (lo[c + 1] - lo[c]) : lo[c];     // signature_algs.py:26
+      D[c] = (q0 + c < QC) ? v : T(0);
+    }
+  };
+  // exclusive prefix (DIR = +1) / suffix (DIR = -1) over all columns of the warp
+  auto scan = [&](const T (&v)[CW], T (&o)[CW], int dir) {
+    T tot = T(0);
+#pragma unroll
+    for (int c = 0; c < CW; ++c) tot += v[c];
+    T incl = tot;
+#pragma unroll
+    for (int s = 1; s < 32; s <<= 1) {
+      const T t = dir > 0 ? __shfl_up_sync(0xffffffffu, incl, s) : __shfl_down_sync(0xffffffffu, incl, s);
+      if (dir > 0 ? lane >= s : lane + s < 32) incl += t;
+    }
+    T run = incl - tot;                                                         // columns of the lanes before / after
+    if (dir > 0) {
+#pragma unroll
+      for (int c = 0; c < CW; ++c) { o[c] = run; run += v[c]; }
+    } else {
+#pragma unroll
+      for (int c = CW - 1; c >= 0; --c) { o[c] = run; run += v[c]; }
+    }
+  };
+
+  T C[MLV][CW];
+  T lo[CW + 1], hi[CW + 1], D[CW];
+  // ---- forward sweep: F_a[p, q], a = 1..m-1 ----------------------------------------------------
+#pragma unroll
+  for (int a = 0; a < MLV; ++a)
+#pragma unroll
+    for (int c = 0; c < CW; ++c) C[a][c] = T(0);
+  Mrow(0, lo);
+  for (int p = 0; p < PR; ++p) {
+    if (diff) Mrow(p + 1, hi);
+    Drow(lo, hi, D);
+    T Fprev[CW];
+#pragma unroll
+    for (int c = 0; c < CW; ++c) Fprev[c] = T(1);                               // F_0
+#pragma unroll
+    for (int a = 0; a < MLV; ++a) {
+      if (a + 1 < m) {
+        T Fa[CW];
+        scan(C[a], Fa, +1);                                                     // rows < p, columns < q
+#pragma unroll
+        for (int c = 0; c < CW; ++c) {
+          if (q0 + c < QC) Fat(a + 1, p, q0 + c) = Fa[c];
+          C[a][c] = gfma<T>(D[c], Fprev[c], C[a][c]);                           // column sum now includes row p
+          Fprev[c] = Fa[c];
+        }
+      }
+    }
+    if (diff) {
+#pragma unroll
+      for (int c = 0; c <= CW; ++c) lo[c] = hi[c];
+    } else if (p + 1 < PR) Mrow(p + 1, lo);
+  }
+  // ---- backward sweep: G_b on the fly, W = sum_a F_a H_a ------------------------------------------
+#pragma unroll
+  for (int a = 0; a < MLV; ++a)
+#pragma unroll
+    for (int c = 0; c < CW; ++c) C[a][c] = T(0);
+  if (diff) Mrow(PR, hi); else Mrow(PR - 1, lo);
+  for (int p = PR - 1; p >= 0; --p) {
+    if (diff) Mrow(p, lo);
+    Drow(lo, hi, D);
+    T G[MLV + 1][CW];
+#pragma unroll
+    for (int c = 0; c < CW; ++c) G[0][c] = T(1);
+#pragma unroll
+    for (int b = 0; b < MLV; ++b) {
+      if (b + 1 < m) {
+        scan(C[b], G[b + 1], -1);                                               // rows > p, columns > q
+#pragma unroll
+        for (int c = 0; c < CW; ++c) C[b][c] = gfma<T>(D[c], G[b][c], C[b][c]);
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < CW; ++c) {
+      if (q0 + c < QC) {
+        T w = T(0);
+#pragma unroll
+        for (int a = 0; a <= MLV; ++a) {
+          if (a < m) {
+            T H = T(0);
+#pragma unroll
+            for (int b = 0; b <= MLV; ++b)
+              if (a + b + 1 <= m) H = gfma<T>(g[a + b + 1], G[b][c], H);
+            const T Fa = a == 0 ? T(1) : Fat(a, p, q0 + c);
+            w = gfma<T>(Fa, H, w);
+          }
+        }
+        W[((size_t)p * QC + q0 + c) * np + pair] = w;
+      }
+    }
+    if (diff) {
+#pragma unroll
+      for (int c = 0; c <= CW; ++c) hi[c] = lo[c];
+    } else if (p > 0) Mrow(p - 1, lo);
+  }
+}
+
+template <typename T>
+static bool launch_trunc_vjp_tables_warp(const TruncVjpParams& P, cudaStream_t s) {
+  const int QC = P.L2 - (P.difference ? 1 : 0);
+  const int cw = (QC + 31) / 32, mlv = P.m - 1;
+  if (cw > 8 || mlv > 7) return false;
+  const unsigned grid = (unsigned)((P.npairs + 3) / 4);
+#define GPSIG_VW(CW_, MLV_) trunc_vjp_tables_warp_kernel<T, CW_, MLV_><<<grid, 128, 0, s>>>(P)
+  if (mlv <= 3) { if (cw <= 2) GPSIG_VW(2, 3); else if (cw <= 4) GPSIG_VW(4, 3); else GPSIG_VW(8, 3); }
+  else { if (cw <= 2) GPSIG_VW(2, 7); else if (cw <= 4) GPSIG_VW(4, 7); else GPSIG_VW(8, 7); }
+#undef GPSIG_VW
+  return true;
+}
+
 // sweep 3: one thread per (pair, point): r < L -> point x_r of the pair, else point y_{r-L}
 template <typename T>
 __global__ void trunc_vjp_grad_kernel(const TruncVjpParams P) {
