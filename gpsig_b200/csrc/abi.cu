@@ -486,7 +486,9 @@ static int tens_seq_vjp_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, i
   const int gz = TT * zs * d, threads = 64;
   const unsigned blocks = (unsigned)((npairs + threads - 1) / threads);
   prof_begin(s);
-  if (gz <= 160) tens_seq_vjp_kernel<T, 160><<<blocks, threads, 0, s>>>(P);
+  const bool warp_per_seq = getenv("GPSIG_VJP_THREAD") == nullptr && launch_tens_seq_vjp_warp<T>(P, s);
+  if (warp_per_seq) {}
+  else if (gz <= 160) tens_seq_vjp_kernel<T, 160><<<blocks, threads, 0, s>>>(P);
   else if (gz <= 480) tens_seq_vjp_kernel<T, 480><<<blocks, threads, 0, s>>>(P);
   else tens_seq_vjp_kernel<T, 1152><<<blocks, threads, 0, s>>>(P);
   prof_end(s);
@@ -508,8 +510,8 @@ static int tens_tens_vjp_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, 
   P.p0 = desc->base_params[0]; P.p1 = desc->base_params[1]; P.base = desc->base;
   P.g = grad_levels; P.gradZ = gradZ;
   const int TT = P.m * (P.m + 1) / 2;
-  dim3 grid((Mz + 63) / 64, TT);
-  tens_tens_vjp_kernel<T><<<grid, 64, 0, static_cast<cudaStream_t>(stream)>>>(P);
+  dim3 grid((Mz + 3) / 4, TT);                                       // 4 warps per CTA, one warp per (component, row)
+  tens_tens_vjp_kernel<T><<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(P);
   GPSIG_LAUNCH_CHECK("tens_tens_vjp_kernel");
   return GPSIG_OK;
 }

@@ -148,7 +148,7 @@ template <> struct TensVec<float> { static constexpr int V = 4; using type = flo
   static __device__ __forceinline__ float get(const float4& v, int e) { return e == 0 ? v.x : (e == 1 ? v.y : (e == 2 ? v.z : v.w)); } };
 constexpr size_t kTens2MaxSmem = 200 * 1024;
 constexpr int kTens2Warps = 4;      // 128 tensors per CTA
-constexpr int kTens2Chunk = 16;     // sequences per CTA
+constexpr int kTens2Chunk = 16;     // sequences per CTA at most (fewer when the grid would not fill the GPU)
 
 template <typename T, int DP, int OP, int ZS, int I>
 __device__ __forceinline__ T tens2_level(const T (&zr)[I * ZS * DP], const T (&zq)[I * ZS], const T* xs, const T* xsq, int L,
@@ -195,9 +195,9 @@ __device__ __forceinline__ T tens2_level(const T (&zr)[I * ZS * DP], const T (&z
 template <typename T> constexpr int tens2_zregs(int m, int zs, int DP) { return m * zs * (DP + 1) * (int)(sizeof(T) / 4); }
 
 template <typename T, int DP, int OP, int ZS, int MMAX>
-__global__ void __launch_bounds__(kTens2Warps * 32) tens_vs_seq_kernel2(const TensSeqParams P) {
+__global__ void __launch_bounds__(kTens2Warps * 32) tens_vs_seq_kernel2(const TensSeqParams P, const int CH) {
   using Op = BaseOp<T, OP>;
-  constexpr int ZB = kTens2Warps * 32, CH = kTens2Chunk;
+  constexpr int ZB = kTens2Warps * 32;
   extern __shared__ __align__(128) unsigned char tens_smem[];
   uint64_t* full = reinterpret_cast<uint64_t*>(tens_smem);                     // [2]
   const size_t xbytes = P.xblk * sizeof(T);
@@ -290,14 +290,17 @@ __global__ void __launch_bounds__(kTens2Warps * 32) tens_vs_seq_kernel2(const Te
 template <typename T, int OP, int DP, int ZS, int MMAX>
 int launch_tens2(const TensSeqParams& P, cudaStream_t stream) {
   const size_t xslot = (P.xblk * sizeof(T) + 127) / 128 * 128;
-  const size_t smem = 128 + 2 * xslot + (size_t)kTens2Chunk * (kTens2Warps * 32 + 1) * sizeof(T);
-  if (smem > kTens2MaxSmem) return -100;                                           // caller falls back to tens_vs_seq_kernel
+  const int ncols = P.col_end - P.col_begin;
+  const int zblocks = (P.Mz + kTens2Warps * 32 - 1) / (kTens2Warps * 32);
+  int ch = (int)((long)ncols * zblocks / (2 * 148));                              // at least two CTAs per SM before a CTA takes a second sequence
+  ch = ch < 1 ? 1 : (ch > kTens2Chunk ? kTens2Chunk : ch);
+  const size_t smem = 128 + 2 * xslot + (size_t)ch * (kTens2Warps * 32 + 1) * sizeof(T);
+  if (128 + 2 * xslot + (size_t)kTens2Chunk * (kTens2Warps * 32 + 1) * sizeof(T) > kTens2MaxSmem) return -100;                                           // caller falls back to tens_vs_seq_kernel
   auto kern = tens_vs_seq_kernel2<T, DP, OP, ZS, MMAX>;
   GPSIG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const int ncols = P.col_end - P.col_begin;
-  dim3 grid((ncols + kTens2Chunk - 1) / kTens2Chunk, (P.Mz + kTens2Warps * 32 - 1) / (kTens2Warps * 32));
+  dim3 grid((ncols + ch - 1) / ch, zblocks);
   prof_begin(stream);
-  kern<<<grid, kTens2Warps * 32, smem, stream>>>(P);
+  kern<<<grid, kTens2Warps * 32, smem, stream>>>(P, ch);
   prof_end(stream);
   GPSIG_LAUNCH_CHECK("tens_vs_seq_kernel2");
   return GPSIG_OK;

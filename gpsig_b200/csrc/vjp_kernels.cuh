@@ -520,7 +520,245 @@ __global__ void tens_seq_vjp_kernel(const TensSeqVjpParams P) {
 }
 
 // ---------------------------------------------------------------------------
-// inducing tensors vs themselves: one thread per (component k, row a); no atomics.
+// inducing tensors vs sequences, training shapes: one warp per (sequence n, chunk of inducing tensors).
+// Lane owns CW consecutive time steps of x_n (registers); the recursion over time becomes warp scans:
+//   E_jj(l)   = S_{jj-1}(l-1) = sum_{l' < l} D_{jj-1}(l') E_{jj-1}(l')      (E_0 = 1)
+//   lam_jj(l) = sum_{l' > l} lam_{jj+1}(l') D_{jj+1}(l')                      (lam_{I-1} = g_I)
+//   aD_jj(l)  = lam_jj(l) E_jj(l)
+// so no scratch in HBM is needed; D / E of the current level live in shared memory as [jj][c][lane].
+// dL/dx accumulates in registers over the warp's tensors, dL/dz is reduced over lanes per (component, sign).
+// ---------------------------------------------------------------------------
+constexpr int kTsvWarps = 4;
+
+template <typename T, int CW>
+__device__ __forceinline__ void warp_excl_prefix(T (&v)[CW], int lane) {
+  T tot = T(0);
+#pragma unroll
+  for (int c = 0; c < CW; ++c) { const T t = v[c]; v[c] = tot; tot += t; }
+  T inc = tot;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { const T t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+  T exc = __shfl_up_sync(0xffffffffu, inc, 1);
+  if (lane == 0) exc = T(0);
+#pragma unroll
+  for (int c = 0; c < CW; ++c) v[c] += exc;
+}
+template <typename T, int CW>
+__device__ __forceinline__ void warp_excl_suffix(T (&v)[CW], int lane) {
+  T tot = T(0);
+#pragma unroll
+  for (int c = CW - 1; c >= 0; --c) { const T t = v[c]; v[c] = tot; tot += t; }
+  T inc = tot;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { const T t = __shfl_down_sync(0xffffffffu, inc, o); if (lane + o < 32) inc += t; }
+  T exc = __shfl_down_sync(0xffffffffu, inc, 1);
+  if (lane == 31) exc = T(0);
+#pragma unroll
+  for (int c = 0; c < CW; ++c) v[c] += exc;
+}
+// sum of v[i] over the 32 lanes for all i < NV with NV-1 + (5 - log2 NV) shuffles; the lane ends up with entry `idx`
+template <typename T, int NV>
+__device__ __forceinline__ T warp_transpose_reduce(T (&v)[NV], int lane, int& idx) {
+  int off = 16;
+  idx = 0;
+#pragma unroll
+  for (int n = NV; n > 1; n >>= 1) {
+    const bool hi = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < n / 2; ++i) {
+      const T send = hi ? v[i] : v[i + n / 2];
+      const T keep = hi ? v[i + n / 2] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+    }
+    if (hi) idx += n / 2;
+    off >>= 1;
+  }
+  for (; off > 0; off >>= 1) v[0] += __shfl_xor_sync(0xffffffffu, v[0], off);
+  return v[0];
+}
+template <typename T>
+__device__ __noinline__ void base_partials_call(int base, T p0, T p1, T dot, T xs, T ys, T& fd, T& fx, T& fy) {
+  base_partials<T>(base, p0, p1, dot, xs, ys, fd, fx, fy);
+}
+
+template <typename T, int CW, int DP>
+__global__ void __launch_bounds__(kTsvWarps * 32, 2) tens_seq_vjp_warp_kernel(const TensSeqVjpParams P, int zchunks, int zper) {
+  extern __shared__ __align__(16) unsigned char tsv_smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m = P.m, d = P.d, zs = P.zs, L = P.L, Mz = P.Mz;
+  const int ncols = P.col_end - P.col_begin;
+  const long wid = (long)blockIdx.x * kTsvWarps + warp;
+  if (wid >= (long)ncols * zchunks) return;                         // warp-uniform; the kernel has no block barrier
+  const int nl = (int)(wid / zchunks), zc = (int)(wid % zchunks), n = P.col_begin + nl;
+  const int z_lo = zc * zper, z_hi = min(Mz, z_lo + zper);
+  const bool diff = P.difference != 0;
+  const int l0 = diff ? 1 : 0;
+  const T p0 = T(P.p0), p1 = T(P.p1);
+  const T* Z = static_cast<const T*>(P.Z);
+  const T* g = static_cast<const T*>(P.g);
+  T* Ds = reinterpret_cast<T*>(tsv_smem) + (size_t)warp * 2 * m * CW * 32;
+  T* Es = Ds + (size_t)m * CW * 32;
+  auto at = [&](T* base, int jj, int c) -> T& { return base[(jj * CW + c) * 32 + lane]; };
+
+  T xr[CW][DP], xsq[CW], gx[CW][DP], gxb[CW];
+  {
+    const T* x = static_cast<const T*>(P.X) + (size_t)n * L * d;
+#pragma unroll
+    for (int c = 0; c < CW; ++c) {
+      const int l = lane * CW + c;
+      xsq[c] = T(0); gxb[c] = T(0);
+#pragma unroll
+      for (int q = 0; q < DP; ++q) {
+        xr[c][q] = (l < L && q < d) ? x[(size_t)l * d + q] : T(0);
+        xsq[c] = gfma<T>(xr[c][q], xr[c][q], xsq[c]);
+        gx[c][q] = T(0);
+      }
+    }
+  }
+  for (int z = z_lo; z < z_hi; ++z) {
+    int k0 = 0;
+    for (int I = 1; I <= m; k0 += I, ++I) {
+      const T gI = g[((size_t)I * Mz + z) * ncols + nl];
+      if (gI == T(0)) continue;
+      // ---- forward: D_jj(l) of this level's components ------------------------------------------
+      for (int jj = 0; jj < I; ++jj) {
+        T mt[CW];
+#pragma unroll
+        for (int c = 0; c < CW; ++c) mt[c] = T(0);
+        for (int s = 0; s < zs; ++s) {
+          const T* zp = Z + (((size_t)(k0 + jj) * Mz + z) * zs + s) * d;
+          T zr[DP], zsq = T(0);
+#pragma unroll
+          for (int q = 0; q < DP; ++q) { zr[q] = q < d ? zp[q] : T(0); zsq = gfma<T>(zr[q], zr[q], zsq); }
+          const bool neg = zs == 2 && s == 0;                        // kernels.py:331
+#pragma unroll
+          for (int c = 0; c < CW; ++c) {
+            T dot = T(0);
+#pragma unroll
+            for (int q = 0; q < DP; ++q) dot = gfma<T>(zr[q], xr[c][q], dot);
+            const T kv = base_eval_call<T>(P.base, p0, p1, dot, zsq, xsq[c]);
+            mt[c] += neg ? -kv : kv;
+          }
+        }
+        const T prev = __shfl_up_sync(0xffffffffu, mt[CW - 1], 1);
+#pragma unroll
+        for (int c = 0; c < CW; ++c) {
+          const int l = lane * CW + c;
+          const T pm = c > 0 ? mt[c > 0 ? c - 1 : 0] : prev;
+          at(Ds, jj, c) = (l >= l0 && l < L) ? (diff ? mt[c] - pm : mt[c]) : T(0);
+        }
+      }
+      // ---- forward: E_jj(l) = S_{jj-1}(l-1) -----------------------------------------------------
+      {
+        T e[CW];
+#pragma unroll
+        for (int c = 0; c < CW; ++c) { e[c] = T(1); at(Es, 0, c) = T(1); }
+        for (int jj = 1; jj < I; ++jj) {
+#pragma unroll
+          for (int c = 0; c < CW; ++c) e[c] *= at(Ds, jj - 1, c);
+          warp_excl_prefix<T, CW>(e, lane);
+#pragma unroll
+          for (int c = 0; c < CW; ++c) at(Es, jj, c) = e[c];
+        }
+      }
+      // ---- reverse: lam, aD, aM, gradients ------------------------------------------------------
+      T lam[CW];
+#pragma unroll
+      for (int c = 0; c < CW; ++c) lam[c] = gI;
+      for (int jj = I - 1; jj >= 0; --jj) {
+        T aM[CW];
+#pragma unroll
+        for (int c = 0; c < CW; ++c) {
+          const int l = lane * CW + c;
+          aM[c] = (l >= l0 && l < L) ? lam[c] * at(Es, jj, c) : T(0);
+        }
+        if (jj > 0) {
+#pragma unroll
+          for (int c = 0; c < CW; ++c) lam[c] *= at(Ds, jj, c);
+          warp_excl_suffix<T, CW>(lam, lane);
+        }
+        if (diff) {                                                  // D(l) = Mt(l) - Mt(l-1)
+          T nxt = __shfl_down_sync(0xffffffffu, aM[0], 1);
+          if (lane == 31) nxt = T(0);
+#pragma unroll
+          for (int c = 0; c < CW; ++c) aM[c] -= (c + 1 < CW) ? aM[c + 1 < CW ? c + 1 : c] : nxt;
+        }
+        for (int s = 0; s < zs; ++s) {
+          const T* zp = Z + (((size_t)(k0 + jj) * Mz + z) * zs + s) * d;
+          T zr[DP], gz[DP], zsq = T(0), gzb = T(0);
+#pragma unroll
+          for (int q = 0; q < DP; ++q) { zr[q] = q < d ? zp[q] : T(0); zsq = gfma<T>(zr[q], zr[q], zsq); gz[q] = T(0); }
+          const bool neg = zs == 2 && s == 0;
+#pragma unroll
+          for (int c = 0; c < CW; ++c) {
+            T dot = T(0), fd, fz, fx;
+#pragma unroll
+            for (int q = 0; q < DP; ++q) dot = gfma<T>(zr[q], xr[c][q], dot);
+            base_partials_call<T>(P.base, p0, p1, dot, zsq, xsq[c], fd, fz, fx);
+            const T w = neg ? -aM[c] : aM[c];
+            const T A = w * fd;
+            gzb = gfma<T>(w, fz, gzb);
+            gxb[c] = gfma<T>(w, fx, gxb[c]);
+#pragma unroll
+            for (int q = 0; q < DP; ++q) { gz[q] = gfma<T>(A, xr[c][q], gz[q]); gx[c][q] = gfma<T>(A, zr[q], gx[c][q]); }
+          }
+#pragma unroll
+          for (int q = 0; q < DP; ++q) gz[q] = gfma<T>(T(2) * gzb, zr[q], gz[q]);
+          int idx;
+          const T tot = warp_transpose_reduce<T, DP>(gz, lane, idx);
+          if ((lane & (32 / DP - 1)) == 0 && idx < d)
+            atomic_add<T>(static_cast<T*>(P.gradZ) + (((size_t)(k0 + jj) * Mz + z) * zs + s) * d + idx, tot);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < CW; ++c) {
+    const int l = lane * CW + c;
+    if (l >= L) continue;
+    T* gxo = static_cast<T*>(P.gradX) + ((size_t)n * L + l) * d;
+#pragma unroll
+    for (int q = 0; q < DP; ++q) {
+      const T v = gfma<T>(T(2) * gxb[c], xr[c][q], gx[c][q]);
+      if (q < d && v != T(0)) atomic_add<T>(gxo + q, v);
+    }
+  }
+}
+
+template <typename T, int CW, int DP>
+static bool launch_tsv_warp_inst(const TensSeqVjpParams& P, cudaStream_t s) {
+  const int ncols = P.col_end - P.col_begin;
+  int zchunks = (148 * 16 + ncols - 1) / ncols;
+  zchunks = zchunks < 1 ? 1 : (zchunks > P.Mz ? P.Mz : zchunks);
+  const int zper = (P.Mz + zchunks - 1) / zchunks;
+  zchunks = (P.Mz + zper - 1) / zper;
+  const size_t smem = (size_t)kTsvWarps * 2 * P.m * CW * 32 * sizeof(T);
+  auto* kern = tens_seq_vjp_warp_kernel<T, CW, DP>;
+  if (smem > 48 * 1024 && cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return false;
+  const long warps = (long)ncols * zchunks;
+  kern<<<(unsigned)((warps + kTsvWarps - 1) / kTsvWarps), kTsvWarps * 32, smem, s>>>(P, zchunks, zper);
+  return true;
+}
+// false when the shape does not fit the register budget (the caller falls back to one thread per pair)
+template <typename T>
+static bool launch_tens_seq_vjp_warp(const TensSeqVjpParams& P, cudaStream_t s) {
+  const int dp = P.d <= 8 ? 8 : 16;
+  const int cw = P.L <= 64 ? 2 : (P.L <= 128 ? 4 : (P.L <= 256 ? 8 : 0));
+  if (cw == 0 || P.d > 16) return false;
+  if (cw * dp * (int)(sizeof(T) / 4) > 64) return false;
+  if (dp == 8) {
+    if (cw == 2) return launch_tsv_warp_inst<T, 2, 8>(P, s);
+    if (cw == 4) return launch_tsv_warp_inst<T, 4, 8>(P, s);
+    if constexpr (sizeof(T) == 4) { if (cw == 8) return launch_tsv_warp_inst<T, 8, 8>(P, s); }
+  } else {
+    if (cw == 2) return launch_tsv_warp_inst<T, 2, 16>(P, s);
+    if constexpr (sizeof(T) == 4) { if (cw == 4) return launch_tsv_warp_inst<T, 4, 16>(P, s); }
+  }
+  return false;
+}
+
+// ---------------------------------------------------------------------------
+// inducing tensors vs themselves: one warp per (component k, row a), lanes stride over b; no atomics.
 //   R_i(a, b) = prod_{jj < i} Mt_{k_i + jj}(a, b),  Mt symmetric in (a, b)
 //   dL/dZ[k, a] = sum_b (g_i[a, b] + g_i[b, a]) * prod_{others} Mt * dMt_k(a, b)/dz_a
 // ---------------------------------------------------------------------------
@@ -533,7 +771,8 @@ struct TensTensVjpParams {
 
 template <typename T>
 __global__ void tens_tens_vjp_kernel(const TensTensVjpParams P) {
-  const int a = blockIdx.x * blockDim.x + threadIdx.x;
+  const int a = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
   const int k = blockIdx.y;                                          // global component index
   if (a >= P.Mz) return;
   const int d = P.d, zs = P.zs, Mz = P.Mz;
@@ -549,14 +788,19 @@ __global__ void tens_tens_vjp_kernel(const TensTensVjpParams P) {
     return kappa_raw<T>(zpt(kk, a, 0), zpt(kk, b, 0), d, P.base, p0, p1);
   };
   const T* g = static_cast<const T*>(P.g) + (size_t)I * Mz * Mz;
-  T acc[2][16];
-  for (int s = 0; s < zs; ++s) for (int q = 0; q < d; ++q) acc[s][q] = T(0);
-  for (int b = 0; b < Mz; ++b) {
+  T acc[2][16];                                                      // registers: every index below is a compile-time constant
+#pragma unroll
+  for (int s = 0; s < 2; ++s)
+#pragma unroll
+    for (int q = 0; q < 16; ++q) acc[s][q] = T(0);
+  for (int b = lane; b < Mz; b += 32) {
     T w = g[(size_t)a * Mz + b] + g[(size_t)b * Mz + a];
     if (w == T(0)) continue;
     for (int jj = 0; jj < I; ++jj) if (k0 + jj != k) w *= Mt(k0 + jj, b);
     // d Mt_k(a, b) / d z_a^s: sum over the two kappas that contain z_a^s
-    for (int s = 0; s < zs; ++s) {
+#pragma unroll
+    for (int s = 0; s < 2; ++s) {
+      if (s >= zs) continue;
       const T* za = zpt(k, a, s);
       for (int s2 = 0; s2 < zs; ++s2) {
         const T sgn = (zs == 2 && s != s2) ? T(-1) : T(1);
@@ -564,12 +808,22 @@ __global__ void tens_tens_vjp_kernel(const TensTensVjpParams P) {
         T dot, xs, ys, fd, fx, fy;
         dot3(za, zb, d, dot, xs, ys);
         base_partials<T>(P.base, p0, p1, dot, xs, ys, fd, fx, fy);
-        for (int q = 0; q < d; ++q) acc[s][q] = gfma<T>(sgn * w, fd * zb[q] + T(2) * fx * za[q], acc[s][q]);
+        const T wf = sgn * w * fd, wx = T(2) * sgn * w * fx;
+#pragma unroll
+        for (int q = 0; q < 16; ++q)
+          if (q < d) acc[s][q] = gfma<T>(wf, zb[q], gfma<T>(wx, za[q], acc[s][q]));
       }
     }
   }
-  for (int s = 0; s < zs; ++s)
-    for (int q = 0; q < d; ++q) static_cast<T*>(P.gradZ)[(((size_t)k * Mz + a) * zs + s) * d + q] = acc[s][q];
+#pragma unroll
+  for (int s = 0; s < 2; ++s)
+#pragma unroll
+    for (int q = 0; q < 16; ++q) {
+      if (s >= zs || q >= d) continue;                               // warp-uniform
+      T v = acc[s][q];
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0) static_cast<T*>(P.gradZ)[(((size_t)k * Mz + a) * zs + s) * d + q] = v;
+    }
 }
 
 }  // namespace gpsig
