@@ -70,6 +70,17 @@ __device__ __forceinline__ T kappa_raw(const T* x, const T* y, int d, int base, 
   return base_eval<T>(base, p0, p1, dot, xs, ys);
 }
 
+// out-of-line copies: the base-kernel switch is large (f64 exp / pow / sqrt), and kernels that run one warp per
+// SM partition stall on instruction fetch when it is inlined at every unrolled site
+template <typename T>
+__device__ __noinline__ T kappa_raw_call(const T* x, const T* y, int d, int base, T p0, T p1) {
+  return kappa_raw<T>(x, y, d, base, p0, p1);
+}
+template <typename T>
+__device__ __noinline__ void base_partials_call(int base, T p0, T p1, T dot, T xs, T ys, T& fd, T& fx, T& fy) {
+  base_partials<T>(base, p0, p1, dot, xs, ys, fd, fx, fy);
+}
+
 template <typename T> __device__ __forceinline__ void atomic_add(T* p, T v) { atomicAdd(p, v); }
 
 struct TruncVjpParams {
@@ -219,7 +230,7 @@ __global__ void __launch_bounds__(128) trunc_vjp_tables_warp_kernel(const TruncV
 #pragma unroll
     for (int c = 0; c <= CW; ++c) {
       const int q = min(q0 + c, P.L2 - 1);
-      o[c] = kappa_raw<T>(x + (size_t)r * d, y + (size_t)q * d, d, P.base, p0, p1);
+      o[c] = kappa_raw_call<T>(x + (size_t)r * d, y + (size_t)q * d, d, P.base, p0, p1);
     }
   };
   auto Drow = [&](const T (&lo)[CW + 1], const T (&hi)[CW + 1], T (&D)[CW]) {   // rows p (lo) and p+1 (hi)
@@ -576,11 +587,6 @@ __device__ __forceinline__ T warp_transpose_reduce(T (&v)[NV], int lane, int& id
   for (; off > 0; off >>= 1) v[0] += __shfl_xor_sync(0xffffffffu, v[0], off);
   return v[0];
 }
-template <typename T>
-__device__ __noinline__ void base_partials_call(int base, T p0, T p1, T dot, T xs, T ys, T& fd, T& fx, T& fy) {
-  base_partials<T>(base, p0, p1, dot, xs, ys, fd, fx, fy);
-}
-
 template <typename T, int CW, int DP>
 __global__ void __launch_bounds__(kTsvWarps * 32, 2) tens_seq_vjp_warp_kernel(const TensSeqVjpParams P, int zchunks, int zper) {
   extern __shared__ __align__(16) unsigned char tsv_smem[];
@@ -783,9 +789,9 @@ __global__ void tens_tens_vjp_kernel(const TensTensVjpParams P) {
   auto zpt = [&](int kk, int zz, int s) { return Z + (((size_t)kk * Mz + zz) * zs + s) * d; };
   auto Mt = [&](int kk, int b) -> T {
     if (zs == 2)
-      return kappa_raw<T>(zpt(kk, a, 1), zpt(kk, b, 1), d, P.base, p0, p1) + kappa_raw<T>(zpt(kk, a, 0), zpt(kk, b, 0), d, P.base, p0, p1) -
-             kappa_raw<T>(zpt(kk, a, 1), zpt(kk, b, 0), d, P.base, p0, p1) - kappa_raw<T>(zpt(kk, a, 0), zpt(kk, b, 1), d, P.base, p0, p1);   // kernels.py:278
-    return kappa_raw<T>(zpt(kk, a, 0), zpt(kk, b, 0), d, P.base, p0, p1);
+      return kappa_raw_call<T>(zpt(kk, a, 1), zpt(kk, b, 1), d, P.base, p0, p1) + kappa_raw_call<T>(zpt(kk, a, 0), zpt(kk, b, 0), d, P.base, p0, p1) -
+             kappa_raw_call<T>(zpt(kk, a, 1), zpt(kk, b, 0), d, P.base, p0, p1) - kappa_raw_call<T>(zpt(kk, a, 0), zpt(kk, b, 1), d, P.base, p0, p1);   // kernels.py:278
+    return kappa_raw_call<T>(zpt(kk, a, 0), zpt(kk, b, 0), d, P.base, p0, p1);
   };
   const T* g = static_cast<const T*>(P.g) + (size_t)I * Mz * Mz;
   T acc[2][16];                                                      // registers: every index below is a compile-time constant
@@ -807,7 +813,7 @@ __global__ void tens_tens_vjp_kernel(const TensTensVjpParams P) {
         const T* zb = zpt(k, b, s2);
         T dot, xs, ys, fd, fx, fy;
         dot3(za, zb, d, dot, xs, ys);
-        base_partials<T>(P.base, p0, p1, dot, xs, ys, fd, fx, fy);
+        base_partials_call<T>(P.base, p0, p1, dot, xs, ys, fd, fx, fy);
         const T wf = sgn * w * fd, wx = T(2) * sgn * w * fx;
 #pragma unroll
         for (int q = 0; q < 16; ++q)

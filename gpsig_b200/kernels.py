@@ -23,6 +23,21 @@ from . import lags as _lags
 from . import ops, settings
 
 
+_SIDE_STREAMS = {}
+
+
+def _side_streams(device):
+    """Two non-default streams per device for the independent covariance blocks of the SVGP step
+    (``GPSIG_NO_STREAMS=1`` keeps everything on the caller's stream)."""
+    import os
+    if os.environ.get('GPSIG_NO_STREAMS') or device.type != 'cuda':
+        return None
+    key = device.index if device.index is not None else torch.cuda.current_device()
+    if key not in _SIDE_STREAMS:
+        _SIDE_STREAMS[key] = (torch.cuda.Stream(device), torch.cuda.Stream(device))
+    return _SIDE_STREAMS[key]
+
+
 class SignatureKernel:
     """gpsig/kernels.py:16-134 (constructor and validators)."""
 
@@ -238,13 +253,33 @@ class SignatureKernel:
         sc = self._d_scale(Xs if Xs is not None else Zs)
         m, jitter = self.num_levels, settings.jitter
         out = {}
-        if 'zz' in want:
-            out['zz'] = ag.tens_tens_levels(Zs, m, increments=increments, **self._d_bk()) * sc[:, None, None]
+        want_diag = Xs is not None and ('zx' in want or 'xx' in want) and (self.normalization or not full_X_cov)
+        # Kzz, the diagonal and Kzx are independent and, at minibatch sizes, each too small to fill the GPU: issue the
+        # first two on side streams.  Autograd replays every node on the stream of its forward, so the three adjoints
+        # overlap as well.
+        side = _side_streams(Zs.device) if ('zz' in want and 'zx' in want and want_diag) else None
+        cur = torch.cuda.current_stream(Zs.device) if side else None
         diag = None
-        if Xs is not None and ('zx' in want or 'xx' in want) and (self.normalization or not full_X_cov):
-            diag = ag.trunc_diag_levels(Xs, m, difference=self.difference, **self._d_bk())
+        if side:
+            for st in side:
+                st.wait_stream(cur)
+            with torch.cuda.stream(side[0]):
+                Zs.record_stream(side[0]); sc.record_stream(side[0])
+                out['zz'] = ag.tens_tens_levels(Zs, m, increments=increments, **self._d_bk()) * sc[:, None, None]
+            with torch.cuda.stream(side[1]):
+                Xs.record_stream(side[1])
+                diag = ag.trunc_diag_levels(Xs, m, difference=self.difference, **self._d_bk())
+        else:
+            if 'zz' in want:
+                out['zz'] = ag.tens_tens_levels(Zs, m, increments=increments, **self._d_bk()) * sc[:, None, None]
+            if want_diag:
+                diag = ag.trunc_diag_levels(Xs, m, difference=self.difference, **self._d_bk())
         if 'zx' in want:
             kzx = ag.tens_vs_seq_levels(Zs, Xs, m, increments=increments, difference=self.difference, **self._d_bk())
+            if side:
+                for st in side:
+                    cur.wait_stream(st)
+                out['zz'].record_stream(cur); diag.record_stream(cur)
             if self.normalization:
                 kzx = kzx / torch.sqrt(diag + jitter)[:, None, :]
             out['zx'] = kzx * sc[:, None, None]
