@@ -238,6 +238,33 @@ def other_configs(torch, ops, lib):
         ms = timed(lambda: ops.tens_vs_seq(Zd, Xd, m, increments=True, base='rbf', return_levels=False))
         out["c4_kzx_" + nm] = {"workload": "K_tens_vs_seq (increments), Mz=500, N=10000, L=100, d=8, m=4", "kernel": "tens_vs_seq_kernel2",
                                "kernel_ms": ms, "pairs_per_s": Mz * N / (ms * 1e-3), "flops_per_pair": 43574}
+        del Xd, Zd
+    # c4 training step (train_gpsig.py:20,67-68): Kzz, Kzx, Kxx_diag of a minibatch of 50, forward + backward
+    from gpsig_b200 import kernels as _k
+    nb = 50
+    for dt, nm in ((torch.float64, 'f64'), (torch.float32, 'f32')):
+        kern = _k.SignatureRBF(L * d, d, m, lengthscales=np.ones(d))
+        Xb = torch.as_tensor(Xn[:nb].reshape(nb, L * d), dtype=dt, device='cuda').requires_grad_(True)
+        Zb = torch.as_tensor(Zn, dtype=dt, device='cuda').requires_grad_(True)
+
+        def step():
+            Xb.grad = None
+            Zb.grad = None
+            Kzz, Kzx, Kxx = kern.K_tens_n_seq_covs(Zb, Xb, full_X_cov=False, increments=True)
+            (Kzz.sum() + Kzx.sum() + Kxx.sum()).backward()
+
+        step()
+        best = 1e30
+        for _ in range(5):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            step()
+            e1.record()
+            e1.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        out["c4_svgp_step_" + nm] = {"workload": "K_tens_n_seq_covs forward + backward (grads of Z and X), minibatch 50, Mz=500, L=100, d=8, m=4",
+                                     "kernels": "tens_tens(+vjp), trunc_gram diag (+vjp tables/grad), tens_vs_seq_kernel2 + tens_seq_vjp_warp_kernel",
+                                     "ms": best}
     return out
 
 
