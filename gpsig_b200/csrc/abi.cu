@@ -453,7 +453,8 @@ static int trunc_vjp_impl(const gpsig_trunc_desc* desc, const T* X, int N, int L
   prof_end(s);
   GPSIG_LAUNCH_CHECK("trunc_vjp_tables_kernel");
   const size_t tot = npairs * (size_t)(L + L2);
-  trunc_vjp_grad_kernel<T><<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(P);
+  if (npairs < 32768 && getenv("GPSIG_VJP_THREAD") == nullptr) trunc_vjp_grad_warp_kernel<T><<<(unsigned)((tot + 7) / 8), 256, 0, s>>>(P);
+  else trunc_vjp_grad_kernel<T><<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(P);
   GPSIG_LAUNCH_CHECK("trunc_vjp_grad_kernel");
   return GPSIG_OK;
 }

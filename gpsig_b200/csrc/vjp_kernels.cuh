@@ -408,6 +408,79 @@ __global__ void trunc_vjp_grad_kernel(const TruncVjpParams P) {
   }
 }
 
+// the same with one warp per (pair, point): for few pairs (training shapes), where a thread per point leaves the GPU idle
+template <typename T>
+__global__ void __launch_bounds__(256) trunc_vjp_grad_warp_kernel(const TruncVjpParams P) {
+  const size_t t = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;   // one warp per (pair, point); lanes stride over the other sequence
+  const int lane = threadIdx.x & 31;
+  const size_t np = P.npairs;
+  const int LL = P.L + P.L2;
+  if (t >= np * LL) return;
+  const int r = (int)(t / np);
+  const size_t pair = t % np;
+  const int d = P.d, diff = P.difference ? 1 : 0;
+  const int PR = P.L - diff, QC = P.L2 - diff;
+  int i, j;
+  if (P.diag) { i = P.row_begin + (int)pair; j = i; }
+  else { i = P.row_begin + (int)(pair / P.N2); j = (int)(pair % P.N2); }
+  const T* x = static_cast<const T*>(P.X) + (size_t)i * P.L * d;
+  const T* y = static_cast<const T*>(P.Y) + (size_t)j * P.L2 * d;
+  const T* W = static_cast<const T*>(P.W);
+  const T p0 = T(P.p0), p1 = T(P.p1);
+  auto Wat = [&](int p, int q) -> T { return (p < 0 || q < 0 || p >= PR || q >= QC) ? T(0) : W[((size_t)p * QC + q) * np + pair]; };
+  // dL/dM[pp, qq]: adjoint of the 2-D difference
+  auto dM = [&](int pp, int qq) -> T {
+    if (!diff) return Wat(pp, qq);
+    return (Wat(pp - 1, qq - 1) - Wat(pp - 1, qq)) - (Wat(pp, qq - 1) - Wat(pp, qq));
+  };
+  T acc[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) acc[k] = T(0);
+  if (r < P.L) {
+    const int pp = r;
+    const T* xp = x + (size_t)pp * d;
+    for (int qq = lane; qq < P.L2; qq += 32) {
+      const T a = dM(pp, qq);
+      if (a == T(0)) continue;
+      const T* yq = y + (size_t)qq * d;
+      T dot, xs, ys, fd, fx, fy;
+      dot3(xp, yq, d, dot, xs, ys);
+      base_partials_call<T>(P.base, p0, p1, dot, xs, ys, fd, fx, fy);
+#pragma unroll
+      for (int k = 0; k < 16; ++k) if (k < d) acc[k] = gfma<T>(a, fd * yq[k] + T(2) * fx * xp[k], acc[k]);
+    }
+    T* gx = static_cast<T*>(P.gradX) + ((size_t)i * P.L + pp) * d;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+      if (k >= d) continue;                                          // warp-uniform
+      T v = acc[k];
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0 && v != T(0)) atomic_add<T>(gx + k, v);
+    }
+  } else {
+    const int qq = r - P.L;
+    const T* yq = y + (size_t)qq * d;
+    for (int pp = lane; pp < P.L; pp += 32) {
+      const T a = dM(pp, qq);
+      if (a == T(0)) continue;
+      const T* xp = x + (size_t)pp * d;
+      T dot, xs, ys, fd, fx, fy;
+      dot3(xp, yq, d, dot, xs, ys);
+      base_partials_call<T>(P.base, p0, p1, dot, xs, ys, fd, fx, fy);
+#pragma unroll
+      for (int k = 0; k < 16; ++k) if (k < d) acc[k] = gfma<T>(a, fd * xp[k] + T(2) * fy * yq[k], acc[k]);
+    }
+    T* gy = static_cast<T*>(P.gradY) + ((size_t)j * P.L2 + qq) * d;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+      if (k >= d) continue;                                          // warp-uniform
+      T v = acc[k];
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0 && v != T(0)) atomic_add<T>(gy + k, v);
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------
 // inducing tensors vs sequences
 // ---------------------------------------------------------------------------
