@@ -338,6 +338,139 @@ __global__ void __launch_bounds__(128) trunc_vjp_tables_warp_kernel(const TruncV
   }
 }
 
+// ---------------------------------------------------------------------------
+// sweep 1+2 with one CTA per pair: D and the current table (F_{a-1} or G_{b-1}) live in shared memory, the 2-D
+// exclusive prefix sum of each level is two parallel passes (down the rows: one thread per column; along the rows:
+// one warp per row, warp scans), and W accumulates in registers (cell e = tid + k * threads).  F_1..F_{m-1} go
+// through the HBM scratch in a private [pair][a][cell] layout (L2-resident, coalesced); W is written in the
+// pair-fastest layout the gradient kernels read.  Needs L * L2 <= 12288 cells.
+// ---------------------------------------------------------------------------
+constexpr int kVjpCtaThreads = 256;
+constexpr int kVjpCtaCells = 48;                                     // cells per thread at most
+
+template <typename T>
+__device__ __forceinline__ T warp_excl_prefix1(T v, int lane, T& total) {
+  T inc = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { const T t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+  total = __shfl_sync(0xffffffffu, inc, 31);
+  const T ex = __shfl_up_sync(0xffffffffu, inc, 1);
+  return lane == 0 ? T(0) : ex;
+}
+template <typename T>
+__device__ __forceinline__ T warp_excl_suffix1(T v, int lane, T& total) {
+  T inc = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { const T t = __shfl_down_sync(0xffffffffu, inc, o); if (lane + o < 32) inc += t; }
+  total = __shfl_sync(0xffffffffu, inc, 0);
+  const T ex = __shfl_down_sync(0xffffffffu, inc, 1);
+  return lane == 31 ? T(0) : ex;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kVjpCtaThreads) trunc_vjp_tables_cta_kernel(const TruncVjpParams P) {
+  extern __shared__ __align__(16) unsigned char vjp_cta_smem[];
+  constexpr int NT = kVjpCtaThreads;
+  const size_t pair = blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const size_t np = P.npairs;
+  const int m = P.m, d = P.d, diff = P.difference ? 1 : 0;
+  const int L = P.L, L2 = P.L2, PR = L - diff, QC = L2 - diff, cells = PR * QC;
+  T* Dt = reinterpret_cast<T*>(vjp_cta_smem);                        // [PR][QC]
+  T* Tc = Dt + (size_t)L * L2;                                       // [L][L2] base kernel, then [PR][QC] current table
+  T* gs = Tc + (size_t)L * L2;                                       // [m + 1]
+  int i, j;
+  if (P.diag) { i = P.row_begin + (int)pair; j = i; }
+  else { i = P.row_begin + (int)(pair / P.N2); j = (int)(pair % P.N2); }
+  const T* x = static_cast<const T*>(P.X) + (size_t)i * L * d;
+  const T* y = static_cast<const T*>(P.Y) + (size_t)j * L2 * d;
+  const T p0 = T(P.p0), p1 = T(P.p1);
+  const size_t gstride = P.diag ? (size_t)(P.row_end - P.row_begin) : (size_t)(P.row_end - P.row_begin) * P.N2;
+  if (tid <= m) gs[tid] = static_cast<const T*>(P.g)[(size_t)tid * gstride + pair];
+  for (int e = tid; e < L * L2; e += NT) {
+    const int p = e / L2, q = e - p * L2;
+    Tc[e] = kappa_raw_call<T>(x + (size_t)p * d, y + (size_t)q * d, d, P.base, p0, p1);
+  }
+  __syncthreads();
+  for (int e = tid; e < cells; e += NT) {
+    const int p = e / QC, q = e - p * QC;
+    const T* M0 = Tc + (size_t)p * L2 + q;
+    Dt[e] = diff ? (M0[L2 + 1] - M0[L2]) - (M0[1] - M0[0]) : M0[0];  // signature_algs.py:26
+  }
+  __syncthreads();
+  // Tc <- 2-D exclusive prefix (dir = +1) or suffix (dir = -1) sums of D * Tc
+  auto step_level = [&](int dir) {
+    for (int q = tid; q < QC; q += NT) {                             // down the rows
+      T run = T(0);
+      if (dir > 0) for (int p = 0; p < PR; ++p) { const int e = p * QC + q; const T v = Dt[e] * Tc[e]; Tc[e] = run; run += v; }
+      else for (int p = PR - 1; p >= 0; --p) { const int e = p * QC + q; const T v = Dt[e] * Tc[e]; Tc[e] = run; run += v; }
+    }
+    __syncthreads();
+    const int nch = (QC + 31) >> 5;
+    for (int p = warp; p < PR; p += NT / 32) {                       // along the rows
+      T carry = T(0), tot;
+      T* row = Tc + (size_t)p * QC;
+      if (dir > 0) for (int c = 0; c < nch; ++c) {
+        const int q = c * 32 + lane;
+        const T ex = warp_excl_prefix1<T>(q < QC ? row[q] : T(0), lane, tot);
+        if (q < QC) row[q] = carry + ex;
+        carry += tot;
+      } else for (int c = nch - 1; c >= 0; --c) {
+        const int q = c * 32 + lane;
+        const T ex = warp_excl_suffix1<T>(q < QC ? row[q] : T(0), lane, tot);
+        if (q < QC) row[q] = carry + ex;
+        carry += tot;
+      }
+    }
+    __syncthreads();
+  };
+  // ---- forward: F_a, a = 1..m-1 ---------------------------------------------------------------
+  T* Fg = static_cast<T*>(P.F) + pair * (size_t)(m - 1) * cells;
+  for (int e = tid; e < cells; e += NT) Tc[e] = T(1);
+  __syncthreads();
+  for (int a = 1; a < m; ++a) {
+    step_level(+1);
+    for (int e = tid; e < cells; e += NT) Fg[(size_t)(a - 1) * cells + e] = Tc[e];
+    __syncthreads();
+  }
+  // ---- backward: G_b on the fly, W = sum_{a + b + 1 <= m} g[a + b + 1] F_a G_b -------------------
+  T w[kVjpCtaCells];
+#pragma unroll
+  for (int k = 0; k < kVjpCtaCells; ++k) w[k] = T(0);
+  for (int e = tid; e < cells; e += NT) Tc[e] = T(1);
+  __syncthreads();
+  for (int b = 0; b < m; ++b) {
+#pragma unroll
+    for (int k = 0; k < kVjpCtaCells; ++k) {
+      const int e = tid + k * NT;
+      if (e < cells) {
+        T h = gs[b + 1];                                             // a = 0: F_0 = 1
+        for (int a = 1; a + b + 1 <= m; ++a) h = gfma<T>(gs[a + b + 1], Fg[(size_t)(a - 1) * cells + e], h);
+        w[k] = gfma<T>(Tc[e], h, w[k]);
+      }
+    }
+    if (b + 1 < m) { __syncthreads(); step_level(-1); }
+  }
+  T* W = static_cast<T*>(P.W);
+#pragma unroll
+  for (int k = 0; k < kVjpCtaCells; ++k) {
+    const int e = tid + k * NT;
+    if (e < cells) W[(size_t)e * np + pair] = w[k];
+  }
+}
+
+template <typename T>
+static bool launch_trunc_vjp_tables_cta(const TruncVjpParams& P, cudaStream_t s) {
+  const size_t table = (size_t)P.L * P.L2;
+  if (table > (size_t)kVjpCtaThreads * kVjpCtaCells || P.m > 8) return false;
+  const size_t smem = (2 * table + 16) * sizeof(T);
+  if (smem > 220 * 1024) return false;
+  auto* kern = trunc_vjp_tables_cta_kernel<T>;
+  if (smem > 48 * 1024 && cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return false;
+  kern<<<(unsigned)P.npairs, kVjpCtaThreads, smem, s>>>(P);
+  return true;
+}
+
 template <typename T>
 static bool launch_trunc_vjp_tables_warp(const TruncVjpParams& P, cudaStream_t s) {
   const int QC = P.L2 - (P.difference ? 1 : 0);
