@@ -327,7 +327,8 @@ static int tens_tens_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, int 
   if (epi) { P.level_scale = epi->level_scale; P.return_levels = epi->return_levels; } else P.return_levels = 1;
   P.out = out;
   dim3 grid((Mz + 127) / 128, Mz);
-  tens_tens_kernel<T><<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(P);
+  if (P.d <= 8) tens_tens_kernel<T, 8><<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(P);
+  else tens_tens_kernel<T, 16><<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(P);
   GPSIG_LAUNCH_CHECK("tens_tens_kernel");
   return GPSIG_OK;
 }
@@ -515,7 +516,8 @@ static int tens_tens_vjp_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, 
   P.g = grad_levels; P.gradZ = gradZ;
   const int TT = P.m * (P.m + 1) / 2;
   dim3 grid((Mz + 3) / 4, TT);                                       // 4 warps per CTA, one warp per (component, row)
-  tens_tens_vjp_kernel<T><<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(P);
+  if (d <= 8) tens_tens_vjp_kernel<T, 8><<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(P);
+  else tens_tens_vjp_kernel<T, 16><<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(P);
   GPSIG_LAUNCH_CHECK("tens_tens_vjp_kernel");
   return GPSIG_OK;
 }

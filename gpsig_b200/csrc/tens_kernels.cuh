@@ -347,8 +347,11 @@ struct TensTensParams {
   void* out;           // [(m+1,)? Mz, Mz]
 };
 
-template <typename T>
-__global__ void tens_tens_kernel(const TensTensParams P) {
+// One thread per entry (a, b).  Each component's coordinates (both tensors, both increment ends, scaled by the
+// lengthscales) are loaded into registers once and the four base-kernel values of kernels.py:278 come from those:
+// the loads are issued back to back instead of one dependent L1 round trip per term.
+template <typename T, int DP>
+__global__ void __launch_bounds__(128) tens_tens_kernel(const TensTensParams P) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;   // column z'
   const int a = blockIdx.y;                              // row z
   if (b >= P.Mz) return;
@@ -358,19 +361,10 @@ __global__ void tens_tens_kernel(const TensTensParams P) {
   const T* len = static_cast<const T*>(P.ls);
   T* out = static_cast<T*>(P.out);
   const size_t MM = (size_t)P.Mz * P.Mz, ab = (size_t)a * P.Mz + b;
-  auto kappa = [&](const T* za, const T* zb) {
-    if (P.base == GPSIG_BASE_SPECTRAL) {
-      T u[16], v[16];
-      for (int k = 0; k < d; ++k) { u[k] = za[k]; v[k] = zb[k]; if (len) { u[k] = u[k] / len[k]; v[k] = v[k] / len[k]; } }
-      return spectral_eval<T>(P.sp, d, u, v);
-    }
-    T dot = T(0), xs = T(0), ys = T(0);
-    for (int k = 0; k < d; ++k) {
-      T u = za[k], v = zb[k];
-      if (len) { u = u / len[k]; v = v / len[k]; }
-      dot = gfma<T>(u, v, dot); xs = gfma<T>(u, u, xs); ys = gfma<T>(v, v, ys);
-    }
-    return base_eval<T>(P.base, p0, p1, dot, xs, ys);
+  auto kappa_spectral = [&](const T* za, const T* zb) {
+    T u[16], v[16];
+    for (int k = 0; k < d; ++k) { u[k] = za[k]; v[k] = zb[k]; if (len) { u[k] = u[k] / len[k]; v[k] = v[k] / len[k]; } }
+    return spectral_eval<T>(P.sp, d, u, v);
   };
   T acc = ls ? ls[0] : T(1);
   if (P.return_levels) out[ab] = acc;
@@ -381,8 +375,32 @@ __global__ void tens_tens_kernel(const TensTensParams P) {
       const T* za = static_cast<const T*>(P.Z) + ((size_t)k * P.Mz + a) * zs * d;
       const T* zb = static_cast<const T*>(P.Z) + ((size_t)k * P.Mz + b) * zs * d;
       T Mt;
-      if (zs == 2) Mt = kappa(za + d, zb + d) + kappa(za, zb) - kappa(za + d, zb) - kappa(za, zb + d);  // kernels.py:278
-      else Mt = kappa(za, zb);
+      if (P.base == GPSIG_BASE_SPECTRAL) {
+        if (zs == 2) Mt = kappa_spectral(za + d, zb + d) + kappa_spectral(za, zb) - kappa_spectral(za + d, zb) - kappa_spectral(za, zb + d);
+        else Mt = kappa_spectral(za, zb);
+      } else {
+        T u[2][DP], v[2][DP], uq[2], vq[2];
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+          uq[s] = vq[s] = T(0);
+#pragma unroll
+          for (int q = 0; q < DP; ++q) {
+            const bool live = s < zs && q < d;
+            T uu = live ? za[s * d + q] : T(0), vv = live ? zb[s * d + q] : T(0);
+            if (len && live) { uu = uu / len[q]; vv = vv / len[q]; }
+            u[s][q] = uu; v[s][q] = vv;
+            uq[s] = gfma<T>(uu, uu, uq[s]); vq[s] = gfma<T>(vv, vv, vq[s]);
+          }
+        }
+        auto ev = [&](int s, int s2) {
+          T dot = T(0);
+#pragma unroll
+          for (int q = 0; q < DP; ++q) dot = gfma<T>(u[s][q], v[s2][q], dot);
+          return base_eval_call<T>(P.base, p0, p1, dot, uq[s], vq[s2]);
+        };
+        if (zs == 2) Mt = ev(1, 1) + ev(0, 0) - ev(1, 0) - ev(0, 1);                                  // kernels.py:278
+        else Mt = ev(0, 0);
+      }
       R = jj == 0 ? Mt : Mt * R;                                                                     // signature_algs.py:91-96
     }
     if (ls) R *= ls[i];

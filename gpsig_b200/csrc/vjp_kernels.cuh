@@ -981,8 +981,8 @@ struct TensTensVjpParams {
   void* gradZ;                       // [T, Mz, zs, d], overwritten
 };
 
-template <typename T>
-__global__ void tens_tens_vjp_kernel(const TensTensVjpParams P) {
+template <typename T, int DP>
+__global__ void __launch_bounds__(128) tens_tens_vjp_kernel(const TensTensVjpParams P) {
   const int a = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   const int k = blockIdx.y;                                          // global component index
@@ -992,45 +992,61 @@ __global__ void tens_tens_vjp_kernel(const TensTensVjpParams P) {
   const T* Z = static_cast<const T*>(P.Z);
   int I = 1, k0 = 0;
   while (k0 + I <= k) { k0 += I; ++I; }                               // level of component k, first component k0
-  auto zpt = [&](int kk, int zz, int s) { return Z + (((size_t)kk * Mz + zz) * zs + s) * d; };
-  auto Mt = [&](int kk, int b) -> T {
-    if (zs == 2)
-      return kappa_raw_call<T>(zpt(kk, a, 1), zpt(kk, b, 1), d, P.base, p0, p1) + kappa_raw_call<T>(zpt(kk, a, 0), zpt(kk, b, 0), d, P.base, p0, p1) -
-             kappa_raw_call<T>(zpt(kk, a, 1), zpt(kk, b, 0), d, P.base, p0, p1) - kappa_raw_call<T>(zpt(kk, a, 0), zpt(kk, b, 1), d, P.base, p0, p1);   // kernels.py:278
-    return kappa_raw_call<T>(zpt(kk, a, 0), zpt(kk, b, 0), d, P.base, p0, p1);
+  // coordinates of tensor zz, component kk, into registers (zero-padded) with their squared norms
+  auto ld = [&](int kk, int zz, T (&r)[2][DP], T (&rq)[2]) {
+    const T* zp = Z + ((size_t)kk * Mz + zz) * zs * d;
+#pragma unroll
+    for (int s = 0; s < 2; ++s) {
+      rq[s] = T(0);
+#pragma unroll
+      for (int q = 0; q < DP; ++q) { r[s][q] = (s < zs && q < d) ? zp[s * d + q] : T(0); rq[s] = gfma<T>(r[s][q], r[s][q], rq[s]); }
+    }
+  };
+  auto dotp = [&](const T (&u)[DP], const T (&v)[DP]) {
+    T dot = T(0);
+#pragma unroll
+    for (int q = 0; q < DP; ++q) dot = gfma<T>(u[q], v[q], dot);
+    return dot;
   };
   const T* g = static_cast<const T*>(P.g) + (size_t)I * Mz * Mz;
-  T acc[2][16];                                                      // registers: every index below is a compile-time constant
+  T za[2][DP], zaq[2], acc[2][DP];
+  ld(k, a, za, zaq);
 #pragma unroll
   for (int s = 0; s < 2; ++s)
 #pragma unroll
-    for (int q = 0; q < 16; ++q) acc[s][q] = T(0);
+    for (int q = 0; q < DP; ++q) acc[s][q] = T(0);
   for (int b = lane; b < Mz; b += 32) {
     T w = g[(size_t)a * Mz + b] + g[(size_t)b * Mz + a];
     if (w == T(0)) continue;
-    for (int jj = 0; jj < I; ++jj) if (k0 + jj != k) w *= Mt(k0 + jj, b);
+    for (int jj = 0; jj < I; ++jj) {
+      if (k0 + jj == k) continue;
+      T ua[2][DP], ub[2][DP], uaq[2], ubq[2];
+      ld(k0 + jj, a, ua, uaq);
+      ld(k0 + jj, b, ub, ubq);
+      auto ev = [&](int s, int s2) { return base_eval_call<T>(P.base, p0, p1, dotp(ua[s], ub[s2]), uaq[s], ubq[s2]); };
+      w *= zs == 2 ? ev(1, 1) + ev(0, 0) - ev(1, 0) - ev(0, 1) : ev(0, 0);                           // kernels.py:278
+    }
     // d Mt_k(a, b) / d z_a^s: sum over the two kappas that contain z_a^s
+    T zb[2][DP], zbq[2];
+    ld(k, b, zb, zbq);
 #pragma unroll
     for (int s = 0; s < 2; ++s) {
-      if (s >= zs) continue;
-      const T* za = zpt(k, a, s);
-      for (int s2 = 0; s2 < zs; ++s2) {
+#pragma unroll
+      for (int s2 = 0; s2 < 2; ++s2) {
+        if (s >= zs || s2 >= zs) continue;
         const T sgn = (zs == 2 && s != s2) ? T(-1) : T(1);
-        const T* zb = zpt(k, b, s2);
-        T dot, xs, ys, fd, fx, fy;
-        dot3(za, zb, d, dot, xs, ys);
-        base_partials_call<T>(P.base, p0, p1, dot, xs, ys, fd, fx, fy);
+        T fd, fx, fy;
+        base_partials_call<T>(P.base, p0, p1, dotp(za[s], zb[s2]), zaq[s], zbq[s2], fd, fx, fy);
         const T wf = sgn * w * fd, wx = T(2) * sgn * w * fx;
 #pragma unroll
-        for (int q = 0; q < 16; ++q)
-          if (q < d) acc[s][q] = gfma<T>(wf, zb[q], gfma<T>(wx, za[q], acc[s][q]));
+        for (int q = 0; q < DP; ++q) acc[s][q] = gfma<T>(wf, zb[s2][q], gfma<T>(wx, za[s][q], acc[s][q]));
       }
     }
   }
 #pragma unroll
   for (int s = 0; s < 2; ++s)
 #pragma unroll
-    for (int q = 0; q < 16; ++q) {
+    for (int q = 0; q < DP; ++q) {
       if (s >= zs || q >= d) continue;                               // warp-uniform
       T v = acc[s][q];
       for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
