@@ -742,7 +742,8 @@ __global__ void tens_seq_vjp_kernel(const TensSeqVjpParams P) {
 //   E_jj(l)   = S_{jj-1}(l-1) = sum_{l' < l} D_{jj-1}(l') E_{jj-1}(l')      (E_0 = 1)
 //   lam_jj(l) = sum_{l' > l} lam_{jj+1}(l') D_{jj+1}(l')                      (lam_{I-1} = g_I)
 //   aD_jj(l)  = lam_jj(l) E_jj(l)
-// so no scratch in HBM is needed; D / E of the current level live in shared memory as [jj][c][lane].
+// so no scratch in HBM is needed; D / E and the base-kernel values of the current level live in shared memory as
+// [jj][c][lane] (for the RBF kernel the partial derivatives follow from the stored value: one exp per element, not two).
 // dL/dx accumulates in registers over the warp's tensors, dL/dz is reduced over lanes per (component, sign).
 // ---------------------------------------------------------------------------
 constexpr int kTsvWarps = 4;
@@ -808,8 +809,10 @@ __global__ void __launch_bounds__(kTsvWarps * 32, 2) tens_seq_vjp_warp_kernel(co
   const T p0 = T(P.p0), p1 = T(P.p1);
   const T* Z = static_cast<const T*>(P.Z);
   const T* g = static_cast<const T*>(P.g);
-  T* Ds = reinterpret_cast<T*>(tsv_smem) + (size_t)warp * 2 * m * CW * 32;
+  T* Ds = reinterpret_cast<T*>(tsv_smem) + (size_t)warp * 4 * m * CW * 32;
   T* Es = Ds + (size_t)m * CW * 32;
+  T* Ks = Es + (size_t)m * CW * 32;                                  // forward base-kernel values [jj][s][c][lane]
+  const bool from_value = P.base == GPSIG_BASE_RBF;                  // partials follow from the value: no second exp
   auto at = [&](T* base, int jj, int c) -> T& { return base[(jj * CW + c) * 32 + lane]; };
 
   T xr[CW][DP], xsq[CW], gx[CW][DP], gxb[CW];
@@ -849,6 +852,7 @@ __global__ void __launch_bounds__(kTsvWarps * 32, 2) tens_seq_vjp_warp_kernel(co
 #pragma unroll
             for (int q = 0; q < DP; ++q) dot = gfma<T>(zr[q], xr[c][q], dot);
             const T kv = base_eval_call<T>(P.base, p0, p1, dot, zsq, xsq[c]);
+            Ks[((jj * 2 + s) * CW + c) * 32 + lane] = kv;
             mt[c] += neg ? -kv : kv;
           }
         }
@@ -903,10 +907,16 @@ __global__ void __launch_bounds__(kTsvWarps * 32, 2) tens_seq_vjp_warp_kernel(co
           const bool neg = zs == 2 && s == 0;
 #pragma unroll
           for (int c = 0; c < CW; ++c) {
-            T dot = T(0), fd, fz, fx;
+            T fd, fz, fx;
+            if (from_value) {                                        // RBF: f_dot = f, f_|z|^2 = f_|x|^2 = -f / 2
+              fd = Ks[((jj * 2 + s) * CW + c) * 32 + lane];
+              fz = fx = T(-0.5) * fd;
+            } else {
+              T dot = T(0);
 #pragma unroll
-            for (int q = 0; q < DP; ++q) dot = gfma<T>(zr[q], xr[c][q], dot);
-            base_partials_call<T>(P.base, p0, p1, dot, zsq, xsq[c], fd, fz, fx);
+              for (int q = 0; q < DP; ++q) dot = gfma<T>(zr[q], xr[c][q], dot);
+              base_partials_call<T>(P.base, p0, p1, dot, zsq, xsq[c], fd, fz, fx);
+            }
             const T w = neg ? -aM[c] : aM[c];
             const T A = w * fd;
             gzb = gfma<T>(w, fz, gzb);
@@ -944,7 +954,7 @@ static bool launch_tsv_warp_inst(const TensSeqVjpParams& P, cudaStream_t s) {
   zchunks = zchunks < 1 ? 1 : (zchunks > P.Mz ? P.Mz : zchunks);
   const int zper = (P.Mz + zchunks - 1) / zchunks;
   zchunks = (P.Mz + zper - 1) / zper;
-  const size_t smem = (size_t)kTsvWarps * 2 * P.m * CW * 32 * sizeof(T);
+  const size_t smem = (size_t)kTsvWarps * 4 * P.m * CW * 32 * sizeof(T);
   auto* kern = tens_seq_vjp_warp_kernel<T, CW, DP>;
   if (smem > 48 * 1024 && cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return false;
   const long warps = (long)ncols * zchunks;
