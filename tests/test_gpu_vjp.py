@@ -210,3 +210,96 @@ def test_kernel_class_differentiable_path(normalization, num_lags):
     assert torch.allclose(k.K(X, X[:5]).detach(), kf.K(X, X[:5]), rtol=1e-9, atol=1e-11)
     assert torch.allclose(k.K(X).detach(), kf.K(X), rtol=1e-9, atol=1e-11)
     assert torch.allclose(k.Kdiag(X).detach(), kf.Kdiag(X), rtol=1e-9, atol=1e-11)
+
+
+def _close(a, b, rtol):
+    scale = float(b.abs().max()) + 1e-30
+    assert float((a - b).abs().max()) <= rtol * scale, (float((a - b).abs().max()), scale)
+
+
+@pytest.mark.parametrize("shape", [
+    # (pairs mode, N, N2, L, L2, d, m, difference)
+    ('diag', 6, 6, 100, 100, 8, 4, True),        # the C4 training shape: CTA per pair, 4 column chunks per row
+    ('gram', 3, 4, 70, 45, 3, 5, False),         # rectangular pairs, no differencing
+    ('gram', 2, 3, 33, 64, 16, 2, True),         # d = 16, two levels
+    ('gram', 2, 2, 130, 120, 4, 3, True),        # too long for shared memory: warp per pair
+    ('diag', 5, 5, 2, 2, 2, 3, True),            # shortest sequences the differenced kernel accepts
+])
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+def test_trunc_vjp_schedules_agree(shape, dtype, monkeypatch):
+    """The CTA-per-pair / warp-per-pair sweeps and the warp-per-point gradient kernel reproduce the
+    thread-per-pair kernels (which the tests above pin against the oracle) at shapes those tests do not reach."""
+    from gpsig_b200 import ops
+    mode, N, N2, L, L2, d, m, difference = shape
+    rng = np.random.default_rng(11)
+    X = _dev(brownian(N, L, d, 0) + 0.1, dtype)
+    Y = None if mode == 'diag' else _dev(brownian(N2, L2, d, 1) - 0.1, dtype)
+    G = _dev(rng.standard_normal((m + 1, N) if mode == 'diag' else (m + 1, N, N2)), dtype)
+    kw = dict(base='rbf', difference=difference, diag=(mode == 'diag'))
+    new = ops.trunc_vjp(X, Y, G, m, **kw)
+    monkeypatch.setenv('GPSIG_VJP_NO_CTA', '1')
+    warp = ops.trunc_vjp(X, Y, G, m, **kw)
+    monkeypatch.setenv('GPSIG_VJP_THREAD', '1')
+    ref = ops.trunc_vjp(X, Y, G, m, **kw)
+    rtol = 1e-10 if dtype == torch.float64 else 2e-4
+    for a, w, b in zip(new, warp, ref):
+        if b is not None:
+            _close(a, b, rtol)
+            _close(w, b, rtol)
+
+
+@pytest.mark.parametrize("shape", [
+    # (N, L, d, m, Mz, increments, base)
+    (7, 100, 8, 4, 37, True, 'rbf'),             # the C4 training shape: 4 time steps per lane, value reuse
+    (5, 100, 8, 4, 9, True, 'matern32'),         # partials evaluated separately
+    (4, 40, 16, 3, 6, False, 'rbf'),             # d = 16, plain tensors
+    (3, 33, 3, 5, 5, True, 'linear'),            # ragged last lane
+    (3, 6, 2, 3, 4, True, 'rbf'),                # short sequences: most lanes idle
+])
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+def test_tens_vjp_schedules_agree(shape, dtype, monkeypatch):
+    from gpsig_b200 import ops
+    N, L, d, m, Mz, increments, base = shape
+    rng = np.random.default_rng(12)
+    Xn = brownian(N, L, d, 0)
+    X, Z = _dev(Xn, dtype), _dev(inducing_tensors(Xn, m, Mz, increments, 2), dtype)
+    G = _dev(rng.standard_normal((m + 1, Mz, N)), dtype)
+    new = ops.tens_vs_seq_vjp(Z, X, G, m, increments=increments, base=base)
+    monkeypatch.setenv('GPSIG_VJP_THREAD', '1')
+    ref = ops.tens_vs_seq_vjp(Z, X, G, m, increments=increments, base=base)
+    rtol = 1e-10 if dtype == torch.float64 else 2e-4
+    for a, b in zip(new, ref):
+        _close(a, b, rtol)
+
+
+def test_tens_vjp_float32_long_sequences():
+    """float32, L = 200 (8 time steps per lane) against the float64 adjoint."""
+    from gpsig_b200 import ops
+    N, L, d, m, Mz = 3, 200, 5, 4, 6
+    rng = np.random.default_rng(13)
+    Xn = brownian(N, L, d, 0)
+    Zn = inducing_tensors(Xn, m, Mz, True, 2)
+    Gn = rng.standard_normal((m + 1, Mz, N))
+    a = ops.tens_vs_seq_vjp(_dev(Zn, torch.float32), _dev(Xn, torch.float32), _dev(Gn, torch.float32), m, increments=True, base='rbf')
+    b = ops.tens_vs_seq_vjp(_dev(Zn), _dev(Xn), _dev(Gn), m, increments=True, base='rbf')
+    for u, v in zip(a, b):
+        _close(u.double(), v, 5e-4)
+
+
+@pytest.mark.parametrize("increments", [False, True])
+def test_tens_tens_wide_state(increments):
+    """Kzz forward and adjoint with d > 8 (the 16-wide register tiles) against the oracle."""
+    from gpsig_b200 import ops
+    N, L, d, m, Mz = 4, 8, 12, 3, 7
+    rng = np.random.default_rng(14)
+    X = brownian(N, L, d, 0)
+    Z = inducing_tensors(X, m, Mz, increments, 2)
+    o, bp = _oracle('rbf', m, L, d)
+    K = ops.tens_tens(_dev(Z), m, increments=increments, base='rbf', return_levels=True).cpu().numpy()
+    Ko = o._K_tens(Z, increments=increments)
+    assert np.max(np.abs(K - Ko)) <= 1e-11 * np.max(np.abs(Ko))
+    G = rng.standard_normal((m + 1, Mz, Mz))
+    V = rng.standard_normal(Z.shape)
+    gZ = ops.tens_tens_vjp(_dev(Z), _dev(G), m, increments=increments, base='rbf', base_params=bp)
+    f = lambda A: float(np.sum(G * o._K_tens(A, increments=increments)))
+    _check([('Zz', float((gZ.cpu().numpy() * V).sum()), (f(Z + EPS * V) - f(Z - EPS * V)) / (2 * EPS))])
