@@ -450,14 +450,16 @@ static int trunc_vjp_impl(const gpsig_trunc_desc* desc, const T* X, int N, int L
   prof_begin(s);
   // few pairs (training shapes): one warp per pair; many pairs: one thread per pair fills the machine
   // sequences short enough for shared memory: one CTA per pair (any number of pairs)
+  P.w_cell_major = 1;
   const bool cta_per_pair = npairs < (1u << 30) && getenv("GPSIG_VJP_THREAD") == nullptr && getenv("GPSIG_VJP_NO_CTA") == nullptr &&
                             launch_trunc_vjp_tables_cta<T>(P, s);
+  if (!cta_per_pair) P.w_cell_major = 0;
   const bool warp_per_pair = !cta_per_pair && npairs < 32768 && getenv("GPSIG_VJP_THREAD") == nullptr && launch_trunc_vjp_tables_warp<T>(P, s);
   if (!cta_per_pair && !warp_per_pair) trunc_vjp_tables_kernel<T><<<(unsigned)((npairs + threads - 1) / threads), threads, 0, s>>>(P);
   prof_end(s);
   GPSIG_LAUNCH_CHECK("trunc_vjp_tables_kernel");
   const size_t tot = npairs * (size_t)(L + L2);
-  if (npairs < 32768 && getenv("GPSIG_VJP_THREAD") == nullptr) trunc_vjp_grad_warp_kernel<T><<<(unsigned)((tot + 7) / 8), 256, 0, s>>>(P);
+  if (cta_per_pair || (npairs < 32768 && getenv("GPSIG_VJP_THREAD") == nullptr)) trunc_vjp_grad_warp_kernel<T><<<(unsigned)((tot + 7) / 8), 256, 0, s>>>(P);
   else trunc_vjp_grad_kernel<T><<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(P);
   GPSIG_LAUNCH_CHECK("trunc_vjp_grad_kernel");
   return GPSIG_OK;

@@ -94,6 +94,7 @@ struct TruncVjpParams {
   void* gradX; void* gradY;          // [N, L, d] / [N2, L2, d], accumulated
   void* F; void* C; void* W;         // scratch: F [(m-1), P, Q, npairs], C [(m-1), Q, npairs], W [P, Q, npairs]
   size_t npairs;
+  int w_cell_major;                  // W is [npairs, P, Q] (written by the CTA-per-pair sweeps) instead of [P, Q, npairs]
 };
 
 // sweep 1+2: one thread per pair
@@ -342,8 +343,8 @@ __global__ void __launch_bounds__(128) trunc_vjp_tables_warp_kernel(const TruncV
 // sweep 1+2 with one CTA per pair: D and the current table (F_{a-1} or G_{b-1}) live in shared memory, the 2-D
 // exclusive prefix sum of each level is two parallel passes (down the rows: one thread per column; along the rows:
 // one warp per row, warp scans), and W accumulates in registers (cell e = tid + k * threads).  F_1..F_{m-1} go
-// through the HBM scratch in a private [pair][a][cell] layout (L2-resident, coalesced); W is written in the
-// pair-fastest layout the gradient kernels read.  Needs L * L2 <= 12288 cells.
+// through the HBM scratch in a private [pair][a][cell] layout (L2-resident, coalesced); W is written cell-fastest
+// per pair (`w_cell_major`), which the warp-per-point gradient kernel reads back coalesced.  Needs L * L2 <= 12288 cells.
 // ---------------------------------------------------------------------------
 constexpr int kVjpCtaThreads = 256;
 constexpr int kVjpCtaCells = 48;                                     // cells per thread at most
@@ -455,7 +456,7 @@ __global__ void __launch_bounds__(kVjpCtaThreads) trunc_vjp_tables_cta_kernel(co
 #pragma unroll
   for (int k = 0; k < kVjpCtaCells; ++k) {
     const int e = tid + k * NT;
-    if (e < cells) W[(size_t)e * np + pair] = w[k];
+    if (e < cells) W[pair * (size_t)cells + e] = w[k];                 // cell-fastest: coalesced, read back the same way
   }
 }
 
@@ -549,8 +550,9 @@ __global__ void __launch_bounds__(256) trunc_vjp_grad_warp_kernel(const TruncVjp
   const size_t np = P.npairs;
   const int LL = P.L + P.L2;
   if (t >= np * LL) return;
-  const int r = (int)(t / np);
-  const size_t pair = t % np;
+  // cell-major W: the 8 warps of a CTA take 8 consecutive points of one pair (its W rows are shared through L1 / L2)
+  const int r = P.w_cell_major ? (int)(t % LL) : (int)(t / np);
+  const size_t pair = P.w_cell_major ? t / LL : t % np;
   const int d = P.d, diff = P.difference ? 1 : 0;
   const int PR = P.L - diff, QC = P.L2 - diff;
   int i, j;
@@ -560,7 +562,7 @@ __global__ void __launch_bounds__(256) trunc_vjp_grad_warp_kernel(const TruncVjp
   const T* y = static_cast<const T*>(P.Y) + (size_t)j * P.L2 * d;
   const T* W = static_cast<const T*>(P.W);
   const T p0 = T(P.p0), p1 = T(P.p1);
-  auto Wat = [&](int p, int q) -> T { return (p < 0 || q < 0 || p >= PR || q >= QC) ? T(0) : W[((size_t)p * QC + q) * np + pair]; };
+  auto Wat = [&](int p, int q) -> T { return (p < 0 || q < 0 || p >= PR || q >= QC) ? T(0) : (P.w_cell_major ? W[pair * ((size_t)PR * QC) + (size_t)p * QC + q] : W[((size_t)p * QC + q) * np + pair]); };
   // dL/dM[pp, qq]: adjoint of the 2-D difference
   auto dM = [&](int pp, int qq) -> T {
     if (!diff) return Wat(pp, qq);

@@ -69,3 +69,15 @@ for dt in DTYPES:
             (Kzz.sum() + Kzx.sum() + Kxx.sum()).backward()
 
         print("%s minibatch %d: K_tens_n_seq_covs fwd+bwd %.3f ms" % (name, nb, ev_time(full_step)), flush=True)
+
+# Gram-sized backward (inducing sequences: K_seq_n_seq_covs): K(X, X2) raw levels, forward + backward
+for dt in DTYPES:
+    for n in (64, 256):
+        X = torch.as_tensor(brownian(n, L, d, 0), dtype=dt, device='cuda').requires_grad_(True)
+        Y = torch.as_tensor(brownian(n, L, d, 1), dtype=dt, device='cuda').requires_grad_(True)
+
+        def gram_step():
+            X.grad = None; Y.grad = None
+            ag.trunc_levels(X, Y, m, base='rbf').sum().backward()
+
+        print("%s K(X, X2) %dx%d L=%d fwd+bwd %.3f ms" % (str(dt)[6:], n, n, L, ev_time(gram_step)), flush=True)
