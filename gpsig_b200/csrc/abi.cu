@@ -459,7 +459,8 @@ static int trunc_vjp_impl(const gpsig_trunc_desc* desc, const T* X, int N, int L
   prof_end(s);
   GPSIG_LAUNCH_CHECK("trunc_vjp_tables_kernel");
   const size_t tot = npairs * (size_t)(L + L2);
-  if (cta_per_pair || (npairs < 32768 && getenv("GPSIG_VJP_THREAD") == nullptr)) trunc_vjp_grad_warp_kernel<T><<<(unsigned)((tot + 7) / 8), 256, 0, s>>>(P);
+  if (cta_per_pair && getenv("GPSIG_VJP_NO_GRAD_CTA") == nullptr && launch_trunc_vjp_grad_cta<T>(P, s)) {}
+  else if (cta_per_pair || (npairs < 32768 && getenv("GPSIG_VJP_THREAD") == nullptr)) trunc_vjp_grad_warp_kernel<T><<<(unsigned)((tot + 7) / 8), 256, 0, s>>>(P);
   else trunc_vjp_grad_kernel<T><<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(P);
   GPSIG_LAUNCH_CHECK("trunc_vjp_grad_kernel");
   return GPSIG_OK;

@@ -796,6 +796,106 @@ __device__ __forceinline__ T warp_transpose_reduce(T (&v)[NV], int lane, int& id
   for (; off > 0; off >>= 1) v[0] += __shfl_xor_sync(0xffffffffu, v[0], off);
   return v[0];
 }
+// ---------------------------------------------------------------------------
+// gradient kernel, one CTA per pair (after the CTA-per-pair sweeps, cell-major W, L2 <= 128): warp = a point of x,
+// lane = up to CQ points of y held in registers.  The base-kernel partials are evaluated ONCE per lifted element and
+// feed both sides: dL/dx_p is reduced over the lanes per point, dL/dy_q accumulates in the lane's registers over the
+// warp's points and is reduced over the 8 warps through shared memory.
+// ---------------------------------------------------------------------------
+template <typename T, int DP, int CQ>
+__global__ void __launch_bounds__(256) trunc_vjp_grad_cta_kernel(const TruncVjpParams P) {
+  extern __shared__ __align__(16) unsigned char vjp_grad_smem[];
+  T* red = reinterpret_cast<T*>(vjp_grad_smem);                      // [8 warps][CQ * 32][DP]
+  const size_t pair = blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int d = P.d, diff = P.difference ? 1 : 0, L = P.L, L2 = P.L2;
+  const int PR = L - diff, QC = L2 - diff;
+  int i, j;
+  if (P.diag) { i = P.row_begin + (int)pair; j = i; }
+  else { i = P.row_begin + (int)(pair / P.N2); j = (int)(pair % P.N2); }
+  const T* x = static_cast<const T*>(P.X) + (size_t)i * L * d;
+  const T* y = static_cast<const T*>(P.Y) + (size_t)j * L2 * d;
+  const T* W = static_cast<const T*>(P.W) + pair * ((size_t)PR * QC);
+  const T p0 = T(P.p0), p1 = T(P.p1);
+  auto Wat = [&](int p, int q) -> T { return (p < 0 || q < 0 || p >= PR || q >= QC) ? T(0) : W[(size_t)p * QC + q]; };
+  T yr[CQ][DP], ysq[CQ], gy[CQ][DP], by[CQ];
+#pragma unroll
+  for (int c = 0; c < CQ; ++c) {
+    const int q = lane + 32 * c;
+    ysq[c] = by[c] = T(0);
+#pragma unroll
+    for (int k = 0; k < DP; ++k) {
+      yr[c][k] = (q < L2 && k < d) ? y[(size_t)q * d + k] : T(0);
+      ysq[c] = gfma<T>(yr[c][k], yr[c][k], ysq[c]);
+      gy[c][k] = T(0);
+    }
+  }
+  for (int p = warp; p < L; p += 8) {
+    T xr[DP], gx[DP], xsq = T(0), bx = T(0);
+#pragma unroll
+    for (int k = 0; k < DP; ++k) { xr[k] = k < d ? x[(size_t)p * d + k] : T(0); xsq = gfma<T>(xr[k], xr[k], xsq); gx[k] = T(0); }
+#pragma unroll
+    for (int c = 0; c < CQ; ++c) {
+      const int q = lane + 32 * c;
+      if (q >= L2) continue;
+      const T a = diff ? (Wat(p - 1, q - 1) - Wat(p - 1, q)) - (Wat(p, q - 1) - Wat(p, q)) : Wat(p, q);   // adjoint of the 2-D difference
+      if (a == T(0)) continue;
+      T dot = T(0), fd, fx, fy;
+#pragma unroll
+      for (int k = 0; k < DP; ++k) dot = gfma<T>(xr[k], yr[c][k], dot);
+      base_partials_call<T>(P.base, p0, p1, dot, xsq, ysq[c], fd, fx, fy);
+      const T A = a * fd;
+      bx = gfma<T>(a, fx, bx);
+      by[c] = gfma<T>(a, fy, by[c]);
+#pragma unroll
+      for (int k = 0; k < DP; ++k) { gx[k] = gfma<T>(A, yr[c][k], gx[k]); gy[c][k] = gfma<T>(A, xr[k], gy[c][k]); }
+    }
+#pragma unroll
+    for (int k = 0; k < DP; ++k) gx[k] = gfma<T>(T(2) * bx, xr[k], gx[k]);
+    int idx;
+    const T tot = warp_transpose_reduce<T, DP>(gx, lane, idx);
+    if ((lane & (32 / DP - 1)) == 0 && idx < d && tot != T(0))
+      atomic_add<T>(static_cast<T*>(P.gradX) + ((size_t)i * L + p) * d + idx, tot);
+  }
+#pragma unroll
+  for (int c = 0; c < CQ; ++c)
+#pragma unroll
+    for (int k = 0; k < DP; ++k)
+      red[((size_t)warp * (CQ * 32) + c * 32 + lane) * DP + k] = gfma<T>(T(2) * by[c], yr[c][k], gy[c][k]);
+  __syncthreads();
+  for (int e = tid; e < CQ * 32 * DP; e += 256) {
+    const int q = e / DP, k = e - q * DP;
+    if (q >= L2 || k >= d) continue;
+    T v = T(0);
+#pragma unroll
+    for (int w = 0; w < 8; ++w) v += red[((size_t)w * (CQ * 32) + q) * DP + k];
+    if (v != T(0)) atomic_add<T>(static_cast<T*>(P.gradY) + ((size_t)j * L2 + q) * d + k, v);
+  }
+}
+
+template <typename T, int DP, int CQ>
+static bool launch_vjp_grad_cta_inst(const TruncVjpParams& P, cudaStream_t s) {
+  const size_t smem = (size_t)8 * CQ * 32 * DP * sizeof(T);
+  auto* kern = trunc_vjp_grad_cta_kernel<T, DP, CQ>;
+  if (smem > 48 * 1024 && cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return false;
+  kern<<<(unsigned)P.npairs, 256, smem, s>>>(P);
+  return true;
+}
+// needs the cell-major W of the CTA-per-pair sweeps; false when y is too long for the lanes' registers
+template <typename T>
+static bool launch_trunc_vjp_grad_cta(const TruncVjpParams& P, cudaStream_t s) {
+  if (!P.w_cell_major || P.L2 > 128 || P.d > 16) return false;
+  const int cq = P.L2 <= 32 ? 1 : (P.L2 <= 64 ? 2 : 4);
+  if (P.d <= 8) {
+    if (cq == 1) return launch_vjp_grad_cta_inst<T, 8, 1>(P, s);
+    if (cq == 2) return launch_vjp_grad_cta_inst<T, 8, 2>(P, s);
+    return launch_vjp_grad_cta_inst<T, 8, 4>(P, s);
+  }
+  if (cq == 1) return launch_vjp_grad_cta_inst<T, 16, 1>(P, s);
+  if (cq == 2) return launch_vjp_grad_cta_inst<T, 16, 2>(P, s);
+  return false;
+}
+
 template <typename T, int CW, int DP>
 __global__ void __launch_bounds__(kTsvWarps * 32, 2) tens_seq_vjp_warp_kernel(const TensSeqVjpParams P, int zchunks, int zper) {
   extern __shared__ __align__(16) unsigned char tsv_smem[];
