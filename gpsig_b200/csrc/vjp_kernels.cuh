@@ -403,12 +403,38 @@ __global__ void __launch_bounds__(kVjpCtaThreads) trunc_vjp_tables_cta_kernel(co
   auto step_level = [&](int dir) {
     for (int q = tid; q < QC; q += NT) {                             // down the rows
       T run = T(0);
-      if (dir > 0) for (int p = 0; p < PR; ++p) { const int e = p * QC + q; const T v = Dt[e] * Tc[e]; Tc[e] = run; run += v; }
-      else for (int p = PR - 1; p >= 0; --p) { const int e = p * QC + q; const T v = Dt[e] * Tc[e]; Tc[e] = run; run += v; }
+      // the next row's operands are read before this row's result is stored (the compiler cannot hoist them itself)
+      if (dir > 0) {
+        T dn = Dt[q], tn = Tc[q];
+        for (int p = 0; p < PR; ++p) {
+          const int e = p * QC + q;
+          const T v = dn * tn;
+          if (p + 1 < PR) { dn = Dt[e + QC]; tn = Tc[e + QC]; }
+          Tc[e] = run; run += v;
+        }
+      } else {
+        T dn = Dt[(PR - 1) * QC + q], tn = Tc[(PR - 1) * QC + q];
+        for (int p = PR - 1; p >= 0; --p) {
+          const int e = p * QC + q;
+          const T v = dn * tn;
+          if (p > 0) { dn = Dt[e - QC]; tn = Tc[e - QC]; }
+          Tc[e] = run; run += v;
+        }
+      }
     }
     __syncthreads();
+    if (QC & 1) {                                                    // along the rows, one thread per row: an odd row
+      for (int p = tid; p < PR; p += NT) {                           // stride keeps the 32 rows of a warp on distinct banks
+        T* row = Tc + (size_t)p * QC;
+        T run = T(0);
+        if (dir > 0) { T nxt = row[0]; for (int q = 0; q < QC; ++q) { const T v = nxt; if (q + 1 < QC) nxt = row[q + 1]; row[q] = run; run += v; } }
+        else { T nxt = row[QC - 1]; for (int q = QC - 1; q >= 0; --q) { const T v = nxt; if (q > 0) nxt = row[q - 1]; row[q] = run; run += v; } }
+      }
+      __syncthreads();
+      return;
+    }
     const int nch = (QC + 31) >> 5;
-    for (int p = warp; p < PR; p += NT / 32) {                       // along the rows
+    for (int p = warp; p < PR; p += NT / 32) {                       // even stride: one warp per row, warp scans
       T carry = T(0), tot;
       T* row = Tc + (size_t)p * QC;
       if (dir > 0) for (int c = 0; c < nch; ++c) {
@@ -446,7 +472,9 @@ __global__ void __launch_bounds__(kVjpCtaThreads) trunc_vjp_tables_cta_kernel(co
       const int e = tid + k * NT;
       if (e < cells) {
         T h = gs[b + 1];                                             // a = 0: F_0 = 1
-        for (int a = 1; a + b + 1 <= m; ++a) h = gfma<T>(gs[a + b + 1], Fg[(size_t)(a - 1) * cells + e], h);
+#pragma unroll
+        for (int a = 1; a < 8; ++a)                                  // m <= 8; branch-free so the loads of all cells overlap
+          if (a + b + 1 <= m) h = gfma<T>(gs[a + b + 1], Fg[(size_t)(a - 1) * cells + e], h);
         w[k] = gfma<T>(Tc[e], h, w[k]);
       }
     }
