@@ -1125,7 +1125,7 @@ template <typename T, int DP>
 __global__ void __launch_bounds__(128) tens_tens_vjp_kernel(const TensTensVjpParams P) {
   const int a = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
-  const int k = blockIdx.y;                                          // global component index
+  const int k = gridDim.y - 1 - blockIdx.y;                          // global component index; the top level's components cost the most: first
   if (a >= P.Mz) return;
   const int d = P.d, zs = P.zs, Mz = P.Mz;
   const T p0 = T(P.p0), p1 = T(P.p1);
