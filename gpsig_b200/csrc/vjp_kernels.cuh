@@ -943,6 +943,8 @@ __global__ void __launch_bounds__(kTsvWarps * 32, 2) tens_seq_vjp_warp_kernel(co
   T* Es = Ds + (size_t)m * CW * 32;
   T* Ks = Es + (size_t)m * CW * 32;                                  // forward base-kernel values [jj][s][c][lane]
   const bool from_value = P.base == GPSIG_BASE_RBF;                  // partials follow from the value: no second exp
+  const double tab = exp2((double)lane * (1.0 / 32.0));             // exp2_tab32's table, one entry per lane
+  (void)tab;
   auto at = [&](T* base, int jj, int c) -> T& { return base[(jj * CW + c) * 32 + lane]; };
 
   T xr[CW][DP], xsq[CW], gx[CW][DP], gxb[CW];
@@ -981,7 +983,13 @@ __global__ void __launch_bounds__(kTsvWarps * 32, 2) tens_seq_vjp_warp_kernel(co
             T dot = T(0);
 #pragma unroll
             for (int q = 0; q < DP; ++q) dot = gfma<T>(zr[q], xr[c][q], dot);
-            const T kv = base_eval_call<T>(P.base, p0, p1, dot, zsq, xsq[c]);
+            T kv;
+            if constexpr (sizeof(T) == 8) {                          // float64 RBF: the table exp2 of the forward kernels (9 FP64 instructions)
+              if (from_value) kv = exp2_tab32(((T(-2) * dot + zsq) + xsq[c]) * T(-0.5 * 1.4426950408889634), tab);   // exp(-r^2 / 2) = 2^(-r^2 log2(e) / 2)
+              else kv = base_eval_call<T>(P.base, p0, p1, dot, zsq, xsq[c]);
+            } else {
+              kv = base_eval_call<T>(P.base, p0, p1, dot, zsq, xsq[c]);
+            }
             Ks[((jj * 2 + s) * CW + c) * 32 + lane] = kv;
             mt[c] += neg ? -kv : kv;
           }
