@@ -169,3 +169,115 @@ def test_base_conditional_restatement_is_the_gaussian_conditional():
     mw, vw = svgp_np.base_conditional(Kmn, Kmm, np.diag(Knn), f, full_cov=False, q_sqrt=q, white=True)
     mu, vu = svgp_np.base_conditional(Kmn, Kmm, np.diag(Knn), Lm @ f, full_cov=False, q_sqrt=np.matmul(Lm[None], q), white=False)
     assert np.allclose(mw, mu) and np.allclose(vw, vu)
+
+
+# ---------------------------------------------------------------------------------------------------
+# Independent definitional pin of the FIRST-ORDER recursions (the reference's TF graph cannot run here).
+# Unrolling R_i = D * cumsum_excl_p cumsum_excl_q R_{i-1}, K_i = sum R_i  (signature_algs.py:26-33) gives
+#     K_i(x, y) = sum over p_1 < ... < p_i, q_1 < ... < q_i of prod_k D[p_k, q_k],
+# and R = M[k'] * cumsum_excl_l R, K_i = sum_l R  (signature_algs.py:114-125) gives
+#     K_i(z, x) = sum over l_1 < ... < l_i of prod_j Md[k_i + j - 1][l_j].
+# Both are enumerated with itertools.combinations from base-kernel values computed point by point
+# (no code shared with oracle/trunc_np.py or the C port).
+# ---------------------------------------------------------------------------------------------------
+import itertools
+
+
+def _kappa(base, x, y):
+    if base == 'linear':
+        return float(np.dot(x, y))
+    return float(np.exp(-0.5 * np.sum((x - y) ** 2)))
+
+
+def _brute_first_order(x, y, m, base, difference=True):
+    L, L2 = len(x), len(y)
+    M = np.array([[_kappa(base, x[p], y[q]) for q in range(L2)] for p in range(L)])
+    D = M[1:, 1:] - M[:-1, 1:] - M[1:, :-1] + M[:-1, :-1] if difference else M
+    P, Q = D.shape
+    out = [1.0]
+    for i in range(1, m + 1):
+        tot = 0.0
+        for ps in itertools.combinations(range(P), i):
+            for qs in itertools.combinations(range(Q), i):
+                term = 1.0
+                for p, q in zip(ps, qs):
+                    term *= D[p, q]
+                tot += term
+        out.append(tot)
+    return np.array(out)
+
+
+def _brute_tens_vs_seq(zrows, x, m, base, increments, difference=True):
+    """zrows: [T, d] (or [T, 2, d] with increments) components of ONE inducing tensor, x: [L, d]."""
+    L = len(x)
+    out = [1.0]
+    k = 0
+    for i in range(1, m + 1):
+        comps = []
+        for j in range(i):
+            if increments:
+                v = np.array([_kappa(base, zrows[k + j, 1], x[l]) - _kappa(base, zrows[k + j, 0], x[l]) for l in range(L)])
+            else:
+                v = np.array([_kappa(base, zrows[k + j], x[l]) for l in range(L)])
+            comps.append(v[1:] - v[:-1] if difference else v)
+        k += i
+        n = len(comps[0])
+        tot = 0.0
+        for ls in itertools.combinations(range(n), i):
+            term = 1.0
+            for j, l in enumerate(ls):
+                term *= comps[j][l]
+            tot += term
+        out.append(tot)
+    return np.array(out)
+
+
+@pytest.mark.parametrize("base", ["linear", "rbf"])
+@pytest.mark.parametrize("difference", [True, False])
+def test_first_order_gram_equals_sum_over_increasing_index_tuples(base, difference):
+    """Pins signature_kern_first_order (recursion, exclusive-cumsum convention, 2-D differencing) of the numpy
+    restatement AND of the C port against brute-force enumeration, L <= 7, m <= 4."""
+    N, N2, L, L2, d, m = 3, 2, 7, 6, 2, 4
+    X, Y = brownian(N, L, d, 21) * 1.5, brownian(N2, L2, d, 22) * 1.5
+    ref = np.array([[_brute_first_order(X[i], Y[j], m, base, difference) for j in range(N2)] for i in range(N)]).transpose(2, 0, 1)
+    o = trunc_np.SignatureKernelOracle(L * d, d, m, base=base, normalization=False, lengthscales=None, difference=difference)
+    assert rel_err(o._K_seq(X, Y), ref) < 1e-12
+    assert rel_err(c_oracle.trunc_gram(X, Y, m, base, difference=difference), ref) < 1e-12
+    # the diagonal form M[N, L, L] (signature_algs.py:13-18) and the symmetric call
+    refd = np.array([_brute_first_order(X[i], X[i], m, base, difference) for i in range(N)]).T
+    assert rel_err(o._K_seq_diag(X), refd) < 1e-12
+    assert rel_err(c_oracle.trunc_diag(X, m, base, difference=difference), refd) < 1e-12
+    assert rel_err(np.diagonal(o._K_seq(X), axis1=1, axis2=2), refd) < 1e-12
+
+
+@pytest.mark.parametrize("base", ["linear", "rbf"])
+@pytest.mark.parametrize("increments", [False, True])
+def test_first_order_tens_vs_seq_equals_sum_over_increasing_times(base, increments):
+    N, L, d, m, Mz = 3, 7, 2, 4, 3
+    X = brownian(N, L, d, 23) * 1.5
+    Z = inducing_tensors(X, m, Mz, increments, 24)
+    ref = np.array([[_brute_tens_vs_seq(Z[:, z], X[n], m, base, increments) for n in range(N)] for z in range(Mz)]).transpose(2, 0, 1)
+    o = trunc_np.SignatureKernelOracle(L * d, d, m, base=base, normalization=False, lengthscales=None)
+    assert rel_err(o._K_tens_vs_seq(Z, X, increments), ref) < 1e-12
+    assert rel_err(c_oracle.tens_vs_seq(Z, X, m, increments, base), ref) < 1e-12
+
+
+def test_normalised_wrapper_equals_definition_on_brute_force_levels():
+    """kernels.py:456-477, the epilogue, from brute-force levels: non-symmetric call = no jitter on the Gram,
+    jitter (gpflow default 1e-6) added to both diagonals before the square root (kernels.py:466-470)."""
+    N, N2, L, d, m = 3, 2, 6, 2, 3
+    X, Y = brownian(N, L, d, 25) * 1.5, brownian(N2, L, d, 26) * 1.5
+    var, sigma = np.linspace(0.5, 1.5, m + 1), 1.3
+    raw = np.array([[_brute_first_order(X[i], Y[j], m, 'rbf') for j in range(N2)] for i in range(N)]).transpose(2, 0, 1)
+    dx = np.array([_brute_first_order(X[i], X[i], m, 'rbf') for i in range(N)]).T
+    dy = np.array([_brute_first_order(Y[j], Y[j], m, 'rbf') for j in range(N2)]).T
+    ref = sigma * var[:, None, None] * raw / (np.sqrt(dx + 1e-6)[:, :, None] * np.sqrt(dy + 1e-6)[:, None, :])
+    o = trunc_np.SignatureKernelOracle(L * d, d, m, base='rbf', lengthscales=None, variances=var, sigma=sigma)
+    assert rel_err(o.K(X.reshape(N, -1), Y.reshape(N2, -1), return_levels=True), ref) < 1e-12
+    assert rel_err(o.K(X.reshape(N, -1), Y.reshape(N2, -1)), ref.sum(0)) < 1e-12
+    # symmetric call (kernels.py:431-434): jitter on the Gram's diagonal, normalised by its own diagonal
+    raws = np.array([[_brute_first_order(X[i], X[j], m, 'rbf') for j in range(N)] for i in range(N)]).transpose(2, 0, 1)
+    raws = raws + 1e-6 * np.eye(N)[None]
+    ds = np.sqrt(np.diagonal(raws, axis1=1, axis2=2))
+    refs = sigma * var[:, None, None] * raws / (ds[:, :, None] * ds[:, None, :])
+    assert rel_err(o.K(X.reshape(N, -1), return_levels=True), refs) < 1e-12
