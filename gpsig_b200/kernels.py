@@ -38,6 +38,31 @@ def _side_streams(device):
     return _SIDE_STREAMS[key]
 
 
+def _scalar_param(value, name):
+    """Base-kernel scalars (SignaturePoly.gamma, SignatureMix.mixing: trainable Parameters in the reference,
+    kernels.py:1016, 1056).  They enter the CUDA kernels as constants; a tensor that requires grad would be
+    detached silently, so it is refused instead."""
+    if torch.is_tensor(value):
+        if value.requires_grad and torch.is_grad_enabled():
+            raise NotImplementedError('gpsig_b200: %s is not trainable (no adjoint w.r.t. the base-kernel scalars); '
+                                      'pass a plain number or a tensor without requires_grad' % name)
+        return float(value.detach().cpu())
+    return float(value)
+
+
+def as_device_tensor(A, what="input"):
+    """Zero-copy ingestion of a device array: a torch tensor is used as it is, any other object that implements
+    the DLPack protocol (``__dlpack__`` / ``__dlpack_device__``: TensorFlow / CuPy / JAX / Numba device arrays) is
+    wrapped with ``torch.from_dlpack`` -- the CUDA kernels then read the producer's own memory through the raw
+    pointer (north star: "TF custom op with DLPack zero-copy"; the TF side is ``tf.experimental.dlpack``)."""
+    if torch.is_tensor(A):
+        return A
+    if hasattr(A, '__dlpack__') and hasattr(A, '__dlpack_device__'):
+        return torch.from_dlpack(A)
+    raise TypeError("gpsig_b200 kernels take torch CUDA tensors or DLPack-capable device arrays for %s "
+                    "(use compute_* for numpy)" % what)
+
+
 class SignatureKernel:
     """gpsig/kernels.py:16-134 (constructor and validators)."""
 
@@ -131,27 +156,30 @@ class SignatureKernel:
     def _seq(self, X):
         """[N, L*d] -> contiguous [N, L, d]  (kernels.py:418-420).  With lags: the scaled, lagged
         sequences [N, L, d*(num_lags+1)] of ``_apply_scaling_and_lags_to_sequences`` (kernels.py:343-365)."""
-        if not torch.is_tensor(X):
-            raise TypeError("gpsig_b200 kernels take torch CUDA tensors (use compute_* for numpy)")
+        X = as_device_tensor(X, "sequences")
         X = X.reshape(X.shape[0], -1, self.num_features)
         if self.num_lags > 0:
             X = _lags.add_lags_to_sequences(X, self._param(self.lags, X))           # [N, L, num_lags+1, d]
             if self.lengthscales is not None:
                 X = X / self._param(self.lengthscales, X)[None, None, None, :]
-            X = X * self._param(self.gamma, X)[None, None, :, None]
+            X = X * self._param(self._lag_gamma(), X)[None, None, :, None]
             X = X.reshape(X.shape[0], X.shape[1], -1)
         return X.contiguous()
 
     def _tens(self, Z, increments):
         """Inducing tensors as the CUDA kernels take them.  Without lags the lengthscales are applied
         inside the library; with lags the scaling of kernels.py:367-399 is done here."""
-        Z = Z.contiguous()
+        Z = as_device_tensor(Z, "inducing tensors").contiguous()
         if self.num_lags > 0 and self.lengthscales is not None:
             shp = Z.shape
             Zr = Z.reshape(shp[:-1] + (self.num_lags + 1, self.num_features))
-            Zr = Zr / self._param(self.lengthscales, Z) * self._param(self.gamma, Z)[:, None]
+            Zr = Zr / self._param(self.lengthscales, Z) * self._param(self._lag_gamma(), Z)[:, None]
             Z = Zr.reshape(shp).contiguous()
         return Z
+
+    def _lag_gamma(self):
+        """Lag weights of kernels.py:82-83 (``self.gamma``; SignatureSpectral re-uses that name for its own block)."""
+        return self.gamma
 
     def _param(self, value, like):
         if value is None:
@@ -208,7 +236,7 @@ class SignatureKernel:
             X = _lags.add_lags_to_sequences(X, self._param(self.lags, X))
             if ls is not None:
                 X = X / ls[None, None, None, :]
-            X = X * self._param(self.gamma, X)[None, None, :, None]
+            X = X * self._tparam(self._lag_gamma(), X)[None, None, :, None]
             return X.reshape(X.shape[0], X.shape[1], -1)
         return X if ls is None else X / ls
 
@@ -219,7 +247,7 @@ class SignatureKernel:
         if self.num_lags > 0:
             shp = Z.shape
             Zr = Z.reshape(shp[:-1] + (self.num_lags + 1, self.num_features))
-            return (Zr / ls * self._param(self.gamma, Z)[:, None]).reshape(shp)
+            return (Zr / ls * self._tparam(self._lag_gamma(), Z)[:, None]).reshape(shp)
         return Z / ls
 
     def _d_scale(self, like):
@@ -294,6 +322,36 @@ class SignatureKernel:
             out = {k: v.sum(dim=0) for k, v in out.items()}
         return out
 
+    def _d_seq_n_seq(self, X, X2, full_X2_cov, return_levels):
+        """Differentiable K_seq_n_seq_covs (kernels.py:706-794): gradients reach the inducing sequences, the inputs,
+        lengthscales, variances and sigma.  Same order of operations as the reference, including the division of
+        the cross term by sqrt(diag Kxx) twice (kernels.py:746 and :783)."""
+        from . import autograd as ag
+        self._d_check()
+        Xs, X2s = self._d_seq(X), self._d_seq(X2)
+        sc = self._d_scale(Xs)
+        m, jitter, bk = self.num_levels, settings.jitter, self._d_bk()
+        Kxx = ag.trunc_levels(Xs, None, m, difference=self.difference, **bk)
+        Kxx2 = ag.trunc_levels(Xs, X2s, m, difference=self.difference, **bk)
+        if self.normalization:
+            Kxx = Kxx + jitter * torch.eye(Xs.shape[0], dtype=Xs.dtype, device=Xs.device)[None]       # :742
+            dsq = torch.sqrt(torch.diagonal(Kxx, dim1=1, dim2=2))                                       # :744
+            Kxx = Kxx / (dsq[:, :, None] * dsq[:, None, :])
+            Kxx2 = Kxx2 / dsq[:, :, None]                                                                # :746
+        if full_X2_cov:                                            # only reachable without normalisation (:756)
+            Kx2x2 = ag.trunc_levels(X2s, None, m, difference=self.difference, **bk) * sc[:, None, None]
+        else:
+            d2 = ag.trunc_diag_levels(X2s, m, difference=self.difference, **bk)
+            if self.normalization:
+                Kxx2 = Kxx2 / (dsq[:, :, None] * torch.sqrt(d2 + jitter)[:, None, :])                    # :783
+                Kx2x2 = sc[:, None].repeat(1, X2s.shape[0])
+            else:
+                Kx2x2 = d2 * sc[:, None]
+        Kxx, Kxx2 = Kxx * sc[:, None, None], Kxx2 * sc[:, None, None]
+        if return_levels:
+            return Kxx, Kxx2, Kx2x2
+        return Kxx.sum(dim=0), Kxx2.sum(dim=0), Kx2x2.sum(dim=0)
+
     # ---- public API ------------------------------------------------------------
     def K(self, X, X2=None, presliced=False, return_levels=False, presliced_X=False, presliced_X2=False, rows=None,
           upper_only=False):
@@ -303,6 +361,8 @@ class SignatureKernel:
         block of the Gram -- the unit of multi-GPU sharding.  ``upper_only`` (with ``X2=None``): the caller only
         needs the entries on and above the diagonal of its rows (``sharding.sharded_gram`` mirrors the rest).
         """
+        X = as_device_tensor(X, "X")
+        X2 = None if X2 is None else as_device_tensor(X2, "X2")
         if presliced:
             presliced_X = presliced_X2 = True
         if not presliced_X and not presliced_X2:
@@ -336,14 +396,22 @@ class SignatureKernel:
 
     def K_norms(self, X, presliced=False):
         """kernels.py:480-506."""
+        X = as_device_tensor(X, "X")
         if not presliced:
             X, _ = self._slice(X, None)
+        if self._wants_grad(X):
+            from . import autograd as ag
+            self._d_check()
+            Xs = self._d_seq(X)
+            const = self._d_scale(Xs).sum().expand(Xs.shape[0])
+            return const, ag.trunc_diag_levels(Xs, self.num_levels, difference=self.difference, **self._d_bk())
         Xs = self._seq(X)
-        const = torch.full((Xs.shape[0],), float(self.sigma) * float(np.sum(self.variances)), dtype=Xs.dtype, device=Xs.device)
+        const = self._level_scale(Xs).sum().expand(Xs.shape[0]).contiguous()
         return const, self._K_seq_diag(Xs)
 
     def Kdiag(self, X, presliced=False, return_levels=False):
         """kernels.py:509-541."""
+        X = as_device_tensor(X, "X")
         N = X.shape[0]
         if self._wants_grad(X):
             self._d_check()
@@ -360,7 +428,7 @@ class SignatureKernel:
             sc = self._level_scale(X)
             if return_levels:
                 return sc[:, None].repeat(1, N)
-            return torch.full((N,), float(self.sigma) * float(np.sum(self.variances)), dtype=X.dtype, device=X.device)
+            return sc.sum().expand(N).contiguous()
         if not presliced:
             X, _ = self._slice(X, None)
         Xs = self._seq(X)
@@ -369,6 +437,7 @@ class SignatureKernel:
 
     def K_tens(self, Z, return_levels=False, increments=False):
         """Square covariance of inducing tensors (kernels.py:543-567)."""
+        Z = as_device_tensor(Z, "Z")
         if self._wants_grad(Z):
             return self._d_tens_n_seq(Z, None, increments, False, return_levels, want=('zz',))['zz']
         Z = self._tens(Z, increments)   # Kzz does not depend on `order` (signature_algs.py:76-99)
@@ -378,6 +447,7 @@ class SignatureKernel:
 
     def K_tens_vs_seq(self, Z, X, return_levels=False, increments=False, presliced=False, cols=None):
         """Inducing tensors vs sequences (kernels.py:570-620)."""
+        Z, X = as_device_tensor(Z, "Z"), as_device_tensor(X, "X")
         if not presliced:
             X, _ = self._slice(X, None)
         if self._wants_grad(Z, X):
@@ -392,6 +462,7 @@ class SignatureKernel:
 
     def K_tens_n_seq_covs(self, Z, X, full_X_cov=False, return_levels=False, increments=False, presliced=False):
         """Kzz, Kzx, Kxx in one call (kernels.py:623-704)."""
+        Z, X = as_device_tensor(Z, "Z"), as_device_tensor(X, "X")
         if not presliced:
             X, _ = self._slice(X, None)
         if self._wants_grad(Z, X):
@@ -431,15 +502,18 @@ class SignatureKernel:
         and ``full_X2_cov=False`` the cross term is divided by sqrt(diag Kxx)
         twice (kernels.py:746 and :783).
         """
+        X, X2 = as_device_tensor(X, "X"), as_device_tensor(X2, "X2")
         if not presliced:
             X2, _ = self._slice(X2, None)
+        if self.normalization and full_X2_cov:
+            raise NameError("name 'K_x2x2_lvls' is not defined")   # kernels.py:756
+        if self._wants_grad(X, X2):
+            return self._d_seq_n_seq(X, X2, full_X2_cov, return_levels)
         Xs, X2s = self._seq(X), self._seq(X2)
         N2 = X2s.shape[0]
         jitter = settings.jitter
         sc = self._level_scale(Xs)
         kw = self._kw(Xs)
-        if self.normalization and full_X2_cov:
-            raise NameError("name 'K_x2x2_lvls' is not defined")   # kernels.py:756
         if self.normalization:
             nx = self._K_seq_diag(Xs) + jitter
             Kxx = ops.trunc_gram(Xs, None, self.num_levels, norm_x=nx, norm_x2=nx, level_scale=sc, sym_jitter=jitter,
@@ -514,11 +588,15 @@ class SignaturePoly(SignatureKernel):
 
     def __init__(self, input_dim, num_features, num_levels, gamma=1, degree=3, **kwargs):
         SignatureKernel.__init__(self, input_dim, num_features, num_levels, **kwargs)
+        self._lag_weights = getattr(self, 'gamma', None)     # kernels.py:82-83 vs :1016 use the same attribute name
         self.gamma = float(gamma)
         self.degree = float(degree)
 
+    def _lag_gamma(self):
+        return self._lag_weights
+
     def _get_base_params(self, like=None):
-        return (self.gamma, self.degree)
+        return (_scalar_param(self.gamma, 'SignaturePoly.gamma'), float(self.degree))
 
 
 class SignatureRBF(SignatureKernel):
@@ -538,7 +616,7 @@ class SignatureMix(SignatureKernel):
         self.mixing = 0.5
 
     def _get_base_params(self, like=None):
-        return (float(self.mixing),)
+        return (_scalar_param(self.mixing, 'SignatureMix.mixing'),)
 
 
 class SignatureSpectral(SignatureKernel):
@@ -566,6 +644,7 @@ class SignatureSpectral(SignatureKernel):
         else:
             raise ValueError("Unrecognized spectral family name.")
         self.Q = Q
+        self._lag_weights = getattr(self, 'gamma', None)     # kernels.py:82-83 vs :1094 use the same attribute name
         self.alpha = np.exp(np.random.randn(Q))
         self.omega = np.exp(np.random.randn(Q, self.num_features))
         self.gamma = np.exp(np.random.randn(Q, self.num_features))
@@ -580,6 +659,9 @@ class SignatureSpectral(SignatureKernel):
             raise ValueError("alpha / omega / gamma must have shapes [Q], [Q, d], [Q, d]")
         block = np.concatenate([np.asarray(self.alpha, dtype=np.float64).ravel(), omega.ravel(), gamma.ravel()])
         return (self.family, self.Q, torch.as_tensor(block, dtype=torch.float64, device=dev).contiguous())
+
+    def _lag_gamma(self):
+        return self._lag_weights
 
     def _d_check(self):
         raise NotImplementedError('gpsig_b200: gradients are not implemented for the spectral base kernel')

@@ -19,6 +19,7 @@ import torch
 
 from . import autograd, ops, settings
 from . import lags as _lags
+from .kernels import as_device_tensor
 
 
 class UntruncSignatureKernel:
@@ -95,6 +96,7 @@ class UntruncSignatureKernel:
 
     def Kdiag(self, X, presliced=False, name=None, rows=None):
         """sigma * k(x_i, x_i) for every sequence (kernels_pde.py:160-185)."""
+        X = as_device_tensor(X, "X")
         if not presliced:
             X = self._slice(X)
         Xs = self._seq(X)
@@ -120,6 +122,8 @@ class UntruncSignatureKernel:
 
     def K(self, X, X2=None, presliced=False, rows=None):
         """Full untruncated Gram sigma * k(x_i, y_j) (extension, see module docstring)."""
+        X = as_device_tensor(X, "X")
+        X2 = None if X2 is None else as_device_tensor(X2, "X2")
         if not presliced:
             X = self._slice(X)
             X2 = None if X2 is None else self._slice(X2)

@@ -123,3 +123,129 @@ def test_elbo_style_gradients_flow_to_inducing_tensors():
     loss.backward()
     for t in (Z, feat.W, k.lengthscales, q_mu):
         assert t.grad is not None and torch.isfinite(t.grad).all() and float(t.grad.abs().max()) > 0
+
+
+def test_inducing_sequences_gradients_reach_Z_and_kernel_parameters():
+    """K_seq_n_seq_covs (kernels.py:706-794) on the differentiable path: same values as the fused forward, and
+    gradients w.r.t. the inducing sequences, lengthscales, variances and sigma (checked by central differences of
+    the non-differentiable CUDA forward)."""
+    from gpsig_b200 import kernels
+    from gpsig_b200.inducing_variables import InducingSequences, Kuu_Kuf_Kff
+    N, L, d, m, Mz = 7, 12, 2, 3, 4
+    X, Zs = brownian(N, L, d, 70), brownian(Mz, L, d, 71)
+    Xd = _dev(X.reshape(N, -1))
+    for norm in (True, False):
+        k = kernels.SignatureRBF(L * d, d, m, normalization=norm, lengthscales=np.array([0.9, 1.2]))
+        with torch.no_grad():
+            ref = k.K_seq_n_seq_covs(_dev(Zs.reshape(Mz, -1)), Xd)
+        Zt = _dev(Zs.reshape(Mz, -1)).requires_grad_(True)
+        k.lengthscales = _dev(np.array([0.9, 1.2])).requires_grad_(True)
+        k.variances = _dev(np.ones(m + 1)).requires_grad_(True)
+        k.sigma = _dev(np.array(1.0)).requires_grad_(True)
+        got = k.K_seq_n_seq_covs(Zt, Xd)
+        for g, r in zip(got, ref):
+            assert g.requires_grad and rel_err(g.detach().cpu().numpy(), r.cpu().numpy()) < 1e-10
+        rng = np.random.default_rng(72)
+        w = [_dev(rng.standard_normal(tuple(g.shape))) for g in got]
+        loss = sum((g * ww).sum() for g, ww in zip(got, w))
+        loss.backward()
+        for t in (Zt, k.lengthscales, k.variances, k.sigma):
+            assert t.grad is not None and torch.isfinite(t.grad).all() and float(t.grad.abs().max()) > 0
+
+        def f(Zv, ls):
+            kk = kernels.SignatureRBF(L * d, d, m, normalization=norm, lengthscales=ls)
+            with torch.no_grad():
+                o = kk.K_seq_n_seq_covs(_dev(Zv), Xd)
+            return float(sum((g * ww).sum() for g, ww in zip(o, w)))
+        # directional derivative w.r.t. Z and w.r.t. the lengthscales
+        dZ = rng.standard_normal((Mz, L * d))
+        h = 1e-5
+        fd = (f(Zs.reshape(Mz, -1) + h * dZ, np.array([0.9, 1.2])) - f(Zs.reshape(Mz, -1) - h * dZ, np.array([0.9, 1.2]))) / (2 * h)
+        an = float((Zt.grad.cpu().numpy() * dZ).sum())
+        assert abs(fd - an) < 2e-6 * max(1.0, abs(fd)), (norm, fd, an)
+        dl = np.array([0.3, -0.7])
+        fd = (f(Zs.reshape(Mz, -1), np.array([0.9, 1.2]) + h * dl) - f(Zs.reshape(Mz, -1), np.array([0.9, 1.2]) - h * dl)) / (2 * h)
+        an = float((k.lengthscales.grad.cpu().numpy() * dl).sum())
+        assert abs(fd - an) < 2e-6 * max(1.0, abs(fd)), (norm, fd, an)
+    # through the SVGP dispatch
+    feat = InducingSequences(_dev(Zs).requires_grad_(True), m)
+    k = kernels.SignatureRBF(L * d, d, m)
+    Kzz, Kzx, Kxx = Kuu_Kuf_Kff(feat, k, Xd, jitter=1e-6)
+    (Kzz.sum() + Kzx.sum() + Kxx.sum()).backward()
+    assert feat.Z.grad is not None and float(feat.Z.grad.abs().max()) > 0
+
+
+def test_tensor_variances_at_prediction_time():
+    """Kdiag / K_norms with trained (tensor) variances and sigma under no_grad (np.sum on a tensor)."""
+    from gpsig_b200 import kernels
+    N, L, d, m = 5, 10, 2, 3
+    X = _dev(brownian(N, L, d, 73).reshape(N, -1))
+    k = kernels.SignatureRBF(L * d, d, m)
+    k.variances = _dev(np.linspace(0.5, 1.5, m + 1)).requires_grad_(True)
+    k.sigma = _dev(np.array(1.3)).requires_grad_(True)
+    with torch.no_grad():
+        kd = k.Kdiag(X)
+        const, _ = k.K_norms(X)
+    assert rel_err(kd.cpu().numpy(), np.full(N, 1.3 * np.linspace(0.5, 1.5, m + 1).sum())) < 1e-12
+    assert rel_err(const.cpu().numpy(), np.full(N, 1.3 * np.linspace(0.5, 1.5, m + 1).sum())) < 1e-12
+    const, lv = k.K_norms(X)                      # differentiable path: reaches sigma / variances
+    const.sum().backward()
+    assert k.variances.grad is not None and float(k.variances.grad.abs().max()) > 0
+
+
+def test_poly_and_mix_scalars_are_refused_when_trainable():
+    from gpsig_b200 import kernels
+    N, L, d, m = 4, 8, 2, 2
+    X = _dev(brownian(N, L, d, 74).reshape(N, -1))
+    k = kernels.SignaturePoly(L * d, d, m, gamma=1.0, degree=3)
+    ref = k.K(X)
+    k.gamma = torch.tensor(1.0, device='cuda')                 # a plain tensor is fine
+    assert rel_err(k.K(X).cpu().numpy(), ref.cpu().numpy()) < 1e-14
+    k.gamma = torch.tensor(1.0, device='cuda', requires_grad=True)
+    with pytest.raises(NotImplementedError):
+        k.K(X)
+    k = kernels.SignatureMix(L * d, d, m)
+    k.mixing = torch.tensor(0.5, device='cuda', requires_grad=True)
+    with pytest.raises(NotImplementedError):
+        k.K(X)
+    # spectral kernel with lags: the lag weights are not clobbered by the [Q, d] gamma block (kernels.py:82 vs :1094)
+    ks = kernels.SignatureSpectral(L * d, d, m, Q=2, num_lags=1)
+    assert np.asarray(ks._lag_gamma()).shape == (2,) and np.asarray(ks.gamma).shape == (2, d)
+
+
+class _DLPackOnly:
+    """A device array that is NOT a torch tensor: exposes only the DLPack protocol (what tf.experimental.dlpack /
+    CuPy / JAX arrays offer)."""
+
+    def __init__(self, t):
+        self._t = t
+        self.shape = tuple(t.shape)
+
+    def __dlpack__(self, *a, **kw):
+        return self._t.__dlpack__(*a, **kw)
+
+    def __dlpack_device__(self):
+        return self._t.__dlpack_device__()
+
+
+def test_dlpack_producers_are_ingested_zero_copy():
+    """north star: 'DLPack zero-copy' -- any __dlpack__ producer is accepted by the kernels' methods and read in place."""
+    from gpsig_b200 import kernels, kernels_pde
+    from gpsig_b200.kernels import as_device_tensor
+    N, L, d, m, Mz = 6, 12, 3, 3, 4
+    Xn = brownian(N, L, d, 75)
+    Xt = _dev(Xn.reshape(N, -1))
+    Xp = _DLPackOnly(Xt)
+    assert not torch.is_tensor(Xp)
+    assert as_device_tensor(Xp).data_ptr() == Xt.data_ptr()            # zero copy: same device memory
+    k = kernels.SignatureRBF(L * d, d, m)
+    assert torch.equal(k.K(Xp), k.K(Xt))
+    assert torch.equal(k.K(Xp, _DLPackOnly(Xt[:3])), k.K(Xt, Xt[:3]))
+    assert torch.equal(k.Kdiag(Xp), k.Kdiag(Xt))
+    Z = _dev(inducing_tensors(Xn, m, Mz, True, 76))
+    for a, b in zip(k.K_tens_n_seq_covs(_DLPackOnly(Z), Xp, increments=True), k.K_tens_n_seq_covs(Z, Xt, increments=True)):
+        assert torch.equal(a, b)
+    kp = kernels_pde.UntruncSignatureKernel(L * d, d, order=1)
+    assert torch.equal(kp.Kdiag(Xp), kp.Kdiag(Xt))
+    with pytest.raises(TypeError):
+        k.K(Xn.reshape(N, -1))                                          # numpy goes through compute_*
