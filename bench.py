@@ -4,11 +4,16 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--dtype f64|f32] [--impl ours|reference]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
-Workload (BASELINE.json configs[1], "c2"): SignatureRBF, num_levels=5, order=1,
-normalization=True, K(X, X2) with N = N2 = 2000 synthetic Brownian paths,
-L = 200, d = 8.  One step = one full K(X, X2) call = 4e6 ordered pairs.  With
-N GPUs every rank owns a 2000-row block of a (2000 N) x 2000 Gram (weak
-scaling, rows are independent: no data-path collective).
+Workload (BASELINE.json configs[4] "c5", per-pair shape of configs[1] "c2"):
+SignatureRBF, num_levels=5, order=1, normalization=True, synthetic Brownian
+paths, L = 200, d = 8.  One step = ONE row slab of the large Gram,
+K(X[slab], X2) with 2000 slab rows against N2 = 20 000 columns = 4e7 ordered
+pairs, computed through gpsig_b200.sharding.sharded_gram: the slab's rows are
+split over the N ranks, every rank computes its rows straight into its slice of
+the [2000, 20000] result and the slices are exchanged with ONE in-place NCCL
+all-gather INSIDE the timed region, so the finished slab is on every rank
+(strong scaling: the total work per step is fixed).  The full c2 Gram
+(N = N2 = 2000) is timed as other_configs.c2_f64 / c2_f32.
 
 Prints ONE JSON line (rank 0).  `value` = pairs/s with the inputs resident in
 HBM; `e2e` = the same through the numpy-in/numpy-out call (pinned host
@@ -33,8 +38,9 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-CFG = dict(workload="c2: SignatureRBF m=5 order=1 normalization=True K(X,X2), N=N2=2000, L=200, d=8, Brownian paths",
-           N=2000, N2=2000, L=200, d=8, m=5)
+CFG = dict(workload="c5 slab: SignatureRBF m=5 order=1 normalization=True, K(X[slab], X2) = 2000 rows x 20000 columns of the large "
+                    "Gram per step (per-pair shape of c2: L=200, d=8), rows sharded over the ranks + in-place NCCL all-gather, Brownian paths",
+           N=2000, N2=20000, L=200, d=8, m=5)
 METRIC = "signature-kernel Gram pairs/sec (L=200,M=5)"
 UNIT = "pairs/s"
 
@@ -87,7 +93,7 @@ def run_reference(args):
     side = int(max(16, min(512, (v0 * 4.0) ** 0.5)))
     v, t = cpu_pairs_per_sec(side, steps=args.steps, warmup=args.warmup)
     line = {"metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": 1e3 * t, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "ms_per_step": 1e3 * t, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic Brownian paths (seeded)", "impl": "reference", "config": dict(CFG, sample="%dx%d pairs per step" % (side, side)),
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                              "sample": "%dx%d sequence pairs of the c2 shape per step, C port of signature_algs.py:8-35 + kernels.py glue, OpenMP over pairs" % (side, side)},
@@ -268,6 +274,37 @@ def other_configs(torch, ops, lib):
     return out
 
 
+def c2_full(torch, kernels, lib, dt, nm, fpeak, steps=3):
+    """The full c2 Gram (N = N2 = 2000, normalised K(X, X2)) on one GPU: value + roofline of trunc_skew_kernel."""
+    N = 2000
+    L, d, m = CFG['L'], CFG['d'], CFG['m']
+    esz = 8 if nm == 'f64' else 4
+    X = torch.as_tensor(brownian(N, L, d, 0).reshape(N, L * d), dtype=dt, device='cuda')
+    X2 = torch.as_tensor(brownian(N, L, d, 1).reshape(N, L * d), dtype=dt, device='cuda')
+    kern = kernels.SignatureRBF(L * d, d, m)
+    kern.K(X, X2)
+    lib.gpsig_profile_enable(1)
+    ms, kms = [], []
+    for _ in range(steps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        kern.K(X, X2)
+        e1.record()
+        e1.synchronize()
+        ms.append(e0.elapsed_time(e1))
+        kms.append(lib.gpsig_profile_last_kernel_ms())
+    lib.gpsig_profile_enable(0)
+    t, kt = statistics.mean(ms), statistics.mean(kms)
+    F = flops_per_pair(L, L, d, m)
+    ach = N * N * F / (kt * 1e-3) / 1e12
+    return {"workload": "c2: SignatureRBF m=5 normalised K(X, X2), N=N2=2000, L=200, d=8 (one GPU)", "dtype": nm, "ms_per_step": t,
+            "pairs_per_s": N * N / (t * 1e-3),
+            "roofline": {"bound": "cuda-core-" + nm, "kernel": "trunc_skew_kernel", "kernel_ms": kt, "achieved": ach, "peak": fpeak,
+                         "unit": "TFLOP/s", "frac": ach / fpeak if fpeak else None, "flops_per_pair": F,
+                         "traffic": NCU_TRAFFIC_BYTES.get(nm),
+                         "algorithmic_bytes_per_launch": N * N * bytes_per_pair(N, N, L, L, d, esz)}}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -280,27 +317,32 @@ def run_ours(args):
     dev = torch.device('cuda', local)
     if world > 1:
         dist.init_process_group('nccl', device_id=dev)
-    from gpsig_b200 import kernels, ops, settings
+    from gpsig_b200 import kernels, ops, settings, sharding
     from gpsig_b200._lib import lib
     dtype = torch.float64 if args.dtype == 'f64' else torch.float32
     esz = 8 if args.dtype == 'f64' else 4
     settings.float_type = dtype
     N, N2, L, d, m = CFG['N'], CFG['N2'], CFG['L'], CFG['d'], CFG['m']
-    # rank r owns rows [r N, (r+1) N) of the (world N) x N2 Gram: its own X block, shared X2
-    X_host = torch.from_numpy(brownian(N, L, d, 1000 + rank).reshape(N, L * d)).to(dtype).pin_memory()
+    # the slab (rows) and the columns of the large Gram: the same on every rank (seeded), replicated as SURVEY 8(e) says
+    X_host = torch.from_numpy(brownian(N, L, d, 0).reshape(N, L * d)).to(dtype).pin_memory()
     X2_host = torch.from_numpy(brownian(N2, L, d, 1).reshape(N2, L * d)).to(dtype).pin_memory()
     out_host = torch.empty((N, N2), dtype=dtype).pin_memory()
     X, X2 = X_host.to(dev), X2_host.to(dev)
+    full = torch.empty((N, N2), dtype=dtype, device=dev)          # the gathered slab, on every rank
     kern = kernels.SignatureRBF(L * d, d, m)
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)   # > 126 MB L2
+    rb, re = sharding.row_range(N, world, rank)
 
     def step_resident():
-        return kern.K(X, X2)
+        return sharding.sharded_gram(kern, X, X2, gather=True, out=full)
+
+    def step_rows_only():                                         # the same without the collective (for `exposed`)
+        return kern.K(X, X2, rows=(rb, re), out=full[rb:re])
 
     def step_e2e():
         x = X_host.to(dev, non_blocking=True)
         x2 = X2_host.to(dev, non_blocking=True)
-        K = kern.K(x, x2)
+        K = sharding.sharded_gram(kern, x, x2, gather=True, out=full)
         out_host.copy_(K, non_blocking=True)
         return K
 
@@ -336,28 +378,53 @@ def run_ours(args):
     sampler = ClockSampler(local) if rank == 0 else None
     tot_ms, launches, kms = timed(step_resident, args.steps, args.warmup, profile_kernel=True)
     clocks = sampler.stop() if sampler else None
-    e2e_ms, _, _ = timed(step_e2e, args.steps, max(1, args.warmup // 2))
-    pairs_per_step = N * N2 * world
+    e2e_steps = args.steps if world > 1 else min(args.steps, 5)
+    e2e_ms, _, _ = timed(step_e2e, e2e_steps, max(1, args.warmup // 2))
+    rows_ms = None
+    if world > 1:
+        rsteps = min(args.steps, 5)
+        rows_ms, _, _ = timed(step_rows_only, rsteps, 1)
+        rows_ms /= rsteps
+    pairs_per_step = N * N2
     value = pairs_per_step * args.steps / (tot_ms * 1e-3)
-    e2e_value = pairs_per_step * args.steps / (e2e_ms * 1e-3)
+    e2e_value = pairs_per_step * e2e_steps / (e2e_ms * 1e-3)
+    # parity of the gathered slab with a single-rank compute: the last rank's first rows, recomputed by rank 0 alone
+    step_resident()
+    gather_check = None
+    if world > 1:
+        b_last, e_last = sharding.row_range(N, world, world - 1)
+        nchk = min(16, e_last - b_last)
+        if rank == 0:
+            alone = kern.K(X, X2, rows=(b_last, b_last + nchk))
+            gather_check = {"rows": [b_last, b_last + nchk], "bit_equal_to_single_rank": bool(torch.equal(alone, full[b_last:b_last + nchk]))}
+    torch.cuda.synchronize()
 
     if rank == 0:
         peaks, how = measured_peaks()
         fpeak = fma_peak_tflops(torch, lib, esz)
         kern_ms = statistics.mean(kms) if kms else None
         F = flops_per_pair(L, L, d, m)
-        achieved = N * N2 * F / (kern_ms * 1e-3) / 1e12 if kern_ms else None
-        Bp = bytes_per_pair(N, N2, L, L, d, esz)
+        pairs_launch = (re - rb) * N2
+        achieved = pairs_launch * F / (kern_ms * 1e-3) / 1e12 if kern_ms else None
+        Bp = bytes_per_pair(re - rb, N2, L, L, d, esz)
         nominal = 37.2 if esz == 8 else 74.4
+        step_ms = tot_ms / args.steps
         roof = {"bound": "cuda-core-" + args.dtype, "achieved": achieved, "peak": fpeak, "unit": "TFLOP/s",
                 "frac": (achieved / fpeak) if (achieved and fpeak) else None,
                 "traffic": NCU_TRAFFIC_BYTES.get(args.dtype), "traffic_source": NCU_TRAFFIC_SOURCE,
                 "peak_source": "FMA-chain microbenchmark in this run (gpsig_fma_peak); nominal %.1f TFLOP/s at 1965 MHz" % nominal,
                 "frac_of_nominal": achieved / nominal if achieved else None,
-                "kernel": "trunc_skew_kernel", "kernel_ms": kern_ms, "kernel_share_of_step": kern_ms * args.steps / tot_ms if kern_ms else None,
-                "flops_per_pair": F, "pairs_per_launch": N * N2,
-                "hbm": {"algorithmic_bytes_per_pair": Bp, "achieved_gbs": N * N2 * Bp / (kern_ms * 1e-3) / 1e9 if kern_ms else None,
+                "kernel": "trunc_skew_kernel", "kernel_ms": kern_ms, "kernel_share_of_step": kern_ms / step_ms if kern_ms else None,
+                "flops_per_pair": F, "pairs_per_launch": pairs_launch, "launch": "rank 0's rows [%d, %d) x %d columns" % (rb, re, N2),
+                "hbm": {"algorithmic_bytes_per_pair": Bp, "achieved_gbs": pairs_launch * Bp / (kern_ms * 1e-3) / 1e9 if kern_ms else None,
                         "peak_gbs": peaks.get("hbm_gbs"), "peak_source": how}}
+        coll = None
+        if world > 1:
+            gathered = (N - (re - rb)) * N2 * esz
+            coll = {"op": "ncclAllGather, in place (torch.distributed.all_gather_into_tensor of the rank's row slice into the full slab)",
+                    "calls_per_step": 1, "received_bytes_per_rank_per_step": gathered, "slab_bytes": N * N2 * esz,
+                    "rows_only_ms_per_step": rows_ms, "exposed_ms_per_step": step_ms - rows_ms,
+                    "exposed_frac_of_step": (step_ms - rows_ms) / step_ms, "gather_check": gather_check}
         # CPU baseline on a bounded sample (N=1 only: under torchrun the host threads are pinned to 1 per rank)
         cpu = None
         if world == 1:
@@ -368,26 +435,44 @@ def run_ours(args):
             cv, ct = cpu_pairs_per_sec(side)
             cpu = {"value": cv, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
                    "sample": "%dx%d pairs of the same shape in %.1f s (C port of the reference algorithm, OpenMP)" % (side, side, ct)}
-        others = other_configs(torch, ops, lib) if world == 1 else None
-        if others and fpeak and esz == 8:
-            c3 = others["c3_pde"]
-            c3["frac_of_fp64_bound"] = c3["cells_per_s"] * 3 / (fpeak * 1e12 / 2)   # 3 FP64 instructions per cell vs measured DFMA rate
+        others = None
+        if world == 1 and not args.no_others:
+            del X, X2, full
+            torch.cuda.empty_cache()
+            others = other_configs(torch, ops, lib)
+            fp64 = fpeak if esz == 8 else fma_peak_tflops(torch, lib, 8)
+            fp32 = fpeak if esz == 4 else fma_peak_tflops(torch, lib, 4)
+            others["c2_f64"] = c2_full(torch, kernels, lib, torch.float64, 'f64', fp64)
+            others["c2_f32"] = c2_full(torch, kernels, lib, torch.float32, 'f32', fp32)
+            post_other_configs(others, fp64)
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": tot_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "ms_per_step": step_ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": args.dtype, "data": "synthetic Brownian paths (seeded, SURVEY.md 8d)",
-                "config": dict(CFG, parallelism="rows x%d" % world, l2="flushed between timed iterations (256 MB write)",
-                               pairs_per_step=pairs_per_step),
+                "config": dict(CFG, parallelism="slab rows split over %d rank(s), %d rows each; X2 replicated" % (world, re - rb),
+                               l2="flushed between timed iterations (256 MB write)", pairs_per_step=pairs_per_step),
                 "clocks": clocks,
-                "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms / args.steps,
+                "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms / e2e_steps, "steps": e2e_steps,
                         "h2d_bytes_per_step": int(X_host.numel() + X2_host.numel()) * esz,
-                        "d2h_bytes_per_step": int(out_host.numel()) * esz},
+                        "d2h_bytes_per_step": int(out_host.numel()) * esz,
+                        "note": "per rank: pinned host X slab + X2 -> device, sharded_gram, gathered slab -> pinned host"},
                 "gpu_launches": int(launches),
                 "roofline": roof,
+                "collective": coll,
                 "other_configs": others,
                 "cpu_baseline": cpu}
         print(json.dumps(line))
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
+
+
+def post_other_configs(others, fp64):
+    """Fractions that need the FP64 FMA peak of this run."""
+    if others and fp64:
+        for key in ("c3_pde",):
+            if key in others:
+                c3 = others[key]
+                c3["frac_of_fp64_bound"] = c3["cells_per_s"] * 3 / (fp64 * 1e12 / 2)   # 3 FP64 instructions per cell vs measured DFMA rate
 
 
 def main():
@@ -397,6 +482,7 @@ def main():
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--dtype', choices=['f64', 'f32'], default='f64')
     ap.add_argument('--impl', choices=['ours', 'reference'], default='ours')
+    ap.add_argument('--no-others', action='store_true', help='skip other_configs (developer runs)')
     args = ap.parse_args()
     if args.impl == 'reference':
         run_reference(args)

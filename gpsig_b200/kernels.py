@@ -207,6 +207,16 @@ class SignatureKernel:
         """Raw per-level diagonals [m+1, N] of [N, L, d] sequences (kernels.py:190-207)."""
         return ops.trunc_diag(X, self.num_levels, **self._kw(X))
 
+    def _K_seq_diag_rows(self, X, rows):
+        """Diagonals for a row block only (the other rows' entries are never read by the Gram epilogue): a rank of
+        a row-sharded Gram does not repeat the whole X-side diagonal."""
+        if rows is None or (rows[0] == 0 and rows[1] == X.shape[0]):
+            return self._K_seq_diag(X)
+        full = torch.zeros((self.num_levels + 1, X.shape[0]), dtype=X.dtype, device=X.device)
+        if rows[1] > rows[0]:
+            full[:, rows[0]:rows[1]] = self._K_seq_diag(X[rows[0]:rows[1]])
+        return full
+
     # ---- differentiable path (training) ------------------------------------------
     # The reference trains lengthscales, variances, sigma and the inducing tensors through TensorFlow
     # autodiff of these methods (training.py; inducing_variables.py:51-137).  Here: when any input or
@@ -353,13 +363,16 @@ class SignatureKernel:
         return Kxx.sum(dim=0), Kxx2.sum(dim=0), Kx2x2.sum(dim=0)
 
     # ---- public API ------------------------------------------------------------
+    supports_out = True          # K(..., out=) writes a row block in place (gpsig_b200.sharding)
+
     def K(self, X, X2=None, presliced=False, return_levels=False, presliced_X=False, presliced_X2=False, rows=None,
-          upper_only=False):
+          upper_only=False, out=None):
         """Signature kernel between sequences (kernels.py:401-477).
 
         ``rows=(begin, end)`` (extension) restricts the computation to a row
         block of the Gram -- the unit of multi-GPU sharding.  ``upper_only`` (with ``X2=None``): the caller only
         needs the entries on and above the diagonal of its rows (``sharding.sharded_gram`` mirrors the rest).
+        ``out`` (extension): preallocated result, e.g. a row slice of the full matrix.
         """
         X = as_device_tensor(X, "X")
         X2 = None if X2 is None else as_device_tensor(X2, "X2")
@@ -373,8 +386,8 @@ class SignatureKernel:
             X2, _ = self._slice(X2, None)
         if self._wants_grad(X, X2):
             self._d_check()
-            if rows is not None:
-                raise NotImplementedError('gpsig_b200: rows= is not supported on the differentiable path')
+            if rows is not None or out is not None:
+                raise NotImplementedError('gpsig_b200: rows= / out= are not supported on the differentiable path')
             return self._d_gram(self._d_seq(X), None if X2 is None else self._d_seq(X2), return_levels)
         Xs = self._seq(X)
         jitter = settings.jitter
@@ -385,14 +398,14 @@ class SignatureKernel:
                 norm = self._K_seq_diag(Xs) + jitter
             return ops.trunc_gram(Xs, None, self.num_levels, norm_x=norm, norm_x2=norm,
                                   level_scale=self._level_scale(Xs), sym_jitter=jitter if self.normalization else 0.0,
-                                  return_levels=return_levels, rows=rows, upper_only=upper_only, **kw)
+                                  return_levels=return_levels, rows=rows, upper_only=upper_only, out=out, **kw)
         X2s = self._seq(X2)
         n1 = n2 = None
         if self.normalization:                                       # kernels.py:456-470
-            n1 = self._K_seq_diag(Xs) + jitter
+            n1 = self._K_seq_diag_rows(Xs, rows) + jitter
             n2 = self._K_seq_diag(X2s) + jitter
         return ops.trunc_gram(Xs, X2s, self.num_levels, norm_x=n1, norm_x2=n2, level_scale=self._level_scale(Xs),
-                              return_levels=return_levels, rows=rows, **kw)
+                              return_levels=return_levels, rows=rows, out=out, **kw)
 
     def K_norms(self, X, presliced=False):
         """kernels.py:480-506."""

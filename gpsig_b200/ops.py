@@ -23,12 +23,13 @@ def _same(t, ref, name):
 
 def trunc_gram(X, X2, num_levels, base='linear', base_params=(), order=1, difference=True, lengthscales=None,
                norm_x=None, norm_x2=None, level_scale=None, sym_jitter=0.0, return_levels=True, rows=None,
-               upper_only=False):
+               upper_only=False, out=None):
     """Rows ``rows=(begin, end)`` (default all) of the truncated signature Gram.
 
     Replaces ``SignatureKernel._K_seq`` + epilogue (gpsig/kernels.py:209-238, 431-477).
     Returns ``[m+1, R, N2]`` (``return_levels``) or ``[R, N2]``.  ``upper_only`` (K(X, X), row-sharded callers):
     entries below the diagonal may be left unwritten; complete the assembled matrix with ``mirror_lower``.
+    ``out``: write into this contiguous tensor of the result's shape (a row slice of a larger matrix: sharding).
     """
     require_cuda(X, 'X')
     for t, n in ((X2, 'X2'), (lengthscales, 'lengthscales'), (norm_x, 'norm_x'), (norm_x2, 'norm_x2'),
@@ -41,7 +42,12 @@ def trunc_gram(X, X2, num_levels, base='linear', base_params=(), order=1, differ
     rb, re = (0, N) if rows is None else rows
     m = int(num_levels)
     shape = (m + 1, re - rb, N2) if return_levels else (re - rb, N2)
-    out = torch.empty(shape, dtype=X.dtype, device=X.device)
+    if out is None:
+        out = torch.empty(shape, dtype=X.dtype, device=X.device)
+    else:
+        _same(out, X, 'out')
+        if tuple(out.shape) != shape or not out.is_contiguous():
+            raise ValueError("gpsig_b200: out must be a contiguous tensor of shape %s, got %s" % (shape, tuple(out.shape)))
     desc = make_desc(base, m, order, difference, base_params)
     epi = make_epilogue(norm_x, norm_x2, level_scale, sym_jitter, return_levels, upper_only and X2 is None)
     esz = X.element_size()

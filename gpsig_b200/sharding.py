@@ -65,39 +65,62 @@ def sym_row_ranges(n_rows, world_size, rank):
     return [blocks[rank], blocks[2 * world_size - 1 - rank]]
 
 
-def _gather_into(full, blk, ranges, group, handles):
-    """All-gather one row block per rank (``ranges[r]`` = rows of rank r, uneven allowed) into ``full`` (rows on
-    dim 0).  Asynchronous: appends (work, finish) to ``handles``; ``finish()`` places the pieces."""
+def _global_rank(group, r):
+    return r if group is None else dist.get_global_rank(group, r)
+
+
+def _gather_piece(full, ranges, rank, group, handles, inplace_ok):
+    """Make every rank's rows ``ranges[r]`` of ``full`` (rows on dim 0; this rank's rows already computed IN PLACE)
+    visible on all ranks.  No staging buffer and no copy: equal blocks in rank order are one in-place all-gather
+    (``ncclAllGather`` with the send buffer inside the receive buffer), anything else (uneven blocks, the mirrored
+    second block of the symmetric sweep, tiles) is one broadcast per owner straight into its row slice.
+    Asynchronous: appends the work handles to ``handles``."""
     world = len(ranges)
-    maxr = max(e - b for b, e in ranges)
-    if maxr == 0:
+    sizes = [e - b for b, e in ranges]
+    if max(sizes) == 0:
         return
-    pad = blk
-    if blk.shape[0] != maxr:
-        pad = blk.new_zeros((maxr,) + tuple(blk.shape[1:]))
-        pad[:blk.shape[0]] = blk
-    buf = blk.new_empty((world * maxr,) + tuple(blk.shape[1:]))
-    work = dist.all_gather_into_tensor(buf, pad.contiguous(), group=group, async_op=True)
-
-    def finish():
-        for r, (b, e) in enumerate(ranges):
-            full[b:e] = buf[r * maxr:r * maxr + (e - b)]
-    handles.append((work, finish))
+    contiguous = all(ranges[r][1] == ranges[r + 1][0] for r in range(world - 1))
+    if inplace_ok and contiguous and min(sizes) == max(sizes):
+        b0, e1 = ranges[0][0], ranges[-1][1]
+        b, e = ranges[rank]
+        handles.append(dist.all_gather_into_tensor(full[b0:e1], full[b:e], group=group, async_op=True))
+        return
+    for r, (b, e) in enumerate(ranges):
+        if e > b:
+            handles.append(dist.broadcast(full[b:e], src=_global_rank(group, r), group=group, async_op=True))
 
 
-def sharded_gram(kernel, X, X2=None, return_levels=False, gather=True, group=None, tiles=1, mirror=None):
+def _call_K(kernel, X, X2, rows, out, return_levels, **kw):
+    """kernel.K on a row block, written straight into ``out`` when the kernel supports it."""
+    if out is not None and getattr(kernel, 'supports_out', False):
+        kernel.K(X, X2, return_levels=return_levels, rows=rows, out=out, **kw)
+        return
+    blk = kernel.K(X, X2, return_levels=return_levels, rows=rows, **kw)
+    if out is not None:
+        out.copy_(blk.movedim(1, 0) if return_levels else blk)
+
+
+def sharded_gram(kernel, X, X2=None, return_levels=False, gather=True, group=None, tiles=1, mirror=None, out=None):
     """``kernel.K(X, X2)`` with the rows split over the ranks; ``gather=True`` returns the full matrix on every rank.
 
-    * ``tiles > 1``: the rank's rows are computed in ``tiles`` pieces and the all-gather of a finished piece
-      (NCCL, its own stream) runs while the next piece is computed -- the collective hides behind the kernel.
+    Who needs the full matrix: the Cholesky of Kuu / Kff (``inducing_variables.py:51-66`` of the reference).
+    * Every rank computes its rows directly into its slice of the full matrix and the slices are exchanged in
+      place (see ``_gather_piece``): one ``[N, N2]`` allocation per rank, no staging buffers, no copies.
+    * ``tiles > 1``: the rank's rows are computed in ``tiles`` pieces and the exchange of a finished piece (NCCL, its
+      own stream) runs while the next piece is computed.  Default 1: at the Gram shapes of BASELINE.json the
+      exchange is < 1 % of a step and splitting the kernel launch costs more than the overlap hides (measured on
+      8 B200: 247 vs 235 ms at N=4000, profiles/r01n_sharded_check_8gpu.txt).
     * ``X2 is None`` and ``gather``: only the entries on and above the diagonal are computed
       (``kernel.K(..., upper_only=True)`` on the mirrored row blocks of ``sym_row_ranges``), the assembled matrix
       is completed by ``mirror`` (default ``gpsig_b200.ops.mirror_lower``): half the pairs, every rank the same share.
+    * ``out``: optional preallocated result (``[N, N2]``; rows-first ``[N, m+1, N2]`` scratch is internal for levels).
     """
     n = X.shape[0]
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     rank = dist.get_rank(group) if dist.is_initialized() else 0
     if world == 1:
+        if out is not None and not return_levels and getattr(kernel, 'supports_out', False):
+            return kernel.K(X, X2, out=out)
         return kernel.K(X, X2, return_levels=return_levels)
     if not gather:
         b, e = row_range(n, world, rank)
@@ -108,23 +131,33 @@ def sharded_gram(kernel, X, X2=None, return_levels=False, gather=True, group=Non
     else:
         per_rank = [[row_range(n, world, r)] for r in range(world)]
     # split every block into `tiles` pieces (same piece count on every rank)
+    nt = max(1, int(tiles))
     pieces = []                                                                    # [piece][rank] -> (b, e)
     for k in range(len(per_rank[0])):
-        for t in range(max(1, int(tiles))):
-            pieces.append([tuple(bb + x for x in row_range(ee - bb, max(1, int(tiles)), t)) for bb, ee in (pr[k] for pr in per_rank)])
-    full = None
+        for t in range(nt):
+            pieces.append([tuple(bb + x for x in row_range(ee - bb, nt, t)) for bb, ee in (pr[k] for pr in per_rank)])
+    # in-place all-gather: NCCL only (gloo's all_gather_into_tensor stages the input; broadcasts are used there)
+    inplace_ok = dist.get_backend(group) == 'nccl'
     handles = []
+    kw = dict(upper_only=True) if sym else {}
+    n2 = n if sym else X2.shape[0]
+    full = None
+    if not return_levels:                       # result shape and dtype are known: allocate once, compute in place
+        full = out if out is not None else X.new_empty((n, n2))
+        if tuple(full.shape) != (n, n2) or not full.is_contiguous():
+            raise ValueError("out must be a contiguous [%d, %d] tensor" % (n, n2))
     for ranges in pieces:
         b, e = ranges[rank]
-        kw = dict(upper_only=True) if sym else {}
-        blk = kernel.K(X, X2, return_levels=return_levels, rows=(b, e), **kw)
-        blk = blk.movedim(1, 0) if return_levels else blk                          # rows first
-        if full is None:
-            full = blk.new_empty((n,) + tuple(blk.shape[1:]))
-        _gather_into(full, blk, ranges, group, handles)
-    for work, finish in handles:
+        if full is None:                        # levels: rows-first scratch [N, m+1, N2], shaped after the first block
+            blk0 = kernel.K(X, X2, return_levels=True, rows=(b, e), **kw).movedim(1, 0)
+            full = blk0.new_empty((n,) + tuple(blk0.shape[1:]))
+            full[b:e] = blk0
+            del blk0
+        elif e > b:
+            _call_K(kernel, X, X2, (b, e), full[b:e], return_levels, **kw)
+        _gather_piece(full, ranges, rank, group, handles, inplace_ok)
+    for work in handles:
         work.wait()
-        finish()
     full = full.movedim(0, 1).contiguous() if return_levels else full
     if sym:
         if mirror is None:

@@ -53,6 +53,20 @@ def test_c2_rbf_m5_2000x2000(dtype):
     assert torch.equal(parts, K)
     # normalised kernel: |K_l| <= 1 per level (Cauchy-Schwarz), so |K| <= m + 1
     assert float(K.abs().max()) <= (m + 1) * (1 + 1e-4)
+    # the NORMALISED output (what bench.py times), same seeded sub-block, against the oracle's K (kernels.py:456-477):
+    # the oracle's diagonals are those of the sub-block's own sequences, as in the full call
+    from oracle.trunc_np import SignatureKernelOracle
+    o = SignatureKernelOracle(L * d, d, m, base='rbf', block=8)
+    refn = o.K(Xn[ri].reshape(24, -1), Yn[ci].reshape(24, -1), return_levels=True)
+    Kl = k.K(X.reshape(N, -1), Y.reshape(N, -1), return_levels=True)
+    gotn = Kl[:, torch.as_tensor(ri, device='cuda')][:, :, torch.as_tensor(ci, device='cuda')].cpu().numpy()
+    assert rel_err(gotn, refn) < TOL[dtype]
+    assert rel_err(K[torch.as_tensor(ri, device='cuda')][:, torch.as_tensor(ci, device='cuda')].cpu().numpy(), refn.sum(0)) < TOL[dtype]
+    del Kl
+    # row block written in place into a slice of a larger matrix (the sharded path's out=)
+    full = torch.full((N, N), float('nan'), dtype=dtype, device='cuda')
+    k.K(X.reshape(N, -1), Y.reshape(N, -1), rows=(700, 2000), out=full[700:2000])
+    assert torch.equal(full[700:2000], K[700:2000]) and bool(torch.isnan(full[:700]).all())
 
 
 def test_c3_pde_n1000_l500_order2():
