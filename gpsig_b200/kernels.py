@@ -57,7 +57,7 @@ def as_device_tensor(A, what="input"):
     pointer (north star: "TF custom op with DLPack zero-copy"; the TF side is ``tf.experimental.dlpack``)."""
     if torch.is_tensor(A):
         return A
-    if hasattr(A, '__dlpack__') and hasattr(A, '__dlpack_device__'):
+    if not isinstance(A, np.ndarray) and hasattr(A, '__dlpack__') and hasattr(A, '__dlpack_device__'):
         return torch.from_dlpack(A)
     raise TypeError("gpsig_b200 kernels take torch CUDA tensors or DLPack-capable device arrays for %s "
                     "(use compute_* for numpy)" % what)
