@@ -63,6 +63,8 @@ def _load():
         f = getattr(lib, 'gpsig_tens_tens_' + sfx)
         f.restype = i
         f.argtypes = [ctypes.POINTER(TruncDesc), vp, i, i, i, vp, ctypes.POINTER(Epilogue), vp, vp]
+    lib.gpsig_trunc_diag_static_f64.restype = i          # no-allocation variant (csrc/static_scratch.cu)
+    lib.gpsig_trunc_diag_static_f64.argtypes = [ctypes.POINTER(TruncDesc), vp, i, i, i, vp, vp, vp]
     lib.gpsig_trunc_vjp_workspace_bytes.restype = sz
     lib.gpsig_trunc_vjp_workspace_bytes.argtypes = [i] * 6
     lib.gpsig_tens_vs_seq_vjp_workspace_bytes.restype = sz

@@ -123,6 +123,19 @@ int gpsig_trunc_diag_f32(const gpsig_trunc_desc* desc, const float* X, int N, in
                          const float* lengthscales, float* out,
                          void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- diagonal without any allocation (gpsig_b200/csrc/static_scratch.cu) ----
+ * No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (CUDA-graph capture, tight serving loops, harnesses that forbid it).
+ * Same result as gpsig_trunc_diag_f64 (raw levels out [m+1, N]); the packed-sequence scratch lives
+ * in a file-scope `static __device__` array of GPSIG_STATIC_SCRATCH_BYTES that every GPU loading the
+ * library holds until exit.  The caller passes inputs and output only; the call allocates nothing.
+ * Shapes with gpsig_trunc_diag_workspace_bytes(N, L, d, 8) > GPSIG_STATIC_SCRATCH_BYTES are refused
+ * (GPSIG_ERR_WORKSPACE).  All calls on a device share the array: calls that overlap on the GPU
+ * (different streams without an ordering event) race -- serialise them. */
+#define GPSIG_STATIC_SCRATCH_BYTES (16u << 20)   /* 16 MiB, e.g. N=2000, L=100, d=8 (14.4 MB) */
+int gpsig_trunc_diag_static_f64(const gpsig_trunc_desc* desc, const double* X, int N, int L, int d,
+                                const double* lengthscales, double* out, void* stream);
+
 /* ---- inducing tensors vs sequences (Kzx) -----------------------------------
  * Z: [T, Mz, d] or, with increments, [T, Mz, 2, d]; T = m(m+1)/2.
  * out: columns [col_begin, col_end) of [(m+1,)? Mz, N]  (sharded over N).
