@@ -223,6 +223,9 @@ def other_configs(torch, ops, lib):
                          "frac": (gbs / hbm_peak) if hbm_peak else None, "dtype": "f64"}
     del g
     torch.cuda.empty_cache()
+    ref_cuda = reference_cuda_pde(torch, ops, timed)
+    if ref_cuda:
+        out["c3_vs_reference_cuda"] = ref_cuda
     # c5 (symmetric sweep) on a 4000-row block: K(X, X) computes the CTAs touching i <= j and mirrors the rest;
     # delivered = N^2 ordered pairs in the output, computed = what the kernel evaluated
     Ns = 4000
@@ -272,6 +275,58 @@ def other_configs(torch, ops, lib):
                                      "kernels": "tens_tens(+vjp), trunc_gram diag (+vjp tables/grad), tens_vs_seq_kernel2 + tens_seq_vjp_warp_kernel",
                                      "ms": best}
     return out
+
+
+def reference_cuda_pde(torch, ops, timed):
+    """SURVEY.md's bar for the PDE kernel: the reference's own UntruncCovKernel (untrunc_cov_op_gpu.cu:5-36, launcher :71-81),
+    compiled unmodified for sm_100a by oracle/build_ref.py into oracle/_ref/, timed beside pde_block_kernel on a shape it can
+    run (P + 1 <= 1024 threads: L=250, dyadic order 2, P=996).  Only its KERNEL is timed (inputs resident: the [A,P,P] increment
+    tensor that kernels_pde.py:176-180 materialises with matmul + tf.repeat, and the [A,P+2,P+2] grid of ones) - the
+    materialisation itself is left out, which favours the reference."""
+    so = os.path.join(ROOT, 'oracle', '_ref', 'libuntrunc_cov_ref.so')
+    if not os.path.exists(so):
+        return None
+    ref = ctypes.CDLL(so)
+    ref.gpsig_ref_untrunc_cov.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
+    ref.gpsig_ref_untrunc_cov.restype = ctypes.c_int
+    A, L, d, order = 1000, 250, 4, 2
+    P = (L - 1) << order
+    X = torch.as_tensor(brownian(A, L, d, 0), dtype=torch.float64, device='cuda')
+    dX = X[:, 1:] - X[:, :-1]
+    E = torch.matmul(dX, dX.transpose(1, 2))                                   # [A, L-1, L-1]
+    E = (E.repeat_interleave(1 << order, 1) / (1 << order)).repeat_interleave(1 << order, 2) / (1 << order)
+    # the kernel also sweeps grid row/column P+1 and reads increments one row past the [P,P] block of the last sequence
+    # (its results there are discarded by kernels_pde.py:183): pad so that the read stays inside the allocation
+    incr = torch.zeros(A * P * P + 2 * P + 2, dtype=torch.float64, device='cuda')
+    incr[:A * P * P] = E.reshape(-1)
+    del E
+    sol = torch.ones((A, P + 2, P + 2), dtype=torch.float64, device='cuda')
+    best, got = 1e30, None
+    for rep in range(3):
+        sol.fill_(1.0)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        # the reference launches on the legacy default stream (untrunc_cov_op_gpu.cu:80); so are these events
+        with torch.cuda.stream(torch.cuda.default_stream()):
+            e0.record()
+            rc = ref.gpsig_ref_untrunc_cov(ctypes.c_void_p(incr.data_ptr()), A, P, ctypes.c_void_p(sol.data_ptr()))
+            e1.record()
+        e1.synchronize()
+        if rc != 0:
+            return {"error": "reference kernel launch failed with cudaError %d" % rc}
+        best = min(best, e0.elapsed_time(e1))
+        got = sol[:, P, P].clone()
+    del incr, sol
+    torch.cuda.empty_cache()
+    ms = timed(lambda: ops.pde(X, None, dyadic_order=order))
+    mine = ops.pde(X, None, dyadic_order=order)
+    # the reference kernel rounds every increment to float32 (untrunc_cov_op_gpu.cu:27): agreement is ~1e-7, not 1e-10
+    rel = float(((mine - got).abs() / got.abs()).max().item())
+    return {"workload": "kernels_pde Kdiag, N=1000, L=250, d=4, dyadic order 2 (P=996; the largest the reference kernel runs is P+1 <= 1024)",
+            "reference_kernel": "UntruncCovKernel, unmodified, nvcc -arch=sm_100a (oracle/_ref/libuntrunc_cov_ref.so)",
+            "reference_kernel_ms": best, "reference_pairs_per_s": A / (best * 1e-3),
+            "kernel": "pde_block_kernel", "kernel_ms": ms, "pairs_per_s": A / (ms * 1e-3), "speedup": best / ms,
+            "max_rel_diff": rel, "note": "reference increments pass through a float (cu:27); its input tensors (8 GB incr + 8 GB grid) are resident and their construction is not timed"}
 
 
 def c2_full(torch, kernels, lib, dt, nm, fpeak, steps=3):

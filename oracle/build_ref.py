@@ -1,4 +1,4 @@
-"""Build the reference's own Cython PDE solver into ``oracle/_ref/``.
+"""Build the reference's own Cython PDE solver, and its own CUDA PDE kernel, into ``oracle/_ref/``.
 
 TEST INFRASTRUCTURE ONLY (see ``oracle/__init__.py``).
 
@@ -10,6 +10,13 @@ and ``pyx:23-24`` is rejected), ``language_level=2``, and the system gcc for
 OpenMP (the default gcc wrapper cannot find ``libgomp.spec``).
 
     python oracle/build_ref.py          # no-op when the reference is absent
+
+``build_cuda()`` does the same for the reference's CUDA op kernel
+(``gpsig/covariance_op/untrunc_cov_op_gpu.cu``: plain CUDA, no TensorFlow headers):
+``nvcc -arch=sm_100a`` on the file where it lies plus the C-ABI doorway
+``oracle/csrc/untrunc_cov_ref_shim.cu`` -> ``oracle/_ref/libuntrunc_cov_ref.so``.  It is the bar
+SURVEY.md sets for the PDE kernel ("this kernel re-compiled on the same box"); ``bench.py``
+times it when the file is there (``other_configs.c3_vs_reference_cuda``).
 
 The GPU box has no ``/root/reference``; it uses the prebuilt module that
 travels with the repository snapshot.
@@ -50,6 +57,24 @@ def build(force=False):
     return so
 
 
+CU = '/root/reference/gpsig/covariance_op/untrunc_cov_op_gpu.cu'
+CU_SO = os.path.join(OUT, 'libuntrunc_cov_ref.so')
+
+
+def build_cuda(force=False):
+    """The reference's UntruncCovKernel compiled for sm_100a (None when the reference or nvcc is absent)."""
+    if os.path.exists(CU_SO) and not force:
+        return CU_SO
+    nvcc = os.environ.get('NVCC', '/usr/local/cuda/bin/nvcc')
+    if not os.path.exists(CU) or not os.path.exists(nvcc):
+        return None
+    os.makedirs(OUT, exist_ok=True)
+    subprocess.check_call([nvcc, '-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-shared',
+                           '-Xcompiler', '-fPIC', CU, os.path.join(HERE, 'csrc', 'untrunc_cov_ref_shim.cu'),
+                           '-o', CU_SO, '-lcudart_static', '-lpthread', '-ldl', '-lrt'])
+    return CU_SO
+
+
 def load():
     """Import the compiled reference module, or return None if it was never built."""
     so = built_module()
@@ -64,3 +89,4 @@ def load():
 
 if __name__ == '__main__':
     print(build(force='--force' in sys.argv))
+    print(build_cuda(force='--force' in sys.argv))
