@@ -9,6 +9,7 @@
 #include "trunc_kernel.cuh"
 #include "trunc_skew_kernel.cuh"
 #include "generic_kernels.cuh"
+#include "lift_mma_kernel.cuh"
 
 namespace gpsig {
 
@@ -65,6 +66,9 @@ __global__ void __launch_bounds__(256) fma_peak_kernel(T* out, int iters, T a, T
   GPSIG_DECL(T, 2, 4) GPSIG_DECL(T, 2, 8) GPSIG_DECL(T, 2, 16)
 GPSIG_DECL_T(float)
 GPSIG_DECL_T(double)
+
+extern template int launch_lift<float>(LiftParams, void*, size_t, const LiftMmaOperands*, cudaStream_t);
+extern template int launch_lift<double>(LiftParams, void*, size_t, const LiftMmaOperands*, cudaStream_t);
 
 // K(X, X) computed on and above the diagonal only: out[l, i, j] = out[l, j, i] for i > j (32 x 32 tiles through
 // shared memory, both sides coalesced).  Every i > j entry is overwritten, so the result is exactly symmetric.
@@ -172,7 +176,6 @@ static int trunc_gram_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
   const bool sym = X2 == nullptr;
   if (sym) { N2 = N; L2 = L; }
   if (N < 0 || N2 < 0 || d < 1) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "bad sizes N=%d N2=%d d=%d", N, N2, d);
-  if (d > 16) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "state dimension d=%d > 16 is not supported", d);
   const int minlen = desc->difference ? 2 : 1;
   if (L < minlen || L2 < minlen) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "sequences too short (L=%d, L2=%d)", L, L2);
   if (row_begin < 0 || row_end > N || row_begin > row_end)
@@ -187,8 +190,12 @@ static int trunc_gram_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   // order > 1: the general higher-order kernel; else the systolic kernel (padded rows) takes the
   // throughput shapes and trunc_gram_kernel the rest
-  const bool generic = desc->order > 1 || desc->base == GPSIG_BASE_SPECTRAL;
-  const bool skew = !generic && skew_eligible(L, L2, sizeof(T)) && getenv("GPSIG_NO_SKEW") == nullptr;
+  // d > 16: the lifted path (GEMM-shaped lift + recursion on the lifted tiles, lifted_kernels.cuh); sequences it does
+  // not take (L2 > 256) run the general kernel, whose contraction is a runtime loop over d
+  const bool big = d > 16;
+  const bool lifted = big && desc->order == 1 && desc->base != GPSIG_BASE_SPECTRAL && lift_eligible(L, L2);
+  const bool generic = desc->order > 1 || desc->base == GPSIG_BASE_SPECTRAL || (big && !lifted);
+  const bool skew = !big && !generic && skew_eligible(L, L2, sizeof(T)) && getenv("GPSIG_NO_SKEW") == nullptr;
   const int RS = skew ? skew_row_stride(d, sizeof(T)) : padded_dim(d);
   T* xp = static_cast<T*>(ws);
   T* yp = sym ? xp : reinterpret_cast<T*>(static_cast<char*>(ws) + packed_bytes_padded(N, L, d, sizeof(T)));
@@ -226,6 +233,17 @@ static int trunc_gram_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
     G.norm_x = P.norm_x; G.norm_x2 = P.norm_x2; G.level_scale = P.level_scale; G.sym_jitter = P.sym_jitter;
     G.return_levels = P.return_levels; G.out = out;
     if (int rc = launch_trunc_generic<T>(G, s)) return rc;
+  } else if (lifted) {
+    LiftParams Q;
+    memset(&Q, 0, sizeof(Q));
+    Q.xp = xp; Q.yp = yp; Q.xblk = P.xblk; Q.yblk = P.yblk; Q.DP = padded_dim(d);
+    Q.N = N; Q.N2 = N2; Q.L = L; Q.L2 = L2; Q.diag = 0; Q.row_begin = row_begin; Q.row_end = row_end;
+    Q.m = desc->num_levels; Q.difference = desc->difference; Q.symmetric = sym;
+    Q.p0 = P.p0; Q.p1 = P.p1; Q.base = P.base;
+    Q.norm_x = P.norm_x; Q.norm_x2 = P.norm_x2; Q.level_scale = P.level_scale; Q.sym_jitter = P.sym_jitter;
+    Q.return_levels = P.return_levels; Q.out = out;
+    const size_t off = packed_bytes_padded(N, L, d, sizeof(T)) + (sym ? 0 : packed_bytes_padded(N2, L2, d, sizeof(T)));
+    if (int rc = launch_lift<T>(Q, static_cast<char*>(ws) + off, ws_bytes - off, nullptr, s)) return rc;
   } else if (skew) {
     // the whole symmetric Gram in one call: compute only the CTAs that touch i <= j
     P.tri = upper_only || (whole_sym && N >= 64 && getenv("GPSIG_NO_TRI") == nullptr);
@@ -243,7 +261,7 @@ static int trunc_diag_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
                            void* ws, size_t ws_bytes, void* stream) {
   if (int rc = check_desc(desc)) return rc;
   if (!X || !out) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "X/out must not be NULL");
-  if (d < 1 || d > 16) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "state dimension d=%d is not supported (1..16)", d);
+  if (d < 1) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "bad state dimension d=%d", d);
   if (L < (desc->difference ? 2 : 1)) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "sequences too short (L=%d)", L);
   if (N == 0) return GPSIG_OK;
   const size_t need = gpsig_trunc_diag_workspace_bytes(N, L, d, sizeof(T));
@@ -263,7 +281,18 @@ static int trunc_diag_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
   P.symmetric = 1; P.diag = 1; P.return_levels = 1;
   P.p0 = desc->base_params[0]; P.p1 = desc->base_params[1]; P.base = desc->base;
   P.out = out;
-  if (desc->order > 1 || desc->base == GPSIG_BASE_SPECTRAL) {
+  const bool lifted = d > 16 && desc->order == 1 && desc->base != GPSIG_BASE_SPECTRAL && lift_eligible(L, L);
+  if (lifted) {
+    LiftParams Q;
+    memset(&Q, 0, sizeof(Q));
+    Q.xp = xp; Q.yp = xp; Q.xblk = Q.yblk = P.xblk; Q.DP = padded_dim(d);
+    Q.N = N; Q.N2 = N; Q.L = L; Q.L2 = L; Q.diag = 1; Q.row_begin = 0; Q.row_end = N;
+    Q.m = desc->num_levels; Q.difference = desc->difference; Q.symmetric = 1;
+    Q.p0 = P.p0; Q.p1 = P.p1; Q.base = P.base; Q.return_levels = 1; Q.out = out;
+    const size_t off = packed_bytes(N, L, d, sizeof(T));
+    return launch_lift<T>(Q, static_cast<char*>(ws) + off, ws_bytes - off, nullptr, s);
+  }
+  if (desc->order > 1 || desc->base == GPSIG_BASE_SPECTRAL || d > 16) {
     GenericParams G;
     memset(&G, 0, sizeof(G));
     G.xp = xp; G.yp = xp; G.xblk = G.yblk = P.xblk; G.N = N; G.N2 = N; G.L = L; G.L2 = L; G.DP = padded_dim(d);
@@ -281,7 +310,7 @@ static int tens_vs_seq_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, in
                             void* ws, size_t ws_bytes, void* stream) {
   if (int rc = check_desc(desc)) return rc;
   if (!Z || !X || !out) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "Z/X/out must not be NULL");
-  if (d < 1 || d > 16) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "state dimension d=%d is not supported (1..16)", d);
+  if (d < 1) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "bad state dimension d=%d", d);
   if (L < (desc->difference ? 2 : 1)) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "sequences too short (L=%d)", L);
   if (col_begin < 0 || col_end > N || col_begin > col_end)
     GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "bad column range [%d, %d) for N=%d", col_begin, col_end, N);
@@ -294,7 +323,8 @@ static int tens_vs_seq_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, in
   T* zp = static_cast<T*>(ws);
   T* xp = reinterpret_cast<T*>(static_cast<char*>(ws) + packed_bytes(TT * Mz, zs, d, sizeof(T)));
   // first-order RBF: coordinates pre-scaled by sqrt(log2 e), the exponent feeds exp2 (tens_kernels.cuh)
-  const double cscale = (desc->order == 1 && desc->base == GPSIG_BASE_RBF) ? 1.2011224087864498 : 1.0;
+  // d > 16 runs the general kernel (runtime loop over d), natural-base exponent
+  const double cscale = (d <= 16 && desc->order == 1 && desc->base == GPSIG_BASE_RBF) ? 1.2011224087864498 : 1.0;
   if (int rc = pack<T>(Z, TT * Mz, zs, d, ls, zp, s, 0, cscale)) return rc;
   if (int rc = pack<T>(X, N, L, d, ls, xp, s, 0, cscale)) return rc;
   TensSeqParams P;
@@ -308,7 +338,7 @@ static int tens_vs_seq_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, in
   else P.return_levels = 1;
   P.out = out;
   P.sp.p = desc->spectral; P.sp.q = desc->spectral_q; P.sp.family = desc->spectral_family; P.d = d;
-  if (desc->order > 1 || desc->base == GPSIG_BASE_SPECTRAL) return launch_tens_seq_generic<T>(P, desc->order, padded_dim(d), s);
+  if (desc->order > 1 || desc->base == GPSIG_BASE_SPECTRAL || d > 16) return launch_tens_seq_generic<T>(P, desc->order, padded_dim(d), s);
   return dispatch_tens_seq<T>(P, desc->base, padded_dim(d), m, s);
 }
 
@@ -323,11 +353,12 @@ static int tens_tens_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, int 
   P.Z = Z; P.ls = ls; P.Mz = Mz; P.zs = increments ? 2 : 1; P.m = desc->num_levels; P.d = d;
   P.p0 = desc->base_params[0]; P.p1 = desc->base_params[1]; P.base = desc->base;
   P.sp.p = desc->spectral; P.sp.q = desc->spectral_q; P.sp.family = desc->spectral_family;
-  if (d > 16) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "state dimension d=%d > 16 is not supported", d);
+  if (d > 16 && desc->base == GPSIG_BASE_SPECTRAL) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "spectral Kzz supports d <= 16 (got %d)", d);
   if (epi) { P.level_scale = epi->level_scale; P.return_levels = epi->return_levels; } else P.return_levels = 1;
   P.out = out;
   dim3 grid((Mz + 127) / 128, Mz);
-  if (P.d <= 8) tens_tens_kernel<T, 8><<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(P);
+  if (P.d > 16) tens_tens_big_kernel<T><<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(P);
+  else if (P.d <= 8) tens_tens_kernel<T, 8><<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(P);
   else tens_tens_kernel<T, 16><<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(P);
   GPSIG_LAUNCH_CHECK("tens_tens_kernel");
   return GPSIG_OK;
@@ -554,9 +585,16 @@ int gpsig_fma_peak(int elem_size, int blocks, int iters, void* scratch, void* st
 }
 
 size_t gpsig_trunc_gram_workspace_bytes(int N, int L, int N2, int L2, int d, int elem) {
-  return packed_bytes_padded(N, L, d, elem) + (N2 > 0 ? packed_bytes_padded(N2, L2, d, elem) : 0);
+  size_t b = packed_bytes_padded(N, L, d, elem) + (N2 > 0 ? packed_bytes_padded(N2, L2, d, elem) : 0);
+  if (d > 16 && lift_eligible(L, N2 > 0 ? L2 : L))       // the lifted tiles in flight (lifted_kernels.cuh)
+    b += lift_plan((size_t)N * (size_t)(N2 > 0 ? N2 : N), L, N2 > 0 ? L2 : L, elem).scratch_bytes;
+  return b;
 }
-size_t gpsig_trunc_diag_workspace_bytes(int N, int L, int d, int elem) { return packed_bytes(N, L, d, elem); }
+size_t gpsig_trunc_diag_workspace_bytes(int N, int L, int d, int elem) {
+  size_t b = packed_bytes(N, L, d, elem);
+  if (d > 16 && lift_eligible(L, L)) b += lift_plan((size_t)N, L, L, elem).scratch_bytes;
+  return b;
+}
 size_t gpsig_tens_vs_seq_workspace_bytes(int Mz, int increments, int N, int L, int d, int m, int elem) {
   return packed_bytes(m * (m + 1) / 2 * Mz, increments ? 2 : 1, d, elem) + packed_bytes(N, L, d, elem);
 }

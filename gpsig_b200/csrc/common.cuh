@@ -43,7 +43,8 @@ void prof_end(cudaStream_t s);
 //     T sqn[LP]         |x_p|^2 of the scaled point (kernels.py:948), LP = L
 //                       rounded up to 16 bytes
 // ---------------------------------------------------------------------------
-__host__ __device__ inline int padded_dim(int d) { return d <= 4 ? 4 : (d <= 8 ? 8 : 16); }
+// d > 16 (the large-state-dimension path, lifted_kernels.cuh, and the general kernels): a multiple of 16
+__host__ __device__ inline int padded_dim(int d) { return d <= 4 ? 4 : (d <= 8 ? 8 : (d + 15) / 16 * 16); }
 __host__ __device__ inline int padded_len(int L, int elem) { int q = 16 / elem; return (L + q - 1) / q * q; }
 __host__ __device__ inline size_t seq_block_elems(int L, int d, int elem) {
   return (size_t)L * padded_dim(d) + padded_len(L, elem);

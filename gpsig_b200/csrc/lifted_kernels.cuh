@@ -1,0 +1,345 @@
+// Truncated signature-kernel Gram for LARGE state dimension (d > 16) on sm_100a.
+//
+// Same contract as trunc_skew_kernel.cuh / trunc_kernel.cuh (gpsig/kernels.py:209-238 _K_seq, :190-207
+// _K_seq_diag, gpsig/signature_algs.py:8-35, epilogue kernels.py:431-477).  The reference has no limit on the
+// state dimension (kernels.py:343-365 reshapes to num_features * (num_lags + 1)); its own experiment driver runs
+// d_eff = 26 ... 1928 (benchmarks/datasets.json with num_lags = 1 and a time channel).
+//
+// At d <= 16 the K = d contraction is a quarter of the per-element work and lives in the lanes' FMA streams of
+// the systolic kernel.  At large d it is most of the work (2 d flops against ~20 for the recursion) and it is a
+// plain GEMM, so the path is split where the work changes character:
+//
+//   (A) LIFT: for a block of sequence pairs, the base-kernel tile M[p, q] = kappa(x_i[p], y_j[q])
+//       (kernels.py:225-231) is produced as a GEMM with the base-kernel epilogue fused
+//         * float32: tcgen05.mma kind::tf32 with a 3-term split (x = hi + lo; hi.hi + hi.lo + lo.hi), operands
+//           pre-packed in the canonical K-major core-matrix layout and brought in by 1-D TMA bulk copies,
+//           accumulator in tensor memory, epilogue warps read it back with tcgen05.ld (lift_mma_kernel);
+//         * float64 (no FP64 MMA kind exists): register-tiled DFMA GEMM (lift_tile_kernel; also float32 for
+//           shapes the MMA kernel does not take)
+//       and written to a scratch in the SKEWED order the recursion consumes it: element (p, q) of the n-th pair
+//       of a stream, owned by lane t = q / COLS, goes to row n*L + p + t of a [rows][32][COLS] array, so that
+//       the warp that runs the recursion reads ONE contiguous 32*COLS-element line per step.
+//   (B) RECURSION: one warp per stream of pairs, the lane-skewed systolic recursion of trunc_skew_kernel.cuh
+//       (lane t one row behind lane t-1, chain values by one shuffle, level totals carried to lane 31 at the
+//       first row of the next pair) with the base-kernel evaluation replaced by that one coalesced load.
+//
+// The lifted tile takes a round trip through HBM/L2 here (4-8 bytes per element against >= 2 d flops); the
+// reference round-trips the WHOLE lifted tensor 3 + 4 (m-1) times.
+#pragma once
+#include <stdlib.h>
+
+#include "trunc_kernel.cuh"
+
+namespace gpsig {
+
+struct LiftParams {
+  const void* xp; const void* yp;        // packed sequences, plain layout (common.cuh), row stride DP
+  size_t xblk, yblk;
+  int DP;
+  int N, N2, L, L2;
+  int diag;                              // pairs (i, i)
+  int row_begin, row_end;                // rows of the whole call (output indexing)
+  int ib, ie, jb, je;                    // this block: rows [ib, ie) x columns [jb, je)   (diag: pairs ib..ie)
+  int SP;                                // pairs per stream (consecutive rows i, same column j)
+  int nci;                               // streams per column: ceil((ie - ib) / SP)
+  int nstreams;
+  size_t stream_elems;                   // (SP * L + 32) * 32 * COLS
+  int m, difference, symmetric;
+  double p0, p1; int base;
+  const void* norm_x; const void* norm_x2; const void* level_scale;
+  double sym_jitter; int return_levels;
+  void* scratch;
+  void* out;
+};
+
+// pair n of stream sg -> (i, j); false if the stream has no such pair
+__device__ __forceinline__ bool lift_pair(const LiftParams& P, int sg, int n, int& i, int& j) {
+  if (P.diag) { i = P.ib + sg * P.SP + n; j = i; }
+  else { const int jj = sg / P.nci, ci = sg - jj * P.nci; i = P.ib + ci * P.SP + n; j = P.jb + jj; }
+  return i < P.ie;
+}
+__device__ __forceinline__ int lift_stream_pairs(const LiftParams& P, int sg) {
+  const int ci = P.diag ? sg : sg % P.nci;
+  return min(P.SP, P.ie - P.ib - ci * P.SP);
+}
+
+// ---------------------------------------------------------------------------
+// (A) register-tiled GEMM with the base-kernel epilogue: one CTA per (pair, 64-row block)
+// ---------------------------------------------------------------------------
+template <typename T, int COLS>
+__global__ void __launch_bounds__(256) lift_tile_kernel(const LiftParams P) {
+  constexpr int BM = 64, BN = 64, BK = 16, PAD = 4;
+  __shared__ __align__(16) T As[BK][BM + PAD];
+  __shared__ __align__(16) T Bs[BK][BN + PAD];
+  const int pi = blockIdx.x;                       // pair of the block
+  const int sg = pi / P.SP, n = pi - sg * P.SP;
+  int i, j;
+  if (sg >= P.nstreams || !lift_pair(P, sg, n, i, j)) return;
+  const int L = P.L, L2 = P.L2, DP = P.DP;
+  const int row0 = blockIdx.y * BM;
+  if (row0 >= L) return;
+  const T* x = static_cast<const T*>(P.xp) + (size_t)i * P.xblk;
+  const T* y = static_cast<const T*>(P.yp) + (size_t)j * P.yblk;
+  const T* xsq = x + (size_t)L * DP;
+  const T* ysq = y + (size_t)L2 * DP;
+  T* S = static_cast<T*>(P.scratch) + (size_t)sg * P.stream_elems;
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int lr = tid >> 2, lk = (tid & 3) * 4;     // loader: row of the tile, first k of 4
+  const T p0 = T(P.p0), p1 = T(P.p1);
+  constexpr int LP2 = 32 * COLS;
+  for (int col0 = 0; col0 < LP2; col0 += BN) {
+    T acc[4][4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+      for (int b = 0; b < 4; ++b) acc[a][b] = T(0);
+    const T* xr = x + (size_t)min(row0 + lr, L - 1) * DP;
+    const T* yr = y + (size_t)min(col0 + lr, L2 - 1) * DP;       // columns past L2 repeat the last point: zero increments
+    for (int k0 = 0; k0 < DP; k0 += BK) {
+      T xa[4], ya[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) { xa[e] = xr[k0 + lk + e]; ya[e] = yr[k0 + lk + e]; }
+      __syncthreads();
+#pragma unroll
+      for (int e = 0; e < 4; ++e) { As[lk + e][lr] = xa[e]; Bs[lk + e][lr] = ya[e]; }
+      __syncthreads();
+#pragma unroll
+      for (int k = 0; k < BK; ++k) {
+        T av[4], bv[4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a) av[a] = As[k][ty * 4 + a];
+#pragma unroll
+        for (int b = 0; b < 4; ++b) bv[b] = Bs[k][tx * 4 + b];
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+          for (int b = 0; b < 4; ++b) acc[a][b] = gfma<T>(av[a], bv[b], acc[a][b]);
+      }
+    }
+    // base kernel (kernels.py:946-1173) + store in the skewed order of the recursion
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+      const int p = row0 + ty * 4 + a;
+      if (p >= L) continue;
+      const T xs = xsq[p];
+      T v[4];
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        const int q = min(col0 + tx * 4 + b, L2 - 1);
+        v[b] = base_eval<T>(P.base, p0, p1, acc[a][b], xs, ysq[q]);
+      }
+      const int q = col0 + tx * 4;
+      if constexpr (COLS >= 4) {
+        const int t = q / COLS, c = q - t * COLS;
+        T* dst = S + ((size_t)(n * L + p + t) * 32 + t) * COLS + c;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) dst[b] = v[b];
+      } else {
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          const int t = (q + b) / COLS, c = (q + b) - t * COLS;
+          S[((size_t)(n * L + p + t) * 32 + t) * COLS + c] = v[b];
+        }
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// (B) the lane-skewed recursion on a stream of lifted tiles: one warp per stream
+// ---------------------------------------------------------------------------
+template <typename T, int COLS> struct LiftVec;
+template <> struct LiftVec<float, 2> { using type = float2; };
+template <> struct LiftVec<float, 4> { using type = float4; };
+template <> struct LiftVec<float, 8> { using type = float4; };
+template <> struct LiftVec<double, 2> { using type = double2; };
+template <> struct LiftVec<double, 4> { using type = double2; };
+template <> struct LiftVec<double, 8> { using type = double2; };
+
+template <typename T, int COLS>
+__device__ __forceinline__ void lift_load_row(T (&dst)[COLS], const T* src) {
+  using VT = typename LiftVec<T, COLS>::type;
+  constexpr int NV = COLS * sizeof(T) / sizeof(VT);
+  union { VT v[NV]; T e[COLS]; } u;
+#pragma unroll
+  for (int k = 0; k < NV; ++k) u.v[k] = __ldcs(reinterpret_cast<const VT*>(src) + k);    // streamed once: evict first
+#pragma unroll
+  for (int c = 0; c < COLS; ++c) dst[c] = u.e[c];
+}
+
+constexpr int kLiftWarps = 4;       // streams per CTA of the recursion kernel
+constexpr int kLiftAhead = 3;       // lines requested ahead of the one being consumed
+
+template <typename T, int COLS, int MLEV>
+__global__ void __launch_bounds__(kLiftWarps * 32) lift_recur_kernel(const LiftParams P) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int sg = blockIdx.x * kLiftWarps + warp;
+  if (sg >= P.nstreams) return;
+  const int npairs = lift_stream_pairs(P, sg);
+  if (npairs <= 0) return;
+  const int L = P.L, L2 = P.L2;
+  const bool diff = P.difference != 0;
+  const T* S = static_cast<const T*>(P.scratch) + (size_t)sg * P.stream_elems + (size_t)lane * COLS;
+  constexpr size_t LINE = 32 * COLS;
+  const int q0 = lane * COLS;
+
+  T C[MLEV - 1][COLS], Ct[COLS], Mp[COLS];
+#pragma unroll
+  for (int c = 0; c < COLS; ++c) {
+    Ct[c] = T(0); Mp[c] = T(0);
+#pragma unroll
+    for (int l = 0; l < MLEV - 1; ++l) C[l][c] = T(0);
+  }
+  T send[MLEV], sendU = T(0);
+#pragma unroll
+  for (int l = 0; l < MLEV; ++l) send[l] = T(0);
+
+  const int nsteps = npairs * L + 32;              // + the step that carries the last totals to lane 31
+  int r = -lane, seg = 0;                          // this lane's row within its pair, and its pair
+  T ring[kLiftAhead][COLS];
+#pragma unroll
+  for (int a = 0; a < kLiftAhead; ++a) lift_load_row<T, COLS>(ring[a], S + (size_t)min(a, nsteps - 1) * LINE);
+  const size_t rows_out = (size_t)(P.row_end - P.row_begin);
+
+  auto step = [&](auto SLOT, const int s) {
+    constexpr int slot = decltype(SLOT)::value;
+    T cur[COLS];
+#pragma unroll
+    for (int c = 0; c < COLS; ++c) cur[c] = ring[slot][c];
+    lift_load_row<T, COLS>(ring[slot], S + (size_t)min(s + kLiftAhead, nsteps - 1) * LINE);
+    // chain values of the lane to the left (the same row, one step ago)
+    T recv[MLEV];
+    T recvU = __shfl_up_sync(0xffffffffu, sendU, 1);
+#pragma unroll
+    for (int l = 0; l < MLEV; ++l) {
+      recv[l] = __shfl_up_sync(0xffffffffu, send[l], 1);
+      if (lane == 0) recv[l] = T(0);
+    }
+    const bool started = r >= 0;
+    T D[COLS];
+    if (diff) {
+      // 2-D increment (signature_algs.py:26): row 0 of a pair is consumed by the first-row branch,
+      // padded columns repeat the last one (increment exactly 0)
+      T U[COLS];
+#pragma unroll
+      for (int c = 0; c < COLS; ++c) { U[c] = cur[c] - Mp[c]; Mp[c] = cur[c]; }
+      const T left = lane == 0 ? U[0] : recvU;
+#pragma unroll
+      for (int c = 0; c < COLS; ++c) D[c] = U[c] - (c > 0 ? U[c - 1] : left);
+      sendU = U[COLS - 1];
+    } else {
+#pragma unroll
+      for (int c = 0; c < COLS; ++c) D[c] = (q0 + c < L2) ? cur[c] : T(0);
+    }
+    if (started && r == 0) {
+      // first row of a pair: the chain carries the level totals of the pair just finished
+      T tot[MLEV];
+#pragma unroll
+      for (int l = 0; l < MLEV; ++l) {
+        T e = recv[l];
+        if (l < MLEV - 1) {
+#pragma unroll
+          for (int c = 0; c < COLS; ++c) e += C[l < MLEV - 1 ? l : 0][c];
+        } else {
+#pragma unroll
+          for (int c = 0; c < COLS; ++c) e += Ct[c];
+        }
+        tot[l] = e;
+        send[l] = e;
+      }
+      if (lane == 31 && seg > 0) {
+        int i, j;
+        lift_pair(P, sg, seg - 1, i, j);
+        // ---- epilogue (kernels.py:431-477; raw levels for the diagonal, kernels.py:190-207) ----
+        T sum = T(0);
+#pragma unroll
+        for (int lvl = 0; lvl <= MLEV; ++lvl) {
+          if (lvl <= P.m) {
+            T v = lvl == 0 ? T(1) : tot[lvl > 0 ? lvl - 1 : 0];
+            if (P.diag) { static_cast<T*>(P.out)[(size_t)lvl * P.N + i] = v; continue; }
+            if (P.symmetric && i == j) v += T(P.sym_jitter);
+            if (P.norm_x) {
+              const T a = gsqrt<T>(static_cast<const T*>(P.norm_x)[(size_t)lvl * P.N + i]);
+              const T b = gsqrt<T>(static_cast<const T*>(P.norm_x2)[(size_t)lvl * P.N2 + j]);
+              v = v / (a * b);
+            }
+            if (P.level_scale) v *= static_cast<const T*>(P.level_scale)[lvl];
+            const size_t rc = (size_t)(i - P.row_begin) * P.N2 + j;
+            if (P.return_levels) static_cast<T*>(P.out)[(size_t)lvl * rows_out * P.N2 + rc] = v;
+            else sum += v;
+          }
+        }
+        if (!P.diag && !P.return_levels) static_cast<T*>(P.out)[(size_t)(i - P.row_begin) * P.N2 + j] = sum;
+      }
+#pragma unroll
+      for (int c = 0; c < COLS; ++c) {
+        Ct[c] = T(0);
+#pragma unroll
+        for (int l = 1; l < MLEV - 1; ++l) C[l][c] = T(0);
+        C[0][c] = diff ? T(0) : D[c];
+      }
+    } else {
+      // C_{l+1}[q] += D[p, q] * sum_{q' < q} C_l[q'], highest level first (signature_algs.py:32 re-associated)
+#pragma unroll
+      for (int l = MLEV - 2; l >= 0; --l) {
+        T e = recv[l];
+#pragma unroll
+        for (int c = 0; c < COLS; ++c) {
+          const T t = e;
+          e += C[l][c];
+          if (l == MLEV - 2) Ct[c] = gfma<T>(D[c], t, Ct[c]);
+          else C[l + 1 < MLEV - 1 ? l + 1 : 0][c] = gfma<T>(D[c], t, C[l + 1 < MLEV - 1 ? l + 1 : 0][c]);
+        }
+        send[l] = e;
+      }
+#pragma unroll
+      for (int c = 0; c < COLS; ++c) C[0][c] += D[c];
+    }
+    if (++r == L) { r = 0; ++seg; }
+  };
+
+  int s = 0;
+  for (; s + kLiftAhead <= nsteps; s += kLiftAhead) {
+    step(std::integral_constant<int, 0>{}, s);
+    step(std::integral_constant<int, 1>{}, s + 1);
+    step(std::integral_constant<int, 2>{}, s + 2);
+  }
+  if (s < nsteps) step(std::integral_constant<int, 0>{}, s++);
+  if (s < nsteps) step(std::integral_constant<int, 1>{}, s++);
+}
+
+// ---------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------
+inline int lift_cols(int L2) { return L2 <= 64 ? 2 : (L2 <= 128 ? 4 : 8); }
+inline bool lift_eligible(int L, int L2) { return L2 <= 256 && L >= 1; }
+constexpr size_t kLiftScratchCap = (size_t)1 << 30;      // bytes of lifted tiles in flight
+
+struct LiftPlan { int COLS, SP, max_streams; size_t stream_elems, scratch_bytes; };
+// npairs: pairs of the whole call (sizes the streams); deterministic in (npairs, L, L2, elem)
+inline LiftPlan lift_plan(size_t npairs, int L, int L2, int elem) {
+  LiftPlan pl;
+  pl.COLS = lift_cols(L2);
+  size_t sp = npairs / (148 * 24);                        // >= ~24 warps per SM before the streams get longer
+  pl.SP = sp < 1 ? 1 : (sp > 8 ? 8 : (int)sp);
+  pl.stream_elems = ((size_t)pl.SP * L + 32) * 32 * pl.COLS;
+  const size_t per = pl.stream_elems * elem;
+  size_t want = (npairs + pl.SP - 1) / pl.SP;
+  size_t capb = kLiftScratchCap;
+  if (const char* e = getenv("GPSIG_LIFT_CAP_MB")) { const long v = atol(e); if (v > 0) capb = (size_t)v << 20; }   // debug switch (tests: many blocks)
+  size_t cap = capb / per;
+  if (cap < 1) cap = 1;
+  if (want > cap) want = cap;
+  if (want < 1) want = 1;
+  pl.max_streams = (int)(want > 0x3fffffff ? 0x3fffffff : want);
+  pl.scratch_bytes = (size_t)pl.max_streams * per;
+  return pl;
+}
+
+struct LiftMmaOperands;
+// P: everything but the block fields; scratch >= lift_plan(...).scratch_bytes; mma: the pre-split tensor-core
+// operands of the float32 path or NULL (lifted.cu)
+template <typename T>
+int launch_lift(LiftParams P, void* scratch, size_t scratch_bytes, const LiftMmaOperands* mma, cudaStream_t s);
+
+}  // namespace gpsig

@@ -409,4 +409,44 @@ __global__ void __launch_bounds__(128) tens_tens_kernel(const TensTensParams P) 
   if (!P.return_levels) out[ab] = acc;
 }
 
+// d > 16: the same entry by entry with the contraction as a runtime loop over d (Kzz is tiny: Mz^2 * T * 4 values)
+template <typename T>
+__global__ void __launch_bounds__(128) tens_tens_big_kernel(const TensTensParams P) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  const int a = blockIdx.y;
+  if (b >= P.Mz) return;
+  const int d = P.d, zs = P.zs;
+  const T p0 = T(P.p0), p1 = T(P.p1);
+  const T* ls = static_cast<const T*>(P.level_scale);
+  const T* len = static_cast<const T*>(P.ls);
+  T* out = static_cast<T*>(P.out);
+  const size_t MM = (size_t)P.Mz * P.Mz, ab = (size_t)a * P.Mz + b;
+  auto ev = [&](const T* u, const T* v) {
+    T dot = T(0), uq = T(0), vq = T(0);
+    for (int q = 0; q < d; ++q) {
+      T uu = u[q], vv = v[q];
+      if (len) { uu = uu / len[q]; vv = vv / len[q]; }
+      dot = gfma<T>(uu, vv, dot); uq = gfma<T>(uu, uu, uq); vq = gfma<T>(vv, vv, vq);
+    }
+    return base_eval_call<T>(P.base, p0, p1, dot, uq, vq);
+  };
+  T acc = ls ? ls[0] : T(1);
+  if (P.return_levels) out[ab] = acc;
+  int k = 0;
+  for (int i = 1; i <= P.m; ++i) {
+    T R = T(1);
+    for (int jj = 0; jj < i; ++jj, ++k) {
+      const T* za = static_cast<const T*>(P.Z) + ((size_t)k * P.Mz + a) * zs * d;
+      const T* zb = static_cast<const T*>(P.Z) + ((size_t)k * P.Mz + b) * zs * d;
+      T Mt;
+      if (zs == 2) Mt = ev(za + d, zb + d) + ev(za, zb) - ev(za + d, zb) - ev(za, zb + d);             // kernels.py:278
+      else Mt = ev(za, zb);
+      R = jj == 0 ? Mt : Mt * R;                                                                     // signature_algs.py:91-96
+    }
+    if (ls) R *= ls[i];
+    if (P.return_levels) out[(size_t)i * MM + ab] = R; else acc += R;
+  }
+  if (!P.return_levels) out[ab] = acc;
+}
+
 }  // namespace gpsig

@@ -1,0 +1,101 @@
+"""GPU parity at state dimensions d > 16 (the reference's benchmark shapes: num_lags=1 with a time channel give
+d_eff = 26, 28, 46, 126, ...; benchmarks/datasets.json, run_gpsig_benchmarks.py:32, train_gpsig.py:28-29).
+
+K / Kdiag run the lifted path (lifted_kernels.cuh: GEMM-shaped lift + recursion on the lifted tiles; float32 lift on
+tcgen05 tensor cores), Kzx / Kzz the general kernels.  Oracle: oracle/trunc_np.py (numpy restatement of
+gpsig/signature_algs.py + kernels.py glue) and the C port.  Tolerances: 1e-10 float64, 1e-5 float32.
+"""
+import numpy as np
+import pytest
+import torch
+
+from tests.util import brownian, inducing_tensors, rel_err
+
+pytestmark = pytest.mark.gpu
+TOL = {torch.float64: 1e-10, torch.float32: 1e-5}
+
+
+def _dev(a, dtype):
+    return torch.as_tensor(np.ascontiguousarray(a), dtype=dtype, device='cuda')
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("d,L,L2,m", [(28, 40, 33, 4), (46, 70, 100, 5), (126, 50, 50, 4), (17, 130, 200, 3), (64, 9, 257, 2),
+                                      (20, 300, 30, 6)])
+def test_gram_raw_levels_large_d(dtype, d, L, L2, m):
+    from gpsig_b200 import ops
+    from oracle import c_oracle
+    N, N2 = 7, 5
+    X, Y = brownian(N, L, d, 2), brownian(N2, L2, d, 3)
+    for base in ('linear', 'rbf'):
+        G = ops.trunc_gram(_dev(X, dtype), _dev(Y, dtype), m, base=base).cpu().numpy()
+        R = c_oracle.trunc_gram(X, Y, m, base)
+        scale = np.abs(R).max(axis=(1, 2), keepdims=True)
+        err = np.max(np.abs(G - R) / scale)
+        assert err < TOL[dtype], (base, d, L, L2, m, err)
+    # rows = a range of a larger Gram (sharding), and the no-difference mode
+    G = ops.trunc_gram(_dev(X, dtype), _dev(Y, dtype), m, base='rbf', rows=(2, 6)).cpu().numpy()
+    R = c_oracle.trunc_gram(X, Y, m, 'rbf')[:, 2:6]
+    assert np.max(np.abs(G - R) / np.abs(R).max(axis=(1, 2), keepdims=True)) < TOL[dtype]
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("base,cls,bp", [('linear', 'SignatureLinear', {}), ('rbf', 'SignatureRBF', {}),
+                                         ('matern32', 'SignatureMatern32', {}), ('poly', 'SignaturePoly', dict(gamma=1.0, degree=3.0))])
+@pytest.mark.parametrize("d", [28, 126])
+def test_kernel_api_large_d(dtype, base, cls, bp, d):
+    """K (normalised, level-summed and per level), K(X, X), Kdiag through the reference-shaped classes."""
+    from gpsig_b200 import kernels
+    from oracle.trunc_np import SignatureKernelOracle
+    N, N2, L, L2, m = 9, 6, 31, 24, 4
+    X, Y = brownian(N, L, d, 0) * 0.5, brownian(N2, L2, d, 1) * 0.5
+    ls = np.linspace(0.8, 1.4, d)
+    var = np.linspace(0.5, 1.5, m + 1)
+    k = getattr(kernels, cls)(L * d, d, m, lengthscales=ls, **bp)
+    k.sigma = 1.3
+    k.variances = var
+    o = SignatureKernelOracle(L * d, d, m, base=base, lengthscales=ls, sigma=1.3, variances=var, **bp)
+    tol = TOL[dtype]
+    for ret in (True, False):
+        G = k.K(_dev(X.reshape(N, -1), dtype), _dev(Y.reshape(N2, -1), dtype), return_levels=ret).cpu().numpy()
+        R = o.K(X.reshape(N, -1), Y.reshape(N2, -1), return_levels=ret)
+        assert rel_err(G, R) < tol, (base, d, ret, rel_err(G, R))
+    Gs = k.K(_dev(X.reshape(N, -1), dtype)).cpu().numpy()
+    assert rel_err(Gs, o.K(X.reshape(N, -1))) < tol
+    assert np.array_equal(Gs, Gs.T)
+    Gd = k.Kdiag(_dev(X.reshape(N, -1), dtype), return_levels=True).cpu().numpy()
+    assert rel_err(Gd, o.Kdiag(X.reshape(N, -1), return_levels=True)) < tol
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("d", [28, 46])
+@pytest.mark.parametrize("increments", [False, True])
+def test_inducing_tensor_covariances_large_d(dtype, d, increments):
+    """Kzz, Kzx, Kxx_diag of K_tens_n_seq_covs (the SVGP shape, kernels.py:623-704) at d > 16."""
+    from gpsig_b200 import kernels
+    from oracle.trunc_np import SignatureKernelOracle
+    N, L, m, Mz = 12, 25, 4, 7
+    X = brownian(N, L, d, 0) * 0.5
+    Z = inducing_tensors(X, m, Mz, increments, 5)
+    k = kernels.SignatureRBF(L * d, d, m)
+    o = SignatureKernelOracle(L * d, d, m, base='rbf')
+    Kzz, Kzx, Kxx = k.K_tens_n_seq_covs(_dev(Z, dtype), _dev(X.reshape(N, -1), dtype), increments=increments)
+    Rzz, Rzx, Rxx = o.K_tens_n_seq_covs(Z, X.reshape(N, -1), increments=increments)
+    tol = TOL[dtype] * (10 if dtype == torch.float32 else 1)     # differences of nearby exp values (kernels.py:331) in float32
+    assert rel_err(Kzz.cpu().numpy(), Rzz) < tol
+    assert rel_err(Kzx.cpu().numpy(), Rzx) < tol
+    assert rel_err(Kxx.cpu().numpy(), Rxx) < TOL[dtype]
+
+
+@pytest.mark.parametrize("cap_mb", [None, 3])
+def test_large_d_many_pairs_blocks(cap_mb, monkeypatch):
+    """Streams of 8 pairs with a ragged last stream; with the scratch capped at 3 MB the Gram takes many blocks."""
+    from gpsig_b200 import ops
+    from oracle import c_oracle
+    if cap_mb:
+        monkeypatch.setenv('GPSIG_LIFT_CAP_MB', str(cap_mb))
+    N, N2, L, d, m = 150, 260, 20, 24, 3
+    X, Y = brownian(N, L, d, 7), brownian(N2, L, d, 8)
+    G = ops.trunc_gram(_dev(X, torch.float64), _dev(Y, torch.float64), m, base='rbf').cpu().numpy()
+    R = c_oracle.trunc_gram(X, Y, m, 'rbf')
+    assert np.max(np.abs(G - R) / np.abs(R).max(axis=(1, 2), keepdims=True)) < 1e-10
