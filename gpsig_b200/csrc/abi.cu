@@ -168,6 +168,28 @@ static size_t packed_bytes_padded(int N, int L, int d, int elem) {
   return align_up((size_t)N * seq_block_elems_rs(L, skew_row_stride(d, elem), elem) * elem, 128);
 }
 
+// float32 tensor-core lift (lift_mma_kernel.cuh): pre-split, pre-tiled operands behind the lifted-tile scratch
+static size_t lift_mma_bytes(int N, int L, int N2, int L2, int d) {
+  return align_up((size_t)N * lift_mma_a_elems(L, d) * 4, 128) + align_up((size_t)N2 * lift_mma_b_elems(L2, d) * 4, 128);
+}
+template <typename T>
+static int lift_mma_prepare(const T*, int, int, const T*, int, int, int, char*, LiftMmaOperands*, cudaStream_t) { return GPSIG_OK; }
+template <>
+int lift_mma_prepare<float>(const float* xp, int N, int L, const float* yp, int N2, int L2, int d, char* dst,
+                            LiftMmaOperands* op, cudaStream_t s) {
+  const int KP = lift_mma_kp(d), DP = padded_dim(d), R2 = 32 * lift_cols(L2), MT = (L + 127) / 128;
+  op->KP = KP; op->xop_blk = lift_mma_a_elems(L, d); op->yop_blk = lift_mma_b_elems(L2, d);
+  float* a = reinterpret_cast<float*>(dst);
+  float* b = reinterpret_cast<float*>(dst + align_up((size_t)N * op->xop_blk * 4, 128));
+  const size_t ta = (size_t)N * MT * 128 * (KP / 4), tb = (size_t)N2 * R2 * (KP / 4);
+  lift_pack_mma_kernel<<<(unsigned)((ta + 255) / 256), 256, 0, s>>>(xp, seq_block_elems(L, d, 4), DP, N, L, d, 128, MT, KP, 0, a, op->xop_blk);
+  GPSIG_LAUNCH_CHECK("lift_pack_mma_kernel");
+  lift_pack_mma_kernel<<<(unsigned)((tb + 255) / 256), 256, 0, s>>>(yp, seq_block_elems(L2, d, 4), DP, N2, L2, d, R2, 1, KP, 1, b, op->yop_blk);
+  GPSIG_LAUNCH_CHECK("lift_pack_mma_kernel");
+  op->xop = a; op->yop = b;
+  return GPSIG_OK;
+}
+
 template <typename T>
 static int trunc_gram_impl(const gpsig_trunc_desc* desc, const T* X, int N, int L, const T* X2, int N2, int L2, int d,
                            const T* ls, int row_begin, int row_end, const gpsig_epilogue* epi, T* out,
@@ -243,7 +265,12 @@ static int trunc_gram_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
     Q.norm_x = P.norm_x; Q.norm_x2 = P.norm_x2; Q.level_scale = P.level_scale; Q.sym_jitter = P.sym_jitter;
     Q.return_levels = P.return_levels; Q.out = out;
     const size_t off = packed_bytes_padded(N, L, d, sizeof(T)) + (sym ? 0 : packed_bytes_padded(N2, L2, d, sizeof(T)));
-    if (int rc = launch_lift<T>(Q, static_cast<char*>(ws) + off, ws_bytes - off, nullptr, s)) return rc;
+    const size_t sbytes = lift_plan((size_t)N * (size_t)N2, L, L2, sizeof(T)).scratch_bytes;
+    LiftMmaOperands mma;
+    memset(&mma, 0, sizeof(mma));
+    if (sizeof(T) == 4 && getenv("GPSIG_NO_MMA") == nullptr)
+      if (int rc = lift_mma_prepare<T>(xp, N, L, yp, N2, L2, d, static_cast<char*>(ws) + off + sbytes, &mma, s)) return rc;
+    if (int rc = launch_lift<T>(Q, static_cast<char*>(ws) + off, sbytes, mma.xop ? &mma : nullptr, s)) return rc;
   } else if (skew) {
     // the whole symmetric Gram in one call: compute only the CTAs that touch i <= j
     P.tri = upper_only || (whole_sym && N >= 64 && getenv("GPSIG_NO_TRI") == nullptr);
@@ -290,7 +317,12 @@ static int trunc_diag_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
     Q.m = desc->num_levels; Q.difference = desc->difference; Q.symmetric = 1;
     Q.p0 = P.p0; Q.p1 = P.p1; Q.base = P.base; Q.return_levels = 1; Q.out = out;
     const size_t off = packed_bytes(N, L, d, sizeof(T));
-    return launch_lift<T>(Q, static_cast<char*>(ws) + off, ws_bytes - off, nullptr, s);
+    const size_t sbytes = lift_plan((size_t)N, L, L, sizeof(T)).scratch_bytes;
+    LiftMmaOperands mma;
+    memset(&mma, 0, sizeof(mma));
+    if (sizeof(T) == 4 && getenv("GPSIG_NO_MMA") == nullptr)
+      if (int rc = lift_mma_prepare<T>(xp, N, L, xp, N, L, d, static_cast<char*>(ws) + off + sbytes, &mma, s)) return rc;
+    return launch_lift<T>(Q, static_cast<char*>(ws) + off, sbytes, mma.xop ? &mma : nullptr, s);
   }
   if (desc->order > 1 || desc->base == GPSIG_BASE_SPECTRAL || d > 16) {
     GenericParams G;
@@ -587,12 +619,13 @@ int gpsig_fma_peak(int elem_size, int blocks, int iters, void* scratch, void* st
 size_t gpsig_trunc_gram_workspace_bytes(int N, int L, int N2, int L2, int d, int elem) {
   size_t b = packed_bytes_padded(N, L, d, elem) + (N2 > 0 ? packed_bytes_padded(N2, L2, d, elem) : 0);
   if (d > 16 && lift_eligible(L, N2 > 0 ? L2 : L))       // the lifted tiles in flight (lifted_kernels.cuh)
-    b += lift_plan((size_t)N * (size_t)(N2 > 0 ? N2 : N), L, N2 > 0 ? L2 : L, elem).scratch_bytes;
+    b += lift_plan((size_t)N * (size_t)(N2 > 0 ? N2 : N), L, N2 > 0 ? L2 : L, elem).scratch_bytes +
+         (elem == 4 ? lift_mma_bytes(N, L, N2 > 0 ? N2 : N, N2 > 0 ? L2 : L, d) : 0);
   return b;
 }
 size_t gpsig_trunc_diag_workspace_bytes(int N, int L, int d, int elem) {
   size_t b = packed_bytes(N, L, d, elem);
-  if (d > 16 && lift_eligible(L, L)) b += lift_plan((size_t)N, L, L, elem).scratch_bytes;
+  if (d > 16 && lift_eligible(L, L)) b += lift_plan((size_t)N, L, L, elem).scratch_bytes + (elem == 4 ? lift_mma_bytes(N, L, N, L, d) : 0);
   return b;
 }
 size_t gpsig_tens_vs_seq_workspace_bytes(int Mz, int increments, int N, int L, int d, int m, int elem) {

@@ -49,7 +49,9 @@ def test_kernel_api_large_d(dtype, base, cls, bp, d):
     from oracle.trunc_np import SignatureKernelOracle
     N, N2, L, L2, m = 9, 6, 31, 24, 4
     X, Y = brownian(N, L, d, 0) * 0.5, brownian(N2, L2, d, 1) * 0.5
-    ls = np.linspace(0.8, 1.4, d)
+    # lengthscales ~ sqrt(d): what the reference's initialisation gives (utils.py:90-100 suggest_initial_lengthscales: sqrt(mean squared
+    # difference per feature x d)), and what keeps |x_p - y_q|^2 O(1) so that the base kernel is well conditioned in float32
+    ls = np.linspace(0.8, 1.4, d) * np.sqrt(d / 8.0)
     var = np.linspace(0.5, 1.5, m + 1)
     k = getattr(kernels, cls)(L * d, d, m, lengthscales=ls, **bp)
     k.sigma = 1.3
@@ -99,3 +101,19 @@ def test_large_d_many_pairs_blocks(cap_mb, monkeypatch):
     G = ops.trunc_gram(_dev(X, torch.float64), _dev(Y, torch.float64), m, base='rbf').cpu().numpy()
     R = c_oracle.trunc_gram(X, Y, m, 'rbf')
     assert np.max(np.abs(G - R) / np.abs(R).max(axis=(1, 2), keepdims=True)) < 1e-10
+
+
+@pytest.mark.parametrize("d,L,L2", [(28, 40, 33), (126, 100, 100), (46, 150, 200)])
+def test_tensor_core_lift_matches_cuda_core_lift(d, L, L2, monkeypatch):
+    """float32: the tcgen05 (3 x TF32) lift and the register-tiled FFMA lift agree within the float32 tolerance, incl. L > 128
+    (two accumulator row tiles per pair) and every columns-per-lane shape."""
+    from gpsig_b200 import ops
+    N, N2, m = 6, 5, 4
+    X, Y = _dev(brownian(N, L, d, 2), torch.float32), _dev(brownian(N2, L2, d, 3), torch.float32)
+    ls = _dev(np.full(d, np.sqrt(d / 8.0)), torch.float32)
+    for base in ('linear', 'rbf', 'matern52'):
+        A = ops.trunc_gram(X, Y, m, base=base, lengthscales=ls).cpu().numpy()
+        monkeypatch.setenv('GPSIG_NO_MMA', '1')
+        B = ops.trunc_gram(X, Y, m, base=base, lengthscales=ls).cpu().numpy()
+        monkeypatch.delenv('GPSIG_NO_MMA')
+        assert np.max(np.abs(A - B) / np.abs(B).max(axis=(1, 2), keepdims=True)) < 1e-5, base      # both are float32 evaluations: each is within 1e-5 of the oracle
