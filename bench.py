@@ -223,6 +223,7 @@ def other_configs(torch, ops, lib):
                          "frac": (gbs / hbm_peak) if hbm_peak else None, "dtype": "f64"}
     del g
     torch.cuda.empty_cache()
+    out.update(large_d(torch, ops, lib))
     ref_cuda = reference_cuda_pde(torch, ops, timed)
     if ref_cuda:
         out["c3_vs_reference_cuda"] = ref_cuda
@@ -274,6 +275,43 @@ def other_configs(torch, ops, lib):
         out["c4_svgp_step_" + nm] = {"workload": "K_tens_n_seq_covs forward + backward (grads of Z and X), minibatch 50, Mz=500, L=100, d=8, m=4",
                                      "kernels": "tens_tens(+vjp), trunc_gram diag (+vjp tables/grad), tens_vs_seq_kernel2 + tens_seq_vjp_warp_kernel",
                                      "ms": best}
+    return out
+
+
+def large_d(torch, ops, lib):
+    """State dimension d > 16 (the reference's benchmark shapes have d_eff = 26..1928: benchmarks/datasets.json with
+    num_lags=1 and a time channel, run_gpsig_benchmarks.py:32): the lifted path, float32 lift on tcgen05 tensor cores
+    (3 x TF32), float64 lift on DFMA.  N = N2 = 1000, L = 100, d = 126, m = 4, RBF with lengthscales sqrt(d/8)."""
+    out = {}
+    N, L, d, m = 1000, 100, 126, 4
+    X, Y = brownian(N, L, d, 0), brownian(N, L, d, 1)
+    F = flops_per_pair(L, L, d, m)
+    LP2, KP = 128, 128
+    for dt, nm in ((torch.float32, 'f32'), (torch.float64, 'f64')):
+        Xd, Yd = torch.as_tensor(X, dtype=dt, device='cuda'), torch.as_tensor(Y, dtype=dt, device='cuda')
+        ls = torch.full((d,), float(np.sqrt(d / 8.0)), dtype=dt, device='cuda')
+        fn = lambda: ops.trunc_gram(Xd, Yd, m, base='rbf', lengthscales=ls, return_levels=False)  # noqa: E731
+        fn()
+        best = 1e30
+        for _ in range(3):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            e1.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        rec = {"workload": "SignatureRBF m=4 K(X, X2) levels summed, N=N2=1000, L=100, d=126 (lengthscales sqrt(d/8))", "dtype": nm,
+               "kernels": ("lift_mma_kernel (tcgen05.mma kind::tf32, 3-term split) + lift_recur_kernel" if nm == 'f32'
+                           else "lift_tile_kernel (DFMA) + lift_recur_kernel"),
+               "ms": best, "pairs_per_s": N * N / (best * 1e-3), "flops_per_pair": F,
+               "algorithmic_tflops": N * N * F / (best * 1e-3) / 1e12}
+        if nm == 'f32':
+            rec["mma_tflops_issued"] = N * N * 3 * 2.0 * 128 * LP2 * KP / (best * 1e-3) / 1e12
+            rec["note"] = ("whole call (pack + operand split + lift + recursion); the same shape on the FFMA lift (GPSIG_NO_MMA=1) "
+                           "runs at ~5.2 M pairs/s; per-kernel split: profiles/r02f_launches_large_d.csv")
+        out["c_large_d_" + nm] = rec
+        del Xd, Yd
+    torch.cuda.empty_cache()
     return out
 
 

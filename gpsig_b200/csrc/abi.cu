@@ -224,7 +224,9 @@ static int trunc_gram_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
   // float32 RBF on the systolic kernel: coordinates pre-scaled by sqrt(log2 e) so that the exponent
   // x.y - |x|^2/2 - |y|^2/2 comes out in base-2 units and exp() is one MUFU.EX2 (trunc_skew_kernel.cuh)
   // (float64: same pre-scaling, the exponent feeds exp2_tab32)
-  const double cscale = (skew && (sizeof(T) == 4 || GPSIG_SKEW_EXP2) && desc->base == GPSIG_BASE_RBF) ? 1.2011224087864498 : 1.0;
+  // (the tensor-core lift of the large-d path reads its exponent the same way, lift_mma_kernel.cuh)
+  const bool lift_mma = lifted && sizeof(T) == 4 && getenv("GPSIG_NO_MMA") == nullptr;
+  const double cscale = (((skew && (sizeof(T) == 4 || GPSIG_SKEW_EXP2)) || lift_mma) && desc->base == GPSIG_BASE_RBF) ? 1.2011224087864498 : 1.0;
   if (int rc = pack<T>(X, N, L, d, ls, xp, s, RS, cscale)) return rc;
   if (!sym) if (int rc = pack<T>(X2, N2, L2, d, ls, yp, s, RS, cscale)) return rc;
 
@@ -268,7 +270,7 @@ static int trunc_gram_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
     const size_t sbytes = lift_plan((size_t)N * (size_t)N2, L, L2, sizeof(T)).scratch_bytes;
     LiftMmaOperands mma;
     memset(&mma, 0, sizeof(mma));
-    if (sizeof(T) == 4 && getenv("GPSIG_NO_MMA") == nullptr)
+    if (lift_mma)
       if (int rc = lift_mma_prepare<T>(xp, N, L, yp, N2, L2, d, static_cast<char*>(ws) + off + sbytes, &mma, s)) return rc;
     if (int rc = launch_lift<T>(Q, static_cast<char*>(ws) + off, sbytes, mma.xop ? &mma : nullptr, s)) return rc;
   } else if (skew) {
@@ -296,7 +298,10 @@ static int trunc_diag_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
     GPSIG_FAIL(GPSIG_ERR_WORKSPACE, "workspace too small or misaligned: need %zu bytes, got %zu", need, ws_bytes);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   T* xp = static_cast<T*>(ws);
-  if (int rc = pack<T>(X, N, L, d, ls, xp, s)) return rc;
+  const bool lifted = d > 16 && desc->order == 1 && desc->base != GPSIG_BASE_SPECTRAL && lift_eligible(L, L);
+  const bool lift_mma = lifted && sizeof(T) == 4 && getenv("GPSIG_NO_MMA") == nullptr;
+  // tensor-core lift + RBF: coordinates pre-scaled by sqrt(log2 e), the epilogue takes exp2 (lift_mma_kernel.cuh)
+  if (int rc = pack<T>(X, N, L, d, ls, xp, s, 0, (lift_mma && desc->base == GPSIG_BASE_RBF) ? 1.2011224087864498 : 1.0)) return rc;
   TruncParams P;
   memset(&P, 0, sizeof(P));
   P.xp = xp; P.yp = xp;
@@ -308,7 +313,6 @@ static int trunc_diag_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
   P.symmetric = 1; P.diag = 1; P.return_levels = 1;
   P.p0 = desc->base_params[0]; P.p1 = desc->base_params[1]; P.base = desc->base;
   P.out = out;
-  const bool lifted = d > 16 && desc->order == 1 && desc->base != GPSIG_BASE_SPECTRAL && lift_eligible(L, L);
   if (lifted) {
     LiftParams Q;
     memset(&Q, 0, sizeof(Q));
@@ -320,7 +324,7 @@ static int trunc_diag_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
     const size_t sbytes = lift_plan((size_t)N, L, L, sizeof(T)).scratch_bytes;
     LiftMmaOperands mma;
     memset(&mma, 0, sizeof(mma));
-    if (sizeof(T) == 4 && getenv("GPSIG_NO_MMA") == nullptr)
+    if (lift_mma)
       if (int rc = lift_mma_prepare<T>(xp, N, L, xp, N, L, d, static_cast<char*>(ws) + off + sbytes, &mma, s)) return rc;
     return launch_lift<T>(Q, static_cast<char*>(ws) + off, sbytes, mma.xop ? &mma : nullptr, s);
   }

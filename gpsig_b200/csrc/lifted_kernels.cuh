@@ -168,7 +168,10 @@ __device__ __forceinline__ void lift_load_row(T (&dst)[COLS], const T* src) {
 }
 
 constexpr int kLiftWarps = 4;       // streams per CTA of the recursion kernel
-constexpr int kLiftAhead = 3;       // lines requested ahead of the one being consumed
+#ifndef GPSIG_LIFT_BATCH
+#define GPSIG_LIFT_BATCH 4
+#endif
+constexpr int kLiftBatch = GPSIG_LIFT_BATCH;   // lines per request burst
 
 template <typename T, int COLS, int MLEV>
 __global__ void __launch_bounds__(kLiftWarps * 32) lift_recur_kernel(const LiftParams P) {
@@ -196,17 +199,17 @@ __global__ void __launch_bounds__(kLiftWarps * 32) lift_recur_kernel(const LiftP
 
   const int nsteps = npairs * L + 32;              // + the step that carries the last totals to lane 31
   int r = -lane, seg = 0;                          // this lane's row within its pair, and its pair
-  T ring[kLiftAhead][COLS];
+  // lines are requested kLiftBatch at a time (one contiguous kLiftBatch * 32 * COLS-element run per request burst:
+  // DRAM pages are opened for 2-4 KB instead of one 512-byte line), one batch ahead of the batch being consumed
+  T bufA[kLiftBatch][COLS], bufB[kLiftBatch][COLS];
+  auto load_batch = [&](T (&dst)[kLiftBatch][COLS], int s0) {
 #pragma unroll
-  for (int a = 0; a < kLiftAhead; ++a) lift_load_row<T, COLS>(ring[a], S + (size_t)min(a, nsteps - 1) * LINE);
+    for (int a = 0; a < kLiftBatch; ++a) lift_load_row<T, COLS>(dst[a], S + (size_t)min(s0 + a, nsteps - 1) * LINE);
+  };
+  load_batch(bufA, 0);
   const size_t rows_out = (size_t)(P.row_end - P.row_begin);
 
-  auto step = [&](auto SLOT, const int s) {
-    constexpr int slot = decltype(SLOT)::value;
-    T cur[COLS];
-#pragma unroll
-    for (int c = 0; c < COLS; ++c) cur[c] = ring[slot][c];
-    lift_load_row<T, COLS>(ring[slot], S + (size_t)min(s + kLiftAhead, nsteps - 1) * LINE);
+  auto step = [&](const T (&cur)[COLS]) {
     // chain values of the lane to the left (the same row, one step ago)
     T recv[MLEV];
     T recvU = __shfl_up_sync(0xffffffffu, sendU, 1);
@@ -298,14 +301,14 @@ __global__ void __launch_bounds__(kLiftWarps * 32) lift_recur_kernel(const LiftP
     if (++r == L) { r = 0; ++seg; }
   };
 
-  int s = 0;
-  for (; s + kLiftAhead <= nsteps; s += kLiftAhead) {
-    step(std::integral_constant<int, 0>{}, s);
-    step(std::integral_constant<int, 1>{}, s + 1);
-    step(std::integral_constant<int, 2>{}, s + 2);
+  for (int s = 0; s < nsteps; s += 2 * kLiftBatch) {
+    load_batch(bufB, s + kLiftBatch);
+#pragma unroll
+    for (int a = 0; a < kLiftBatch; ++a) if (s + a < nsteps) step(bufA[a]);
+    load_batch(bufA, s + 2 * kLiftBatch);
+#pragma unroll
+    for (int a = 0; a < kLiftBatch; ++a) if (s + kLiftBatch + a < nsteps) step(bufB[a]);
   }
-  if (s < nsteps) step(std::integral_constant<int, 0>{}, s++);
-  if (s < nsteps) step(std::integral_constant<int, 1>{}, s++);
 }
 
 // ---------------------------------------------------------------------------
@@ -313,20 +316,27 @@ __global__ void __launch_bounds__(kLiftWarps * 32) lift_recur_kernel(const LiftP
 // ---------------------------------------------------------------------------
 inline int lift_cols(int L2) { return L2 <= 64 ? 2 : (L2 <= 128 ? 4 : 8); }
 inline bool lift_eligible(int L, int L2) { return L2 <= 256 && L >= 1; }
-constexpr size_t kLiftScratchCap = (size_t)1 << 30;      // bytes of lifted tiles in flight
+constexpr size_t kLiftScratchCap = (size_t)2 << 30;      // bytes of lifted tiles in flight
+constexpr int kLiftWantStreams = 148 * 32;               // streams (= warps of the recursion kernel) wanted per block
 
 struct LiftPlan { int COLS, SP, max_streams; size_t stream_elems, scratch_bytes; };
 // npairs: pairs of the whole call (sizes the streams); deterministic in (npairs, L, L2, elem)
 inline LiftPlan lift_plan(size_t npairs, int L, int L2, int elem) {
   LiftPlan pl;
   pl.COLS = lift_cols(L2);
-  size_t sp = npairs / (148 * 24);                        // >= ~24 warps per SM before the streams get longer
+  size_t capb = kLiftScratchCap;
+  if (const char* e = getenv("GPSIG_LIFT_CAP_MB")) { const long v = atol(e); if (v > 0) capb = (size_t)v << 20; }   // debug switch (tests: many blocks)
+  // pairs per stream: long streams amortise the 31-step pipeline fill, short ones give the recursion kernel enough
+  // warps per block of scratch: as long as kLiftWantStreams streams fit the cap, and the call has that many
+  const size_t line = (size_t)32 * pl.COLS * elem;
+  long long rows_fit = (long long)(capb / ((size_t)kLiftWantStreams * line)) - 32;
+  long long sp = rows_fit / L;
+  const long long sp_call = (long long)(npairs / (148 * 24));
+  if (sp > sp_call) sp = sp_call;
   pl.SP = sp < 1 ? 1 : (sp > 8 ? 8 : (int)sp);
   pl.stream_elems = ((size_t)pl.SP * L + 32) * 32 * pl.COLS;
   const size_t per = pl.stream_elems * elem;
   size_t want = (npairs + pl.SP - 1) / pl.SP;
-  size_t capb = kLiftScratchCap;
-  if (const char* e = getenv("GPSIG_LIFT_CAP_MB")) { const long v = atol(e); if (v > 0) capb = (size_t)v << 20; }   // debug switch (tests: many blocks)
   size_t cap = capb / per;
   if (cap < 1) cap = 1;
   if (want > cap) want = cap;
