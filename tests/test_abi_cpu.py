@@ -89,3 +89,20 @@ def test_ops_refuse_cpu_tensors():
         ops.trunc_gram(torch.zeros(2, 3, 2, dtype=torch.float64), None, 2)
     with pytest.raises(RuntimeError, match="CUDA"):
         ops.pde(torch.zeros(2, 3, 2, dtype=torch.float64))
+
+
+def test_tf_shim_compiles_against_the_c_abi():
+    """shim/gpsig_tf_ops.cc (REGISTER_OP / OpKernel / REGISTER_KERNEL_BUILDER over the C ABI, the pattern of
+    gpsig/covariance_op/untrunc_cov_op_gpu.cc:13-40,61-102,148-149) type-checks against include/gpsig_b200.h.
+    TensorFlow is not installed here: its few types come from the declaration-only stubs under tests/tf_stub."""
+    import importlib.util
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location('build_shim', os.path.join(root, 'shim', 'build_shim.py'))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    r = mod.check()
+    assert r.returncode == 0, r.stderr
+    src = open(os.path.join(root, 'shim', 'gpsig_tf_ops.cc')).read()
+    for op in ('GpsigTruncGram', 'GpsigTruncGramGrad', 'GpsigTensVsSeq', 'GpsigPdeDiag', 'GpsigPdeDiagGrad'):
+        assert 'REGISTER_OP("%s")' % op in src and 'Name("%s")' % op in src
