@@ -439,23 +439,31 @@ static int pde_impl(const double* X, int N, int L, const double* Y, int N2, int 
   // kernel plus ticket overhead, so order 0 keeps pde_pipe_kernel (measured: 0.41 ms against 0.53 ms at N=1000, L=500)
   const bool rowstep = order == 0 || getenv("GPSIG_PDE_ROWSTEP") != nullptr;
   // persistent mode needs the dy coefficients in registers (they are per pair) and room for two dx buffers
+  // diagonal pairs k(x, x): the grid is symmetric and pde_block_kernel<.., SYM> lets the strips solve from their diagonal
+  // block down (36 of 64 blocks at c3).  OPT-IN (GPSIG_PDE_SYM=1), because it is SLOWER as measured (c3: 1.89 ms against
+  // 1.49 ms): with warp = strip the CTA's period per pair is set by strip 0, which still sweeps all rows, and the
+  // strips that finish early only leave their warps idle
+  bool sym = pipe && !rowstep && same && pair_mode == GPSIG_PDE_DIAG && nstrips >= 2 && getenv("GPSIG_PDE_SYM") != nullptr;
+  // persistent mode needs the dy coefficients in registers (they are per pair) and room for two dx buffers
   bool persist = pipe && !rowstep && pde_dy_in_regs(P.DP, order) && getenv("GPSIG_PDE_NOPERSIST") == nullptr &&
-                 pde_block_smem_bytes(L, L2, P.DP, order, nstrips, true) <= kMaxSmem;
+                 pde_block_smem_bytes(L, L2, P.DP, order, nstrips, true, sym) <= kMaxSmem;
+  if (sym && pde_block_smem_bytes(L, L2, P.DP, order, nstrips, persist, true) > kMaxSmem) sym = false;
   const size_t smem = !pipe ? pde_smem_bytes(L, L2, P.DP, order)
                             : rowstep ? pde_pipe_smem_bytes(L, L2, P.DP, order, nstrips)
-                                      : pde_block_smem_bytes(L, L2, P.DP, order, nstrips, persist);
+                                      : pde_block_smem_bytes(L, L2, P.DP, order, nstrips, persist, sym);
   if (smem > kMaxSmem)
     GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "PDE grid too large for the on-chip plan: %zu bytes of shared memory (L=%d, L2=%d, order=%d)", smem, L, L2, order);
   unsigned* ticket = reinterpret_cast<unsigned*>(static_cast<char*>(ws) + need - 128);
   if (persist) GPSIG_CUDA_CHECK(cudaMemsetAsync(ticket, 0, sizeof(unsigned), s));
   int sms = 148;
   { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
-#define GPSIG_PDE_GO(DP_, O_) do { if (pipe && !rowstep) { auto kern = pde_block_kernel<DP_, O_>; \
+#define GPSIG_PDE_BLOCK(DP_, O_, SYM_) do { auto kern = pde_block_kernel<DP_, O_, SYM_>; \
     GPSIG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
     unsigned grid = (unsigned)npairs; \
     if (persist) { int occ = 1; GPSIG_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 32 * nstrips, smem)); \
       const size_t slots = (size_t)(occ > 0 ? occ : 1) * sms; if (npairs > slots) grid = (unsigned)slots; else persist = false; } \
-    prof_begin(s); kern<<<grid, 32 * nstrips, smem, s>>>(P, persist ? 1 : 0, ticket); prof_end(s); } else if (pipe) { auto kern = pde_pipe_kernel<DP_, O_>; \
+    prof_begin(s); kern<<<grid, 32 * nstrips, smem, s>>>(P, persist ? 1 : 0, ticket); prof_end(s); } while (0)
+#define GPSIG_PDE_GO(DP_, O_) do { if (pipe && !rowstep) { if (sym) GPSIG_PDE_BLOCK(DP_, O_, true); else GPSIG_PDE_BLOCK(DP_, O_, false); } else if (pipe) { auto kern = pde_pipe_kernel<DP_, O_>; \
     GPSIG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
     prof_begin(s); kern<<<(unsigned)npairs, 32 * nstrips, smem, s>>>(P); prof_end(s); } else { auto kern = pde_wavefront_kernel<DP_, O_>; \
     GPSIG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \

@@ -375,12 +375,20 @@ __host__ __device__ constexpr int pde_block_maxreg(int DP, int ORDER) {
 #ifndef GPSIG_PDE_SLEEP
 #define GPSIG_PDE_SLEEP 256
 #endif
-inline size_t pde_block_smem_bytes(int L, int L2, int DP, int order, int nstrips, bool persist) {
+inline size_t pde_block_smem_bytes(int L, int L2, int DP, int order, int nstrips, bool persist, bool sym = false) {
   return ((size_t)(persist ? 2 : 1) * (L - 1) * (DP + 2) + pde_dy_smem_elems(L2, DP, order) + (size_t)nstrips * kPdeRing) * sizeof(double) +
-         (2 * kPdeMaxStrips + 8) * sizeof(int);
+         (2 * kPdeMaxStrips + 8) * sizeof(int) + (sym ? (size_t)nstrips * 264 * sizeof(double) : 0);
 }
 
-template <int DP, int ORDER>
+// SYM (diagonal pairs k(x, x), Y == NULL): the grid is symmetric, so strip w only solves the rows from its own diagonal
+// block down (cell rows i >= 256 w), as the reference does (sigKer_fast.pyx:33-61 fills the lower triangle and doubles
+// the sub-diagonal value).  The node row above its first cell row, K[256 w, 256 w + 1 ..], is by symmetry the node
+// COLUMN 256 w below the diagonal, i.e. the first 256 right-edge values of strip w-1: those go to a per-boundary
+// buffer (diagc) instead of the ring, strip w starts once they are all there, uses them as its initial `up` row AND as
+// its left boundary for the diagonal block, and takes the ring from there on.  36 of the 64 blocks of 256 x 256 cells
+// are solved at c3 (the diagonal blocks in full) instead of 64.
+constexpr int kPdeDiagPad = 264;    // doubles per boundary: node column values K[256 w + r, 256 w], r = 0..256
+template <int DP, int ORDER, bool SYM>
 __global__ void __maxnreg__(pde_block_maxreg(DP, ORDER)) pde_block_kernel(const PdeParams Pm, const int persist,
                                                                                       unsigned* __restrict__ ticket) {
   constexpr int W = kPdeW;
@@ -406,6 +414,7 @@ __global__ void __maxnreg__(pde_block_maxreg(DP, ORDER)) pde_block_kernel(const 
   int* pairq = cons + kPdeMaxStrips;                              // [4] ticket queue (pair index or -1)
   int* npub = pairq + 4;                                          // tickets published by warp 0
   int* fin = npub + 1;                                            // pairs finished by the last warp
+  double* diagc = reinterpret_cast<double*>(fin + 3);             // SYM: [NS][kPdeDiagPad]
 
   if (threadIdx.x < kPdeMaxStrips) { prod[threadIdx.x] = 0; cons[threadIdx.x] = 0; }
   if (threadIdx.x == 0) { *npub = 0; *fin = 0; }
@@ -423,7 +432,15 @@ __global__ void __maxnreg__(pde_block_maxreg(DP, ORDER)) pde_block_kernel(const 
   const uint32_t npub_s = opaque_u32(smem_u32(npub)), fin_s = opaque_u32(smem_u32(fin));
   const bool lane0 = lane == 0, lane_last = lane == 31;
   const double fscale = 1.0 / (double)(1 << (2 * ORDER));
-  const int nsteps = PB + LL;
+  // SYM: first block row of this strip (its diagonal block starts at cell row 256 w) and block rows of a diagonal block
+  constexpr int DBF = (32 * W) / RS;
+  const int b0 = SYM ? w * DBF : 0;
+  const int DBw = SYM ? min(DBF, PB - b0) : 0;               // block rows of MY diagonal block
+  const int bn0 = SYM ? (w + 1) * DBF : 0;                   // first block row of the NEXT strip
+  const int DBn = SYM ? min(DBF, max(PB - bn0, 0)) : 0;
+  const uint32_t diag_in_s = opaque_u32(smem_u32(diagc + (size_t)w * kPdeDiagPad));
+  const uint32_t diag_out_s = opaque_u32(smem_u32(diagc + (size_t)(w + 1 < NS ? w + 1 : w) * kPdeDiagPad));
+  const int nsteps = PB - b0 + LL;
 
   for (int n = 0;; ++n) {                                    // n-th pair of this CTA
     const int base = n * PB;                                // cumulative block rows before this pair
@@ -490,17 +507,46 @@ __global__ void __maxnreg__(pde_block_maxreg(DP, ORDER)) pde_block_kernel(const 
 #pragma unroll
     for (int r = 0; r < RS; ++r) send[r] = 1.0;
     double dgl = 1.0;                                       // K[i, j0]
-    int b = -lane;                                          // block row of this lane at step s
+    if (SYM && has_left) {
+      // the node row above my first cell row = the node column to my left (symmetry): wait for all of it
+      const int need0 = base + b0 + DBw;
+      while (ld_volatile_shared_u(prod_in_s) - need0 < 0) __nanosleep(GPSIG_PDE_SLEEP);
+      __threadfence_block();
+      asm volatile("ld.shared.f64 %0, [%1];" : "=d"(dgl) : "r"(diag_in_s + (uint32_t)(W * lane) * 8u) : "memory");
+#pragma unroll
+      for (int c = 0; c < W; ++c)
+        asm volatile("ld.shared.f64 %0, [%1];" : "=d"(up[c]) : "r"(diag_in_s + (uint32_t)(W * lane + 1 + c) * 8u) : "memory");
+    }
+    int b = b0 - lane;                                      // block row of this lane at step s
     for (int s = 0; s < nsteps; ++s, ++b) {
       if ((s & (G - 1)) == 0) {
         // ---- hand-off window: block rows [s, s+G) of this pair ----------------------------
         if (has_left) {
-          const int need = base + min(s + G, PB);
+          const int need = base + min(b0 + s + G, PB);
           while (ld_volatile_shared_u(prod_in_s) - need < 0) __nanosleep(GPSIG_PDE_SLEEP);
         }
         if (has_right) {
-          const int top = base + min(s + G - LL, PB);
-          while (top - ld_volatile_shared_u(cons_out_s) > RBb) __nanosleep(GPSIG_PDE_SLEEP);
+          if (!SYM) {
+            const int top = base + min(s + G - LL, PB);
+            while (top - ld_volatile_shared_u(cons_out_s) > RBb) __nanosleep(GPSIG_PDE_SLEEP);
+          } else {
+            const int topb = min(b0 + s + G - LL, PB);         // block rows (of this pair) lane LL will have written after this window
+            // (a) its rows that land in the next strip's diagonal buffer: that strip must have finished reading the
+            //     buffer of the PREVIOUS pair (it has, once it is past its diagonal block there)
+            if (n > 0 && topb >= bn0) {
+              const int freed = base - PB + bn0 + DBn;
+              while (ld_volatile_shared_u(cons_out_s) - freed < 0) __nanosleep(GPSIG_PDE_SLEEP);
+            }
+            // (b) its rows that land in the ring (past the next strip's diagonal block): the reader has left the
+            //     previous pair and is at most a ring behind, counting from where it starts to read the ring
+            if (topb > bn0 + DBn) {
+              for (;;) {
+                const int c = ld_volatile_shared_u(cons_out_s) - base;
+                if (c >= 0 && topb - max(c, bn0 + DBn) <= RBb) break;
+                __nanosleep(GPSIG_PDE_SLEEP);
+              }
+            }
+          }
         }
         __threadfence_block();
       }
@@ -536,12 +582,17 @@ __global__ void __maxnreg__(pde_block_maxreg(DP, ORDER)) pde_block_kernel(const 
       double recv[RS];
 #pragma unroll
       for (int r = 0; r < RS; ++r) recv[r] = __shfl_up_sync(0xffffffffu, send[r], 1);
-      const bool rowok = (b >= 0) && (b < PB) && (ncell > 0);
+      const bool rowok = (b >= b0) && (b < PB) && (ncell > 0);
       const uint32_t slot = (uint32_t)(((base + b) * RS) & (RB - 1)) * 8u;
       if (lane0) {
 #pragma unroll
         for (int r = 0; r < RS; ++r) recv[r] = 1.0;         // K[., 0] = 1 (pyx:29-31)
-        if (has_left && rowok) {
+        if (SYM && has_left && rowok && b < b0 + DBw) {
+          // inside my diagonal block the left boundary comes from the diagonal buffer (node rows RS b + 1 ..)
+#pragma unroll
+          for (int r = 0; r < RS; ++r)
+            asm volatile("ld.shared.f64 %0, [%1];" : "=d"(recv[r]) : "r"(diag_in_s + (uint32_t)((b - b0) * RS + 1 + r) * 8u) : "memory");
+        } else if (has_left && rowok) {
           if (RS == 4) {
             asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(recv[0]), "=d"(recv[RS > 1 ? 1 : 0]) : "r"(ring_in_s + slot) : "memory");
             asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(recv[RS > 2 ? 2 : 0]), "=d"(recv[RS > 3 ? 3 : 0]) : "r"(ring_in_s + slot + 16u) : "memory");
@@ -593,7 +644,15 @@ __global__ void __maxnreg__(pde_block_maxreg(DP, ORDER)) pde_block_kernel(const 
         for (int c = 0; c < W; ++c) up[c] = Kv[RS][c + 1];
 #pragma unroll
         for (int r = 0; r < RS; ++r) send[r] = Kv[r + 1][W];
-        if (lane_last && has_right) {
+        if (SYM && lane_last && has_right && b < bn0 + DBn) {
+          // node rows RS b + 1 .. RS b + RS of my right edge = entries RS (b - bn0) + 1 + r of the next strip's diagonal
+          // buffer (entry 0, the corner K[256 (w+1), 256 (w+1)], is the last value of block row bn0 - 1)
+#pragma unroll
+          for (int r = 0; r < RS; ++r) {
+            const int e = (b - bn0) * RS + 1 + r;
+            if (e >= 0) asm volatile("st.shared.f64 [%0], %1;" ::"r"(diag_out_s + (uint32_t)e * 8u), "d"(send[r]) : "memory");
+          }
+        } else if (lane_last && has_right) {
           if (RS == 4) {
             asm volatile("st.shared.v2.f64 [%0], {%1,%2};" ::"r"(ring_out_s + slot), "d"(send[0]), "d"(send[RS > 1 ? 1 : 0]) : "memory");
             asm volatile("st.shared.v2.f64 [%0], {%1,%2};" ::"r"(ring_out_s + slot + 16u), "d"(send[RS > 2 ? 2 : 0]), "d"(send[RS > 3 ? 3 : 0]) : "memory");
@@ -609,9 +668,9 @@ __global__ void __maxnreg__(pde_block_maxreg(DP, ORDER)) pde_block_kernel(const 
         __syncwarp();
         if (has_right && lane == LL) {
           __threadfence_block();
-          st_volatile_shared(&prod[w + 1], base + max(0, min(s - LL + 1, PB)));
+          st_volatile_shared(&prod[w + 1], base + max(0, min(b0 + s - LL + 1, PB)));
         }
-        if (has_left && lane0) st_volatile_shared(&cons[w], base + min(s + 1, PB));
+        if (has_left && lane0) st_volatile_shared(&cons[w], base + min(b0 + s + 1, PB));
       }
     }
     if (w == NS - 1) {

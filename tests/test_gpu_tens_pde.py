@@ -86,6 +86,19 @@ def test_pde_diag_vs_oracle(L, d, order):
     assert np.max(np.abs(G - R) / np.abs(R)) < 1e-10, (np.max(np.abs(G - R) / np.abs(R)))
 
 
+@pytest.mark.parametrize("N,L,d,order", [(40, 200, 4, 2), (500, 300, 3, 1), (7, 130, 8, 3), (1200, 140, 2, 2)])
+def test_pde_diag_lower_triangle_schedule(N, L, d, order, monkeypatch):
+    """GPSIG_PDE_SYM=1: the strips of a diagonal pair solve only from their diagonal block down, as sigKer_fast.pyx:33-61
+    fills only the lower triangle (opt-in: measured slower).  Same values as the full-grid schedule, with
+    few pairs (one CTA per pair) and with more pairs than resident CTAs (persistent CTAs, buffers reused across pairs)."""
+    from gpsig_b200 import ops
+    X = _dev(brownian(N, L, d, 11))
+    full = ops.pde(X, None, dyadic_order=order)
+    monkeypatch.setenv('GPSIG_PDE_SYM', '1')
+    tri = ops.pde(X, None, dyadic_order=order)
+    assert float(((tri - full).abs() / full.abs()).max()) < 1e-11
+
+
 def test_pde_golden_from_reference_cython():
     """Golden vectors produced by the reference's own compiled sigKer_fast (tests/golden/make_golden.py)."""
     import os
