@@ -498,7 +498,7 @@ static int trunc_vjp_impl(const gpsig_trunc_desc* desc, const T* X, int N, int L
   const bool sym = X2 == nullptr;
   if (sym) { X2 = X; N2 = N; L2 = L; gradX2 = gradX; }
   if (!X || !grad_levels || !gradX || !gradX2) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "X/grad_levels/gradX must not be NULL");
-  if (d < 1 || d > 16) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "state dimension d=%d is not supported (1..16)", d);
+  if (d < 1) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "bad state dimension d=%d", d);
   const int minlen = desc->difference ? 2 : 1;
   if (L < minlen || L2 < minlen) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "sequences too short (L=%d, L2=%d)", L, L2);
   if (row_begin < 0 || row_end > N || row_begin > row_end) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "bad row range [%d, %d) for N=%d", row_begin, row_end, N);
@@ -550,7 +550,7 @@ static int tens_seq_vjp_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, i
   if (desc->order != 1) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "reverse mode is implemented for order == 1 only (got %d)", desc->order);
   if (desc->num_levels > 8) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "reverse mode supports num_levels <= 8");
   if (!Z || !X || !grad_levels || !gradZ || !gradX) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "Z/X/grad_levels/gradZ/gradX must not be NULL");
-  if (d < 1 || d > 16) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "state dimension d=%d is not supported (1..16)", d);
+  if (d < 1) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "bad state dimension d=%d", d);
   if (L < (desc->difference ? 2 : 1)) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "sequences too short (L=%d)", L);
   if (col_begin < 0 || col_end > N || col_begin > col_end) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "bad column range [%d, %d) for N=%d", col_begin, col_end, N);
   const size_t npairs = (size_t)Mz * (col_end - col_begin);
@@ -566,14 +566,24 @@ static int tens_seq_vjp_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, i
   P.col_begin = col_begin; P.col_end = col_end; P.difference = desc->difference;
   P.p0 = desc->base_params[0]; P.p1 = desc->base_params[1]; P.base = desc->base;
   P.g = grad_levels; P.gradZ = gradZ; P.gradX = gradX; P.S = ws; P.npairs = npairs;
-  const int gz = TT * zs * d, threads = 64;
+  const int threads = 64;
   const unsigned blocks = (unsigned)((npairs + threads - 1) / threads);
   prof_begin(s);
   const bool warp_per_seq = getenv("GPSIG_VJP_THREAD") == nullptr && launch_tens_seq_vjp_warp<T>(P, s);
   if (warp_per_seq) {}
-  else if (gz <= 160) tens_seq_vjp_kernel<T, 160><<<blocks, threads, 0, s>>>(P);
-  else if (gz <= 480) tens_seq_vjp_kernel<T, 480><<<blocks, threads, 0, s>>>(P);
-  else tens_seq_vjp_kernel<T, 1152><<<blocks, threads, 0, s>>>(P);
+  else {
+    // d > 16: the reverse sweep runs once per chunk of coordinates (per-thread accumulators of dL/dZ: T * zs * chunk <= 1152)
+    int chunk = d;
+    if (d > 16) { chunk = 1152 / (TT * zs); if (chunk > kTsvChunk) chunk = kTsvChunk; if (chunk > d) chunk = d; }
+    if (chunk < 1) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "reverse mode: too many tensor components for d=%d (num_levels=%d)", d, m);
+    for (int k0 = 0; k0 < d; k0 += chunk) {
+      P.kc0 = k0; P.kcn = d - k0 < chunk ? d - k0 : chunk;
+      const int gz = TT * zs * P.kcn;
+      if (gz <= 160) tens_seq_vjp_kernel<T, 160><<<blocks, threads, 0, s>>>(P);
+      else if (gz <= 480) tens_seq_vjp_kernel<T, 480><<<blocks, threads, 0, s>>>(P);
+      else tens_seq_vjp_kernel<T, 1152><<<blocks, threads, 0, s>>>(P);
+    }
+  }
   prof_end(s);
   GPSIG_LAUNCH_CHECK("tens_seq_vjp_kernel");
   return GPSIG_OK;
@@ -585,7 +595,7 @@ static int tens_tens_vjp_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, 
   if (int rc = check_desc(desc)) return rc;
   if (desc->base == GPSIG_BASE_SPECTRAL) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "reverse mode is not implemented for the spectral base kernel");
   if (!Z || !grad_levels || !gradZ) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "Z/grad_levels/gradZ must not be NULL");
-  if (d < 1 || d > 16) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "state dimension d=%d is not supported (1..16)", d);
+  if (d < 1) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "bad state dimension d=%d", d);
   if (Mz == 0) return GPSIG_OK;
   TensTensVjpParams P;
   memset(&P, 0, sizeof(P));
@@ -594,7 +604,8 @@ static int tens_tens_vjp_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, 
   P.g = grad_levels; P.gradZ = gradZ;
   const int TT = P.m * (P.m + 1) / 2;
   dim3 grid((Mz + 3) / 4, TT);                                       // 4 warps per CTA, one warp per (component, row)
-  if (d <= 8) tens_tens_vjp_kernel<T, 8><<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(P);
+  if (d > 16) tens_tens_vjp_big_kernel<T><<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(P);
+  else if (d <= 8) tens_tens_vjp_kernel<T, 8><<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(P);
   else tens_tens_vjp_kernel<T, 16><<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(P);
   GPSIG_LAUNCH_CHECK("tens_tens_vjp_kernel");
   return GPSIG_OK;

@@ -537,8 +537,12 @@ __global__ void trunc_vjp_grad_kernel(const TruncVjpParams P) {
     if (!diff) return Wat(pp, qq);
     return (Wat(pp - 1, qq - 1) - Wat(pp - 1, qq)) - (Wat(pp, qq - 1) - Wat(pp, qq));
   };
+  // d > 16: the coordinates are taken 16 at a time (the partials are re-evaluated per chunk; the large-d training
+  // shapes are small, the forward Gram at large d runs the lifted path)
+  for (int k0 = 0; k0 < d; k0 += 16) {
+  const int kd = min(16, d - k0);
   T acc[16];
-  for (int k = 0; k < d; ++k) acc[k] = T(0);
+  for (int k = 0; k < kd; ++k) acc[k] = T(0);
   if (r < P.L) {
     const int pp = r;
     const T* xp = x + (size_t)pp * d;
@@ -549,10 +553,10 @@ __global__ void trunc_vjp_grad_kernel(const TruncVjpParams P) {
       T dot, xs, ys, fd, fx, fy;
       dot3(xp, yq, d, dot, xs, ys);
       base_partials<T>(P.base, p0, p1, dot, xs, ys, fd, fx, fy);
-      for (int k = 0; k < d; ++k) acc[k] = gfma<T>(a, fd * yq[k] + T(2) * fx * xp[k], acc[k]);
+      for (int k = 0; k < kd; ++k) acc[k] = gfma<T>(a, fd * yq[k0 + k] + T(2) * fx * xp[k0 + k], acc[k]);
     }
-    T* gx = static_cast<T*>(P.gradX) + ((size_t)i * P.L + pp) * d;
-    for (int k = 0; k < d; ++k) atomic_add<T>(gx + k, acc[k]);
+    T* gx = static_cast<T*>(P.gradX) + ((size_t)i * P.L + pp) * d + k0;
+    for (int k = 0; k < kd; ++k) atomic_add<T>(gx + k, acc[k]);
   } else {
     const int qq = r - P.L;
     const T* yq = y + (size_t)qq * d;
@@ -563,10 +567,11 @@ __global__ void trunc_vjp_grad_kernel(const TruncVjpParams P) {
       T dot, xs, ys, fd, fx, fy;
       dot3(xp, yq, d, dot, xs, ys);
       base_partials<T>(P.base, p0, p1, dot, xs, ys, fd, fx, fy);
-      for (int k = 0; k < d; ++k) acc[k] = gfma<T>(a, fd * xp[k] + T(2) * fy * yq[k], acc[k]);
+      for (int k = 0; k < kd; ++k) acc[k] = gfma<T>(a, fd * xp[k0 + k] + T(2) * fy * yq[k0 + k], acc[k]);
     }
-    T* gy = static_cast<T*>(P.gradY) + ((size_t)j * P.L2 + qq) * d;
-    for (int k = 0; k < d; ++k) atomic_add<T>(gy + k, acc[k]);
+    T* gy = static_cast<T*>(P.gradY) + ((size_t)j * P.L2 + qq) * d + k0;
+    for (int k = 0; k < kd; ++k) atomic_add<T>(gy + k, acc[k]);
+  }
   }
 }
 
@@ -596,6 +601,7 @@ __global__ void __launch_bounds__(256) trunc_vjp_grad_warp_kernel(const TruncVjp
     if (!diff) return Wat(pp, qq);
     return (Wat(pp - 1, qq - 1) - Wat(pp - 1, qq)) - (Wat(pp, qq - 1) - Wat(pp, qq));
   };
+  for (int k0 = 0; k0 < d; k0 += 16) {                               // d > 16: 16 coordinates at a time
   T acc[16];
 #pragma unroll
   for (int k = 0; k < 16; ++k) acc[k] = T(0);
@@ -610,12 +616,12 @@ __global__ void __launch_bounds__(256) trunc_vjp_grad_warp_kernel(const TruncVjp
       dot3(xp, yq, d, dot, xs, ys);
       base_partials_call<T>(P.base, p0, p1, dot, xs, ys, fd, fx, fy);
 #pragma unroll
-      for (int k = 0; k < 16; ++k) if (k < d) acc[k] = gfma<T>(a, fd * yq[k] + T(2) * fx * xp[k], acc[k]);
+      for (int k = 0; k < 16; ++k) if (k0 + k < d) acc[k] = gfma<T>(a, fd * yq[k0 + k] + T(2) * fx * xp[k0 + k], acc[k]);
     }
-    T* gx = static_cast<T*>(P.gradX) + ((size_t)i * P.L + pp) * d;
+    T* gx = static_cast<T*>(P.gradX) + ((size_t)i * P.L + pp) * d + k0;
 #pragma unroll
     for (int k = 0; k < 16; ++k) {
-      if (k >= d) continue;                                          // warp-uniform
+      if (k0 + k >= d) continue;                                          // warp-uniform
       T v = acc[k];
       for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
       if (lane == 0 && v != T(0)) atomic_add<T>(gx + k, v);
@@ -631,17 +637,18 @@ __global__ void __launch_bounds__(256) trunc_vjp_grad_warp_kernel(const TruncVjp
       dot3(xp, yq, d, dot, xs, ys);
       base_partials_call<T>(P.base, p0, p1, dot, xs, ys, fd, fx, fy);
 #pragma unroll
-      for (int k = 0; k < 16; ++k) if (k < d) acc[k] = gfma<T>(a, fd * xp[k] + T(2) * fy * yq[k], acc[k]);
+      for (int k = 0; k < 16; ++k) if (k0 + k < d) acc[k] = gfma<T>(a, fd * xp[k0 + k] + T(2) * fy * yq[k0 + k], acc[k]);
     }
-    T* gy = static_cast<T*>(P.gradY) + ((size_t)j * P.L2 + qq) * d;
+    T* gy = static_cast<T*>(P.gradY) + ((size_t)j * P.L2 + qq) * d + k0;
 #pragma unroll
     for (int k = 0; k < 16; ++k) {
-      if (k >= d) continue;                                          // warp-uniform
+      if (k0 + k >= d) continue;                                          // warp-uniform
       T v = acc[k];
       for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
       if (lane == 0 && v != T(0)) atomic_add<T>(gy + k, v);
     }
   }
+}
 }
 
 // ---------------------------------------------------------------------------
@@ -657,12 +664,14 @@ struct TensSeqVjpParams {
   void* gradZ; void* gradX;
   void* S;                           // scratch [T, L, npairs]: running sums S_k(l) of the forward recursion
   size_t npairs;
+  int kc0, kcn;                      // coordinates [kc0, kc0 + kcn) of this launch (d > 16 runs the reverse sweep in chunks; kcn = 0: all)
 };
 
 // Forward (tens_level in tens_kernels.cuh): within level I, components jj = 0..I-1 (global index k),
 //   S_jj(l) = S_jj(l-1) + D_jj(l) * S_{jj-1}(l-1)   (S_{-1} = 1),  K_I = S_{I-1}(L-1).
 // Reverse: lam_jj(l-1) += lam_jj(l);  aD_jj(l) = lam_jj(l) * S_{jj-1}(l-1);  lam_{jj-1}(l-1) += lam_jj(l) * D_jj(l).
-template <typename T, int GZ>                         // GZ >= T * zs * d: per-thread accumulators of dL/dZ
+constexpr int kTsvChunk = 64;                         // coordinates per launch at d > 16
+template <typename T, int GZ>                         // GZ >= T * zs * (coordinates of this launch): per-thread accumulators of dL/dZ
 __global__ void tens_seq_vjp_kernel(const TensSeqVjpParams P) {
   const size_t pair = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (pair >= P.npairs) return;
@@ -683,8 +692,9 @@ __global__ void tens_seq_vjp_kernel(const TensSeqVjpParams P) {
   };
   auto Sat = [&](int k, int l) -> T& { return S[((size_t)k * L + l) * np + pair]; };
   const int l0 = diff ? 1 : 0;                                       // first time index that carries a D
-  // ---- forward: store S_k(l) -------------------------------------------------------------------
-  {
+  const int kc0 = P.kcn > 0 ? P.kc0 : 0, kcn = P.kcn > 0 ? P.kcn : d;
+  // ---- forward: store S_k(l) (first chunk only: the scratch persists across the launches of one call) ----------
+  if (kc0 == 0) {
     T Sv[36], Mprev[36];
     for (int k = 0; k < TT; ++k) { Sv[k] = T(0); Mprev[k] = T(0); }
     for (int l = 0; l < L; ++l) {
@@ -705,15 +715,15 @@ __global__ void tens_seq_vjp_kernel(const TensSeqVjpParams P) {
   // ---- reverse -----------------------------------------------------------------------------------
   T lam[36], aDnext[36], gz[GZ];
   for (int k = 0; k < TT; ++k) { lam[k] = T(0); aDnext[k] = T(0); }
-  for (int e = 0; e < TT * zs * d; ++e) gz[e] = T(0);
+  for (int e = 0; e < TT * zs * kcn; ++e) gz[e] = T(0);
   {
     int k0 = 0;
     for (int I = 1; I <= m; ++I) { lam[k0 + I - 1] = static_cast<const T*>(P.g)[((size_t)I * P.Mz + z) * ncols + nl]; k0 += I; }
   }
   for (int l = L - 1; l >= 0; --l) {
     const T* xl = x + (size_t)l * d;
-    T gx[16];
-    for (int q = 0; q < d; ++q) gx[q] = T(0);
+    T gx[kTsvChunk];
+    for (int q = 0; q < kcn; ++q) gx[q] = T(0);
     int k0 = 0;
     for (int I = 1; I <= m; ++I) {
       for (int jj = 0; jj < I; ++jj) {
@@ -735,9 +745,9 @@ __global__ void tens_seq_vjp_kernel(const TensSeqVjpParams P) {
             dot3(zp, xl, d, dot, zsq, xsq);
             base_partials<T>(P.base, p0, p1, dot, zsq, xsq, fd, fz, fx);
             const T w = sgn * aM;
-            for (int q = 0; q < d; ++q) {
-              gz[(k * zs + s) * d + q] = gfma<T>(w, fd * xl[q] + T(2) * fz * zp[q], gz[(k * zs + s) * d + q]);
-              gx[q] = gfma<T>(w, fd * zp[q] + T(2) * fx * xl[q], gx[q]);
+            for (int q = 0; q < kcn; ++q) {
+              gz[(k * zs + s) * kcn + q] = gfma<T>(w, fd * xl[kc0 + q] + T(2) * fz * zp[kc0 + q], gz[(k * zs + s) * kcn + q]);
+              gx[q] = gfma<T>(w, fd * zp[kc0 + q] + T(2) * fx * xl[kc0 + q], gx[q]);
             }
           }
         }
@@ -756,13 +766,13 @@ __global__ void tens_seq_vjp_kernel(const TensSeqVjpParams P) {
         k0 += I;
       }
     }
-    T* gxo = static_cast<T*>(P.gradX) + ((size_t)n * L + l) * d;
-    for (int q = 0; q < d; ++q) if (gx[q] != T(0)) atomic_add<T>(gxo + q, gx[q]);
+    T* gxo = static_cast<T*>(P.gradX) + ((size_t)n * L + l) * d + kc0;
+    for (int q = 0; q < kcn; ++q) if (gx[q] != T(0)) atomic_add<T>(gxo + q, gx[q]);
   }
   for (int k = 0; k < TT; ++k)
     for (int s = 0; s < zs; ++s) {
-      T* gzo = static_cast<T*>(P.gradZ) + (((size_t)k * P.Mz + z) * zs + s) * d;
-      for (int q = 0; q < d; ++q) atomic_add<T>(gzo + q, gz[(k * zs + s) * d + q]);
+      T* gzo = static_cast<T*>(P.gradZ) + (((size_t)k * P.Mz + z) * zs + s) * d + kc0;
+      for (int q = 0; q < kcn; ++q) atomic_add<T>(gzo + q, gz[(k * zs + s) * kcn + q]);
     }
 }
 
@@ -1200,6 +1210,70 @@ __global__ void __launch_bounds__(128) tens_tens_vjp_kernel(const TensTensVjpPar
       for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
       if (lane == 0) static_cast<T*>(P.gradZ)[(((size_t)k * Mz + a) * zs + s) * d + q] = v;
     }
+}
+
+// d > 16: the same adjoint with one warp per (component, row a) working on ONE column b at a time: the lanes stride over
+// the coordinates, dot products are warp reductions, lane t accumulates dL/dz_a[q] for q = t, t + 32, ... (256 per pass)
+template <typename T>
+__device__ __forceinline__ void warp_dot3(const T* __restrict__ u, const T* __restrict__ v, int d, int lane, T& dot, T& us, T& vs) {
+  dot = us = vs = T(0);
+  for (int q = lane; q < d; q += 32) { const T a = u[q], b = v[q]; dot = gfma<T>(a, b, dot); us = gfma<T>(a, a, us); vs = gfma<T>(b, b, vs); }
+  dot = warp_sum<T>(dot); us = warp_sum<T>(us); vs = warp_sum<T>(vs);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(128) tens_tens_vjp_big_kernel(const TensTensVjpParams P) {
+  const int a = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  const int k = gridDim.y - 1 - blockIdx.y;
+  if (a >= P.Mz) return;
+  const int d = P.d, zs = P.zs, Mz = P.Mz;
+  const T p0 = T(P.p0), p1 = T(P.p1);
+  const T* Z = static_cast<const T*>(P.Z);
+  int I = 1, k0 = 0;
+  while (k0 + I <= k) { k0 += I; ++I; }
+  const T* g = static_cast<const T*>(P.g) + (size_t)I * Mz * Mz;
+  auto zpt = [&](int kk, int zz, int sidx) { return Z + (((size_t)kk * Mz + zz) * zs + sidx) * d; };
+  auto ev = [&](int kk, int b, int sa, int sb) {
+    T dot, us, vs;
+    warp_dot3<T>(zpt(kk, a, sa), zpt(kk, b, sb), d, lane, dot, us, vs);
+    return base_eval_call<T>(P.base, p0, p1, dot, us, vs);
+  };
+  for (int q0 = 0; q0 < d; q0 += 256) {
+    T acc[2][8];
+#pragma unroll
+    for (int sidx = 0; sidx < 2; ++sidx)
+#pragma unroll
+      for (int c = 0; c < 8; ++c) acc[sidx][c] = T(0);
+    for (int b = 0; b < Mz; ++b) {
+      T w = g[(size_t)a * Mz + b] + g[(size_t)b * Mz + a];
+      if (w == T(0)) continue;                                         // warp-uniform
+      for (int jj = 0; jj < I; ++jj) {
+        if (k0 + jj == k) continue;
+        w *= zs == 2 ? ev(k0 + jj, b, 1, 1) + ev(k0 + jj, b, 0, 0) - ev(k0 + jj, b, 1, 0) - ev(k0 + jj, b, 0, 1) : ev(k0 + jj, b, 0, 0);   // kernels.py:278
+      }
+      for (int sa = 0; sa < zs; ++sa)
+        for (int sb = 0; sb < zs; ++sb) {
+          const T sgn = (zs == 2 && sa != sb) ? T(-1) : T(1);
+          const T* za = zpt(k, a, sa); const T* zb = zpt(k, b, sb);
+          T dot, us, vs, fd, fx, fy;
+          warp_dot3<T>(za, zb, d, lane, dot, us, vs);
+          base_partials_call<T>(P.base, p0, p1, dot, us, vs, fd, fx, fy);
+          const T wf = sgn * w * fd, wx = T(2) * sgn * w * fx;
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            const int q = q0 + lane + 32 * c;
+            if (q < d) acc[sa][c] = gfma<T>(wf, zb[q], gfma<T>(wx, za[q], acc[sa][c]));
+          }
+        }
+    }
+    for (int sa = 0; sa < zs; ++sa)
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        const int q = q0 + lane + 32 * c;
+        if (q < d) static_cast<T*>(P.gradZ)[(((size_t)k * Mz + a) * zs + sa) * d + q] = acc[sa][c];
+      }
+  }
 }
 
 }  // namespace gpsig

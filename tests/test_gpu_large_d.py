@@ -117,3 +117,61 @@ def test_tensor_core_lift_matches_cuda_core_lift(d, L, L2, monkeypatch):
         B = ops.trunc_gram(X, Y, m, base=base, lengthscales=ls).cpu().numpy()
         monkeypatch.delenv('GPSIG_NO_MMA')
         assert np.max(np.abs(A - B) / np.abs(B).max(axis=(1, 2), keepdims=True)) < 1e-5, base      # both are float32 evaluations: each is within 1e-5 of the oracle
+
+
+@pytest.mark.parametrize("base", ['linear', 'rbf', 'matern32'])
+@pytest.mark.parametrize("d", [20, 70])
+def test_reverse_mode_large_d(base, d):
+    """Adjoints at d > 16 (the feature dimension is taken in chunks): vector-Jacobian identity against central
+    differences of the oracle's raw levels, as tests/test_gpu_vjp.py does at d <= 16.  Gram pairs, diagonal pairs,
+    tensors vs sequences (with increments) and tensors vs tensors -- what K_tens_n_seq_covs differentiates."""
+    from gpsig_b200 import ops
+    from oracle.trunc_np import SignatureKernelOracle
+    EPS, TOLV = 1e-5, 2e-6
+    N, N2, L, L2, m, Mz = 4, 3, 8, 7, 3, 4
+    rng = np.random.default_rng(5)
+    sc = np.sqrt(8.0 / d)
+    X, Y = (brownian(N, L, d, 0) + 0.3) * sc, (brownian(N2, L2, d, 1) - 0.2) * sc
+    o = SignatureKernelOracle(L * d, d, m, base=base, lengthscales=None, normalization=False)
+    dev = lambda a: _dev(a, torch.float64)  # noqa: E731
+
+    def check(nm, a, f):
+        assert abs(a - f) <= TOLV * max(abs(f), abs(a), 1e-12) + 1e-9, (nm, a, f)
+
+    G = rng.standard_normal((m + 1, N, N2))
+    VX, VY = rng.standard_normal(X.shape), rng.standard_normal(Y.shape)
+    gX, gY = ops.trunc_vjp(dev(X), dev(Y), dev(G), m, base=base)
+    f = lambda A, B: float(np.sum(G * o._K_seq(A, B)))  # noqa: E731
+    check('X', float((gX.cpu().numpy() * VX).sum()), (f(X + EPS * VX, Y) - f(X - EPS * VX, Y)) / (2 * EPS))
+    check('X2', float((gY.cpu().numpy() * VY).sum()), (f(X, Y + EPS * VY) - f(X, Y - EPS * VY)) / (2 * EPS))
+    Gd = rng.standard_normal((m + 1, N))
+    gX, _ = ops.trunc_vjp(dev(X), None, dev(Gd), m, base=base, diag=True)
+    f = lambda A: float(np.sum(Gd * o._K_seq_diag(A)))  # noqa: E731
+    check('diag', float((gX.cpu().numpy() * VX).sum()), (f(X + EPS * VX) - f(X - EPS * VX)) / (2 * EPS))
+    for increments in (False, True):
+        Z = inducing_tensors(X, m, Mz, increments, 2)
+        VZ = rng.standard_normal(Z.shape)
+        Gz = rng.standard_normal((m + 1, Mz, N))
+        gZ, gX = ops.tens_vs_seq_vjp(dev(Z), dev(X), dev(Gz), m, increments=increments, base=base)
+        f = lambda A, B: float(np.sum(Gz * o._K_tens_vs_seq(A, B, increments=increments)))  # noqa: E731
+        check('Z', float((gZ.cpu().numpy() * VZ).sum()), (f(Z + EPS * VZ, X) - f(Z - EPS * VZ, X)) / (2 * EPS))
+        check('Xz', float((gX.cpu().numpy() * VX).sum()), (f(Z, X + EPS * VX) - f(Z, X - EPS * VX)) / (2 * EPS))
+        G2 = rng.standard_normal((m + 1, Mz, Mz))
+        gZ = ops.tens_tens_vjp(dev(Z), dev(G2), m, increments=increments, base=base)
+        f = lambda A: float(np.sum(G2 * o._K_tens(A, increments=increments)))  # noqa: E731
+        check('Zz', float((gZ.cpu().numpy() * VZ).sum()), (f(Z + EPS * VZ) - f(Z - EPS * VZ)) / (2 * EPS))
+
+
+def test_svgp_covariances_differentiable_at_large_d():
+    """K_tens_n_seq_covs under autograd at d = 28 (ArabicDigits with num_lags=1 and time): gradients reach the inducing
+    tensors and the lengthscales (finite and non-zero)."""
+    from gpsig_b200 import kernels
+    N, L, d, m, Mz = 10, 20, 28, 4, 6
+    X = brownian(N, L, d, 0) * 0.5
+    Z = torch.nn.Parameter(_dev(inducing_tensors(X, m, Mz, True, 5), torch.float64))
+    k = kernels.SignatureRBF(L * d, d, m)
+    k.lengthscales = torch.nn.Parameter(torch.full((d,), 2.0, dtype=torch.float64, device='cuda'))
+    Kzz, Kzx, Kxx = k.K_tens_n_seq_covs(Z, _dev(X.reshape(N, -1), torch.float64), increments=True)
+    (Kzz.sum() + (Kzx ** 2).sum() + Kxx.sum()).backward()
+    for t in (Z.grad, k.lengthscales.grad):
+        assert t is not None and bool(torch.isfinite(t).all()) and float(t.abs().max()) > 0
