@@ -224,6 +224,14 @@ def other_configs(torch, ops, lib):
     del g
     torch.cuda.empty_cache()
     out.update(large_d(torch, ops, lib))
+    # c1 with the higher-order recursion (order = num_levels = 4: the variant the reference validates against signatures,
+    # notebooks/signature_kernel.ipynb cells 11-13): the general kernel (generic_kernels.cuh), one CTA per pair
+    Xc = torch.as_tensor(brownian(100, 50, 3, 0), dtype=torch.float64, device='cuda')
+    for order in (1, 4):
+        ms = timed(lambda: ops.trunc_gram(Xc, None, 4, base='linear', order=order, return_levels=False), reps=5)
+        out["c1_order%d_f64" % order] = {"workload": "c1: SignatureLinear m=4 order=%d K(X, X), N=100, L=50, d=3" % order,
+                                         "kernel": "trunc_generic_kernel" if order > 1 else "trunc_skew_kernel (tri) + mirror_lower_kernel",
+                                         "kernel_ms": ms, "delivered_pairs_per_s": 100 * 100 / (ms * 1e-3)}
     ref_cuda = reference_cuda_pde(torch, ops, timed)
     if ref_cuda:
         out["c3_vs_reference_cuda"] = ref_cuda
