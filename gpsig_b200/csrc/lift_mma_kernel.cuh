@@ -9,9 +9,9 @@
 // Operands are pre-split and pre-tiled by lift_pack_mma_kernel into the canonical K-major, no-swizzle UMMA layout
 // (core matrix = 8 rows x 16 bytes, contiguous), K stages outermost, so one K stage of an operand is ONE contiguous
 // block = one 1-D TMA bulk copy (cp.async.bulk, SASS UBLKCP) into a 4-deep shared-memory ring (full/empty mbarriers).
-// Warp roles (320 threads, one CTA per SM, persistent over streams of pairs):
+// Warp roles (64 + 128 kMmaEpq threads, one CTA per SM, persistent over streams of pairs):
 //   warp 0   TMA producer          warp 1   MMA issuer (one elected lane; tcgen05.mma, tcgen05.commit -> mbarriers)
-//   warps 2-9 epilogue: tcgen05.ld their 32 accumulator rows (tensor memory, double buffered: the MMAs of tile n+1
+//   the others: epilogue: tcgen05.ld their 32 accumulator rows (tensor memory, double buffered: the MMAs of tile n+1
 //            overlap the epilogue of tile n; two warps per lane quarter split the columns), base-kernel epilogue, store
 //            in the skewed order of the recursion kernel.
 #pragma once
@@ -22,7 +22,11 @@ namespace gpsig {
 
 constexpr int kMmaKC = 16;            // K elements per pipeline stage (2 MMA K-steps of 8)
 constexpr int kMmaStages = 4;
-constexpr int kMmaThreads = 320;          // TMA warp, MMA warp, 8 epilogue warps
+#ifndef GPSIG_MMA_EPQ
+#define GPSIG_MMA_EPQ 2     // measured: 4 per quarter is slower (51.5 against 43.8 ms at N=1000 L=100 d=126)
+#endif
+constexpr int kMmaEpq = GPSIG_MMA_EPQ;                 // epilogue warps per lane quarter (they split the column groups)
+constexpr int kMmaThreads = 64 + 128 * kMmaEpq;       // TMA warp, MMA warp, 4 * kMmaEpq epilogue warps
 
 struct LiftMmaOperands {
   const void* xop; const void* yop;      // pre-split operands (floats), or NULL: the CUDA-core lift runs instead
@@ -148,7 +152,7 @@ __global__ void __launch_bounds__(kMmaThreads, 1) lift_mma_kernel(const LiftPara
 
   if (threadIdx.x == 0) {
     for (int b = 0; b < NS; ++b) { mbar_init(&full_bar[b], 1); mbar_init(&empty_bar[b], 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], 8); }
+    for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], 4 * kMmaEpq); }
     mbar_init(bfull_bar, 1); mbar_init(bfree_bar, 1);
     fence_mbar_init();
   }
@@ -226,8 +230,8 @@ __global__ void __launch_bounds__(kMmaThreads, 1) lift_mma_kernel(const LiftPara
     }
   } else {
     // ===== epilogue: 8 warps; warps w and w + 4 share accumulator rows 32 * (w % 4) .. + 31 and split the column groups =====
-    const int wq = warp & 3, half = (warp - 2) >> 2;
-    const int et = threadIdx.x - 64;                                  // 0..255 among the epilogue threads
+    const int wq = warp & 3, half = (warp - 2) >> 2;                  // half: which share of the column groups
+    const int et = threadIdx.x - 64;                                  // index among the epilogue threads
     int buf = 0; uint32_t tph = 0;
     const float p0 = (float)P.p0, p1 = (float)P.p1;
     // MODE 0: linear; 1: RBF on coordinates pre-scaled by sqrt(log2 e) (abi.cu): 2^(x.y - |x|^2/2 - |y|^2/2) is two
@@ -245,25 +249,24 @@ __global__ void __launch_bounds__(kMmaThreads, 1) lift_mma_kernel(const LiftPara
           const float* xsq = static_cast<const float*>(P.xp) + (size_t)(i0 + n) * P.xblk + (size_t)L * DP;
           for (int mt = 0; mt < MT; ++mt) {
             float* ys = ysm + buf * LP2;
-            for (int q = et; q < LP2; q += 256) { const float y = ysq[min(q, L2 - 1)]; ys[q] = mode == 1 ? -0.5f * y : y; }
+            for (int q = et; q < LP2; q += 128 * kMmaEpq) { const float y = ysq[min(q, L2 - 1)]; ys[q] = mode == 1 ? -0.5f * y : y; }
             const int p = mt * 128 + wq * 32 + lane;
             float xs = p < L ? xsq[p] : 0.f;
             if (mode == 1) xs *= -0.5f;
-            asm volatile("bar.sync 1, 256;" ::: "memory");           // the tile's column constants are staged
+            asm volatile("bar.sync 1, %0;" ::"n"(128 * kMmaEpq) : "memory");           // the tile's column constants are staged
             mbar_wait(&tfull_bar[buf], tph);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t ta = tbase + ((uint32_t)(wq * 32) << 16) + (uint32_t)(buf * LP2);
             constexpr int NG = LP2 / 16;
+            constexpr int NGW = NG / kMmaEpq;                         // column groups of 16 per warp
+            static_assert(NG % kMmaEpq == 0, "column groups must split evenly over the epilogue warps");
             uint32_t r[2][16];
             tmem_ld16(r[0], ta + (uint32_t)(half * 16));
 #pragma unroll
-            for (int gi = 0; gi < NG / 2; ++gi) {
-              const int g = half + 2 * gi;
+            for (int gi = 0; gi < NGW; ++gi) {
+              const int g = half + kMmaEpq * gi;
               tmem_ld_wait();
-              if (gi + 1 < NG / 2) tmem_ld16(r[(gi + 1) & 1], ta + (uint32_t)((g + 2) * 16));    // next group in flight during the math
-              else {
-                // all of this warp's reads of the accumulator have been issued and the last one waited for below
-              }
+              if (gi + 1 < NGW) tmem_ld16(r[(gi + 1) & 1], ta + (uint32_t)((g + kMmaEpq) * 16));  // next group in flight during the math
               float v[16];
               const float4* yv = reinterpret_cast<const float4*>(ys + g * 16);
 #pragma unroll

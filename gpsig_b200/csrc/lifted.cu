@@ -6,8 +6,9 @@
 
 namespace gpsig {
 
+// lift on stream s, recursion on stream sr (== s, or the side stream when consecutive blocks are overlapped)
 template <typename T, int COLS, int MLEV>
-static int lift_block(const LiftParams& P, const LiftMmaOperands* mma, cudaStream_t s) {
+static int lift_block(const LiftParams& P, const LiftMmaOperands* mma, cudaStream_t s, cudaStream_t sr, cudaEvent_t lifted) {
   const int npair_slots = P.nstreams * P.SP;
   bool done = false;
   if constexpr (sizeof(T) == 4) {
@@ -18,19 +19,39 @@ static int lift_block(const LiftParams& P, const LiftMmaOperands* mma, cudaStrea
     lift_tile_kernel<T, COLS><<<grid, 256, 0, s>>>(P);
     GPSIG_LAUNCH_CHECK("lift_tile_kernel");
   }
-  lift_recur_kernel<T, COLS, MLEV><<<(unsigned)((P.nstreams + kLiftWarps - 1) / kLiftWarps), kLiftWarps * 32, 0, s>>>(P);
+  if (sr != s) { GPSIG_CUDA_CHECK(cudaEventRecord(lifted, s)); GPSIG_CUDA_CHECK(cudaStreamWaitEvent(sr, lifted, 0)); }
+  lift_recur_kernel<T, COLS, MLEV><<<(unsigned)((P.nstreams + kLiftWarps - 1) / kLiftWarps), kLiftWarps * 32, 0, sr>>>(P);
   GPSIG_LAUNCH_CHECK("lift_recur_kernel");
   return GPSIG_OK;
 }
 
 template <typename T, int COLS>
-static int lift_block_mlev(const LiftParams& P, const LiftMmaOperands* mma, cudaStream_t s) {
-  if (P.m <= 3) return lift_block<T, COLS, 3>(P, mma, s);
-  if (P.m <= 4) return lift_block<T, COLS, 4>(P, mma, s);
-  if (P.m <= 5) return lift_block<T, COLS, 5>(P, mma, s);
-  if (P.m <= 6) return lift_block<T, COLS, 6>(P, mma, s);
-  if (P.m <= 8) return lift_block<T, COLS, 8>(P, mma, s);
+static int lift_block_mlev(const LiftParams& P, const LiftMmaOperands* mma, cudaStream_t s, cudaStream_t sr, cudaEvent_t ev) {
+  if (P.m <= 3) return lift_block<T, COLS, 3>(P, mma, s, sr, ev);
+  if (P.m <= 4) return lift_block<T, COLS, 4>(P, mma, s, sr, ev);
+  if (P.m <= 5) return lift_block<T, COLS, 5>(P, mma, s, sr, ev);
+  if (P.m <= 6) return lift_block<T, COLS, 6>(P, mma, s, sr, ev);
+  if (P.m <= 8) return lift_block<T, COLS, 8>(P, mma, s, sr, ev);
   GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "num_levels=%d is not supported (1..8)", P.m);
+}
+
+// Side stream and events of the block pipeline, per host thread and device (created on first use; streams and events
+// are driver objects, not device memory).
+constexpr int kLiftMaxDev = 64;
+struct LiftSide { cudaStream_t stream = nullptr; cudaEvent_t lifted[2] = {nullptr, nullptr}, consumed[2] = {nullptr, nullptr}; };
+static thread_local LiftSide g_side[kLiftMaxDev];
+static LiftSide* lift_side() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kLiftMaxDev) return nullptr;
+  LiftSide& S = g_side[dev];
+  if (!S.stream) {
+    if (cudaStreamCreateWithFlags(&S.stream, cudaStreamNonBlocking) != cudaSuccess) { S.stream = nullptr; return nullptr; }
+    for (int k = 0; k < 2; ++k) {
+      if (cudaEventCreateWithFlags(&S.lifted[k], cudaEventDisableTiming) != cudaSuccess) return nullptr;
+      if (cudaEventCreateWithFlags(&S.consumed[k], cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    }
+  }
+  return &S;
 }
 
 // P: everything but the block fields (ib, ie, jb, je, SP, nci, nstreams, stream_elems, scratch)
@@ -42,30 +63,51 @@ int launch_lift(LiftParams P, void* scratch, size_t scratch_bytes, const LiftMma
   const LiftPlan pl = lift_plan(npairs, P.L, P.L2, sizeof(T));
   if (scratch_bytes < pl.scratch_bytes)
     GPSIG_FAIL(GPSIG_ERR_WORKSPACE, "workspace too small for the lifted tiles: need %zu bytes, got %zu", pl.scratch_bytes, scratch_bytes);
-  P.SP = pl.SP; P.stream_elems = pl.stream_elems; P.scratch = scratch;
+  P.SP = pl.SP; P.stream_elems = pl.stream_elems;
   const int r0 = P.diag ? 0 : P.row_begin, r1 = P.diag ? P.N : P.row_end;
+  const size_t call_pairs = P.diag ? (size_t)(r1 - r0) : (size_t)(r1 - r0) * (size_t)P.N2;
+  // More pairs than one block of scratch holds: the scratch is used as two halves and the recursion of block b (side
+  // stream) overlaps the lift of block b + 1 (caller's stream): the lift is bound by the tensor pipe / its stores, the
+  // recursion by its loads, and both fit on an SM together.  (GPSIG_LIFT_NO_OVERLAP: one stream, whole scratch.)
+  int max_streams = pl.max_streams;
+  LiftSide* side = nullptr;
+  if (call_pairs > (size_t)pl.max_streams * pl.SP && pl.max_streams >= 2 && getenv("GPSIG_LIFT_NO_OVERLAP") == nullptr) side = lift_side();
+  if (side) max_streams = pl.max_streams / 2;
   // rows per block: as many streams of SP rows as fit; then as many columns as fit next to them
-  const long long max_rows = (long long)pl.max_streams * pl.SP;
+  const long long max_rows = (long long)max_streams * pl.SP;
   const int NI = (int)((long long)(r1 - r0) < max_rows ? (r1 - r0) : max_rows);
   prof_begin(s);
+  int blk = 0;
   for (int ib = r0; ib < r1; ib += NI) {
     P.ib = ib; P.ie = ib + NI < r1 ? ib + NI : r1;
     P.nci = (P.ie - P.ib + P.SP - 1) / P.SP;
-    int NJ = P.diag ? 1 : pl.max_streams / P.nci;
+    int NJ = P.diag ? 1 : max_streams / P.nci;
     if (NJ < 1) NJ = 1;
     if (!P.diag && NJ > P.N2) NJ = P.N2;
     const int jend = P.diag ? 1 : P.N2;
-    for (int jb = 0; jb < jend; jb += NJ) {
+    for (int jb = 0; jb < jend; jb += NJ, ++blk) {
       P.jb = jb; P.je = jb + NJ < jend ? jb + NJ : jend;
       P.nstreams = P.nci * (P.diag ? 1 : (P.je - P.jb));
+      const int h = blk & 1;
+      P.scratch = static_cast<char*>(scratch) + (side ? (size_t)h * max_streams * pl.stream_elems * sizeof(T) : 0);
+      // this half was last read by the recursion of block blk - 2
+      if (side && blk >= 2) GPSIG_CUDA_CHECK(cudaStreamWaitEvent(s, side->consumed[h], 0));
       int rc;
+      cudaStream_t sr = side ? side->stream : s;
+      cudaEvent_t ev = side ? side->lifted[h] : nullptr;
       switch (pl.COLS) {
-        case 2: rc = lift_block_mlev<T, 2>(P, mma, s); break;
-        case 4: rc = lift_block_mlev<T, 4>(P, mma, s); break;
-        default: rc = lift_block_mlev<T, 8>(P, mma, s); break;
+        case 2: rc = lift_block_mlev<T, 2>(P, mma, s, sr, ev); break;
+        case 4: rc = lift_block_mlev<T, 4>(P, mma, s, sr, ev); break;
+        default: rc = lift_block_mlev<T, 8>(P, mma, s, sr, ev); break;
       }
       if (rc) return rc;
+      if (side) GPSIG_CUDA_CHECK(cudaEventRecord(side->consumed[h], sr));
     }
+  }
+  // join: the caller's stream continues after the last recursions
+  if (side) {
+    if (blk >= 1) GPSIG_CUDA_CHECK(cudaStreamWaitEvent(s, side->consumed[(blk - 1) & 1], 0));
+    if (blk >= 2) GPSIG_CUDA_CHECK(cudaStreamWaitEvent(s, side->consumed[(blk - 2) & 1], 0));
   }
   prof_end(s);
   return GPSIG_OK;
