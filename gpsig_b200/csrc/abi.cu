@@ -149,13 +149,13 @@ static int check_desc(const gpsig_trunc_desc* d) {
 }
 
 template <typename T>
-static int pack(const T* X, int N, int L, int d, const T* ls, T* dst, cudaStream_t s, int RS = 0, double scale = 1.0) {
+static int pack(const T* X, int N, int L, int d, const T* ls, T* dst, cudaStream_t s, int RS = 0, double scale = 1.0, int dup = 0) {
   const size_t tot = (size_t)N * L;
   if (tot == 0) return GPSIG_OK;
   if (RS == 0) RS = padded_dim(d);
   const int threads = 256;
   const size_t blocks = (tot + threads - 1) / threads;
-  pack_sequences_kernel<T><<<(unsigned)blocks, threads, 0, s>>>(X, N, L, d, padded_dim(d), RS, ls, dst, seq_block_elems_rs(L, RS, sizeof(T)), T(scale));
+  pack_sequences_kernel<T><<<(unsigned)blocks, threads, 0, s>>>(X, N, L, d, padded_dim(d), RS, ls, dst, seq_block_elems_rs(L, RS, sizeof(T)), T(scale), dup);
   GPSIG_LAUNCH_CHECK("pack_sequences_kernel");
   return GPSIG_OK;
 }
@@ -165,7 +165,7 @@ static size_t packed_bytes(int N, int L, int d, int elem) {
 }
 // with the padded row stride of the systolic Gram kernel (an upper bound of the plain layout)
 static size_t packed_bytes_padded(int N, int L, int d, int elem) {
-  return align_up((size_t)N * seq_block_elems_rs(L, skew_row_stride(d, elem), elem) * elem, 128);
+  return align_up((size_t)N * seq_block_elems_rs(L, skew_row_stride(d, elem, GPSIG_SKEW_DUP_F32 && elem == 4), elem) * elem, 128);
 }
 
 // float32 tensor-core lift (lift_mma_kernel.cuh): pre-split, pre-tiled operands behind the lifted-tile scratch
@@ -218,7 +218,8 @@ static int trunc_gram_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
   const bool lifted = big && desc->order == 1 && desc->base != GPSIG_BASE_SPECTRAL && lift_eligible(L, L2);
   const bool generic = desc->order > 1 || desc->base == GPSIG_BASE_SPECTRAL || (big && !lifted);
   const bool skew = !big && !generic && skew_eligible(L, L2, sizeof(T)) && getenv("GPSIG_NO_SKEW") == nullptr;
-  const int RS = skew ? skew_row_stride(d, sizeof(T)) : padded_dim(d);
+  const bool dup = skew && skew_uses_dup(d, L2, sizeof(T));      // float32: coordinates stored twice for the packed-pair contraction
+  const int RS = skew ? skew_row_stride(d, sizeof(T), dup) : padded_dim(d);
   T* xp = static_cast<T*>(ws);
   T* yp = sym ? xp : reinterpret_cast<T*>(static_cast<char*>(ws) + packed_bytes_padded(N, L, d, sizeof(T)));
   // float32 RBF on the systolic kernel: coordinates pre-scaled by sqrt(log2 e) so that the exponent
@@ -227,8 +228,8 @@ static int trunc_gram_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
   // (the tensor-core lift of the large-d path reads its exponent the same way, lift_mma_kernel.cuh)
   const bool lift_mma = lifted && sizeof(T) == 4 && getenv("GPSIG_NO_MMA") == nullptr;
   const double cscale = (((skew && (sizeof(T) == 4 || GPSIG_SKEW_EXP2)) || lift_mma) && desc->base == GPSIG_BASE_RBF) ? 1.2011224087864498 : 1.0;
-  if (int rc = pack<T>(X, N, L, d, ls, xp, s, RS, cscale)) return rc;
-  if (!sym) if (int rc = pack<T>(X2, N2, L2, d, ls, yp, s, RS, cscale)) return rc;
+  if (int rc = pack<T>(X, N, L, d, ls, xp, s, RS, cscale, dup)) return rc;
+  if (!sym) if (int rc = pack<T>(X2, N2, L2, d, ls, yp, s, RS, cscale, dup)) return rc;
 
   TruncParams P;
   memset(&P, 0, sizeof(P));

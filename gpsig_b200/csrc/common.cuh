@@ -54,11 +54,12 @@ __host__ __device__ inline size_t seq_block_elems_rs(int L, int RS, int elem) {
 }
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
-// RS = row stride of the packed rows in elements (>= DP; the pad is never read)
+// RS = row stride of the packed rows in elements (>= DP; the pad is never read).  dup: every coordinate is written
+// twice (x0, x0, x1, x1, ...; RS >= 2 DP) for the packed-pair float32 contraction of the systolic kernel.
 template <typename T>
 __global__ void pack_sequences_kernel(const T* __restrict__ X, int N, int L, int d, int DP, int RS,
                                       const T* __restrict__ lengthscales, T* __restrict__ packed,
-                                      size_t block_elems, T scale) {
+                                      size_t block_elems, T scale, int dup = 0) {
   // one thread per point (n, p): reads d contiguous values, writes DP + 1
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (size_t)N * L) return;
@@ -70,7 +71,7 @@ __global__ void pack_sequences_kernel(const T* __restrict__ X, int N, int L, int
   for (int k = 0; k < DP; ++k) {
     T v = 0;
     if (k < d) { v = src[k]; if (lengthscales) v = v / lengthscales[k]; if (scale != T(1)) v *= scale; }
-    dst[k] = v;
+    if (dup) { dst[2 * k] = v; dst[2 * k + 1] = v; } else dst[k] = v;
     s += v * v;              // tf.reduce_sum(tf.square(X), axis=-1), kernels.py:948
   }
   blk[(size_t)L * RS + p] = s;

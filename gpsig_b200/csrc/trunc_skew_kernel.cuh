@@ -33,9 +33,19 @@ namespace gpsig {
 
 constexpr int kSkewBufs = 3;
 
+// float32: the streamed x rows are stored with every coordinate DUPLICATED (x0, x0, x1, x1, ...), so that one 16-byte
+// shared-memory load yields two ready-made (x_k, x_k) pairs for the packed FFMA2 of the contraction: two adjacent
+// columns per instruction, no register moves to assemble the pairs (the y pairs are loop invariant).  Build-time
+// option, OFF: measured at c2 (N = N2 = 1000, 12 warps at 168 registers) it is 4-5 % faster where registers allow
+// (RBF m = 4: 43.96 against 45.67 ms, linear m = 5: 42.8 against 45.1 ms) and 4 % SLOWER at the headline shape
+// (RBF m = 5: 50.6 against 48.4 ms, 16 bytes of spills) -- the contraction drops from 8 to 4.6 instructions per element
+// but the kernel is not bound by issue slots alone; it also moves 67 % more x bytes.
+#ifndef GPSIG_SKEW_DUP_F32
+#define GPSIG_SKEW_DUP_F32 0
+#endif
 // row stride (in elements) of the padded packed layout: an odd number of 16-byte units
-__host__ __device__ inline int skew_row_stride(int d, int elem) {
-  const int dp = padded_dim(d);
+__host__ __device__ inline int skew_row_stride(int d, int elem, bool dup = false) {
+  const int dp = padded_dim(d) * (dup ? 2 : 1);
   int u = dp * elem / 16;
   if ((u & 1) == 0) ++u;
   return u * 16 / elem;
@@ -245,6 +255,11 @@ template <typename T, int DP, int COLS> struct SkewYTmem {
                                 (SkewNW<T, DP, COLS>::value / 4) * COLS * DP * (sizeof(T) / 4) <= 512;
 };
 
+// which instantiations read the duplicated layout: float32 with the y tile in registers (and not in tensor memory)
+template <typename T, int DP, int COLS> struct SkewDup {
+  static constexpr bool value = GPSIG_SKEW_DUP_F32 && sizeof(T) == 4 && YPolicy<T, DP, COLS>::kInRegs && !SkewYTmem<T, DP, COLS>::value;
+};
+
 // float32 RBF: the packed coordinates are pre-scaled by sqrt(log2 e) (abi.cu), so the exponent
 // arrives in base-2 units and exp() is a single MUFU.EX2
 template <> struct SkewFinish<float, OP_RBF> {
@@ -268,6 +283,7 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
   constexpr int NW = SkewNW<T, DP, COLS>::value;
   constexpr bool YREG = YPolicy<T, DP, COLS>::kInRegs;
   constexpr bool YTM = SkewYTmem<T, DP, COLS>::value;      // y tile in tensor memory (float64)
+  constexpr bool DUP = SkewDup<T, DP, COLS>::value;        // x / y rows stored with duplicated coordinates (float32, y in registers)
   constexpr int CE = 32 / sizeof(T);                        // elements per 8-word tensor-memory load (4 doubles / 8 floats)
   constexpr int KC = DP / CE > 0 ? DP / CE : 1;             // chunks per column
   constexpr int TMW = COLS * DP * (sizeof(T) / 4);          // TMEM words (columns) per warp
@@ -336,7 +352,13 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
     } else {
 #pragma unroll
       for (int kv = 0; kv < KV; ++kv) {
-        const V16 v = *reinterpret_cast<const V16*>(yblk + (size_t)q * P.yrs + kv * V);
+        V16 v;
+        if constexpr (DUP) {                       // duplicated layout: coordinate k sits at 2k
+          const float4 a = *reinterpret_cast<const float4*>(yblk + (size_t)q * P.yrs + 2 * kv * V);
+          const float4 b = *reinterpret_cast<const float4*>(yblk + (size_t)q * P.yrs + 2 * kv * V + 4);
+          float4 t = make_float4(a.x, a.z, b.x, b.z);
+          v = *reinterpret_cast<V16*>(&t);
+        } else v = *reinterpret_cast<const V16*>(yblk + (size_t)q * P.yrs + kv * V);
         if (YREG) yreg[YREG ? c : 0][YREG ? kv : 0] = v;
         else *reinterpret_cast<V16*>(ysm + ((size_t)(c * KV + kv) * 32 + lane) * V) = v;
       }
@@ -344,6 +366,15 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
   }
   if (YTM) tmem_st_wait();
   else if (!YREG) __syncwarp();
+  // float32, duplicated x rows: the y tile as loop-invariant pairs of ADJACENT COLUMNS (y_c[k], y_{c+1}[k])
+  [[maybe_unused]] u64 ypk[DUP ? (COLS / 2 > 0 ? COLS / 2 : 1) : 1][DUP ? DP : 1];
+  if constexpr (DUP) {
+#pragma unroll
+    for (int c2 = 0; c2 < COLS / 2; ++c2)
+#pragma unroll
+      for (int k = 0; k < DP; ++k)
+        ypk[c2][k] = pk2((float)vget(yreg[YREG ? 2 * c2 : 0][YREG ? k / V : 0], k % V), (float)vget(yreg[YREG ? 2 * c2 + 1 : 0][YREG ? k / V : 0], k % V));
+  }
   double tab = 0.0;
   if (OP == OP_RBF && sizeof(T) == 8) tab = exp2((double)lane * (1.0 / 32.0));
 
@@ -491,6 +522,44 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
           for (int l = 0; l < MLEV; ++l) {
             if (!(l < MLEV - 1 || rr == 0)) recv[rr][l] = T(0);
             if (lane == 0) recv[rr][l] = T(0);
+          }
+      } else if constexpr (DUP) {
+        // packed pairs: one FFMA2 advances two adjacent columns; x arrives as ready-made (x_k, x_k) pairs
+        u64 accp[R][COLS / 2 > 0 ? COLS / 2 : 1];
+#pragma unroll
+        for (int rr = 0; rr < R; ++rr)
+#pragma unroll
+          for (int c2 = 0; c2 < COLS / 2; ++c2) accp[rr][c2] = pk2((float)acc[rr][2 * c2], (float)acc[rr][2 * c2 + 1]);
+#pragma unroll
+        for (int j = 0; j < DP / 2; ++j) {
+          ulonglong2 xd[R];
+#pragma unroll
+          for (int rr = 0; rr < R; ++rr)
+            xd[rr] = *reinterpret_cast<const ulonglong2*>(xb + (size_t)min(r0 + rr, L - 1) * RS + 4 * j);
+#pragma unroll
+          for (int rr = 0; rr < R; ++rr) {
+#pragma unroll
+            for (int c2 = 0; c2 < COLS / 2; ++c2) {
+              asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(accp[rr][c2]) : "l"(xd[rr].x), "l"(ypk[c2][2 * j]));
+              asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(accp[rr][c2]) : "l"(xd[rr].y), "l"(ypk[c2][2 * j + 1]));
+            }
+            if constexpr ((COLS & 1) != 0) {
+              float x0, x1, dmy;
+              unpk2(xd[rr].x, x0, dmy);
+              unpk2(xd[rr].y, x1, dmy);
+              const V16 yv = yreg[YREG ? COLS - 1 : 0][YREG ? (2 * j) / V : 0];
+              acc[rr][COLS - 1] = gfma<T>(T(x0), vget(yv, (2 * j) % V), acc[rr][COLS - 1]);
+              acc[rr][COLS - 1] = gfma<T>(T(x1), vget(yv, (2 * j + 1) % V), acc[rr][COLS - 1]);
+            }
+          }
+        }
+#pragma unroll
+        for (int rr = 0; rr < R; ++rr)
+#pragma unroll
+          for (int c2 = 0; c2 < COLS / 2; ++c2) {
+            float lo, hi;
+            unpk2(accp[rr][c2], lo, hi);
+            acc[rr][2 * c2] = T(lo); acc[rr][2 * c2 + 1] = T(hi);
           }
       } else {
 #pragma unroll
@@ -709,6 +778,17 @@ int launch_skew_mlev(const TruncParams& P, cudaStream_t stream) {
   GPSIG_SKEW_MLEV(GPSIG_CASE)
 #undef GPSIG_CASE
   GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "num_levels=%d is not supported by this build", P.m);
+}
+
+// host mirror of the dispatch below: does the instantiation that takes (d, L2, elem) read the duplicated layout?
+inline bool skew_uses_dup(int d, int L2, int elem) {
+  if (!GPSIG_SKEW_DUP_F32 || elem != 4) return false;
+  const int need = (L2 + 31) / 32, dp = padded_dim(d);
+  int cols = 0;
+#define GPSIG_CASE(C_) if (cols == 0 && need <= C_) cols = C_;
+  GPSIG_SKEW_COLS(GPSIG_CASE)
+#undef GPSIG_CASE
+  return cols > 0 && cols * dp * 4 <= 256 && !(GPSIG_SKEW_TMEM && GPSIG_SKEW_TMEM_F32);
 }
 
 template <typename T, int OP, int DP>
