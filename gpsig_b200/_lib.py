@@ -67,6 +67,8 @@ def _load():
     lib.gpsig_trunc_diag_static_f64.argtypes = [ctypes.POINTER(TruncDesc), vp, i, i, i, vp, vp, vp]
     lib.gpsig_trunc_vjp_workspace_bytes.restype = sz
     lib.gpsig_trunc_vjp_workspace_bytes.argtypes = [i] * 6
+    lib.gpsig_trunc_vjp_workspace_bytes_order.restype = sz
+    lib.gpsig_trunc_vjp_workspace_bytes_order.argtypes = [i] * 7
     lib.gpsig_tens_vs_seq_vjp_workspace_bytes.restype = sz
     lib.gpsig_tens_vs_seq_vjp_workspace_bytes.argtypes = [i] * 5
     for sfx in ('f32', 'f64'):

@@ -10,6 +10,7 @@
 #include "trunc_skew_kernel.cuh"
 #include "generic_kernels.cuh"
 #include "lift_mma_kernel.cuh"
+#include "generic_vjp_kernels.cuh"
 
 namespace gpsig {
 
@@ -482,9 +483,11 @@ static int pde_impl(const double* X, int N, int L, const double* Y, int N2, int 
 
 // ---- reverse mode (vjp_kernels.cuh) ---------------------------------------------------------------
 extern "C" size_t gpsig_tens_vs_seq_vjp_workspace_bytes(int Mz, int ncols, int L, int m, int elem);
-static size_t trunc_vjp_ws(size_t npairs, int L, int L2, int m, int difference, int elem) {
+static size_t trunc_vjp_ws(size_t npairs, int L, int L2, int m, int difference, int elem, int order = 1) {
   const size_t PR = L - (difference ? 1 : 0), QC = L2 - (difference ? 1 : 0);
   const size_t mm = m > 1 ? m - 1 : 0;
+  // order > 1 (generic_vjp_kernels.cuh): D, the factor tiles of every level, W
+  if (order > 1) return align_up(npairs * (size_t)(generic_vjp_tiles(m, order) + 2) * PR * QC * elem, 128);
   return align_up(npairs * (mm * PR * QC + mm * QC + PR * QC) * elem, 128);
 }
 
@@ -494,7 +497,6 @@ static int trunc_vjp_impl(const gpsig_trunc_desc* desc, const T* X, int N, int L
                           void* ws, size_t ws_bytes, void* stream) {
   if (int rc = check_desc(desc)) return rc;
   if (desc->base == GPSIG_BASE_SPECTRAL) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "reverse mode is not implemented for the spectral base kernel");
-  if (desc->order != 1) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "reverse mode is implemented for order == 1 only (got %d)", desc->order);
   if (desc->num_levels > 8) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "reverse mode supports num_levels <= 8");
   const bool sym = X2 == nullptr;
   if (sym) { X2 = X; N2 = N; L2 = L; gradX2 = gradX; }
@@ -507,7 +509,7 @@ static int trunc_vjp_impl(const gpsig_trunc_desc* desc, const T* X, int N, int L
   if (diag && (N2 != N || L2 != L)) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "diagonal pairing needs matching X and X2");
   const size_t npairs = diag ? (size_t)(row_end - row_begin) : (size_t)(row_end - row_begin) * N2;
   if (npairs == 0) return GPSIG_OK;
-  const size_t need = trunc_vjp_ws(npairs, L, L2, desc->num_levels, desc->difference, sizeof(T));
+  const size_t need = trunc_vjp_ws(npairs, L, L2, desc->num_levels, desc->difference, sizeof(T), desc->order);
   if (!ws || ws_bytes < need || (reinterpret_cast<uintptr_t>(ws) & 15))
     GPSIG_FAIL(GPSIG_ERR_WORKSPACE, "workspace too small or misaligned: need %zu bytes, got %zu", need, ws_bytes);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
@@ -519,6 +521,28 @@ static int trunc_vjp_impl(const gpsig_trunc_desc* desc, const T* X, int N, int L
   P.g = grad_levels; P.gradX = gradX; P.gradY = gradX2; P.npairs = npairs;
   const size_t PR = L - (desc->difference ? 1 : 0), QC = L2 - (desc->difference ? 1 : 0), mm = desc->num_levels - 1;
   T* w = static_cast<T*>(ws);
+  if (desc->order > 1) {
+    // higher-order recursion: one CTA per pair stores D and the factor tiles, sweeps back and leaves W = dL/dD
+    // (cell-major); the chain into the coordinates is the first-order path's gradient kernel
+    if (QC > 1024) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "order > 1 supports at most 1024 tile columns (L2=%d)", L2);
+    if (npairs > 0x7fffffffull) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "too many pairs in one call (%zu)", npairs);
+    GenericVjpParams G;
+    memset(&G, 0, sizeof(G));
+    G.order = desc->order;
+    G.Dt = w; w += npairs * PR * QC;
+    G.Ft = w; w += npairs * (size_t)generic_vjp_tiles(desc->num_levels, desc->order) * PR * QC;
+    P.W = w; P.w_cell_major = 1;
+    G.V = P;
+    prof_begin(s);
+    trunc_generic_vjp_kernel<T><<<(unsigned)npairs, (unsigned)((QC + 31) / 32 * 32), 0, s>>>(G);
+    prof_end(s);
+    GPSIG_LAUNCH_CHECK("trunc_generic_vjp_kernel");
+    const size_t tot = npairs * (size_t)(L + L2);
+    if (getenv("GPSIG_VJP_NO_GRAD_CTA") == nullptr && launch_trunc_vjp_grad_cta<T>(P, s)) {}
+    else trunc_vjp_grad_warp_kernel<T><<<(unsigned)((tot + 7) / 8), 256, 0, s>>>(P);
+    GPSIG_LAUNCH_CHECK("trunc_vjp_grad_kernel");
+    return GPSIG_OK;
+  }
   P.F = w; w += npairs * mm * PR * QC;
   P.C = w; w += npairs * mm * QC;
   P.W = w;
@@ -548,7 +572,6 @@ static int tens_seq_vjp_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, i
                              void* ws, size_t ws_bytes, void* stream) {
   if (int rc = check_desc(desc)) return rc;
   if (desc->base == GPSIG_BASE_SPECTRAL) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "reverse mode is not implemented for the spectral base kernel");
-  if (desc->order != 1) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "reverse mode is implemented for order == 1 only (got %d)", desc->order);
   if (desc->num_levels > 8) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "reverse mode supports num_levels <= 8");
   if (!Z || !X || !grad_levels || !gradZ || !gradX) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "Z/X/grad_levels/gradZ/gradX must not be NULL");
   if (d < 1) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "bad state dimension d=%d", d);
@@ -566,16 +589,16 @@ static int tens_seq_vjp_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, i
   P.Z = Z; P.X = X; P.Mz = Mz; P.zs = zs; P.N = N; P.L = L; P.d = d; P.m = m;
   P.col_begin = col_begin; P.col_end = col_end; P.difference = desc->difference;
   P.p0 = desc->base_params[0]; P.p1 = desc->base_params[1]; P.base = desc->base;
-  P.g = grad_levels; P.gradZ = gradZ; P.gradX = gradX; P.S = ws; P.npairs = npairs;
+  P.g = grad_levels; P.gradZ = gradZ; P.gradX = gradX; P.S = ws; P.npairs = npairs; P.order = desc->order;
   const int threads = 64;
   const unsigned blocks = (unsigned)((npairs + threads - 1) / threads);
   prof_begin(s);
-  const bool warp_per_seq = getenv("GPSIG_VJP_THREAD") == nullptr && launch_tens_seq_vjp_warp<T>(P, s);
+  const bool warp_per_seq = desc->order == 1 && getenv("GPSIG_VJP_THREAD") == nullptr && launch_tens_seq_vjp_warp<T>(P, s);
   if (warp_per_seq) {}
   else {
     // d > 16: the reverse sweep runs once per chunk of coordinates (per-thread accumulators of dL/dZ: T * zs * chunk <= 1152)
     int chunk = d;
-    if (d > 16) { chunk = 1152 / (TT * zs); if (chunk > kTsvChunk) chunk = kTsvChunk; if (chunk > d) chunk = d; }
+    if (d > 16 || TT * zs * d > 1152) { chunk = 1152 / (TT * zs); if (chunk > kTsvChunk) chunk = kTsvChunk; if (chunk > d) chunk = d; }
     if (chunk < 1) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "reverse mode: too many tensor components for d=%d (num_levels=%d)", d, m);
     for (int k0 = 0; k0 < d; k0 += chunk) {
       P.kc0 = k0; P.kcn = d - k0 < chunk ? d - k0 : chunk;
@@ -687,6 +710,9 @@ int gpsig_tens_vs_seq_f32(const gpsig_trunc_desc* desc, const float* Z, int Mz, 
 
 size_t gpsig_trunc_vjp_workspace_bytes(int npairs, int L, int L2, int m, int difference, int elem) {
   return trunc_vjp_ws((size_t)npairs, L, L2, m, difference, elem);
+}
+size_t gpsig_trunc_vjp_workspace_bytes_order(int npairs, int L, int L2, int m, int order, int difference, int elem) {
+  return trunc_vjp_ws((size_t)npairs, L, L2, m, difference, elem, order);
 }
 size_t gpsig_tens_vs_seq_vjp_workspace_bytes(int Mz, int ncols, int L, int m, int elem) {
   return align_up((size_t)Mz * ncols * (m * (m + 1) / 2) * L * elem, 128);

@@ -665,6 +665,7 @@ struct TensSeqVjpParams {
   void* S;                           // scratch [T, L, npairs]: running sums S_k(l) of the forward recursion
   size_t npairs;
   int kc0, kcn;                      // coordinates [kc0, kc0 + kcn) of this launch (d > 16 runs the reverse sweep in chunks; kcn = 0: all)
+  int order;                         // > 1: higher-order recursion (signature_algs.py:129-160), thread-per-pair kernel only
 };
 
 // Forward (tens_level in tens_kernels.cuh): within level I, components jj = 0..I-1 (global index k),
@@ -694,7 +695,37 @@ __global__ void tens_seq_vjp_kernel(const TensSeqVjpParams P) {
   const int l0 = diff ? 1 : 0;                                       // first time index that carries a D
   const int kc0 = P.kcn > 0 ? P.kc0 : 0, kcn = P.kcn > 0 ? P.kcn : d;
   // ---- forward: store S_k(l) (first chunk only: the scratch persists across the launches of one call) ----------
-  if (kc0 == 0) {
+  const int order = P.order > 1 ? P.order : 1;
+  if (kc0 == 0 && order > 1) {
+    // higher order (signature_algs.py:140-158): component jj of a level carries a family cur[jj][0..min(jj+1,order)-1];
+    // stored: S_k(l) = sum over EARLIER times of the component's family total (what cur[jj+1][0] multiplies, :153)
+    T Sv[36], Mprev[36];
+    for (int k = 0; k < TT; ++k) { Sv[k] = T(0); Mprev[k] = T(0); }
+    for (int l = 0; l < L; ++l) {
+      for (int k = 0; k < TT; ++k) Sat(k, l) = Sv[k];
+      int k0 = 0;
+      for (int I = 1; I <= m; ++I) {
+        T cur[8][8];
+        for (int jj = 0; jj < I; ++jj) {
+          const int k = k0 + jj;
+          const T mt = Mt(k, l);
+          T D = mt;
+          if (diff) { D = mt - Mprev[k]; Mprev[k] = mt; }
+          if (l < l0) continue;
+          const int dj = min(jj + 1, order);
+          cur[jj][0] = jj == 0 ? D : D * Sat(k - 1, l);
+          for (int c = 1; c < dj; ++c) cur[jj][c] = D * cur[jj - 1][c - 1] / T(c + 1);              // :155
+        }
+        if (l >= l0)
+          for (int jj = 0; jj + 1 < I; ++jj) {
+            T sm = T(0);
+            for (int c = 0; c < min(jj + 1, order); ++c) sm += cur[jj][c];
+            Sv[k0 + jj] += sm;
+          }
+        k0 += I;
+      }
+    }
+  } else if (kc0 == 0) {
     T Sv[36], Mprev[36];
     for (int k = 0; k < TT; ++k) { Sv[k] = T(0); Mprev[k] = T(0); }
     for (int l = 0; l < L; ++l) {
@@ -720,17 +751,49 @@ __global__ void tens_seq_vjp_kernel(const TensSeqVjpParams P) {
     int k0 = 0;
     for (int I = 1; I <= m; ++I) { lam[k0 + I - 1] = static_cast<const T*>(P.g)[((size_t)I * P.Mz + z) * ncols + nl]; k0 += I; }
   }
+  T Aacc[36];                                                       // order > 1: adjoint of S_k, summed over LATER times
+  for (int k = 0; k < TT; ++k) Aacc[k] = T(0);
   for (int l = L - 1; l >= 0; --l) {
     const T* xl = x + (size_t)l * d;
     T gx[kTsvChunk];
     for (int q = 0; q < kcn; ++q) gx[q] = T(0);
+    T aDk[36];
+    if (order > 1) {
+      int kq = 0;
+      for (int I = 1; I <= m; ++I) {
+        if (l < l0) { for (int jj = 0; jj < I; ++jj) aDk[kq + jj] = T(0); kq += I; continue; }
+        const T gI = static_cast<const T*>(P.g)[((size_t)I * P.Mz + z) * ncols + nl];
+        T Dl[8], cur[8][8], cb[8][8];
+        for (int jj = 0; jj < I; ++jj) Dl[jj] = diff ? Mt(kq + jj, l) - Mt(kq + jj, l - 1) : Mt(kq + jj, l);
+        for (int jj = 0; jj < I; ++jj) {                              // the forward families at this time, from the stored sums
+          const int dj = min(jj + 1, order);
+          cur[jj][0] = jj == 0 ? Dl[0] : Dl[jj] * Sat(kq + jj - 1, l);
+          for (int c = 1; c < dj; ++c) cur[jj][c] = Dl[jj] * cur[jj - 1][c - 1] / T(c + 1);
+        }
+        for (int jj = I - 1; jj >= 0; --jj) {
+          const int dj = min(jj + 1, order);
+          const T sbar = jj == I - 1 ? gI : Aacc[kq + jj];
+          for (int c = 0; c < dj; ++c) {
+            T v = sbar;
+            if (jj + 1 < I && c + 1 < min(jj + 2, order)) v += cb[jj + 1][c + 1] * Dl[jj + 1] / T(c + 2);
+            cb[jj][c] = v;
+          }
+          T aD = jj == 0 ? cb[0][0] : cb[jj][0] * Sat(kq + jj - 1, l);
+          for (int c = 1; c < dj; ++c) aD += cb[jj][c] * cur[jj - 1][c - 1] / T(c + 1);
+          aDk[kq + jj] = aD;
+        }
+        for (int jj = 1; jj < I; ++jj) Aacc[kq + jj - 1] += cb[jj][0] * Dl[jj];
+        kq += I;
+      }
+    }
     int k0 = 0;
     for (int I = 1; I <= m; ++I) {
       for (int jj = 0; jj < I; ++jj) {
         const int k = k0 + jj;
         // adjoint of D_k(l) (zero where the forward skipped the update)
         T aD = T(0);
-        if (l >= l0) {
+        if (order > 1) aD = aDk[k];
+        else if (l >= l0) {
           const T Sprev = jj > 0 ? (l > 0 ? Sat(k - 1, l - 1) : T(0)) : T(1);
           aD = lam[k] * Sprev;
         }
@@ -755,7 +818,7 @@ __global__ void tens_seq_vjp_kernel(const TensSeqVjpParams P) {
       k0 += I;
     }
     // propagate lam to time l-1 (needs D_k(l), highest component first within a level)
-    if (l >= l0) {
+    if (order == 1 && l >= l0) {
       k0 = 0;
       for (int I = 1; I <= m; ++I) {
         for (int jj = 1; jj < I; ++jj) {

@@ -223,7 +223,7 @@ class SignatureKernel:
     # parameter is a torch tensor that requires grad, the methods below route through the CUDA ops'
     # hand-written adjoints (gpsig_b200/autograd.py -> csrc/vjp_kernels.cuh); scaling, normalisation and
     # the sigma * variances weighting are the same formulas written as differentiable torch expressions.
-    # order == 1 only (the adjoints of the higher-order recursion are not built).
+    # Any order (order > 1: the general adjoint kernels, csrc/generic_vjp_kernels.cuh); not the spectral base kernel.
     def _wants_grad(self, *tensors):
         if not torch.is_grad_enabled():
             return False
@@ -236,8 +236,7 @@ class SignatureKernel:
         return self._param(value, like)
 
     def _d_check(self):
-        if self.order != 1:
-            raise NotImplementedError('gpsig_b200: gradients are implemented for order == 1 only')
+        pass
 
     def _d_seq(self, X):
         X = X.reshape(X.shape[0], -1, self.num_features)
@@ -264,8 +263,11 @@ class SignatureKernel:
         sigma = self.sigma if torch.is_tensor(self.sigma) else float(self.sigma)
         return sigma * self._tparam(self.variances, like).reshape(-1)
 
-    def _d_bk(self):
-        return dict(base=self._base, base_params=self._get_base_params())
+    def _d_bk(self, order=True):
+        kw = dict(base=self._base, base_params=self._get_base_params())
+        if order:
+            kw['order'] = self.order
+        return kw
 
     def _d_gram(self, Xs, X2s, return_levels):
         """Differentiable K(X, X2) from scaled sequences (kernels.py:431-477)."""
@@ -303,13 +305,13 @@ class SignatureKernel:
                 st.wait_stream(cur)
             with torch.cuda.stream(side[0]):
                 Zs.record_stream(side[0]); sc.record_stream(side[0])
-                out['zz'] = ag.tens_tens_levels(Zs, m, increments=increments, **self._d_bk()) * sc[:, None, None]
+                out['zz'] = ag.tens_tens_levels(Zs, m, increments=increments, **self._d_bk(order=False)) * sc[:, None, None]
             with torch.cuda.stream(side[1]):
                 Xs.record_stream(side[1])
                 diag = ag.trunc_diag_levels(Xs, m, difference=self.difference, **self._d_bk())
         else:
             if 'zz' in want:
-                out['zz'] = ag.tens_tens_levels(Zs, m, increments=increments, **self._d_bk()) * sc[:, None, None]
+                out['zz'] = ag.tens_tens_levels(Zs, m, increments=increments, **self._d_bk(order=False)) * sc[:, None, None]
             if want_diag:
                 diag = ag.trunc_diag_levels(Xs, m, difference=self.difference, **self._d_bk())
         if 'zx' in want:

@@ -165,7 +165,7 @@ def pde(X, Y=None, dyadic_order=0, gram=False, lengthscales=None, sigma=1.0, row
 _VJP_WS_BYTES = 4 << 30      # scratch budget of one trunc_vjp launch; larger problems are chunked over rows
 
 
-def trunc_vjp(X, X2, grad_levels, num_levels, base='linear', base_params=(), difference=True, diag=False):
+def trunc_vjp(X, X2, grad_levels, num_levels, base='linear', base_params=(), difference=True, diag=False, order=1):
     """dL/dX, dL/dX2 of the raw levels of ``trunc_gram`` (``diag=False``, grad_levels [m+1, N, N2]) or
     ``trunc_diag`` (``diag=True``, grad_levels [m+1, N]).  X, X2 are the coordinates the forward was called
     with (already scaled).  Returns (gradX, gradX2) (gradX2 is None when X2 is None)."""
@@ -177,23 +177,24 @@ def trunc_vjp(X, X2, grad_levels, num_levels, base='linear', base_params=(), dif
     m = int(num_levels)
     gradX = torch.zeros_like(X)
     gradX2 = None if X2 is None else torch.zeros_like(X2)
-    desc = make_desc(base, m, 1, difference, base_params)
+    order = max(1, min(int(order), m))
+    desc = make_desc(base, m, order, difference, base_params)
     esz = X.element_size()
     fn = getattr(lib, 'gpsig_trunc_vjp_' + sfx(X.dtype))
     per_row = 1 if diag else N2
-    rows_per_call = max(1, int(_VJP_WS_BYTES // max(1, lib.gpsig_trunc_vjp_workspace_bytes(per_row, L, L2, m, int(difference), esz))))
+    rows_per_call = max(1, int(_VJP_WS_BYTES // max(1, lib.gpsig_trunc_vjp_workspace_bytes_order(per_row, L, L2, m, order, int(difference), esz))))
     with torch.cuda.device(X.device):
         for rb in range(0, N, rows_per_call):
             re = min(N, rb + rows_per_call)
             g = grad_levels[:, rb:re].contiguous()
-            wsb = lib.gpsig_trunc_vjp_workspace_bytes((re - rb) * per_row, L, L2, m, int(difference), esz)
+            wsb = lib.gpsig_trunc_vjp_workspace_bytes_order((re - rb) * per_row, L, L2, m, order, int(difference), esz)
             ws = workspace(wsb, X.device)
             check(fn(desc, ptr(X), N, L, ptr(X2), N2, L2, d, _lib.PDE_DIAG if diag else _lib.PDE_GRAM, rb, re, ptr(g),
                      ptr(gradX), ptr(gradX2), ptr(ws), wsb, stream_handle(X.device)))
     return gradX, gradX2
 
 
-def tens_vs_seq_vjp(Z, X, grad_levels, num_levels, increments=False, base='linear', base_params=(), difference=True):
+def tens_vs_seq_vjp(Z, X, grad_levels, num_levels, increments=False, base='linear', base_params=(), difference=True, order=1):
     """dL/dZ, dL/dX of the raw levels [m+1, Mz, N] of ``tens_vs_seq``."""
     require_cuda(X, 'X')
     _same(Z, X, 'Z')
@@ -202,7 +203,7 @@ def tens_vs_seq_vjp(Z, X, grad_levels, num_levels, increments=False, base='linea
     m = int(num_levels)
     Mz = Z.shape[1]
     gradZ, gradX = torch.zeros_like(Z), torch.zeros_like(X)
-    desc = make_desc(base, m, 1, difference, base_params)
+    desc = make_desc(base, m, max(1, min(int(order), m)), difference, base_params)
     esz = X.element_size()
     fn = getattr(lib, 'gpsig_tens_vs_seq_vjp_' + sfx(X.dtype))
     cols_per_call = max(1, int(_VJP_WS_BYTES // max(1, lib.gpsig_tens_vs_seq_vjp_workspace_bytes(Mz, 1, L, m, esz))))

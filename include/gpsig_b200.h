@@ -166,8 +166,12 @@ int gpsig_tens_tens_f32(const gpsig_trunc_desc* desc, const float* Z, int Mz, in
  *   gradX / gradX2 / gradZ: same shapes as X / X2 / Z.  gradX, gradX2 are ACCUMULATED into (zero them first);
  *   X2 == NULL: symmetric case, both roles accumulate into gradX.  gpsig_tens_tens_vjp overwrites gradZ.
  * pair_mode: GPSIG_PDE_GRAM = rows [row_begin,row_end) x all N2 columns; GPSIG_PDE_DIAG = pairs (i, i).
- * order must be 1; num_levels <= 8. */
+ * num_levels <= 8.  order > 1 (signature_algs.py:37-74, :129-160): gpsig_trunc_vjp_* and gpsig_tens_vs_seq_vjp_* run the
+ * general adjoint kernels (generic_vjp_kernels.cuh); gpsig_tens_tens_* does not depend on the order. */
 size_t gpsig_trunc_vjp_workspace_bytes(int npairs, int L, int L2, int num_levels, int difference, int elem_size);
+/* the same for any `order` (order > 1: the higher-order recursion of signature_algs.py:37-74 stores its per-level factor
+ * tiles; order == 1 equals the function above) */
+size_t gpsig_trunc_vjp_workspace_bytes_order(int npairs, int L, int L2, int num_levels, int order, int difference, int elem_size);
 int gpsig_trunc_vjp_f64(const gpsig_trunc_desc* desc, const double* X, int N, int L, const double* X2, int N2, int L2,
                         int d, int pair_mode, int row_begin, int row_end, const double* grad_levels,
                         double* gradX, double* gradX2, void* workspace, size_t workspace_bytes, void* stream);

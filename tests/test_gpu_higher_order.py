@@ -115,3 +115,72 @@ def test_golden_fixtures_first_order(dtype):
                 Kzz, Kzx, Kxx = k.K_tens_n_seq_covs(_dev(g['Z_inc%d' % inc], dtype), Xd, return_levels=True, increments=bool(inc))
                 assert rel_err(Kzx.cpu().numpy(), g['Kzx_%s_i%d' % (tag, inc)]) < TOL[dtype]
                 assert rel_err(Kzz.cpu().numpy(), g['Kzz_%s_i%d' % (tag, inc)]) < TOL[dtype]
+
+
+@pytest.mark.parametrize("base", ['linear', 'rbf'])
+@pytest.mark.parametrize("m,order", [(2, 2), (3, 2), (4, 4), (5, 3)])
+@pytest.mark.parametrize("difference", [True, False])
+def test_higher_order_reverse_mode(base, m, order, difference):
+    """Adjoints of the higher-order recursion (csrc/generic_vjp_kernels.cuh; the reference gets them from TF autodiff of
+    signature_algs.py:37-74, 129-160): vector-Jacobian identity against central differences of the oracle's raw levels,
+    for Gram pairs, diagonal pairs and tensors vs sequences (with and without increments)."""
+    import torch
+    from gpsig_b200 import ops
+    from oracle.trunc_np import SignatureKernelOracle
+    from tests.util import brownian, inducing_tensors
+    EPS, TOLV = 1e-5, 2e-6
+    N, N2, L, L2, d, Mz = 4, 3, 8, 7, 3, 4
+    rng = np.random.default_rng(9)
+    X, Y = brownian(N, L, d, 0) + 0.3, brownian(N2, L2, d, 1) - 0.2
+    o = SignatureKernelOracle(L * d, d, m, base=base, lengthscales=None, normalization=False, order=order, difference=difference)
+    dev = lambda a: torch.as_tensor(np.ascontiguousarray(a), dtype=torch.float64, device='cuda')  # noqa: E731
+
+    def check(nm, a, f):
+        assert abs(a - f) <= TOLV * max(abs(f), abs(a), 1e-12) + 1e-9, (nm, a, f)
+
+    G = rng.standard_normal((m + 1, N, N2))
+    VX, VY = rng.standard_normal(X.shape), rng.standard_normal(Y.shape)
+    gX, gY = ops.trunc_vjp(dev(X), dev(Y), dev(G), m, base=base, order=order, difference=difference)
+    f = lambda A, B: float(np.sum(G * o._K_seq(A, B)))  # noqa: E731
+    check('X', float((gX.cpu().numpy() * VX).sum()), (f(X + EPS * VX, Y) - f(X - EPS * VX, Y)) / (2 * EPS))
+    check('X2', float((gY.cpu().numpy() * VY).sum()), (f(X, Y + EPS * VY) - f(X, Y - EPS * VY)) / (2 * EPS))
+    Gd = rng.standard_normal((m + 1, N))
+    gX, _ = ops.trunc_vjp(dev(X), None, dev(Gd), m, base=base, order=order, difference=difference, diag=True)
+    f = lambda A: float(np.sum(Gd * o._K_seq_diag(A)))  # noqa: E731
+    check('diag', float((gX.cpu().numpy() * VX).sum()), (f(X + EPS * VX) - f(X - EPS * VX)) / (2 * EPS))
+    for increments in (False, True):
+        Z = inducing_tensors(X, m, Mz, increments, 2)
+        VZ = rng.standard_normal(Z.shape)
+        Gz = rng.standard_normal((m + 1, Mz, N))
+        gZ, gX = ops.tens_vs_seq_vjp(dev(Z), dev(X), dev(Gz), m, increments=increments, base=base, order=order, difference=difference)
+        f = lambda A, B: float(np.sum(Gz * o._K_tens_vs_seq(A, B, increments=increments)))  # noqa: E731
+        check('Z', float((gZ.cpu().numpy() * VZ).sum()), (f(Z + EPS * VZ, X) - f(Z - EPS * VZ, X)) / (2 * EPS))
+        check('Xz', float((gX.cpu().numpy() * VX).sum()), (f(Z, X + EPS * VX) - f(Z, X - EPS * VX)) / (2 * EPS))
+
+
+def test_higher_order_kernel_trains():
+    """order = num_levels (what train_gpsig_.py:62 / train_gpsig_vosf.py:102 use) through the kernel classes under
+    autograd: gradient of a scalar of K_tens_n_seq_covs w.r.t. the lengthscales against central differences of the same
+    CUDA forward."""
+    import torch
+    from gpsig_b200 import kernels
+    from tests.util import brownian, inducing_tensors
+    N, L, d, m, Mz = 6, 12, 3, 3, 4
+    X = brownian(N, L, d, 0)
+    Xt = torch.as_tensor(X.reshape(N, -1), dtype=torch.float64, device='cuda')
+    Z = torch.as_tensor(inducing_tensors(X, m, Mz, True, 5), dtype=torch.float64, device='cuda')
+
+    def loss(ls):
+        k = kernels.SignatureRBF(L * d, d, m, order=m)
+        k.lengthscales = ls
+        Kzz, Kzx, Kxx = k.K_tens_n_seq_covs(Z, Xt, increments=True)
+        return (Kzz * Kzz).sum() + Kzx.sum() + (Kxx * Kxx).sum()
+
+    ls = torch.nn.Parameter(torch.tensor([1.1, 0.9, 1.3], dtype=torch.float64, device='cuda'))
+    loss(ls).backward()
+    g = ls.grad.clone()
+    for i in range(d):
+        e = torch.zeros(d, dtype=torch.float64, device='cuda'); e[i] = 1e-6
+        with torch.no_grad():
+            fd = (loss(ls.detach() + e) - loss(ls.detach() - e)) / 2e-6
+        assert abs(float(g[i]) - float(fd)) <= 1e-5 * max(abs(float(fd)), 1e-8), (i, float(g[i]), float(fd))

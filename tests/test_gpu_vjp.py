@@ -144,17 +144,25 @@ def test_autograd_end_to_end_float32_and_64():
     assert torch.allclose(ls32.grad.double(), ls64.grad, rtol=2e-3, atol=1e-3)
 
 
-def test_vjp_rejects_higher_order():
-    from gpsig_b200 import _lib, ops
+def test_vjp_rejects_what_is_not_built():
+    """Status codes at the C ABI: a workspace that is too small (-3), the spectral base kernel (-2: its adjoint is not
+    written).  order > 1 is served by the general adjoint kernels (tests/test_gpu_higher_order.py)."""
+    from gpsig_b200 import _lib
     X = _dev(brownian(3, 5, 2, 0))
     G = torch.zeros(4, 3, 3, dtype=torch.float64, device='cuda')
-    desc = _lib.make_desc('linear', 3, 2, True)
     gX = torch.zeros_like(X)
     ws = _lib.workspace(1 << 20, X.device)
+    desc = _lib.make_desc('linear', 3, 2, True)
+    rc = _lib.lib.gpsig_trunc_vjp_f64(desc, _lib.ptr(X), 3, 5, None, 3, 5, 2, _lib.PDE_GRAM, 0, 3, _lib.ptr(G), _lib.ptr(gX), None,
+                                      _lib.ptr(ws), 64, _lib.stream_handle(X.device))
+    assert rc == -3
     rc = _lib.lib.gpsig_trunc_vjp_f64(desc, _lib.ptr(X), 3, 5, None, 3, 5, 2, _lib.PDE_GRAM, 0, 3, _lib.ptr(G), _lib.ptr(gX), None,
                                       _lib.ptr(ws), 1 << 20, _lib.stream_handle(X.device))
-    assert rc == -2
-    assert ops is not None
+    assert rc == 0
+    desc.base = 8                                     # GPSIG_BASE_SPECTRAL
+    rc = _lib.lib.gpsig_trunc_vjp_f64(desc, _lib.ptr(X), 3, 5, None, 3, 5, 2, _lib.PDE_GRAM, 0, 3, _lib.ptr(G), _lib.ptr(gX), None,
+                                      _lib.ptr(ws), 1 << 20, _lib.stream_handle(X.device))
+    assert rc in (-1, -2)
 
 
 @pytest.mark.parametrize("normalization", [False, True])
