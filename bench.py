@@ -159,8 +159,11 @@ def measured_peaks():
 
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the headline kernel at the bench shape (c2), from the
 # committed ncu --set full captures (algorithmic bytes: 83.2 MB f64 / 41.6 MB f32 per launch)
-NCU_TRAFFIC_BYTES = {"f64": 76.51e6 + 21.26e6, "f32": 41.83e6 + 0.67e6}
-NCU_TRAFFIC_SOURCE = "profiles/r01e_ncu_trunc_skew_f64.txt, profiles/r01f_ncu_trunc_skew_f32.txt (ncu --set full, N=N2=2000; the 16-32 MB output still sits in L2 when the kernel ends)"
+NCU_TRAFFIC_BYTES = {"f64": 79.60e6 + 21.56e6, "f32": 41.73e6 + 1.15e6}
+# the slab launch of the headline step (rank 0's 2000 rows x 20000 columns, float64): dram read + write of that one launch
+NCU_TRAFFIC_SLAB_F64 = 811917312 + 323673600
+NCU_TRAFFIC_SLAB_SOURCE = "profiles/r02k_slab_traffic.csv (ncu dram__bytes_read.sum + dram__bytes_write.sum of the slab launch at N=1: 0.81 GB read, 0.32 GB written, against 0.60 GB algorithmic; the x rows are re-streamed from L2 by every CTA)"
+NCU_TRAFFIC_SOURCE = "profiles/r02k_ncu_trunc_skew_f64.txt, profiles/r02k_ncu_trunc_skew_f32.txt (ncu --set full, N=N2=2000 = c2; per launch of the slab step multiply by 10: 20000 columns; the 16-32 MB output still sits in L2 when the kernel ends)"
 
 
 def fma_peak_tflops(torch, lib, esz):
@@ -512,7 +515,9 @@ def run_ours(args):
         step_ms = tot_ms / args.steps
         roof = {"bound": "cuda-core-" + args.dtype, "achieved": achieved, "peak": fpeak, "unit": "TFLOP/s",
                 "frac": (achieved / fpeak) if (achieved and fpeak) else None,
-                "traffic": NCU_TRAFFIC_BYTES.get(args.dtype), "traffic_source": NCU_TRAFFIC_SOURCE,
+                "traffic": (NCU_TRAFFIC_SLAB_F64 if (args.dtype == 'f64' and world == 1) else None),
+                "traffic_source": NCU_TRAFFIC_SLAB_SOURCE if (args.dtype == 'f64' and world == 1) else None,
+                "algorithmic_bytes_per_launch": pairs_launch * Bp,
                 "peak_source": "FMA-chain microbenchmark in this run (gpsig_fma_peak); nominal %.1f TFLOP/s at 1965 MHz" % nominal,
                 "frac_of_nominal": achieved / nominal if achieved else None,
                 "kernel": "trunc_skew_kernel", "kernel_ms": kern_ms, "kernel_share_of_step": kern_ms / step_ms if kern_ms else None,
