@@ -76,6 +76,13 @@ __host__ __device__ inline int skew_row_stride(int d, int elem, bool dup = false
 #ifndef GPSIG_SKEW_EXP2
 #define GPSIG_SKEW_EXP2 1
 #endif
+// float64 RBF: exp2 with a 2048-entry shared-memory table and a degree-3 polynomial (7 FP64 instructions, common.cuh)
+// instead of the 32-entry shuffle table and degree 5 (9)
+#ifndef GPSIG_SKEW_EXP2_T2048
+#define GPSIG_SKEW_EXP2_T2048 1
+#endif
+constexpr size_t kSkewExpTableBytes = 2048 * sizeof(double);
+template <typename T, int OP> struct SkewExpTable { static constexpr bool value = GPSIG_SKEW_EXP2 && GPSIG_SKEW_EXP2_T2048 && sizeof(T) == 8 && OP == OP_RBF; };
 
 // ---- tensor memory as per-lane storage (PTX tcgen05.alloc / st / ld) ---------
 __device__ __forceinline__ uint32_t tmem_alloc(uint32_t* slot, int ncols) {    // whole CTA; warp 0 allocates
@@ -218,7 +225,9 @@ template <typename T, int OP> struct SkewFinish {
 };
 template <> struct SkewFinish<double, OP_RBF> {
   static __device__ __forceinline__ double apply(double acc, double, double, int, double, double, double tab) {
-#if GPSIG_SKEW_EXP2
+#if GPSIG_SKEW_EXP2 && GPSIG_SKEW_EXP2_T2048
+    return exp2_tab2048(acc, (uint32_t)__double2loint(tab));      // `tab` carries the table's shared-memory address
+#elif GPSIG_SKEW_EXP2
     return exp2_tab32(acc, tab);
 #else
     return exp_tab32(acc, tab);
@@ -269,6 +278,9 @@ template <> struct SkewFinish<float, OP_RBF> {
     return r;
   }
 };
+
+template <typename T, int DP, int COLS>
+constexpr size_t skew_ywarp_bytes() { return SkewYTmem<T, DP, COLS>::value ? 0 : trunc_ywarp_bytes<T, DP, COLS>(); }
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
@@ -377,6 +389,13 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
   }
   double tab = 0.0;
   if (OP == OP_RBF && sizeof(T) == 8) tab = exp2((double)lane * (1.0 / 32.0));
+  if constexpr (SkewExpTable<T, OP>::value) {
+    // 2^(j/2048), j = 0..2047, behind the x ring and the y tiles; the address travels in the low word of `tab`
+    double* etab = reinterpret_cast<double*>(xring + NB * xslot + (size_t)NW * skew_ywarp_bytes<T, DP, COLS>());
+    for (int e = threadIdx.x; e < 2048; e += NW * 32) etab[e] = exp2((double)e * (1.0 / 2048.0));
+    __syncthreads();
+    tab = __hiloint2double(0, (int)smem_u32(etab));
+  }
 
   // ---- state ------------------------------------------------------------------------
   // column sums C_l[q] of levels 0..MLEV-2; of the top level only the total is ever used: partial sums
@@ -731,8 +750,6 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
 // ---------------------------------------------------------------------------
 // Shapes this kernel takes (the rest runs trunc_gram_kernel): one column pass, rows long
 // enough (>= 32 steps per pair) that a lane-skewed warp touches at most two consecutive pairs.
-template <typename T, int DP, int COLS>
-constexpr size_t skew_ywarp_bytes() { return SkewYTmem<T, DP, COLS>::value ? 0 : trunc_ywarp_bytes<T, DP, COLS>(); }
 
 inline bool skew_eligible(int L, int L2, int elem) { return L >= 32 * (elem == 8 ? GPSIG_SKEW_R_F64 : GPSIG_SKEW_R_F32) + 1 && L2 <= 256; }
 
@@ -740,7 +757,8 @@ template <typename T, int DP, int COLS, int MLEV, int OP>
 int launch_skew_inst(TruncParams P, cudaStream_t stream) {
   const int RS = P.xrs;
   const size_t xslot = align_up_dev(P.xblk * sizeof(T));
-  const size_t smem = 128 + kSkewBufs * xslot + (size_t)SkewNW<T, DP, COLS>::value * skew_ywarp_bytes<T, DP, COLS>();
+  const size_t smem = 128 + kSkewBufs * xslot + (size_t)SkewNW<T, DP, COLS>::value * skew_ywarp_bytes<T, DP, COLS>() +
+                      (SkewExpTable<T, OP>::value ? kSkewExpTableBytes : 0);
   if (smem > kMaxSmem)
     GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "sequence too long for the on-chip plan: needs %zu bytes of shared memory (L=%d)", smem, P.L);
   auto kern = trunc_skew_kernel<T, DP, COLS, MLEV, OP>;
