@@ -46,6 +46,11 @@ struct TensSeqParams {
 template <typename T> struct TensExp2;
 template <> struct TensExp2<double> { static __device__ __forceinline__ double ex(double t, double tab) { return exp2_tab32(t, tab); } };
 template <> struct TensExp2<float> { static __device__ __forceinline__ float ex(float t, double) { return exp2_approx(t); } };
+// register-resident kernel (tens_vs_seq_kernel2): float64 exp2 from the 2048-entry shared-memory table (7 FP64 instructions
+// instead of 9; `tab` carries the table's shared-memory address in its low word)
+template <typename T> struct TensExp2T;
+template <> struct TensExp2T<double> { static __device__ __forceinline__ double ex(double t, double tab) { return exp2_tab2048(t, (uint32_t)__double2loint(tab)); } };
+template <> struct TensExp2T<float> { static __device__ __forceinline__ float ex(float t, double) { return exp2_approx(t); } };
 
 template <typename T, int DP, int OP, int I>
 __device__ __forceinline__ T tens_level(const T* zc, const T* zq, int zs, const T* xblk, const T* xsq, int L,
@@ -173,7 +178,7 @@ __device__ __forceinline__ T tens2_level(const T (&zr)[I * ZS * DP], const T (&z
 #pragma unroll
       for (int k = 0; k < DP; ++k) acc = gfma<T>(zr[e * DP + k], xv[k], acc);
       if (OP == OP_GENERIC) return base_eval_call<T>(base, p0, p1, acc, zq[e], xc);
-      if (OP == OP_RBF) return TensExp2<T>::ex(acc, tab);
+      if (OP == OP_RBF) return TensExp2T<T>::ex(acc, tab);
       return Op::finish(acc, zq[e], xc, base, p0, p1);
     };
     const bool first = difference && l == 0;
@@ -206,17 +211,23 @@ __global__ void __launch_bounds__(kTens2Warps * 32) tens_vs_seq_kernel2(const Te
   T* tile = reinterpret_cast<T*>(xbuf + 2 * xslot);                            // [CH][ZB + 1]
   const int lane = threadIdx.x & 31;
   const int m = P.m;
+  constexpr bool ETAB = sizeof(T) == 8 && OP == OP_RBF;                        // 2^(j/2048) table behind the tile
   const int ncols = P.col_end - P.col_begin;
   const int c0 = blockIdx.x * CH, nseq = min(CH, ncols - c0);                  // this CTA's sequences (local column indices)
   const int zraw = blockIdx.y * ZB + threadIdx.x;
   const bool zlive = zraw < P.Mz;
   const int z = zlive ? zraw : P.Mz - 1;                                       // clamped: the warp stays convergent (table shuffle)
-  const double tab = exp2((double)lane * (1.0 / 32.0));
+  double tab = exp2((double)lane * (1.0 / 32.0));
   const T p0 = T(P.p0), p1 = T(P.p1);
   const bool diff = P.difference != 0;
   const T* xg = static_cast<const T*>(P.xp) + (size_t)(P.col_begin + c0) * P.xblk;
 
   if (threadIdx.x == 0) { mbar_init(&full[0], 1); mbar_init(&full[1], 1); fence_mbar_init(); }
+  if constexpr (ETAB) {
+    double* etab = reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(tile) + (((size_t)CH * (ZB + 1) * sizeof(T) + 15) & ~(size_t)15));
+    for (int e = threadIdx.x; e < 2048; e += ZB) etab[e] = exp2((double)e * (1.0 / 2048.0));
+    tab = __hiloint2double(0, (int)smem_u32(etab));
+  }
   __syncthreads();
   const int nitems = m * nseq;                                                 // (level, sequence) items, level-major
   if (threadIdx.x == 0 && nitems > 0) { mbar_expect_tx(&full[0], (uint32_t)xbytes); tma_load_1d(xbuf, xg, (uint32_t)xbytes, &full[0]); }
@@ -294,8 +305,9 @@ int launch_tens2(const TensSeqParams& P, cudaStream_t stream) {
   const int zblocks = (P.Mz + kTens2Warps * 32 - 1) / (kTens2Warps * 32);
   int ch = (int)((long)ncols * zblocks / (2 * 148));                              // at least two CTAs per SM before a CTA takes a second sequence
   ch = ch < 1 ? 1 : (ch > kTens2Chunk ? kTens2Chunk : ch);
-  const size_t smem = 128 + 2 * xslot + (size_t)ch * (kTens2Warps * 32 + 1) * sizeof(T);
-  if (128 + 2 * xslot + (size_t)kTens2Chunk * (kTens2Warps * 32 + 1) * sizeof(T) > kTens2MaxSmem) return -100;                                           // caller falls back to tens_vs_seq_kernel
+  const size_t etab = (sizeof(T) == 8 && OP == OP_RBF) ? 2048 * sizeof(double) + 16 : 0;
+  const size_t smem = 128 + 2 * xslot + (size_t)ch * (kTens2Warps * 32 + 1) * sizeof(T) + etab;
+  if (128 + 2 * xslot + (size_t)kTens2Chunk * (kTens2Warps * 32 + 1) * sizeof(T) + etab > kTens2MaxSmem) return -100;                                           // caller falls back to tens_vs_seq_kernel
   auto kern = tens_vs_seq_kernel2<T, DP, OP, ZS, MMAX>;
   GPSIG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid((ncols + ch - 1) / ch, zblocks);
