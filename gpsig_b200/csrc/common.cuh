@@ -160,9 +160,16 @@ __device__ __forceinline__ double exp2_tab32(double t, double tab_lane) {
 
 // The same with a 2048-entry table 2^(j/2048) in SHARED memory (16 KB per CTA, one LDS.64 per call instead of two
 // shuffles) and a degree-3 polynomial (|f| <= 2^-12: truncation 3.4e-17): 7 FP64-pipe instructions.
+// in-place update of the high word of a double (sign / exponent / top mantissa bits): written so that ptxas keeps the
+// register pair where it is instead of assembling a new one with two moves
+__device__ __forceinline__ void hi_min_u32(double& v, unsigned cap) {
+  asm("{\n\t.reg .b32 lo, hi;\n\tmov.b64 {lo, hi}, %0;\n\tmin.u32 hi, hi, %1;\n\tmov.b64 %0, {lo, hi};\n\t}" : "+d"(v) : "r"(cap));
+}
+__device__ __forceinline__ void hi_mad(double& v, int k, int scale) {      // hi += k * scale
+  asm("{\n\t.reg .b32 lo, hi;\n\tmov.b64 {lo, hi}, %0;\n\tmad.lo.s32 hi, %1, %2, hi;\n\tmov.b64 %0, {lo, hi};\n\t}" : "+d"(v) : "r"(k), "r"(scale));
+}
 __device__ __forceinline__ double exp2_tab2048(double t, uint32_t table_smem) {
-  const unsigned hi = min((unsigned)__double2hiint(t), 0xC08FE800u);
-  t = __hiloint2double((int)hi, __double2loint(t));
+  hi_min_u32(t, 0xC08FE800u);                                       // t >= -1021 (integer min on the sign/exponent word)
   const double s = t + 0x1.8p+41;                                   // ulp = 2^-11
   const int n = __double2loint(s);
   const double f = t - (s - 0x1.8p+41);
@@ -171,8 +178,9 @@ __device__ __forceinline__ double exp2_tab2048(double t, uint32_t table_smem) {
   double q = fma(0x1.c6b08d704a0c0p-5, f, 0x1.ebfbdff82c58fp-3);     // (ln 2)^3 / 6, (ln 2)^2 / 2
   q = fma(q, f, 0x1.62e42fefa39efp-1);                              // ln 2
   const double w = q * f;
-  const double res = fma(tj, w, tj);
-  return __hiloint2double(__double2hiint(res) + ((n >> 11) << 20), __double2loint(res));
+  double res = fma(tj, w, tj);
+  hi_mad(res, n >> 11, 1 << 20);                                    // * 2^(n >> 11): exponent-field add
+  return res;
 }
 
 __device__ __forceinline__ float exp2_approx(float t) {
