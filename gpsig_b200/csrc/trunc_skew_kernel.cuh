@@ -308,7 +308,9 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(skew_smem);       // [NB]
   uint64_t* empty_bar = full_bar + NB;                               // [NB]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const bool diff = P.difference != 0;
+  // the systolic kernel is built for the differenced tile only (difference = False, a non-default option, runs
+  // trunc_gram_kernel): as a compile-time constant the per-row branch disappears and the rows of a step are one basic block
+  constexpr bool diff = true;
   const int L = P.L, L2 = P.L2;
   const size_t xbytes = P.xblk * sizeof(T);
   const size_t xslot = align_up_dev(xbytes);
