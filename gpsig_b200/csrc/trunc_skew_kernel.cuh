@@ -81,7 +81,35 @@ __host__ __device__ inline int skew_row_stride(int d, int elem, bool dup = false
 #ifndef GPSIG_SKEW_EXP2_T2048
 #define GPSIG_SKEW_EXP2_T2048 1
 #endif
+// ... or with a 16384-entry table (128 KB per CTA) and a degree-2 polynomial (6 FP64 instructions; 3.9e-16 relative),
+// taken whenever the table fits next to the x ring (launch_skew_inst); 98.96 -> 96.69 ms at c2
+#ifndef GPSIG_SKEW_EXP2_T16K
+#define GPSIG_SKEW_EXP2_T16K 1
+#endif
+// first row of a pair on the common recursion path (see the recursion below): 1 = on.  Measured at c2, N = N2 = 1000:
+// float64 98.96 -> 97.43 ms; float32 46.17 -> 46.78 ms (its top level keeps one partial sum per column: 6 more adds per step)
+#ifndef GPSIG_SKEW_FRF_F64
+#define GPSIG_SKEW_FRF_F64 1
+#endif
+#ifndef GPSIG_SKEW_FRF_F32
+#define GPSIG_SKEW_FRF_F32 0
+#endif
+// lane 0 as a dummy lane (see the kernel): no per-step selects for the start of the chains; taken when L2 <= 31 COLS.
+// Measured at c2: float64 95.5 -> 93.3 ms (the selects sat right behind the chain shuffles and stalled the in-order
+// warp on their latency); float32 46.17 -> 46.34 ms
+#ifndef GPSIG_SKEW_L0D_F64
+#define GPSIG_SKEW_L0D_F64 1
+#endif
+#ifndef GPSIG_SKEW_L0D_F32
+#define GPSIG_SKEW_L0D_F32 0
+#endif
+// float64, DP = 8: the y tile column-major in tensor memory, one tcgen05.ld.x16 per column instead of two x8
+// (7 instead of 14 loads and address moves per step; 98.96 -> 98.32 ms at c2)
+#ifndef GPSIG_SKEW_TM16
+#define GPSIG_SKEW_TM16 1
+#endif
 constexpr size_t kSkewExpTableBytes = 2048 * sizeof(double);
+constexpr size_t kSkewExpTableBytesBig = 16384 * sizeof(double);
 template <typename T, int OP> struct SkewExpTable { static constexpr bool value = GPSIG_SKEW_EXP2 && GPSIG_SKEW_EXP2_T2048 && sizeof(T) == 8 && OP == OP_RBF; };
 
 // ---- tensor memory as per-lane storage (PTX tcgen05.alloc / st / ld) ---------
@@ -117,6 +145,17 @@ __device__ __forceinline__ void tmem_ld4(TmemQuad& r, uint32_t addr) {
   asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                : "=r"(r.w[0]), "=r"(r.w[1]), "=r"(r.w[2]), "=r"(r.w[3]), "=r"(r.w[4]), "=r"(r.w[5]), "=r"(r.w[6]), "=r"(r.w[7])
                : "r"(addr));
+}
+struct TmemHex { uint32_t w[16]; };
+__device__ __forceinline__ void tmem_ld8d(TmemHex& r, uint32_t addr) {      // 8 doubles (16 words) per lane
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+               : "=r"(r.w[0]), "=r"(r.w[1]), "=r"(r.w[2]), "=r"(r.w[3]), "=r"(r.w[4]), "=r"(r.w[5]), "=r"(r.w[6]), "=r"(r.w[7]),
+                 "=r"(r.w[8]), "=r"(r.w[9]), "=r"(r.w[10]), "=r"(r.w[11]), "=r"(r.w[12]), "=r"(r.w[13]), "=r"(r.w[14]), "=r"(r.w[15])
+               : "r"(addr));
+}
+__device__ __forceinline__ void tmem_tie(TmemHex& r) {
+  asm volatile("" : "+r"(r.w[0]), "+r"(r.w[1]), "+r"(r.w[2]), "+r"(r.w[3]), "+r"(r.w[4]), "+r"(r.w[5]), "+r"(r.w[6]), "+r"(r.w[7]),
+                    "+r"(r.w[8]), "+r"(r.w[9]), "+r"(r.w[10]), "+r"(r.w[11]), "+r"(r.w[12]), "+r"(r.w[13]), "+r"(r.w[14]), "+r"(r.w[15]));
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 // empty volatile asm that redefines the loaded registers after the wait: no use of them can be scheduled above it
@@ -212,20 +251,25 @@ template <> struct PairOps<float> {
 };
 #endif
 
+template <typename T> __device__ __forceinline__ void zero_on_lane0(T& v, int lane) { if (lane == 0) v = T(0); }   // (ptxas turns a predicated 64-bit move into the same two selects)
+
 template <int N, typename F, int I = 0>
 __device__ __forceinline__ void static_for(F&& f) {
   if constexpr (I < N) { f(std::integral_constant<int, I>{}); static_for<N, F, I + 1>(static_cast<F&&>(f)); }
 }
 
 template <typename T, int OP> struct SkewFinish {
+  template <int BIG>
   static __device__ __forceinline__ T apply(T acc, T xc, T yc, int base, T p0, T p1, double tab) {
     if (OP == OP_GENERIC) return base_eval_call<T>(base, p0, p1, acc, xc, yc);
     return BaseOp<T, OP>::finish(acc, xc, yc, base, p0, p1);
   }
 };
 template <> struct SkewFinish<double, OP_RBF> {
+  template <int BIG>
   static __device__ __forceinline__ double apply(double acc, double, double, int, double, double, double tab) {
 #if GPSIG_SKEW_EXP2 && GPSIG_SKEW_EXP2_T2048
+    if constexpr (BIG != 0) return exp2_tab16k(acc, (uint32_t)__double2loint(tab));
     return exp2_tab2048(acc, (uint32_t)__double2loint(tab));      // `tab` carries the table's shared-memory address
 #elif GPSIG_SKEW_EXP2
     return exp2_tab32(acc, tab);
@@ -272,6 +316,7 @@ template <typename T, int DP, int COLS> struct SkewDup {
 // float32 RBF: the packed coordinates are pre-scaled by sqrt(log2 e) (abi.cu), so the exponent
 // arrives in base-2 units and exp() is a single MUFU.EX2
 template <> struct SkewFinish<float, OP_RBF> {
+  template <int BIG>
   static __device__ __forceinline__ float apply(float acc, float, float, int, float, float, double) {
     float r;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(acc));
@@ -286,7 +331,7 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
-template <typename T, int DP, int COLS, int MLEV, int OP>
+template <typename T, int DP, int COLS, int MLEV, int OP, int BIG = 0, int L0D = 0>
 __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew_kernel(const TruncParams P, const int RS) {
   using V16 = typename Vec16<T>::type;
   constexpr int V = Vec16<T>::V;
@@ -302,6 +347,7 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
   constexpr int TMCOLS = tmem_cols_pow2((NW / 4) * TMW);
   static_assert(!YTM || (NW % 4 == 0 && (NW / 4) * TMW <= 512), "tensor memory plan does not fit");
   constexpr int NB = kSkewBufs;
+  constexpr bool TM16 = YTM && GPSIG_SKEW_TM16 != 0 && sizeof(T) == 8 && KC == 2;   // column-major tile, x16 loads
   using Op = BaseOp<T, OP>;
 
   extern __shared__ __align__(128) unsigned char skew_smem[];
@@ -348,12 +394,17 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
   // ---- this lane's columns of y (fixed for the whole kernel) ---------------------
   // Slots past the last column repeat it: their first differences equal their left
   // neighbour's, so their 2-D increments are exactly zero without any masking.
-  const int q0 = lane * COLS;
+  // L0D: lane 0 is a DUMMY lane to the left of column 0 and the columns start at lane 1.  All its slots repeat column 0
+  // (as the slots past the last column repeat that one), so its 2-D increments and column sums are exactly 0, and what
+  // it hands to lane 1 -- the start of every chain -- is what it received from ITSELF (shfl.up leaves lane 0 its own
+  // value): the zeros its send registers start with.  The chain values need no per-step select for lane 0 any more;
+  // only the first difference to the left of its first slot still does (`left` below).
+  const int q0 = (L0D != 0 ? lane - 1 : lane) * COLS;
   T yc[COLS];
   V16 yreg[YREG ? COLS : 1][YREG ? KV : 1];
 #pragma unroll
   for (int c = 0; c < COLS; ++c) {
-    const int q = min(q0 + c, L2 - 1);
+    const int q = max(min(q0 + c, L2 - 1), 0);
     yc[c] = Op::col_const(ysqn[q]);
     if constexpr (YTM) {
 #pragma unroll
@@ -361,7 +412,7 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
         union { V16 v[2]; uint32_t w[8]; } u;
         u.v[0] = *reinterpret_cast<const V16*>(yblk + (size_t)q * P.yrs + kc * CE);
         u.v[1] = *reinterpret_cast<const V16*>(yblk + (size_t)q * P.yrs + kc * CE + V);
-        tmem_st8w(ta + (uint32_t)((kc * COLS + c) * 8), u.w);
+        tmem_st8w(ta + (uint32_t)((TM16 ? c * KC + kc : kc * COLS + c) * 8), u.w);
       }
     } else {
 #pragma unroll
@@ -394,7 +445,8 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
   if constexpr (SkewExpTable<T, OP>::value) {
     // 2^(j/2048), j = 0..2047, behind the x ring and the y tiles; the address travels in the low word of `tab`
     double* etab = reinterpret_cast<double*>(xring + NB * xslot + (size_t)NW * skew_ywarp_bytes<T, DP, COLS>());
-    for (int e = threadIdx.x; e < 2048; e += NW * 32) etab[e] = exp2((double)e * (1.0 / 2048.0));
+    constexpr int NE = BIG != 0 ? 16384 : 2048;
+    for (int e = threadIdx.x; e < NE; e += NW * 32) etab[e] = exp2((double)e * (1.0 / NE));
     __syncthreads();
     tab = __hiloint2double(0, (int)smem_u32(etab));
   }
@@ -453,7 +505,7 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
         for (int l = 0; l < MLEV; ++l) {
           if (l < MLEV - 1 || rr == 0) recv[rr][l] = __shfl_up_sync(0xffffffffu, send[rr][l], 1);
           else recv[rr][l] = T(0);
-          if (lane == 0) recv[rr][l] = T(0);
+          if (L0D == 0 && lane == 0) recv[rr][l] = T(0);
         }
       }
     }
@@ -491,7 +543,9 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
         recv[rr][l] = shfl_up1_pinned(send[rr][l]);
       } else if constexpr (k == NCH - 1) recv[0][MLEV - 1] = shfl_up1_pinned(send[0][MLEV - 1]);
     };
-    if constexpr (YTM) tm_issue(std::integral_constant<int, 0>{});
+    [[maybe_unused]] TmemHex yh[2];
+    if constexpr (TM16) tmem_ld8d(yh[0], ta);
+    else if constexpr (YTM) tm_issue(std::integral_constant<int, 0>{});
     {
       T xc[R];
       T acc[R][COLS];
@@ -502,7 +556,42 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
 #pragma unroll
         for (int c = 0; c < COLS; ++c) acc[rr][c] = Op::init(xc[rr], yc[c]);
       }
-      if constexpr (YTM) {
+      if constexpr (TM16) {
+        // one 16-word load per column; the rows' coordinates stay in registers for the whole step
+        V16 xr[R][KV];
+#pragma unroll
+        for (int rr = 0; rr < R; ++rr)
+#pragma unroll
+          for (int kv = 0; kv < KV; ++kv)
+            xr[rr][kv] = *reinterpret_cast<const V16*>(xb + (size_t)min(r0 + rr, L - 1) * RS + kv * V);
+        constexpr int CPC = (NCH + COLS - 1) / COLS;       // chain values shuffled per column
+        static_for<COLS>([&](auto CI) {
+          constexpr int c = decltype(CI)::value;
+          tmem_ld_wait();
+          if (GPSIG_TMEM_TIE) tmem_tie(yh[c & 1]);
+          if constexpr (c + 1 < COLS) tmem_ld8d(yh[(c + 1) & 1], ta + (uint32_t)((c + 1) * 16));
+          static_for<CPC>([&](auto J) {
+            constexpr int k = c * CPC + decltype(J)::value;
+            if constexpr (k < NCH) chain_slot(std::integral_constant<int, k>{});
+          });
+          const TmemHex& cur = yh[c & 1];
+#pragma unroll
+          for (int rr = 0; rr < R; ++rr) {
+            T a = acc[rr][c];
+#pragma unroll
+            for (int e = 0; e < DP; ++e)
+              a = gfma<T>(vget(xr[rr][e / V], e % V), T(__hiloint2double((int)cur.w[2 * e + 1], (int)cur.w[2 * e])), a);
+            acc[rr][c] = a;
+          }
+        });
+#pragma unroll
+        for (int rr = 0; rr < R; ++rr)
+#pragma unroll
+          for (int l = 0; l < MLEV; ++l) {
+            if (!(l < MLEV - 1 || rr == 0)) recv[rr][l] = T(0);
+            else if constexpr (L0D == 0) zero_on_lane0(recv[rr][l], lane);
+          }
+      } else if constexpr (YTM) {
         V16 xa[R], xq[R];
         static_for<NGT>([&](auto G) {
           constexpr int g = decltype(G)::value;
@@ -542,7 +631,7 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
 #pragma unroll
           for (int l = 0; l < MLEV; ++l) {
             if (!(l < MLEV - 1 || rr == 0)) recv[rr][l] = T(0);
-            if (lane == 0) recv[rr][l] = T(0);
+            else if constexpr (L0D == 0) zero_on_lane0(recv[rr][l], lane);
           }
       } else if constexpr (DUP) {
         // packed pairs: one FFMA2 advances two adjacent columns; x arrives as ready-made (x_k, x_k) pairs
@@ -625,7 +714,7 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
       for (int rr = 0; rr < R; ++rr)
 #pragma unroll
         for (int c = 0; c < COLS; ++c) {
-          const T v = SkewFinish<T, OP>::apply(acc[rr][c], xc[rr], yc[c], P.base, p0, p1, tab);
+          const T v = SkewFinish<T, OP>::template apply<BIG>(acc[rr][c], xc[rr], yc[c], P.base, p0, p1, tab);
           if (rr == R - 1) Mp[par ^ 1][c] = v; else Mc[rr][c] = v;
         }
     }
@@ -652,11 +741,14 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
 #pragma unroll
         for (int c = 0; c < COLS; ++c) {
           const T cur = (rr == R - 1) ? Mp[par ^ 1][c] : Mc[rr][c];
-          D[c] = (rowok && q0 + c < L2) ? cur : T(0);
+          D[c] = (rowok && q0 + c < L2 && q0 + c >= 0) ? cur : T(0);
         }
       }
 
-      if (rr == 0 && started && kk == lane) {
+      constexpr bool FRF = sizeof(T) == 8 ? (GPSIG_SKEW_FRF_F64 != 0) : (GPSIG_SKEW_FRF_F32 != 0);
+      const bool first = rr == 0 && started && kk == lane;          // first row of a pair (one lane per step)
+      if constexpr (!FRF) {
+      if (first) {
         // first row of a pair: the chain carries the level totals of the pair just finished
         T tot[MLEV];
 #pragma unroll
@@ -736,6 +828,82 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
         for (int c = 0; c + 1 < COLS; c += 2) PairOps<T>::add(C[0][c], C[0][c + 1], C[0][c], C[0][c + 1], D[c], D[c + 1]);
         if (COLS & 1) C[0][COLS - 1] += D[COLS - 1];
       }
+      } else {
+        // The first row of a pair takes the common path as well: every level reads C_l (and the chain value from the
+        // left, which at this row is the left lanes' TOTAL of the pair just finished) before it writes C_{l+1}, so
+        // send[0][l] comes out as the level total, whatever D holds; what the row's D (new pair's row 0 minus the old
+        // pair's last row) adds to C and Ct afterwards is wiped by the reset below.  The top level's total needs Ct
+        // from before the row: summed here, once per step.
+        T ctsum = T(0);
+        if (rr == 0) {
+#pragma unroll
+          for (int k = 0; k < NT; ++k) ctsum += Ct[k];
+        }
+        // C_{l+1}[q] += D[p, q] * sum_{q' < q} C_l[q'], highest level first (C_l is read before row p updates it)
+#pragma unroll
+        for (int l = MLEV - 2; l >= 0; --l) {
+          T e = recv[rr][l];
+          if constexpr (PairOps<T>::kPacked && NT == COLS) {
+            T t[COLS];
+#pragma unroll
+            for (int c = 0; c < COLS; ++c) { t[c] = e; e += C[l][c]; }
+            const int ln = l + 1 < MLEV - 1 ? l + 1 : 0;
+#pragma unroll
+            for (int c = 0; c + 1 < COLS; c += 2) {
+              if (l == MLEV - 2) PairOps<T>::fma(Ct[c], Ct[c + 1 < NT ? c + 1 : 0], D[c], D[c + 1], t[c], t[c + 1]);
+              else PairOps<T>::fma(C[ln][c], C[ln][c + 1], D[c], D[c + 1], t[c], t[c + 1]);
+            }
+            if (COLS & 1) {
+              if (l == MLEV - 2) Ct[(COLS - 1) % NT] = gfma<T>(D[COLS - 1], t[COLS - 1], Ct[(COLS - 1) % NT]);
+              else C[ln][COLS - 1] = gfma<T>(D[COLS - 1], t[COLS - 1], C[ln][COLS - 1]);
+            }
+          } else {
+#pragma unroll
+          for (int c = 0; c < COLS; ++c) {
+            const T t = e;
+            e += C[l][c];
+            if (l == MLEV - 2) Ct[c % NT] = gfma<T>(D[c], t, Ct[c % NT]);
+            else C[l + 1 < MLEV - 1 ? l + 1 : 0][c] = gfma<T>(D[c], t, C[l + 1 < MLEV - 1 ? l + 1 : 0][c]);
+          }
+          }
+          send[rr][l] = e;
+        }
+#pragma unroll
+        for (int c = 0; c + 1 < COLS; c += 2) PairOps<T>::add(C[0][c], C[0][c + 1], C[0][c], C[0][c + 1], D[c], D[c + 1]);
+        if (COLS & 1) C[0][COLS - 1] += D[COLS - 1];
+        if (first) {
+          const T toptot = recv[0][MLEV - 1] + ctsum;
+          send[0][MLEV - 1] = toptot;
+          if (lane == 31 && seg > 0 && active) {
+            // ---- epilogue: normalise, scale, store (kernels.py:431-477) ----
+            const int i = i_lo + seg - 1;
+            const size_t rc = (size_t)(i - P.row_begin) * P.N2 + j;
+            T sum = T(0);
+#pragma unroll
+            for (int lvl = 0; lvl <= MLEV; ++lvl) {
+              if (lvl <= P.m) {
+                T v = lvl == 0 ? T(1) : (lvl == MLEV ? toptot : send[0][lvl > 0 && lvl < MLEV ? lvl - 1 : 0]);
+                if (P.symmetric && i == j) v += T(P.sym_jitter);
+                if (P.norm_x) {
+                  const T a = gsqrt<T>(static_cast<const T*>(P.norm_x)[(size_t)lvl * P.N + i]);
+                  const T b = gsqrt<T>(static_cast<const T*>(P.norm_x2)[(size_t)lvl * P.N2 + j]);
+                  v = v / (a * b);
+                }
+                if (P.level_scale) v *= static_cast<const T*>(P.level_scale)[lvl];
+                if (P.return_levels) static_cast<T*>(P.out)[(size_t)lvl * rows_out * P.N2 + rc] = v;
+                else sum += v;
+              }
+            }
+            if (!P.return_levels) static_cast<T*>(P.out)[rc] = sum;
+          }
+#pragma unroll
+          for (int l = 0; l < MLEV - 1; ++l)
+#pragma unroll
+            for (int c = 0; c < COLS; ++c) C[l][c] = T(0);
+#pragma unroll
+          for (int k = 0; k < NT; ++k) Ct[k] = T(0);
+        }
+      }
     }
     if (++kk == SPS) { kk = 0; ++sseg; ubuf_prev = ubuf; if (++ubuf == NB) ubuf = 0; }
   };
@@ -755,15 +923,23 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
 
 inline bool skew_eligible(int L, int L2, int elem) { return L >= 32 * (elem == 8 ? GPSIG_SKEW_R_F64 : GPSIG_SKEW_R_F32) + 1 && L2 <= 256; }
 
-template <typename T, int DP, int COLS, int MLEV, int OP>
+template <typename T, int DP, int COLS, int MLEV, int OP, int BIG = 0, int L0D = 0>
 int launch_skew_inst(TruncParams P, cudaStream_t stream) {
+  if constexpr (L0D == 0 && (sizeof(T) == 8 ? GPSIG_SKEW_L0D_F64 != 0 : GPSIG_SKEW_L0D_F32 != 0)) {
+    // the columns fit on lanes 1..31: lane 0 becomes the dummy lane
+    if (P.L2 <= 31 * COLS) return launch_skew_inst<T, DP, COLS, MLEV, OP, BIG, 1>(P, stream);
+  }
   const int RS = P.xrs;
   const size_t xslot = align_up_dev(P.xblk * sizeof(T));
-  const size_t smem = 128 + kSkewBufs * xslot + (size_t)SkewNW<T, DP, COLS>::value * skew_ywarp_bytes<T, DP, COLS>() +
-                      (SkewExpTable<T, OP>::value ? kSkewExpTableBytes : 0);
+  const size_t smem0 = 128 + kSkewBufs * xslot + (size_t)SkewNW<T, DP, COLS>::value * skew_ywarp_bytes<T, DP, COLS>();
+  if constexpr (BIG == 0 && GPSIG_SKEW_EXP2_T16K != 0 && SkewExpTable<T, OP>::value) {
+    // the large exp2 table whenever it fits next to the x ring
+    if (smem0 + kSkewExpTableBytesBig <= kMaxSmem) return launch_skew_inst<T, DP, COLS, MLEV, OP, 1, L0D>(P, stream);
+  }
+  const size_t smem = smem0 + (SkewExpTable<T, OP>::value ? (BIG != 0 ? kSkewExpTableBytesBig : kSkewExpTableBytes) : 0);
   if (smem > kMaxSmem)
     GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "sequence too long for the on-chip plan: needs %zu bytes of shared memory (L=%d)", smem, P.L);
-  auto kern = trunc_skew_kernel<T, DP, COLS, MLEV, OP>;
+  auto kern = trunc_skew_kernel<T, DP, COLS, MLEV, OP, BIG, L0D>;
   GPSIG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid;
   constexpr int NW = SkewNW<T, DP, COLS>::value;

@@ -77,6 +77,27 @@ def test_gram_shapes_raw_levels(dtype, L, L2, d, m):
 
 
 @pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("L,L2", [(200, 200), (200, 217), (200, 218), (200, 224), (400, 200), (400, 224), (376, 31)])
+def test_systolic_schedules(dtype, L, L2):
+    """The launch-time variants of the systolic kernel (trunc_skew_kernel.cuh): lane 0 as a dummy lane (L2 <= 31 x
+    columns per lane) or as a working lane, the 16384-entry exp2 table (fits next to the x ring up to L = 375 at d = 8)
+    or the 2048-entry one; also with points far apart (the exponent clamp of the table exp2)."""
+    from gpsig_b200 import ops
+    from oracle import c_oracle
+    N, N2, d, m = 6, 9, 8, 5
+    for scale in ((1.0, 10.0) if dtype == torch.float64 else (1.0,)):      # float32 cannot hold a 1e-5 exponent at that range
+        X, Y = scale * brownian(N, L, d, 12), scale * brownian(N2, L2, d, 13)
+        for base in ('rbf', 'linear'):
+            G = ops.trunc_gram(_dev(X, dtype), _dev(Y, dtype), m, base=base).cpu().numpy()
+            R = c_oracle.trunc_gram(X, Y, m, base)
+            ref = np.abs(R).max(axis=(1, 2), keepdims=True)
+            err = np.max(np.abs(G - R) / ref)
+            # scaled paths: |x|^2 ~ 1e3..1e4, so the exponent x.y - |x|^2/2 - |y|^2/2 carries ~1e-12 of rounding in ANY
+            # float64 evaluation order (the oracle's included): 1e-9 there
+            assert np.isfinite(G).all() and err < (TOL[dtype] if scale == 1.0 else 1e-9), (base, scale, L, L2, err)
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
 def test_diag_matches_gram_diagonal_and_oracle(dtype):
     from gpsig_b200 import ops
     from oracle import c_oracle
