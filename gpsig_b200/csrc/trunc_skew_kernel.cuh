@@ -103,6 +103,38 @@ __host__ __device__ inline int skew_row_stride(int d, int elem, bool dup = false
 #ifndef GPSIG_SKEW_L0D_F32
 #define GPSIG_SKEW_L0D_F32 0
 #endif
+// x rows read through a 32-bit shared-memory address held in a register (ld.shared by inline PTX) instead of a generic
+// pointer: at the float32 kernel's 168 registers the compiler otherwise rebuilds the shared window base from
+// SR_CgaCtaId (S2R, ~20 cycles on the short scoreboard) in every step
+// (measured at c2: float64 93.29 -> 92.90 ms; float32, where the S2R was seen, 45.63 -> 45.89 ms: off there)
+#ifndef GPSIG_SKEW_SADDR_F32
+#define GPSIG_SKEW_SADDR_F32 0
+#endif
+#ifndef GPSIG_SKEW_SADDR_F64
+#define GPSIG_SKEW_SADDR_F64 1
+#endif
+__device__ __forceinline__ float4 lds16(uint32_t a, float) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ double2 lds16(uint32_t a, double) {
+  double2 v;
+  asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ float lds1(uint32_t a, float) { float v; asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a)); return v; }
+__device__ __forceinline__ double lds1(uint32_t a, double) { double v; asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a)); return v; }
+// ring bookkeeping behind one test per step instead of two (see the step prologue): float32 46.17 -> 45.63 ms at c2
+// (there the compiler keeps the step counters in vector registers and every test costs a divergence check), float64 unchanged
+#ifndef GPSIG_SKEW_RING1
+#define GPSIG_SKEW_RING1 1
+#endif
+static_assert(kSkewBufs == 3 || GPSIG_SKEW_RING1 == 0, "the merged ring bookkeeping assumes three slots");
+// partial sums of the top level (float64; 4 measured slower: 93.3 -> 94.9 ms)
+#ifndef GPSIG_SKEW_NT_F64
+#define GPSIG_SKEW_NT_F64 2
+#endif
 // float64, DP = 8: the y tile column-major in tensor memory, one tcgen05.ld.x16 per column instead of two x8
 // (7 instead of 14 loads and address moves per step; 98.96 -> 98.32 ms at c2)
 #ifndef GPSIG_SKEW_TM16
@@ -458,7 +490,7 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
   for (int l = 0; l < MLEV - 1; ++l)
 #pragma unroll
     for (int c = 0; c < COLS; ++c) C[l][c] = T(0);
-  constexpr int NT = sizeof(T) == 8 ? 2 : COLS;            // float32: one per column (a 2-deep FFMA chain would stall on latency)
+  constexpr int NT = sizeof(T) == 8 ? GPSIG_SKEW_NT_F64 : COLS;            // float32: one per column (a 2-deep FFMA chain would stall on latency)
   T Ct[NT];
 #pragma unroll
   for (int k = 0; k < NT; ++k) Ct[k] = T(0);
@@ -473,6 +505,9 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
     for (int l = 0; l < MLEV; ++l) send[rr][l] = T(0);
   }
 
+  constexpr bool SADDR = sizeof(T) == 8 ? (GPSIG_SKEW_SADDR_F64 != 0) : (GPSIG_SKEW_SADDR_F32 != 0);
+  uint32_t xring_s = smem_u32(xring);
+  if constexpr (SADDR) asm volatile("" : "+r"(xring_s));      // opaque: kept in a register, not rebuilt
   const int SPS = (L + R - 1) / R;                 // steps per pair (>= 32, see skew_eligible)
   const int nsteps = npairs * SPS + 32;            // + finalisation step + pipeline drain
   int kk = 0, sseg = 0, ubuf = 0, ubuf_prev = NB - 1;   // warp-uniform: step within pair, pair and ring slot of lane 0
@@ -482,6 +517,26 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
   auto step = [&](auto PAR, const int s) {
     constexpr int par = decltype(PAR)::value;
     // ---- ring: wait for the pair lane 0 enters now; hand back the slot lane 31 just left ----
+#if GPSIG_SKEW_RING1
+    // ONE warp-uniform test per step: at the first step of a pair the warp waits for that pair's rows and hands back
+    // the slot of the pair before the previous one (lane 31 left it 69 steps ago); thread 0 refills it with the NEXT
+    // pair, which then has a whole pair's time to arrive.
+    if (kk == 0) {
+      if (sseg < npairs) mbar_wait(&full_bar[ubuf], (sseg / NB) & 1);
+      if (sseg >= 2) {
+        const int dseg = sseg - 2;
+        const int fslot = ubuf + 1 == NB ? 0 : ubuf + 1;        // slot of pair sseg - 2 == slot of pair sseg + 1 (NB = 3)
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty_bar[fslot]);
+        const int nxt = dseg + NB;
+        if (threadIdx.x == 0 && nxt < npairs) {
+          mbar_wait(&empty_bar[fslot], (dseg / NB) & 1);
+          mbar_expect_tx(&full_bar[fslot], (uint32_t)xbytes);
+          tma_load_1d(xring + fslot * xslot, xg + (size_t)(i_lo + nxt) * P.xblk, (uint32_t)xbytes, &full_bar[fslot]);
+        }
+      }
+    }
+#else
     if (kk == 0 && sseg < npairs) mbar_wait(&full_bar[ubuf], (sseg / NB) & 1);
     if (kk == 31 && sseg >= 1) {
       const int dseg = sseg - 1;
@@ -494,6 +549,7 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
         tma_load_1d(xring + ubuf_prev * xslot, xg + (size_t)(i_lo + nxt) * P.xblk, (uint32_t)xbytes, &full_bar[ubuf_prev]);
       }
     }
+#endif
     // ---- chain values from the lane to the left (computed one step ago) -----------
     // (tensor-memory variant: the shuffles are issued inside the contraction below)
     T recv[R][MLEV], recvU[R];
@@ -517,6 +573,11 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
     const bool live = started && seg < npairs;                // rows of a real pair (else: fill / finalisation / drain)
     const T* xb = reinterpret_cast<const T*>(xring + (live ? (behind ? ubuf_prev : ubuf) : 0) * xslot);
     const T* xsq = xb + (size_t)L * RS;
+    const uint32_t xb_s = xring_s + (uint32_t)((live ? (behind ? ubuf_prev : ubuf) : 0) * xslot);
+    auto ldx = [&](int row, int off) -> V16 {          // 16 bytes of x row `row` from element `off`
+      if constexpr (SADDR) return lds16(xb_s + (uint32_t)((row * RS + off) * (int)sizeof(T)), T(0));
+      else return *reinterpret_cast<const V16*>(xb + (size_t)row * RS + off);
+    };
     const int r0 = live ? rstep * R : 0;
 
     // ---- base kernel on R rows x COLS columns -------------------------------------
@@ -552,7 +613,8 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
 #pragma unroll
       for (int rr = 0; rr < R; ++rr) {
         const int row = min(r0 + rr, L - 1);
-        xc[rr] = Op::row_const(xsq[row]);
+        if constexpr (SADDR) xc[rr] = Op::row_const(lds1(xb_s + (uint32_t)((L * RS + row) * (int)sizeof(T)), T(0)));
+        else xc[rr] = Op::row_const(xsq[row]);
 #pragma unroll
         for (int c = 0; c < COLS; ++c) acc[rr][c] = Op::init(xc[rr], yc[c]);
       }
@@ -563,7 +625,7 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
         for (int rr = 0; rr < R; ++rr)
 #pragma unroll
           for (int kv = 0; kv < KV; ++kv)
-            xr[rr][kv] = *reinterpret_cast<const V16*>(xb + (size_t)min(r0 + rr, L - 1) * RS + kv * V);
+            xr[rr][kv] = ldx(min(r0 + rr, L - 1), kv * V);
         constexpr int CPC = (NCH + COLS - 1) / COLS;       // chain values shuffled per column
         static_for<COLS>([&](auto CI) {
           constexpr int c = decltype(CI)::value;
@@ -599,9 +661,8 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
           if constexpr (g % NG == 0) {
 #pragma unroll
             for (int rr = 0; rr < R; ++rr) {
-              const T* xr = xb + (size_t)min(r0 + rr, L - 1) * RS + kc * CE;
-              xa[rr] = *reinterpret_cast<const V16*>(xr);
-              xq[rr] = *reinterpret_cast<const V16*>(xr + V);
+              xa[rr] = ldx(min(r0 + rr, L - 1), kc * CE);
+              xq[rr] = ldx(min(r0 + rr, L - 1), kc * CE + V);
             }
           }
           tmem_ld_wait();
@@ -677,7 +738,7 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
         V16 xv[R];
 #pragma unroll
         for (int rr = 0; rr < R; ++rr)
-          xv[rr] = *reinterpret_cast<const V16*>(xb + (size_t)min(r0 + rr, L - 1) * RS + kv * V);
+          xv[rr] = ldx(min(r0 + rr, L - 1), kv * V);
         if constexpr (PairOps<T>::kPacked && YREG) {
           // adjacent columns as packed pairs (the y pairs are loop invariant: packed once by the compiler)
 #pragma unroll
