@@ -219,7 +219,7 @@ static int trunc_gram_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
   const bool lifted = big && desc->order == 1 && desc->base != GPSIG_BASE_SPECTRAL && lift_eligible(L, L2);
   const bool generic = desc->order > 1 || desc->base == GPSIG_BASE_SPECTRAL || (big && !lifted);
   const bool skew = !big && !generic && desc->difference && skew_eligible(L, L2, sizeof(T)) && getenv("GPSIG_NO_SKEW") == nullptr;
-  const bool dup = skew && skew_uses_dup(d, L2, sizeof(T));      // float32: coordinates stored twice for the packed-pair contraction
+  const bool dup = skew && skew_uses_dup(d, L2, sizeof(T), desc->num_levels, desc->base);      // float32: coordinates stored twice for the packed-pair contraction
   const int RS = skew ? skew_row_stride(d, sizeof(T), dup) : padded_dim(d);
   T* xp = static_cast<T*>(ws);
   T* yp = sym ? xp : reinterpret_cast<T*>(static_cast<char*>(ws) + packed_bytes_padded(N, L, d, sizeof(T)));

@@ -93,6 +93,13 @@ template <typename T> __device__ __forceinline__ T gfma(T a, T b, T c);
 template <> __device__ __forceinline__ double gfma<double>(double a, double b, double c) { return fma(a, b, c); }
 template <> __device__ __forceinline__ float gfma<float>(float a, float b, float c) { return fmaf(a, b, c); }
 
+// SMs of the current device (grids are sized in whole waves of it)
+inline int device_sm_count() {
+  int dev = 0, sms = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
+  return sms;
+}
+
 struct BaseParams { double p0, p1; int base; };
 
 // Generic evaluation (runtime switch; used for everything but the two hot

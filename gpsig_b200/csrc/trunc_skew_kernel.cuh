@@ -40,8 +40,10 @@ constexpr int kSkewBufs = 3;
 // (RBF m = 4: 43.96 against 45.67 ms, linear m = 5: 42.8 against 45.1 ms) and 4 % SLOWER at the headline shape
 // (RBF m = 5: 50.6 against 48.4 ms, 16 bytes of spills) -- the contraction drops from 8 to 4.6 instructions per element
 // but the kernel is not bound by issue slots alone; it also moves 67 % more x bytes.
+// Round 2 (after the ring bookkeeping moved behind one test per step the headline instantiation no longer spills): ON for the
+// instantiations that hold it without spills (SkewDup below): c2 float32 45.64 -> 44.67 ms.
 #ifndef GPSIG_SKEW_DUP_F32
-#define GPSIG_SKEW_DUP_F32 0
+#define GPSIG_SKEW_DUP_F32 1
 #endif
 // row stride (in elements) of the padded packed layout: an odd number of 16-byte units
 __host__ __device__ inline int skew_row_stride(int d, int elem, bool dup = false) {
@@ -341,8 +343,12 @@ template <typename T, int DP, int COLS> struct SkewYTmem {
 };
 
 // which instantiations read the duplicated layout: float32 with the y tile in registers (and not in tensor memory)
-template <typename T, int DP, int COLS> struct SkewDup {
-  static constexpr bool value = GPSIG_SKEW_DUP_F32 && sizeof(T) == 4 && YPolicy<T, DP, COLS>::kInRegs && !SkewYTmem<T, DP, COLS>::value;
+// ... and whose state leaves room for the pair registers at 168 registers per thread (no spills: up to 7 columns per
+// lane and 5 levels; the 8-level / 8-column instantiations spill 16-484 bytes with it and keep the plain layout)
+constexpr int kSkewDupMaxCols = 7, kSkewDupMaxLev = 5;
+template <typename T, int DP, int COLS, int MLEV, int OP> struct SkewDup {
+  static constexpr bool value = GPSIG_SKEW_DUP_F32 && sizeof(T) == 4 && YPolicy<T, DP, COLS>::kInRegs && !SkewYTmem<T, DP, COLS>::value &&
+                                COLS <= kSkewDupMaxCols && MLEV <= kSkewDupMaxLev && OP != OP_GENERIC;
 };
 
 // float32 RBF: the packed coordinates are pre-scaled by sqrt(log2 e) (abi.cu), so the exponent
@@ -372,7 +378,7 @@ __global__ void __launch_bounds__(SkewNW<T, DP, COLS>::value * 32, 1) trunc_skew
   constexpr int NW = SkewNW<T, DP, COLS>::value;
   constexpr bool YREG = YPolicy<T, DP, COLS>::kInRegs;
   constexpr bool YTM = SkewYTmem<T, DP, COLS>::value;      // y tile in tensor memory (float64)
-  constexpr bool DUP = SkewDup<T, DP, COLS>::value;        // x / y rows stored with duplicated coordinates (float32, y in registers)
+  constexpr bool DUP = SkewDup<T, DP, COLS, MLEV, OP>::value;        // x / y rows stored with duplicated coordinates (float32, y in registers)
   constexpr int CE = 32 / sizeof(T);                        // elements per 8-word tensor-memory load (4 doubles / 8 floats)
   constexpr int KC = DP / CE > 0 ? DP / CE : 1;             // chunks per column
   constexpr int TMW = COLS * DP * (sizeof(T) / 4);          // TMEM words (columns) per warp
@@ -1012,6 +1018,24 @@ int launch_skew_inst(TruncParams P, cudaStream_t stream) {
   int ichunk = (rows + want_y - 1) / want_y;
   if (ichunk < 16) ichunk = 16;
   if (ichunk > rows) ichunk = rows;
+  if (!P.tri) {
+    // All CTAs take the same time (one CTA per SM, ichunk pairs per warp), so the launch runs in whole waves: pick the
+    // row split y whose last wave is full, i.e. minimise waves(y) x (pairs per chunk + pipeline fill) around the
+    // value above (c2, 250 x 15 CTAs = 25.3 waves of 134 pairs -> 250 x 13 = 21.96 waves of 154: 2.8 % less).
+    const int sms = device_sm_count();
+    const int ymax = rows / 16 > 0 ? rows / 16 : 1;
+    double best = 1e300;
+    int best_y = 0;
+    for (int y = 1; y <= ymax && y <= 4 * want_y + 8; ++y) {
+      const int ch = (rows + y - 1) / y;
+      const int ny = (rows + ch - 1) / ch;
+      const long ctas = (long)grid.x * ny;
+      const double waves = (double)((ctas + sms - 1) / sms);
+      const double cost = waves * ((double)ch + 0.32) * (ctas < sms ? (double)sms / ctas : 1.0);   // fewer CTAs than SMs: idle SMs
+      if (cost < best * (1.0 - 1e-9)) { best = cost; best_y = y; }
+    }
+    if (best_y > 0) ichunk = (rows + best_y - 1) / best_y;
+  }
   P.ichunk = ichunk;
   grid.y = (rows + ichunk - 1) / ichunk;
   prof_begin(stream);
@@ -1038,14 +1062,18 @@ int launch_skew_mlev(const TruncParams& P, cudaStream_t stream) {
 }
 
 // host mirror of the dispatch below: does the instantiation that takes (d, L2, elem) read the duplicated layout?
-inline bool skew_uses_dup(int d, int L2, int elem) {
-  if (!GPSIG_SKEW_DUP_F32 || elem != 4) return false;
+inline bool skew_uses_dup(int d, int L2, int elem, int m, int base) {
+  if (!GPSIG_SKEW_DUP_F32 || elem != 4 || (base != GPSIG_BASE_LINEAR && base != GPSIG_BASE_RBF)) return false;
   const int need = (L2 + 31) / 32, dp = padded_dim(d);
-  int cols = 0;
+  int cols = 0, mlev = 0;
 #define GPSIG_CASE(C_) if (cols == 0 && need <= C_) cols = C_;
   GPSIG_SKEW_COLS(GPSIG_CASE)
 #undef GPSIG_CASE
-  return cols > 0 && cols * dp * 4 <= 256 && !(GPSIG_SKEW_TMEM && GPSIG_SKEW_TMEM_F32);
+#define GPSIG_CASE(M_) if (mlev == 0 && m <= M_) mlev = M_;
+  GPSIG_SKEW_MLEV(GPSIG_CASE)
+#undef GPSIG_CASE
+  return cols > 0 && cols * dp * 4 <= 256 && !(GPSIG_SKEW_TMEM && GPSIG_SKEW_TMEM_F32) && cols <= kSkewDupMaxCols && mlev > 0 &&
+         mlev <= kSkewDupMaxLev;
 }
 
 template <typename T, int OP, int DP>

@@ -30,8 +30,9 @@ def test_version_and_workspace_queries():
     assert L.lib.gpsig_version() == 100
     # packed block: L*DP + padded L elements per sequence, 128-byte aligned regions
     assert L.lib.gpsig_trunc_diag_workspace_bytes(10, 200, 8, 8) == 10 * (200 * 8 + 200) * 8
-    # the Gram workspace uses the padded row stride of the systolic kernel (an odd number of 16-byte units per row)
-    assert L.lib.gpsig_trunc_gram_workspace_bytes(3, 5, 0, 0, 3, 4) == ((3 * (5 * 4 + 8) * 4 + 127) // 128) * 128
+    # the Gram workspace uses the padded row stride of the systolic kernel (an odd number of 16-byte units per row;
+    # float32 rows with every coordinate stored twice for the packed-pair contraction: 2 x 4 floats = 2 units -> 3)
+    assert L.lib.gpsig_trunc_gram_workspace_bytes(3, 5, 0, 0, 3, 4) == ((3 * (5 * 12 + 8) * 4 + 127) // 128) * 128
     assert L.lib.gpsig_trunc_gram_workspace_bytes(4, 50, 6, 70, 3, 8) == \
         ((4 * (50 * 6 + 50) * 8 + 127) // 128) * 128 + ((6 * (70 * 6 + 70) * 8 + 127) // 128) * 128
 
