@@ -89,12 +89,13 @@ __host__ __device__ inline int skew_row_stride(int d, int elem, bool dup = false
 #define GPSIG_SKEW_EXP2_T16K 1
 #endif
 // first row of a pair on the common recursion path (see the recursion below): 1 = on.  Measured at c2, N = N2 = 1000:
-// float64 98.96 -> 97.43 ms; float32 46.17 -> 46.78 ms (its top level keeps one partial sum per column: 6 more adds per step)
+// float64 98.96 -> 97.43 ms; float32 46.17 -> 46.78 ms with the plain contraction (its top level keeps one partial sum per
+// column: 6 more adds per step), but 177.3 -> 165.5 ms at N = N2 = 2000 next to the packed FFMA2 contraction (GPSIG_SKEW_DUP_F32)
 #ifndef GPSIG_SKEW_FRF_F64
 #define GPSIG_SKEW_FRF_F64 1
 #endif
 #ifndef GPSIG_SKEW_FRF_F32
-#define GPSIG_SKEW_FRF_F32 0
+#define GPSIG_SKEW_FRF_F32 1
 #endif
 // lane 0 as a dummy lane (see the kernel): no per-step selects for the start of the chains; taken when L2 <= 31 COLS.
 // Measured at c2: float64 95.5 -> 93.3 ms (the selects sat right behind the chain shuffles and stalled the in-order
