@@ -35,11 +35,10 @@ constexpr int kSkewBufs = 3;
 
 // float32: the streamed x rows are stored with every coordinate DUPLICATED (x0, x0, x1, x1, ...), so that one 16-byte
 // shared-memory load yields two ready-made (x_k, x_k) pairs for the packed FFMA2 of the contraction: two adjacent
-// columns per instruction, no register moves to assemble the pairs (the y pairs are loop invariant).  Build-time
-// option, OFF: measured at c2 (N = N2 = 1000, 12 warps at 168 registers) it is 4-5 % faster where registers allow
-// (RBF m = 4: 43.96 against 45.67 ms, linear m = 5: 42.8 against 45.1 ms) and 4 % SLOWER at the headline shape
-// (RBF m = 5: 50.6 against 48.4 ms, 16 bytes of spills) -- the contraction drops from 8 to 4.6 instructions per element
-// but the kernel is not bound by issue slots alone; it also moves 67 % more x bytes.
+// columns per instruction, no register moves to assemble the pairs (the y pairs are loop invariant).  Round 1 measured
+// it at c2 (N = N2 = 1000, 12 warps at 168 registers) 4-5 % faster where registers allow (RBF m = 4: 43.96 against
+// 45.67 ms, linear m = 5: 42.8 against 45.1 ms) and 4 % SLOWER at the headline shape (RBF m = 5: 50.6 against 48.4 ms,
+// 16 bytes of spills) -- the contraction drops from 8 to 4.6 instructions per element; it also moves 67 % more x bytes.
 // Round 2 (after the ring bookkeeping moved behind one test per step the headline instantiation no longer spills): ON for the
 // instantiations that hold it without spills (SkewDup below): c2 float32 45.64 -> 44.67 ms.
 #ifndef GPSIG_SKEW_DUP_F32
