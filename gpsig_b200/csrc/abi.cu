@@ -218,8 +218,19 @@ static int trunc_gram_impl(const gpsig_trunc_desc* desc, const T* X, int N, int 
   const bool big = d > 16;
   const bool lifted = big && desc->order == 1 && desc->base != GPSIG_BASE_SPECTRAL && lift_eligible(L, L2);
   const bool generic = desc->order > 1 || desc->base == GPSIG_BASE_SPECTRAL || (big && !lifted);
-  const bool skew = !big && !generic && desc->difference && skew_eligible(L, L2, sizeof(T)) && getenv("GPSIG_NO_SKEW") == nullptr;
-  const bool dup = skew && skew_uses_dup(d, L2, sizeof(T), desc->num_levels, desc->base);      // float32: coordinates stored twice for the packed-pair contraction
+  bool skew = !big && !generic && desc->difference && skew_eligible(L, L2, sizeof(T)) && getenv("GPSIG_NO_SKEW") == nullptr;
+  bool dup = skew && skew_uses_dup(d, L2, sizeof(T), desc->num_levels, desc->base);      // float32: coordinates stored twice for the packed-pair contraction
+  if (skew) {
+    // rows too long for the three-slot x ring of the systolic kernel (about L > 800 at d = 8 in float64): the general
+    // kernel streams them instead (asked of the launcher itself, which knows the instantiation's shared-memory plan)
+    TruncParams Q;
+    memset(&Q, 0, sizeof(Q));
+    const int rs0 = skew_row_stride(d, sizeof(T), dup);
+    Q.xblk = seq_block_elems_rs(L, rs0, sizeof(T)); Q.yblk = seq_block_elems_rs(L2, rs0, sizeof(T));
+    Q.xrs = Q.yrs = rs0; Q.N = N; Q.N2 = N2; Q.L = L; Q.L2 = L2; Q.row_begin = row_begin; Q.row_end = row_end;
+    Q.m = desc->num_levels; Q.difference = 1; Q.base = desc->base; Q.dry_run = 1;
+    if (dispatch_skew<T>(Q, desc->base, padded_dim(d), s) != GPSIG_OK) { skew = false; dup = false; }
+  }
   const int RS = skew ? skew_row_stride(d, sizeof(T), dup) : padded_dim(d);
   T* xp = static_cast<T*>(ws);
   T* yp = sym ? xp : reinterpret_cast<T*>(static_cast<char*>(ws) + packed_bytes_padded(N, L, d, sizeof(T)));

@@ -48,6 +48,7 @@ struct TruncParams {
   const void* norm_x; const void* norm_x2; const void* level_scale;
   double sym_jitter; int return_levels;
   void* out;
+  int dry_run;             // systolic launcher only: report whether the shape fits its on-chip plan, launch nothing
 };
 
 template <typename T> struct Vec16;   // 16-byte vector of T

@@ -1004,6 +1004,7 @@ int launch_skew_inst(TruncParams P, cudaStream_t stream) {
     if (smem0 + kSkewExpTableBytesBig <= kMaxSmem) return launch_skew_inst<T, DP, COLS, MLEV, OP, 1, L0D>(P, stream);
   }
   const size_t smem = smem0 + (SkewExpTable<T, OP>::value ? (BIG != 0 ? kSkewExpTableBytesBig : kSkewExpTableBytes) : 0);
+  if (P.dry_run) return smem > kMaxSmem ? GPSIG_ERR_UNSUPPORTED : GPSIG_OK;       // the caller then takes trunc_gram_kernel
   if (smem > kMaxSmem)
     GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "sequence too long for the on-chip plan: needs %zu bytes of shared memory (L=%d)", smem, P.L);
   auto kern = trunc_skew_kernel<T, DP, COLS, MLEV, OP, BIG, L0D>;

@@ -98,6 +98,23 @@ def test_systolic_schedules(dtype, L, L2):
 
 
 @pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("L,L2,d", [(1000, 200, 8), (2500, 64, 8), (1500, 256, 16)])
+def test_rows_longer_than_the_systolic_ring(dtype, L, L2, d):
+    """Row sequences too long for the three-slot shared-memory ring of the systolic kernel (about 800 points at d = 8
+    in float64) are taken by the general kernel, which streams them: same result, no 'sequence too long' error."""
+    from gpsig_b200 import ops
+    from oracle import c_oracle
+    X, Y = brownian(3, L, d, 21), brownian(4, L2, d, 22)
+    for base in ('rbf', 'linear'):
+        G = ops.trunc_gram(_dev(X, dtype), _dev(Y, dtype), 4, base=base).cpu().numpy()
+        R = c_oracle.trunc_gram(X, Y, 4, base)
+        ref = np.abs(R).max(axis=(1, 2), keepdims=True)
+        # float32 sums 2500 x 64 increments per level: 5e-5 at that length (rounding of the float32 recursion, not the kernel choice)
+        tol = TOL[dtype] if (dtype == torch.float64 or L < 2000) else 5e-5
+        assert np.max(np.abs(G - R) / ref) < tol, (base, L, L2, d)
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
 def test_diag_matches_gram_diagonal_and_oracle(dtype):
     from gpsig_b200 import ops
     from oracle import c_oracle
