@@ -46,11 +46,20 @@ struct TensSeqParams {
 template <typename T> struct TensExp2;
 template <> struct TensExp2<double> { static __device__ __forceinline__ double ex(double t, double tab) { return exp2_tab32(t, tab); } };
 template <> struct TensExp2<float> { static __device__ __forceinline__ float ex(float t, double) { return exp2_approx(t); } };
-// register-resident kernel (tens_vs_seq_kernel2): float64 exp2 from the 2048-entry shared-memory table (7 FP64 instructions
+// register-resident kernel (tens_vs_seq_kernel2): float64 exp2 from an 8192-entry shared-memory table (6 FP64 instructions,
+// exp2_tab8k; 2048 entries and 7 instructions with GPSIG_TENS_EXP2_8K=0: c4 float64 14.65 -> see DESIGN 4.3)
 // instead of 9; `tab` carries the table's shared-memory address in its low word)
 template <typename T> struct TensExp2T;
-template <> struct TensExp2T<double> { static __device__ __forceinline__ double ex(double t, double tab) { return exp2_tab2048(t, (uint32_t)__double2loint(tab)); } };
-template <> struct TensExp2T<float> { static __device__ __forceinline__ float ex(float t, double) { return exp2_approx(t); } };
+#ifndef GPSIG_TENS_EXP2_8K
+#define GPSIG_TENS_EXP2_8K 1
+#endif
+template <> struct TensExp2T<double> {
+  template <int EBITS> static __device__ __forceinline__ double ex(double t, double tab) {
+    if constexpr (EBITS == 13) return exp2_tab8k(t, (uint32_t)__double2loint(tab));
+    else return exp2_tab2048(t, (uint32_t)__double2loint(tab));
+  }
+};
+template <> struct TensExp2T<float> { template <int EBITS> static __device__ __forceinline__ float ex(float t, double) { return exp2_approx(t); } };
 
 template <typename T, int DP, int OP, int I>
 __device__ __forceinline__ T tens_level(const T* zc, const T* zq, int zs, const T* xblk, const T* xsq, int L,
@@ -155,7 +164,7 @@ constexpr size_t kTens2MaxSmem = 200 * 1024;
 constexpr int kTens2Warps = 4;      // 128 tensors per CTA
 constexpr int kTens2Chunk = 16;     // sequences per CTA at most (fewer when the grid would not fill the GPU)
 
-template <typename T, int DP, int OP, int ZS, int I>
+template <typename T, int DP, int OP, int ZS, int I, int EBITS>
 __device__ __forceinline__ T tens2_level(const T (&zr)[I * ZS * DP], const T (&zq)[I * ZS], const T* xs, const T* xsq, int L,
                                          bool difference, int base, T p0, T p1, double tab) {
   using Op = BaseOp<T, OP>;
@@ -178,7 +187,7 @@ __device__ __forceinline__ T tens2_level(const T (&zr)[I * ZS * DP], const T (&z
 #pragma unroll
       for (int k = 0; k < DP; ++k) acc = gfma<T>(zr[e * DP + k], xv[k], acc);
       if (OP == OP_GENERIC) return base_eval_call<T>(base, p0, p1, acc, zq[e], xc);
-      if (OP == OP_RBF) return TensExp2T<T>::ex(acc, tab);
+      if (OP == OP_RBF) return TensExp2T<T>::template ex<EBITS>(acc, tab);
       return Op::finish(acc, zq[e], xc, base, p0, p1);
     };
     const bool first = difference && l == 0;
@@ -199,7 +208,7 @@ __device__ __forceinline__ T tens2_level(const T (&zr)[I * ZS * DP], const T (&z
 // registers the z tile of the top level needs (32-bit units); the kernel is used when this fits
 template <typename T> constexpr int tens2_zregs(int m, int zs, int DP) { return m * zs * (DP + 1) * (int)(sizeof(T) / 4); }
 
-template <typename T, int DP, int OP, int ZS, int MMAX>
+template <typename T, int DP, int OP, int ZS, int MMAX, int EBITS = 11>
 __global__ void __launch_bounds__(kTens2Warps * 32) tens_vs_seq_kernel2(const TensSeqParams P, const int CH) {
   using Op = BaseOp<T, OP>;
   constexpr int ZB = kTens2Warps * 32;
@@ -225,7 +234,7 @@ __global__ void __launch_bounds__(kTens2Warps * 32) tens_vs_seq_kernel2(const Te
   if (threadIdx.x == 0) { mbar_init(&full[0], 1); mbar_init(&full[1], 1); fence_mbar_init(); }
   if constexpr (ETAB) {
     double* etab = reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(tile) + (((size_t)CH * (ZB + 1) * sizeof(T) + 15) & ~(size_t)15));
-    for (int e = threadIdx.x; e < 2048; e += ZB) etab[e] = exp2((double)e * (1.0 / 2048.0));
+    exp2_table_fill<EBITS>(etab, etab + (1 << EBITS), threadIdx.x, ZB);
     tab = __hiloint2double(0, (int)smem_u32(etab));
   }
   __syncthreads();
@@ -283,7 +292,7 @@ __global__ void __launch_bounds__(kTens2Warps * 32) tens_vs_seq_kernel2(const Te
       }
       mbar_wait(&full[b], (it >> 1) & 1);
       const T* xs = reinterpret_cast<const T*>(xbuf + (size_t)b * xslot);
-      T v = tens2_level<T, DP, OP, ZS, I>(zr, zq, xs, xs + (size_t)P.L * DP, P.L, diff, P.base, p0, p1, tab);
+      T v = tens2_level<T, DP, OP, ZS, I, EBITS>(zr, zq, xs, xs + (size_t)P.L * DP, P.L, diff, P.base, p0, p1, tab);
       if (P.norm_x) v = v / gsqrt<T>(static_cast<const T*>(P.norm_x)[(size_t)I * P.N + P.col_begin + c0 + j]);   // kernels.py:610-614
       v *= ls;
       T* tl = tile + j * (ZB + 1) + threadIdx.x;
@@ -298,17 +307,22 @@ __global__ void __launch_bounds__(kTens2Warps * 32) tens_vs_seq_kernel2(const Te
   if (!P.return_levels) flush(0);
 }
 
-template <typename T, int OP, int DP, int ZS, int MMAX>
+template <typename T, int OP, int DP, int ZS, int MMAX, int EBITS = 11>
 int launch_tens2(const TensSeqParams& P, cudaStream_t stream) {
   const size_t xslot = (P.xblk * sizeof(T) + 127) / 128 * 128;
   const int ncols = P.col_end - P.col_begin;
   const int zblocks = (P.Mz + kTens2Warps * 32 - 1) / (kTens2Warps * 32);
   int ch = (int)((long)ncols * zblocks / (2 * 148));                              // at least two CTAs per SM before a CTA takes a second sequence
   ch = ch < 1 ? 1 : (ch > kTens2Chunk ? kTens2Chunk : ch);
-  const size_t etab = (sizeof(T) == 8 && OP == OP_RBF) ? 2048 * sizeof(double) + 16 : 0;
+  const size_t etab = (sizeof(T) == 8 && OP == OP_RBF) ? ((size_t)(1 << EBITS) + 256) * sizeof(double) + 16 : 0;   // table + fill scratch
+  if constexpr (EBITS == 11 && GPSIG_TENS_EXP2_8K != 0 && sizeof(T) == 8 && OP == OP_RBF) {
+    // the 8192-entry table whenever two CTAs per SM still fit with it
+    const size_t big = 128 + 2 * xslot + (size_t)kTens2Chunk * (kTens2Warps * 32 + 1) * sizeof(T) + ((size_t)(1 << 13) + 256) * sizeof(double) + 16;
+    if (2 * (big + 1024) <= 227 * 1024) return launch_tens2<T, OP, DP, ZS, MMAX, 13>(P, stream);
+  }
   const size_t smem = 128 + 2 * xslot + (size_t)ch * (kTens2Warps * 32 + 1) * sizeof(T) + etab;
   if (128 + 2 * xslot + (size_t)kTens2Chunk * (kTens2Warps * 32 + 1) * sizeof(T) + etab > kTens2MaxSmem) return -100;                                           // caller falls back to tens_vs_seq_kernel
-  auto kern = tens_vs_seq_kernel2<T, DP, OP, ZS, MMAX>;
+  auto kern = tens_vs_seq_kernel2<T, DP, OP, ZS, MMAX, EBITS>;
   GPSIG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid((ncols + ch - 1) / ch, zblocks);
   prof_begin(stream);
