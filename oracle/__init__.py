@@ -24,9 +24,14 @@ Parity pinning status
 * PDE path: PINNED against the reference's own Cython solver run in the build
   container (``tests/golden/pde_ref_*.npz`` were produced by
   ``oracle/_ref/sigKer_fast`` -- see ``tests/golden/make_golden.py``).
-* Truncated path: the reference executes inside TensorFlow 1.15 / GPflow 1.5
-  which cannot be installed here (Python 3.12, no network) and the reference
-  holds no golden vectors or tests.  It is pinned by the reference notebooks'
-  known-answer properties (signature inner products) instead; in the
-  golden-vector sense it is "parity unpinned".
+* Truncated path: PINNED against the reference's own Python code.  TensorFlow 1.15 /
+  GPflow 1.5.1 cannot be installed here (Python 3.12, no network), so
+  ``oracle/refrun`` executes ``gpsig/kernels.py`` + ``signature_algs.py`` +
+  ``lags.py`` where they lie under ``/root/reference`` on minimal EAGER numpy
+  stand-ins for the two dependencies (the ~30 TF ops the path calls, with TF's
+  semantics; ``Parameter`` / decorators / ``Kernel`` of GPflow); the outputs are the
+  committed fixtures ``tests/golden/trunc_ref.npz`` (``make_golden.py --trunc-ref``).
+  The numpy restatement and the C port reproduce them to 1e-13, the CUDA path to
+  1e-10 / 1e-5.  Independent of that: the brute-force definition of the first-order
+  kernel and the signature known answers of the reference notebooks.
 """

@@ -6,10 +6,12 @@ Every function follows one function of the reference (cited file:line relative
 to ``/root/reference``) and deliberately keeps the reference's *shape* of the
 computation: the lifted base-kernel tensor ``M`` is materialised (in row
 blocks, so it fits in RAM) and the recursions are whole-tensor exclusive
-cumulative sums, exactly as the TensorFlow graph does.  Parity status: the
-reference's TF-1.15 path cannot run here, so this restatement is pinned only
-by the known-answer properties in ``tests/test_oracle_known_answers.py``
-("parity unpinned" in the golden-vector sense).
+cumulative sums, exactly as the TensorFlow graph does.  Parity status: PINNED --
+``tests/golden/trunc_ref.npz`` holds what the reference's own ``kernels.py`` /
+``signature_algs.py`` / ``lags.py`` return when executed on eager numpy stand-ins
+for TensorFlow / GPflow (``oracle/refrun``); this restatement reproduces them to
+1e-13 (``tests/test_reference_golden_cpu.py``), next to the brute-force definition
+and the signature known answers of ``tests/test_oracle_cpu.py``.
 """
 import numpy as np
 

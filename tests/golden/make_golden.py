@@ -2,6 +2,11 @@
 (it needs /root/reference for the PDE vectors):
 
     python tests/golden/make_golden.py
+    python tests/golden/make_golden.py --trunc-ref
+
+* ``trunc_ref.npz``  outputs of the REFERENCE's own Python code for the truncated path (gpsig/kernels.py,
+                     signature_algs.py, lags.py executed where they lie, on the eager numpy stand-ins for
+                     TensorFlow / GPflow of oracle/refrun) -- pins the truncated path to the reference itself.
 
 * ``pde_ref.npz``    outputs of the REFERENCE's own compiled Cython solver
                      (gpsig/sigKer_fast.pyx via oracle/build_ref.py) -- pins the PDE path; the
@@ -9,8 +14,8 @@
                      the TF algebra of ``_KdiagGrad``) evaluated on the reference's own two grids.
 * ``trunc_oracle.npz`` outputs of the numpy restatement of the TensorFlow path
                      (oracle/trunc_np.py) on seeded inputs -- pins later refactors of the
-                     oracle and the CUDA path to today's numbers (the reference's TF-1.15
-                     path itself cannot run here: "parity unpinned" in the strict sense).
+                     oracle and the CUDA path to today's numbers (kept next to trunc_ref.npz,
+                     which holds the reference's own outputs for the same inputs).
 """
 import os
 import sys
@@ -68,7 +73,82 @@ def make_trunc():
     np.savez_compressed(os.path.join(HERE, 'trunc_oracle.npz'), **out)
 
 
+def _val(t):
+    while hasattr(t, 'a'):
+        t = t.a
+    return np.asarray(t, dtype=np.float64)
+
+
+# (oracle base name, reference class, reference constructor extras, oracle base parameters)
+REF_BASES = [('linear', 'SignatureLinear', {}, {}), ('rbf', 'SignatureRBF', {}, {}), ('cosine', 'SignatureCosine', {}, {}),
+             ('poly', 'SignaturePoly', dict(gamma=0.7, degree=3), dict(gamma=0.7, degree=3.0)), ('mix', 'SignatureMix', {}, {}),
+             ('matern12', 'SignatureMatern12', {}, {}), ('matern32', 'SignatureMatern32', {}, {}),
+             ('matern52', 'SignatureMatern52', {}, {})]
+
+
+def make_trunc_ref():
+    """Outputs of the REFERENCE's own gpsig/kernels.py + signature_algs.py + lags.py, executed where they lie under
+    /root/reference on the eager numpy stand-ins for TensorFlow / GPflow (oracle/refrun): pins the truncated path --
+    oracle and CUDA kernels -- to the reference's code itself.  Same inputs and keys as trunc_oracle.npz, plus every
+    base kernel, lags, difference = False and the sequence-vs-sequence covariances."""
+    from oracle import refrun
+    ref = refrun.load_reference()
+    N, N2, L, L2, d, m, Mz = 6, 5, 14, 11, 3, 4, 4
+    X, Y = brownian(N, L, d, 101), brownian(N2, L2, d, 102)
+    Xf, Yf = X.reshape(N, -1), Y.reshape(N2, -1)
+    Y14 = brownian(N2, L, d, 104)                      # same length as X (the lag interpolation needs a common time grid)
+    ls = np.array([0.9, 1.2, 0.8])
+    var = np.linspace(0.5, 1.5, m + 1)
+    out = {'X': X, 'Y': Y, 'Y14': Y14, 'lengthscales': ls, 'variances': var, 'sigma': np.float64(1.5)}
+    for inc in (False, True):
+        out['Z_inc%d' % inc] = inducing_tensors(X, m, Mz, inc, 103)
+
+    def kern(cls, extra, **kw):
+        k = getattr(ref, cls)(L * d, d, m, lengthscales=ls, variances=var, **extra, **kw)
+        k.sigma = k.sigma * 0. + 1.5
+        return k
+
+    for base, cls in (('linear', 'SignatureLinear'), ('rbf', 'SignatureRBF')):
+        for order in (1, 2, m):
+            for norm in (False, True):
+                k = kern(cls, {}, order=order, normalization=norm)
+                tag = '%s_o%d_n%d' % (base, order, norm)
+                out['K_' + tag] = _val(k.K(Xf, Yf, return_levels=True))
+                out['Ksym_' + tag] = _val(k.K(Xf, return_levels=True))
+                out['Kdiag_' + tag] = _val(k.Kdiag(Xf, return_levels=True))
+                for inc in (False, True):
+                    Kzz, Kzx, Kxx = k.K_tens_n_seq_covs(out['Z_inc%d' % inc], Xf, return_levels=True, increments=inc)
+                    out['Kzz_%s_i%d' % (tag, inc)] = _val(Kzz)
+                    out['Kzx_%s_i%d' % (tag, inc)] = _val(Kzx)
+                    out['Kxxd_%s_i%d' % (tag, inc)] = _val(Kxx)
+    # every base kernel, first order (the BASELINE configs), summed levels and the per-level diagonals
+    for base, cls, extra, _ in REF_BASES:
+        for norm in (False, True):
+            k = kern(cls, extra, order=1, normalization=norm)
+            tag = '%s_n%d' % (base, norm)
+            out['Kall_' + tag] = _val(k.K(Xf, Yf))
+            out['Kdiagall_' + tag] = _val(k.Kdiag(Xf))
+            out['Kzxall_' + tag] = _val(k.K_tens_vs_seq(out['Z_inc1'], Xf, increments=True))
+            out['Kzzall_' + tag] = _val(k.K_tens(out['Z_inc1'], increments=True))
+    # options: no differencing, lags, the sequence-vs-sequence covariance triple
+    k = kern('SignatureRBF', {}, order=1, normalization=True, difference=False)
+    out['Knodiff_rbf'] = _val(k.K(Xf, Yf, return_levels=True))
+    k = kern('SignatureRBF', {}, order=1, normalization=False, difference=False)
+    out['Knodiff_rbf_n0'] = _val(k.K(Xf, Yf, return_levels=True))
+    for norm in (False, True):
+        k = kern('SignatureRBF', {}, order=1, normalization=norm, num_lags=2)
+        out['Klags_rbf_n%d' % norm] = _val(k.K(Xf, Y14.reshape(N2, -1), return_levels=True))
+        out['Kdiaglags_rbf_n%d' % norm] = _val(k.Kdiag(Xf, return_levels=True))
+        k = kern('SignatureRBF', {}, order=1, normalization=norm)
+        Kxx, Kxx2, Kx2x2 = k.K_seq_n_seq_covs(Xf, Yf, return_levels=True)
+        out['Ksns_xx_n%d' % norm], out['Ksns_xx2_n%d' % norm], out['Ksns_x2x2_n%d' % norm] = _val(Kxx), _val(Kxx2), _val(Kx2x2)
+    np.savez_compressed(os.path.join(HERE, 'trunc_ref.npz'), **out)
+
+
 if __name__ == '__main__':
-    make_pde()
-    make_trunc()
+    if '--trunc-ref' in sys.argv:       # in a process of its own: the stand-in `tensorflow` must be the first one imported
+        make_trunc_ref()
+    else:
+        make_pde()
+        make_trunc()
     print('wrote', sorted(f for f in os.listdir(HERE) if f.endswith('.npz')))
