@@ -36,3 +36,9 @@ def load_reference(root='/root/reference'):
     pkg.__path__ = [pkg_dir]
     sys.modules['gpsig'] = pkg
     return importlib.import_module('gpsig.kernels')
+
+
+def load_reference_inducing(root='/root/reference'):
+    """``gpsig.inducing_variables`` of the reference (InducingTensors / InducingSequences, Kuu, Kuf, Kuu_Kuf_Kff)."""
+    load_reference(root)
+    return importlib.import_module('gpsig.inducing_variables')

@@ -25,3 +25,15 @@ class Kernel:
             if X2 is not None:
                 X2 = tf.gather(X2, self.active_dims, axis=-1)
         return X, X2
+
+
+class Combination(Kernel):
+    pass
+
+
+class Sum(Combination):
+    pass
+
+
+class Product(Combination):
+    pass

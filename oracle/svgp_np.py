@@ -6,8 +6,10 @@ TEST INFRASTRUCTURE ONLY (see ``oracle/__init__.py``).
 * ``base_conditional``: the algorithm lives in the reference's un-vendored dependency **gpflow==1.5.1**
   (``requirements.txt:8``; call site gpsig/models.py:116); restated from that release's
   ``gpflow/conditionals.py:base_conditional`` (Cholesky of Kmm, two triangular solves, ``fvar = Knn - A^T A +
-  (L_q^T A)^T (L_q^T A)``).  Parity unpinned in the golden-vector sense (GPflow cannot be installed here); it is
-  checked against the closed-form Gaussian conditional instead (tests/test_oracle_cpu.py).
+  (L_q^T A)^T (L_q^T A)``).  That one function is unpinned in the golden-vector sense (GPflow is not under
+  /root/reference and cannot be installed here); it is checked against the closed-form Gaussian conditional instead
+  (tests/test_oracle_cpu.py).  ``Kuu_Kuf_Kff`` above IS pinned: tests/golden/trunc_ref.npz holds what the reference's own
+  gpsig/inducing_variables.py returns (oracle/refrun), tests/test_reference_golden_cpu.py.
 """
 import numpy as np
 import scipy.linalg as sla

@@ -142,6 +142,36 @@ def make_trunc_ref():
         k = kern('SignatureRBF', {}, order=1, normalization=norm)
         Kxx, Kxx2, Kx2x2 = k.K_seq_n_seq_covs(Xf, Yf, return_levels=True)
         out['Ksns_xx_n%d' % norm], out['Ksns_xx2_n%d' % norm], out['Ksns_x2x2_n%d' % norm] = _val(Kxx), _val(Kxx2), _val(Kx2x2)
+    # spectral base kernel: the constructor draws alpha / omega / gamma itself (kernels.py:1092-1094), read back here.
+    # Only the un-normalised K(X, X2) can be evaluated in the reference (its batched 3-D call fails, see gpsig_b200/kernels.py)
+    for fam in ('rbf', 'exp'):
+        np.random.seed(7)
+        k = getattr(ref, 'SignatureSpectral')(L * d, d, m, family=fam, Q=3, variances=var, normalization=False)
+        k.sigma = k.sigma * 0. + 1.5
+        for nm in ('alpha', 'omega', 'gamma'):
+            out['spec_%s_%s' % (fam, nm)] = _val(getattr(k, nm))
+        out['Kspec_' + fam] = _val(k.K(Xf, Yf, return_levels=True))
+    # the SVGP glue around the path (gpsig/inducing_variables.py:51-137): Kuu_Kuf_Kff / Kuu / Kuf for inducing tensors
+    # (both forms, with and without the per-level mixing weights) and inducing sequences
+    iv = refrun.load_reference_inducing()
+    import tensorflow as tf_stub
+    rng = np.random.default_rng(106)
+    Zs = brownian(4, 9, d, 105)
+    out['Zseq'] = Zs
+    out['W_tens'] = np.eye(Mz)[None] + 0.3 * rng.standard_normal((m, Mz, Mz))
+    out['W_seq'] = np.eye(4)[None] + 0.3 * rng.standard_normal((m, 4, 4))
+    k = kern('SignatureRBF', {}, order=1, normalization=True)
+    for lw in (0, 1):
+        feats = [('tens_i%d' % inc, iv.InducingTensors(out['Z_inc%d' % inc], m, increments=bool(inc), learn_weights=bool(lw)), 'W_tens')
+                 for inc in (0, 1)] + [('seq', iv.InducingSequences(Zs, m, learn_weights=bool(lw)), 'W_seq')]
+        for name, feat, wkey in feats:
+            if lw:
+                feat.W = tf_stub.Tensor(out[wkey])
+            Kzz, Kzx, Kxx = iv.Kuu_Kuf_Kff(feat, k, Xf, jitter=1e-3)
+            tag = 'glue_%s_w%d' % (name, lw)
+            out[tag + '_Kzz'], out[tag + '_Kzx'], out[tag + '_Kxx'] = _val(Kzz), _val(Kzx), _val(Kxx)
+            out[tag + '_Kuu'] = _val(iv.Kuu(feat, k, jitter=1e-3))
+            out[tag + '_Kuf'] = _val(iv.Kuf(feat, k, Xf))
     np.savez_compressed(os.path.join(HERE, 'trunc_ref.npz'), **out)
 
 

@@ -91,3 +91,38 @@ def test_options_no_difference_lags_seq_covs(g, dtype):
         assert rel_err(_np(Kxx), g['Ksns_xx_n%d' % norm]) < tol
         assert rel_err(_np(Kxx2), g['Ksns_xx2_n%d' % norm]) < tol
         assert rel_err(_np(Kx2x2), g['Ksns_x2x2_n%d' % norm]) < tol
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("family", ['rbf', 'exp'])
+def test_spectral_base_kernel(g, dtype, family):
+    from gpsig_b200 import kernels
+    N, L, d = g['X'].shape
+    k = kernels.SignatureSpectral(L * d, d, M, family=family, Q=3, normalization=False)
+    k.sigma, k.variances = float(g['sigma']), g['variances']
+    k.alpha, k.omega, k.gamma = (g['spec_%s_%s' % (family, nm)] for nm in ('alpha', 'omega', 'gamma'))
+    X, Y = _dev(g['X'].reshape(N, -1), dtype), _dev(g['Y'].reshape(g['Y'].shape[0], -1), dtype)
+    assert rel_err(_np(k.K(X, Y, return_levels=True)), g['Kspec_' + family]) < TOL[dtype]
+
+
+@pytest.mark.parametrize("lw", [0, 1])
+def test_svgp_glue_kuu_kuf_kff(g, lw):
+    """Kuu_Kuf_Kff / Kuu / Kuf of gpsig/inducing_variables.py:51-137, as the reference's own module returns them."""
+    from gpsig_b200.inducing_variables import InducingSequences, InducingTensors, Kuf, Kuu, Kuu_Kuf_Kff
+    dt = torch.float64
+    k = _kern(g, 'SignatureRBF', order=1, normalization=True)
+    N = g['X'].shape[0]
+    X = _dev(g['X'].reshape(N, -1), dt)
+    feats = [('tens_i%d' % inc, InducingTensors(_dev(g['Z_inc%d' % inc], dt), M, increments=bool(inc), learn_weights=bool(lw)), 'W_tens')
+             for inc in (0, 1)]
+    feats.append(('seq', InducingSequences(_dev(g['Zseq'], dt), M, learn_weights=bool(lw)), 'W_seq'))
+    for name, feat, wkey in feats:
+        if lw:
+            feat.W = _dev(g[wkey], dt)
+        tag = 'glue_%s_w%d' % (name, lw)
+        Kzz, Kzx, Kxx = Kuu_Kuf_Kff(feat, k, X, jitter=1e-3)
+        assert rel_err(_np(Kzz), g[tag + '_Kzz']) < 1e-10
+        assert rel_err(_np(Kzx), g[tag + '_Kzx']) < 1e-10
+        assert rel_err(_np(Kxx), g[tag + '_Kxx']) < 1e-10
+        assert rel_err(_np(Kuu(feat, k, jitter=1e-3)), g[tag + '_Kuu']) < 1e-10
+        assert rel_err(_np(Kuf(feat, k, X)), g[tag + '_Kuf']) < 1e-10

@@ -86,3 +86,30 @@ def test_c_port_raw_levels(g, base):
     R = c_oracle.trunc_gram(X, Y, M, base)
     ref = g['K_%s_o1_n0' % base] / (float(g['sigma']) * g['variances'])[:, None, None]
     assert rel_err(R, ref) < 1e-13
+
+
+@pytest.mark.parametrize("family", ['rbf', 'exp'])
+def test_spectral_base_kernel(g, family):
+    """SignatureSpectral (kernels.py:1084-1122) with the parameters the reference's constructor drew."""
+    N, L, d = g['X'].shape
+    o = trunc_np.SignatureKernelOracle(L * d, d, M, base='spectral', lengthscales=None, variances=g['variances'], sigma=float(g['sigma']),
+                                       normalization=False, family=family, alpha=g['spec_%s_alpha' % family],
+                                       omega=g['spec_%s_omega' % family], gamma=g['spec_%s_gamma' % family])
+    assert rel_err(o.K(_flat(g['X']), _flat(g['Y']), return_levels=True), g['Kspec_' + family]) < 1e-13
+
+
+@pytest.mark.parametrize("lw", [0, 1])
+def test_svgp_glue_kuu_kuf_kff(g, lw):
+    """gpsig/inducing_variables.py:51-137 executed by the reference itself vs oracle/svgp_np.py (inducing tensors in both
+    forms, inducing sequences; with the per-level mixing weights W)."""
+    from oracle import svgp_np
+    o = _oracle(g, 'rbf', order=1, normalization=True)
+    X = _flat(g['X'])
+    cases = [('tens_i%d' % inc, g['Z_inc%d' % inc], dict(increments=bool(inc)), g['W_tens']) for inc in (0, 1)]
+    cases.append(('seq', _flat(g['Zseq']), dict(sequences=True), g['W_seq']))
+    for name, Z, kw, W in cases:
+        tag = 'glue_%s_w%d' % (name, lw)
+        Kzz, Kzx, Kxx = svgp_np.Kuu_Kuf_Kff(o, Z, X, W=W if lw else None, jitter=1e-3, **kw)
+        assert rel_err(Kzz, g[tag + '_Kzz']) < 1e-12
+        assert rel_err(Kzx, g[tag + '_Kzx']) < 1e-12
+        assert rel_err(Kxx, g[tag + '_Kxx']) < 1e-12
