@@ -38,6 +38,21 @@ def load_reference(root='/root/reference'):
     return importlib.import_module('gpsig.kernels')
 
 
+def load_reference_pde(root='/root/reference'):
+    """``gpsig.kernels_pde`` of the reference with ``implementation='cython'``: its ``.sigKer_fast`` import resolves to
+    the reference's own Cython solver compiled by oracle/build_ref.py into oracle/_ref/ (built from the sources where
+    they lie)."""
+    load_reference(root)
+    ref_dir = os.path.join(os.path.dirname(HERE), '_ref')
+    pkg = sys.modules['gpsig']
+    if ref_dir not in pkg.__path__:
+        pkg.__path__.append(ref_dir)
+    gp = os.path.join(root, 'gpsig')
+    if gp not in sys.path:
+        sys.path.append(gp)                       # kernels_pde.py:24-25 does ``from covariance_op import ...``
+    return importlib.import_module('gpsig.kernels_pde')
+
+
 def load_reference_inducing(root='/root/reference'):
     """``gpsig.inducing_variables`` of the reference (InducingTensors / InducingSequences, Kuu, Kuf, Kuu_Kuf_Kff)."""
     load_reference(root)

@@ -222,6 +222,53 @@ def _unary(f):
 square, sqrt, exp, log, cos, sin, floor, ceil, abs = (_unary(f) for f in (np.square, np.sqrt, np.exp, np.log, np.cos, np.sin, np.floor, np.ceil, np.abs))
 
 
+def repeat(x, repeats, axis=None):
+    return _t(np.repeat(_a(x), int(_a(repeats)), axis=axis))
+
+
+def reverse(x, axis, name=None):
+    return _t(np.flip(_a(x), axis=tuple(int(v) for v in np.atleast_1d(_a(axis)))))
+
+
+class math:
+    @staticmethod
+    def pow(x, y):
+        return _t(np.power(_a(x), _a(y)))
+
+
+class dtypes:
+    cast = staticmethod(cast)
+
+
+# graph plumbing of the Cython path (kernels_pde.py:444-463): py_func evaluates at once, gradients are not registered
+def py_func(func, inp, Tout, stateful=True, name=None):
+    outs = func(*[_a(v) if isinstance(v, Tensor) else v for v in inp])
+    return [_t(np.asarray(o)) for o in outs]
+
+
+def RegisterGradient(name):
+    def deco(fn):
+        return fn
+    return deco
+
+
+class _Graph:
+    import contextlib as _cl
+
+    @_cl.contextmanager
+    def gradient_override_map(self, mapping):
+        yield
+
+
+def get_default_graph():
+    return _Graph()
+
+
+def load_op_library(path):
+    """The compiled TF custom op (covariance_op/untrunc_cov_op_gpu.so) does not exist here; nothing on the Cython path calls it."""
+    return None
+
+
 def random_uniform(*args, **kwargs):
     raise NotImplementedError('low-rank (randomised) paths are out of scope of this stand-in')
 

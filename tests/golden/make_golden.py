@@ -4,6 +4,8 @@
     python tests/golden/make_golden.py
     python tests/golden/make_golden.py --trunc-ref
 
+* ``pde_ref_py.npz`` the reference's PDE Python layer on the same stand-ins: ``UntruncSignatureKernel.Kdiag`` (lengthscales,
+                     sigma, lags) and its own backward function ``_KdiagGrad``.
 * ``trunc_ref.npz``  outputs of the REFERENCE's own Python code for the truncated path (gpsig/kernels.py,
                      signature_algs.py, lags.py executed where they lie, on the eager numpy stand-ins for
                      TensorFlow / GPflow of oracle/refrun) -- pins the truncated path to the reference itself.
@@ -175,9 +177,44 @@ def make_trunc_ref():
     np.savez_compressed(os.path.join(HERE, 'trunc_ref.npz'), **out)
 
 
+def make_pde_ref_py():
+    """The reference's PDE PYTHON layer executed on the stand-ins (oracle/refrun.load_reference_pde; its Cython solver is the
+    compiled oracle/_ref module): ``UntruncSignatureKernel.Kdiag`` with lengthscales / sigma / lags (kernels_pde.py:136-185)
+    and its hand-written backward ``_KdiagGrad`` (kernels_pde.py:465-509), called with the forward op's inputs and outputs
+    as TensorFlow would.  Same X as pde_ref.npz."""
+    from oracle import refrun
+    kp = refrun.load_reference_pde()
+    import tensorflow as tf_stub
+    X = np.load(os.path.join(HERE, 'pde_ref.npz'))['X']
+    N, L, d = X.shape
+    ls = np.array([0.9, 1.2, 0.8])
+    gout = np.random.default_rng(107).standard_normal(N)
+    out = {'X': X, 'lengthscales': ls, 'sigma': np.float64(1.7), 'gout': gout}
+
+    class Op:
+        pass
+
+    for order in (0, 1, 2):
+        k = kp.UntruncSignatureKernel(L * d, d, lengthscales=ls, order=order, implementation='cython')
+        k.sigma = k.sigma * 0. + 1.7
+        out['Kdiag_class_order%d' % order] = _val(k.Kdiag(X.reshape(N, -1)))
+        K, K_rev = (np.array(a) for a in kp.sig_kern_diag(X, order))
+        op = Op()
+        op.inputs = [tf_stub.Tensor(X), tf_stub.Tensor(np.int64(order))]
+        op.outputs = [tf_stub.Tensor(K.copy()), tf_stub.Tensor(K_rev.copy())]
+        G = np.zeros_like(K)
+        G[:, -1, -1] = gout
+        grad, _ = kp._KdiagGrad(op, tf_stub.Tensor(G), None)
+        out['KdiagGrad_fn_order%d' % order] = _val(grad)
+    k = kp.UntruncSignatureKernel(L * d, d, lengthscales=ls, order=1, num_lags=2, implementation='cython')
+    out['Kdiag_class_lags2_order1'] = _val(k.Kdiag(X.reshape(N, -1)))
+    np.savez_compressed(os.path.join(HERE, 'pde_ref_py.npz'), **out)
+
+
 if __name__ == '__main__':
     if '--trunc-ref' in sys.argv:       # in a process of its own: the stand-in `tensorflow` must be the first one imported
         make_trunc_ref()
+        make_pde_ref_py()
     else:
         make_pde()
         make_trunc()

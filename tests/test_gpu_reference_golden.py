@@ -126,3 +126,24 @@ def test_svgp_glue_kuu_kuf_kff(g, lw):
         assert rel_err(_np(Kxx), g[tag + '_Kxx']) < 1e-10
         assert rel_err(_np(Kuu(feat, k, jitter=1e-3)), g[tag + '_Kuu']) < 1e-10
         assert rel_err(_np(Kuf(feat, k, X)), g[tag + '_Kuf']) < 1e-10
+
+
+def test_pde_python_layer_and_backward_function():
+    """tests/golden/pde_ref_py.npz: the reference's ``UntruncSignatureKernel.Kdiag`` (Cython implementation, with
+    lengthscales / sigma / lags) and its own ``_KdiagGrad`` executed on the stand-ins, vs the CUDA kernels."""
+    from gpsig_b200 import kernels_pde
+    g = np.load(os.path.join(GOLD, 'pde_ref_py.npz'))
+    X, ls, gout = g['X'], g['lengthscales'], g['gout']
+    N, L, d = X.shape
+    Xd = _dev(X.reshape(N, -1), torch.float64)
+    for order in (0, 1, 2):
+        k = kernels_pde.UntruncSignatureKernel(L * d, d, lengthscales=ls, order=order, implementation='cython')
+        k.sigma = float(g['sigma'])
+        assert rel_err(_np(k.Kdiag(Xd)), g['Kdiag_class_order%d' % order]) < 1e-10
+        # the reference's backward function differentiates w.r.t. the op's input sequences
+        k0 = kernels_pde.UntruncSignatureKernel(L * d, d, lengthscales=None, order=order, implementation='cython')
+        Xg = Xd.clone().requires_grad_()
+        (k0.Kdiag(Xg) * _dev(gout, torch.float64)).sum().backward()
+        assert rel_err(_np(Xg.grad).reshape(N, L, d), g['KdiagGrad_fn_order%d' % order]) < 1e-10
+    k = kernels_pde.UntruncSignatureKernel(L * d, d, lengthscales=ls, order=1, num_lags=2, implementation='cython')
+    assert rel_err(_np(k.Kdiag(Xd)), g['Kdiag_class_lags2_order1']) < 1e-10

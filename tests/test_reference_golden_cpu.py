@@ -113,3 +113,21 @@ def test_svgp_glue_kuu_kuf_kff(g, lw):
         assert rel_err(Kzz, g[tag + '_Kzz']) < 1e-12
         assert rel_err(Kzx, g[tag + '_Kzx']) < 1e-12
         assert rel_err(Kxx, g[tag + '_Kxx']) < 1e-12
+
+
+def test_pde_python_layer_and_backward_function():
+    """tests/golden/pde_ref_py.npz: the reference's ``UntruncSignatureKernel.Kdiag`` (kernels_pde.py:136-185, Cython
+    implementation = the compiled oracle/_ref solver) and its own ``_KdiagGrad`` (kernels_pde.py:465-509) executed on the
+    stand-ins.  The backward function's output is BIT-EQUAL to the transcription the CUDA backward is tested against
+    (``kdiag_grad_order*`` of pde_ref.npz, oracle/pde_np.kdiag_grad_from_grids)."""
+    from oracle import pde_np
+    g = np.load(os.path.join(GOLD, 'pde_ref_py.npz'))
+    p = np.load(os.path.join(GOLD, 'pde_ref.npz'))
+    X, ls, gout = g['X'], g['lengthscales'], g['gout']
+    assert np.array_equal(X, p['X'])
+    for order in (0, 1, 2):
+        assert np.array_equal(float(g['sigma']) * pde_np.pde_kernel(X / ls, None, order), g['Kdiag_class_order%d' % order])
+        assert np.array_equal(p['kdiag_grad_order%d' % order] * gout[:, None, None], g['KdiagGrad_fn_order%d' % order])
+    o = trunc_np.SignatureKernelOracle(X.shape[1] * X.shape[2], X.shape[2], 2, base='linear', lengthscales=ls, num_lags=2)
+    Xl = o._seq(X.reshape(X.shape[0], -1))                 # lags + scaling as kernels.py / kernels_pde.py:136-157 apply them
+    assert rel_err(pde_np.pde_kernel(Xl, None, 1), g['Kdiag_class_lags2_order1']) < 1e-13
