@@ -14,6 +14,13 @@ static int lift_block(const LiftParams& P, const LiftMmaOperands* mma, cudaStrea
   if constexpr (sizeof(T) == 4) {
     if (mma && mma->xop) { if (int rc = launch_lift_mma<COLS>(P, *mma, s)) return rc; done = true; }
   }
+  if constexpr (sizeof(T) == 8) {
+    if (!done && getenv("GPSIG_LIFT_TILE_OLD") == nullptr) {
+      if (int rc = lift_tile2_wide(P.L, P.L2) ? launch_lift_tile2<T, COLS, 7, 7>(P, npair_slots, s) : launch_lift_tile2<T, COLS, 4, 4>(P, npair_slots, s))
+        return rc;
+      done = true;
+    }
+  }
   if (!done) {
     dim3 grid((unsigned)npair_slots, (unsigned)((P.L + 63) / 64));
     lift_tile_kernel<T, COLS><<<grid, 256, 0, s>>>(P);

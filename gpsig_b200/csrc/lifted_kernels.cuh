@@ -146,6 +146,213 @@ __global__ void __launch_bounds__(256) lift_tile_kernel(const LiftParams P) {
 }
 
 // ---------------------------------------------------------------------------
+// (A') float64 lift, second version: one CTA per (pair, BM x BN block) with BM = 16 TM, BN = 16 TN and a TM x TN register
+// tile per thread whose rows / columns are STRIDED by 16 (thread (ty, tx) owns rows ty + 16 a, columns tx + 16 b), so the
+// block can be 112 x 112 (TM = TN = 7: a 100-point pair wastes 20 % of the tile, not the 39 % of 64-blocks), the
+// shared-memory reads are a broadcast (A) and 16 consecutive doubles (B), 49 DFMA per 14 loads.  k-slabs of 16 are
+// double buffered: the next slab is fetched into registers while the current one is multiplied, one barrier per slab.
+// Only the L2 real columns go through the GEMM; the slots past the last column (the recursion wants 32 COLS of them)
+// repeat the last column's value, written by the thread that owns it.
+// c_large_d float64 (N = N2 = 1000, L = 100, d = 126): lift 430 -> see DESIGN 4.8.
+// ---------------------------------------------------------------------------
+template <typename T, int COLS, int TM, int TN>
+__global__ void __launch_bounds__(256) lift_tile_kernel2(const LiftParams P, const int ncb, const int nblk, const int nitems) {
+  constexpr int BM = 16 * TM, BN = 16 * TN, BK = 16;
+  constexpr int SA = BM + 1, SB = BN + 1;            // odd strides: the transposing stores of a k-slab are conflict free
+  extern __shared__ __align__(16) unsigned char lift2_smem[];
+  T* As = reinterpret_cast<T*>(lift2_smem);          // [2][BK][SA]
+  T* Bs = As + 2 * BK * SA;                          // [2][BK][SB]
+  T* Qs = Bs + 2 * BK * SB;                          // [BM + BN] squared norms of the block's rows / columns
+  T* VL = Qs + BM + BN;                              // [BM] the last real column's value per row (for the padded slots)
+  static_assert(sizeof(T) == 8, "lift_tile_kernel2 is the float64 lift");
+  static_assert(BM + BN <= 256, "one squared norm per thread");
+  const int L = P.L, L2 = P.L2, DP = P.DP;
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  // Work items (pair, block of the pair) are taken round robin by a PERSISTENT grid: with 200 registers only one CTA
+  // fits an SM, so the first k-slab of the NEXT item is fetched (into registers) before the epilogue of the current
+  // one - the global-load latency and the epilogue would otherwise be exposed once per item.
+  struct Item { const T* x; const T* y; T* S; int n, row0, col0; };
+  auto setup = [&](int it, Item& I) -> bool {
+    const int pi = it / nblk, blk = it - pi * nblk;
+    const int sg = pi / P.SP;
+    I.n = pi - sg * P.SP;
+    int i, j;
+    if (sg >= P.nstreams || !lift_pair(P, sg, I.n, i, j)) return false;
+    I.row0 = (blk / ncb) * BM; I.col0 = (blk % ncb) * BN;
+    I.x = static_cast<const T*>(P.xp) + (size_t)i * P.xblk;
+    I.y = static_cast<const T*>(P.yp) + (size_t)j * P.yblk;
+    I.S = static_cast<T*>(P.scratch) + (size_t)sg * P.stream_elems;
+    return true;
+  };
+  auto next_valid = [&](int it, Item& I) -> int {
+    while (it < nitems && !setup(it, I)) it += gridDim.x;
+    return it;
+  };
+  // loader: unit u = (row, pair of k); a slab of A has BM * 8 units of two doubles
+  constexpr int UA = (BM * 8 + 255) / 256, UB = (BN * 8 + 255) / 256;
+  using V2 = typename Vec16<T>::type;                // two doubles
+  V2 ra[UA], rb[UB];
+  auto fetch = [&](const Item& I, int k0) {
+#pragma unroll
+    for (int u = 0; u < UA; ++u) {
+      const int idx = tid + 256 * u, r = idx >> 3, kk = (idx & 7) * 2;
+      if (idx < BM * 8) ra[u] = *reinterpret_cast<const V2*>(I.x + (size_t)min(I.row0 + r, L - 1) * DP + k0 + kk);
+    }
+#pragma unroll
+    for (int u = 0; u < UB; ++u) {
+      const int idx = tid + 256 * u, r = idx >> 3, kk = (idx & 7) * 2;
+      if (idx < BN * 8) rb[u] = *reinterpret_cast<const V2*>(I.y + (size_t)min(I.col0 + r, L2 - 1) * DP + k0 + kk);
+    }
+  };
+  auto stash = [&](int buf) {
+    T* A = As + buf * BK * SA;
+    T* B = Bs + buf * BK * SB;
+#pragma unroll
+    for (int u = 0; u < UA; ++u) {
+      const int idx = tid + 256 * u, r = idx >> 3, kk = (idx & 7) * 2;
+      if (idx < BM * 8) { A[kk * SA + r] = ra[u].x; A[(kk + 1) * SA + r] = ra[u].y; }
+    }
+#pragma unroll
+    for (int u = 0; u < UB; ++u) {
+      const int idx = tid + 256 * u, r = idx >> 3, kk = (idx & 7) * 2;
+      if (idx < BN * 8) { B[kk * SB + r] = rb[u].x; B[(kk + 1) * SB + r] = rb[u].y; }
+    }
+  };
+  const T p0 = T(P.p0), p1 = T(P.p1);
+  const int base = P.base;
+  constexpr int LP2 = 32 * COLS;
+  const double tab = exp2((double)(tid & 31) * (1.0 / 32.0));
+
+  Item cur;
+  int it = next_valid((int)blockIdx.x, cur);
+  if (it >= nitems) return;
+  fetch(cur, 0);
+  for (;;) {
+    stash(0);
+    __syncthreads();
+    Item nxt;
+    const int nx = next_valid(it + (int)gridDim.x, nxt);
+    // squared norms of this block's points: requested now, parked in shared memory before the epilogue
+    T qv = T(0);
+    if (tid < BM) qv = cur.x[(size_t)L * DP + min(cur.row0 + tid, L - 1)];
+    else if (tid < BM + BN) qv = cur.y[(size_t)L2 * DP + min(cur.col0 + tid - BM, L2 - 1)];
+    T acc[TM][TN];
+#pragma unroll
+    for (int a = 0; a < TM; ++a)
+#pragma unroll
+      for (int b = 0; b < TN; ++b) acc[a][b] = T(0);
+    int buf = 0;
+    for (int k0 = 0; k0 < DP; k0 += BK) {
+      const bool more = k0 + BK < DP;
+      if (more) fetch(cur, k0 + BK);
+      else if (nx < nitems) fetch(nxt, 0);
+      const T* A = As + buf * BK * SA + ty;
+      const T* B = Bs + buf * BK * SB + tx;
+#pragma unroll
+      for (int k = 0; k < BK; ++k) {
+        T av[TM], bv[TN];
+#pragma unroll
+        for (int a = 0; a < TM; ++a) av[a] = A[k * SA + 16 * a];
+#pragma unroll
+        for (int b = 0; b < TN; ++b) bv[b] = B[k * SB + 16 * b];
+#pragma unroll
+        for (int a = 0; a < TM; ++a)
+#pragma unroll
+          for (int b = 0; b < TN; ++b) acc[a][b] = gfma<T>(av[a], bv[b], acc[a][b]);
+      }
+      if (more) stash(buf ^ 1);
+      __syncthreads();
+      buf ^= 1;
+    }
+    // base kernel (kernels.py:946-1173) + store in the skewed order of the recursion
+    const int row0 = cur.row0, col0 = cur.col0, n = cur.n;
+    T* S = cur.S;
+    if (tid < BM + BN) Qs[tid] = qv;
+    __syncthreads();
+    const T* xsq = Qs + ty;                           // [16 a]
+    const T* ysq = Qs + BM + tx;                      // [16 b]
+    auto put = [&](int p, int q, T v) {
+      const int t = q / COLS, c = q - t * COLS;
+      S[((size_t)(n * L + p + t) * 32 + t) * COLS + c] = v;
+    };
+    const bool last_cols = col0 <= L2 - 1 && L2 - 1 < col0 + BN;      // this block holds the last real column
+    if (base == GPSIG_BASE_RBF) {
+      // exp(-(|x|^2 + |y|^2 - 2 x.y) / 2) = 2^((x.y - |x|^2/2 - |y|^2/2) log2 e) by the table exp2 of the fused kernels
+      // (exp2_tab32: 9 FP64 instructions + a table shuffle against ~35 for exp(); the warp stays convergent: every lane
+      // evaluates all its TM x TN slots on clamped indices, only the stores are predicated)
+      constexpr double kLog2e = 1.4426950408889634;
+      T yc[TN];
+#pragma unroll
+      for (int b = 0; b < TN; ++b) yc[b] = T(-0.5 * kLog2e) * ysq[16 * b];
+#pragma unroll
+      for (int a = 0; a < TM; ++a) {
+        const int p = row0 + ty + 16 * a;
+        const T xc = T(-0.5 * kLog2e) * xsq[16 * a];
+#pragma unroll
+        for (int b = 0; b < TN; ++b) {
+          const int q = col0 + tx + 16 * b;
+          const T v = T(exp2_tab32((double)gfma<T>(acc[a][b], T(kLog2e), xc + yc[b]), tab));
+          if (p < L && q < L2) put(p, q, v);
+          if (q == L2 - 1) VL[ty + 16 * a] = v;
+        }
+      }
+    } else {
+#pragma unroll
+      for (int a = 0; a < TM; ++a) {
+        const int p = row0 + ty + 16 * a;
+        if (p >= L) continue;
+        const T xs = xsq[16 * a];
+#pragma unroll
+        for (int b = 0; b < TN; ++b) {
+          const int q = col0 + tx + 16 * b;
+          if (q >= L2) continue;
+          // one out-of-line copy of the base-kernel switch: inlined at all TM x TN sites it made 34 k instructions of
+          // epilogue, which ran out of the instruction cache (55 % of the samples)
+          const T v = base == GPSIG_BASE_LINEAR ? acc[a][b] : base_eval_call<T>(base, p0, p1, acc[a][b], xs, ysq[16 * b]);
+          put(p, q, v);
+          if (q == L2 - 1) VL[ty + 16 * a] = v;
+        }
+      }
+    }
+    // the slots past the last column repeat it (zero increments): all threads share the rows x (32 COLS - L2) stores
+    if (last_cols && LP2 > L2) {                      // uniform over the CTA
+      __syncthreads();
+      const int npad = LP2 - L2, nrow = min(BM, L - row0);
+      for (int e = tid; e < nrow * npad; e += 256) {
+        const int r = e / npad, qq = L2 + (e - r * npad);
+        put(row0 + r, qq, VL[r]);
+      }
+    }
+    if (nx >= nitems) break;
+    cur = nxt;
+    it = nx;
+  }
+}
+
+template <typename T, int COLS, int TM, int TN>
+int launch_lift_tile2(const LiftParams& P, int npair_slots, cudaStream_t s) {
+  constexpr int BM = 16 * TM, BN = 16 * TN, BK = 16;
+  const int nrb = (P.L + BM - 1) / BM, ncb = (P.L2 + BN - 1) / BN;
+  const size_t smem = ((size_t)2 * BK * ((BM + 1) + (BN + 1)) + 2 * BM + BN) * sizeof(T);
+  auto kern = lift_tile_kernel2<T, COLS, TM, TN>;
+  if (smem > 48 * 1024) GPSIG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int occ = 1;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 256, smem) != cudaSuccess || occ < 1) occ = 1;
+  const long nitems = (long)npair_slots * nrb * ncb;
+  if (nitems > 0x7fffffffL) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "too many lift tiles in one block (%ld)", nitems);
+  const long want = (long)occ * device_sm_count();
+  const unsigned grid = (unsigned)(nitems < want ? nitems : want);
+  kern<<<grid, 256, smem, s>>>(P, ncb, nrb * ncb, (int)nitems);
+  GPSIG_LAUNCH_CHECK("lift_tile_kernel2");
+  return GPSIG_OK;
+}
+// block shape by the waste of the pair's L x L2 points: 112 x 112 unless 64-blocks tile them tighter
+inline bool lift_tile2_wide(int L, int L2) {
+  auto cover = [](int n, int b) { return (long)((n + b - 1) / b) * b; };
+  return cover(L, 112) * cover(L2, 112) <= cover(L, 64) * cover(L2, 64);
+}
+
+// ---------------------------------------------------------------------------
 // (B) the lane-skewed recursion on a stream of lifted tiles: one warp per stream
 // ---------------------------------------------------------------------------
 template <typename T, int COLS> struct LiftVec;
