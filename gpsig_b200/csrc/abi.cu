@@ -11,6 +11,7 @@
 #include "generic_kernels.cuh"
 #include "lift_mma_kernel.cuh"
 #include "generic_vjp_kernels.cuh"
+#include "tens_lifted_kernels.cuh"
 
 namespace gpsig {
 
@@ -70,6 +71,8 @@ GPSIG_DECL_T(double)
 
 extern template int launch_lift<float>(LiftParams, void*, size_t, const LiftMmaOperands*, cudaStream_t);
 extern template int launch_lift<double>(LiftParams, void*, size_t, const LiftMmaOperands*, cudaStream_t);
+extern template int launch_tens_seq_lifted<float>(const TensSeqParams&, int, void*, size_t, cudaStream_t);
+extern template int launch_tens_seq_lifted<double>(const TensSeqParams&, int, void*, size_t, cudaStream_t);
 
 // K(X, X) computed on and above the diagonal only: out[l, i, j] = out[l, j, i] for i > j (32 x 32 tiles through
 // shared memory, both sides coalesced).  Every i > j entry is overwritten, so the result is exactly symmetric.
@@ -387,6 +390,12 @@ static int tens_vs_seq_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, in
   else P.return_levels = 1;
   P.out = out;
   P.sp.p = desc->spectral; P.sp.q = desc->spectral_q; P.sp.family = desc->spectral_family; P.d = d;
+  // d > 16, first order: the lifted form (GEMM of all tensor points against blocks of sequences + time recursion,
+  // tens_lifted_kernels.cuh); higher order / spectral: the general kernel
+  if (d > 16 && desc->order == 1 && desc->base != GPSIG_BASE_SPECTRAL && getenv("GPSIG_TENS_NO_LIFT") == nullptr) {
+    const size_t off = packed_bytes(TT * Mz, zs, d, sizeof(T)) + packed_bytes(N, L, d, sizeof(T));
+    return launch_tens_seq_lifted<T>(P, padded_dim(d), static_cast<char*>(ws) + off, ws_bytes - off, s);
+  }
   if (desc->order > 1 || desc->base == GPSIG_BASE_SPECTRAL || d > 16) return launch_tens_seq_generic<T>(P, desc->order, padded_dim(d), s);
   return dispatch_tens_seq<T>(P, desc->base, padded_dim(d), m, s);
 }
@@ -687,7 +696,9 @@ size_t gpsig_trunc_diag_workspace_bytes(int N, int L, int d, int elem) {
   return b;
 }
 size_t gpsig_tens_vs_seq_workspace_bytes(int Mz, int increments, int N, int L, int d, int m, int elem) {
-  return packed_bytes(m * (m + 1) / 2 * Mz, increments ? 2 : 1, d, elem) + packed_bytes(N, L, d, elem);
+  size_t b = packed_bytes(m * (m + 1) / 2 * Mz, increments ? 2 : 1, d, elem) + packed_bytes(N, L, d, elem);
+  if (d > 16) b += gpsig::tens_lift_bytes(Mz, increments ? 2 : 1, m, L, N, elem);      // lifted Kzx values of a block of sequences
+  return b;
 }
 
 int gpsig_trunc_gram_f64(const gpsig_trunc_desc* desc, const double* X, int N, int L, const double* X2, int N2, int L2,

@@ -3,6 +3,7 @@
 
 #include "lifted_kernels.cuh"
 #include "lift_mma_kernel.cuh"
+#include "tens_lifted_kernels.cuh"
 
 namespace gpsig {
 
@@ -122,5 +123,52 @@ int launch_lift(LiftParams P, void* scratch, size_t scratch_bytes, const LiftMma
 
 template int launch_lift<float>(LiftParams, void*, size_t, const LiftMmaOperands*, cudaStream_t);
 template int launch_lift<double>(LiftParams, void*, size_t, const LiftMmaOperands*, cudaStream_t);
+
+// ---- Kzx at d > 16 (tens_lifted_kernels.cuh): blocks of sequences, GEMM + recursion per block ----
+template <typename T, int TM, int TN>
+static int tens_lift_gemm(const TensSeqParams& P, int DP, int n0, int nb, T* C, cudaStream_t s) {
+  constexpr int BM = 16 * TM, BN = 16 * TN, BK = 16;
+  const int R = P.m * (P.m + 1) / 2 * P.zs * P.Mz;
+  const long E = (long)P.L * nb;
+  const int nrb = (R + BM - 1) / BM, ncb = (int)((E + BN - 1) / BN);
+  const size_t smem = ((size_t)2 * BK * ((BM + 1) + (BN + 1)) + BM + BN) * sizeof(T);
+  auto kern = tens_lift_gemm_kernel<T, TM, TN>;
+  if (smem > 48 * 1024) GPSIG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int occ = 1;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 256, smem) != cudaSuccess || occ < 1) occ = 1;
+  const long nitems = (long)nrb * ncb;
+  if (nitems > 0x7fffffffL || E > 0x7fffffffL) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "Kzx block too large (%ld tiles)", nitems);
+  const long want = (long)occ * device_sm_count();
+  kern<<<(unsigned)(nitems < want ? nitems : want), 256, smem, s>>>(P, DP, n0, nb, C, nrb, ncb);
+  GPSIG_LAUNCH_CHECK("tens_lift_gemm_kernel");
+  return GPSIG_OK;
+}
+
+template <typename T>
+int launch_tens_seq_lifted(const TensSeqParams& P, int DP, void* scratch, size_t scratch_bytes, cudaStream_t s) {
+  const int ncols = P.col_end - P.col_begin;
+  if (ncols <= 0 || P.Mz <= 0) return GPSIG_OK;
+  if (P.m < 1 || P.m > 8) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "num_levels=%d is not supported (1..8)", P.m);
+  // the plan is sized by N (like the workspace query), the blocks cover this call's columns
+  const int nbmax = tens_lift_block(P.Mz, P.zs, P.m, P.L, P.N, sizeof(T));
+  if (scratch_bytes < tens_lift_bytes(P.Mz, P.zs, P.m, P.L, P.N, sizeof(T)))
+    GPSIG_FAIL(GPSIG_ERR_WORKSPACE, "workspace too small for the lifted Kzx values");
+  T* C = static_cast<T*>(scratch);
+  prof_begin(s);
+  for (int n0 = 0; n0 < ncols; n0 += nbmax) {
+    const int nb = ncols - n0 < nbmax ? ncols - n0 : nbmax;
+    if (int rc = tens_lift_gemm<T, 7, 7>(P, DP, n0, nb, C, s)) return rc;
+    dim3 grid((unsigned)((nb + 127) / 128), (unsigned)P.Mz);
+    if (P.m <= 2) tens_lift_recur_kernel<T, 2><<<grid, 128, 0, s>>>(P, n0, nb, C);
+    else if (P.m <= 4) tens_lift_recur_kernel<T, 4><<<grid, 128, 0, s>>>(P, n0, nb, C);
+    else if (P.m <= 6) tens_lift_recur_kernel<T, 6><<<grid, 128, 0, s>>>(P, n0, nb, C);
+    else tens_lift_recur_kernel<T, 8><<<grid, 128, 0, s>>>(P, n0, nb, C);
+    GPSIG_LAUNCH_CHECK("tens_lift_recur_kernel");
+  }
+  prof_end(s);
+  return GPSIG_OK;
+}
+template int launch_tens_seq_lifted<float>(const TensSeqParams&, int, void*, size_t, cudaStream_t);
+template int launch_tens_seq_lifted<double>(const TensSeqParams&, int, void*, size_t, cudaStream_t);
 
 }  // namespace gpsig

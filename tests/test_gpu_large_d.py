@@ -175,3 +175,27 @@ def test_svgp_covariances_differentiable_at_large_d():
     (Kzz.sum() + (Kzx ** 2).sum() + Kxx.sum()).backward()
     for t in (Z.grad, k.lengthscales.grad):
         assert t is not None and bool(torch.isfinite(t).all()) and float(t.abs().max()) > 0
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("base", ['rbf', 'linear', 'matern32'])
+@pytest.mark.parametrize("increments", [False, True])
+def test_kzx_lifted_blocks_and_column_ranges(dtype, base, increments, monkeypatch):
+    """Kzx at d > 16 on the lifted form (tens_lifted_kernels.cuh): several blocks of sequences (scratch capped so that a
+    block holds 32 of them, the last one ragged), per-level output, a column sub-range."""
+    from gpsig_b200 import ops
+    from oracle.trunc_np import SignatureKernelOracle
+    monkeypatch.setenv('GPSIG_TENS_LIFT_CAP_KB', '400')
+    N, L, d, m, Mz = 75, 9, 20, 3, 7
+    X = brownian(N, L, d, 31) / np.sqrt(d / 8.0)
+    Z = inducing_tensors(X, m, Mz, increments, 32)
+    o = SignatureKernelOracle(L * d, d, m, base=base, normalization=False, lengthscales=None)
+    R = o._K_tens_vs_seq(Z, X, increments=increments)                      # [m+1, Mz, N]
+    scale = np.abs(R).max(axis=(1, 2), keepdims=True)
+    tol = 1e-10 if dtype == torch.float64 else 1e-5
+    G = ops.tens_vs_seq(_dev(Z, dtype), _dev(X, dtype), m, increments=increments, base=base).cpu().numpy()
+    assert np.max(np.abs(G - R) / scale) < tol
+    Gc = ops.tens_vs_seq(_dev(Z, dtype), _dev(X, dtype), m, increments=increments, base=base, cols=(10, 61)).cpu().numpy()
+    assert np.max(np.abs(Gc - R[:, :, 10:61]) / scale) < tol
+    Gs = ops.tens_vs_seq(_dev(Z, dtype), _dev(X, dtype), m, increments=increments, base=base, return_levels=False).cpu().numpy()
+    assert np.max(np.abs(Gs - R.sum(axis=0))) / np.abs(R.sum(axis=0)).max() < tol
