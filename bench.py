@@ -260,6 +260,20 @@ def other_configs(torch, ops, lib):
         out["c4_kzx_" + nm] = {"workload": "K_tens_vs_seq (increments), Mz=500, N=10000, L=100, d=8, m=4", "kernel": "tens_vs_seq_kernel2",
                                "kernel_ms": ms, "pairs_per_s": Mz * N / (ms * 1e-3), "flops_per_pair": 43574}
         del Xd, Zd
+    # the same at d = 28 (ArabicDigits with num_lags=1 and a time channel, the reference's own experiment shape): the
+    # lifted Kzx (tens_lift_gemm_kernel + tens_lift_recur_kernel)
+    d28 = 28
+    rng28 = np.random.default_rng(8)
+    X28 = np.cumsum(rng28.standard_normal((N, L, d28)) / np.sqrt(L), axis=1) / np.sqrt(d28 / 8.0)
+    Z28 = rng28.standard_normal((m * (m + 1) // 2, Mz, 2, d28)) * 0.5 / np.sqrt(d28 / 8.0)
+    for dt, nm in ((torch.float64, 'f64'), (torch.float32, 'f32')):
+        Xd = torch.as_tensor(X28, dtype=dt, device='cuda')
+        Zd = torch.as_tensor(Z28, dtype=dt, device='cuda')
+        ms = timed(lambda: ops.tens_vs_seq(Zd, Xd, m, increments=True, base='rbf', return_levels=False))
+        out["c4_kzx_d28_" + nm] = {"workload": "K_tens_vs_seq (increments), Mz=500, N=10000, L=100, d=28, m=4",
+                                   "kernel": "tens_lift_gemm_kernel + tens_lift_recur_kernel", "kernel_ms": ms,
+                                   "pairs_per_s": Mz * N / (ms * 1e-3)}
+        del Xd, Zd
     # c4 training step (train_gpsig.py:20,67-68): Kzz, Kzx, Kxx_diag of a minibatch of 50, forward + backward
     from gpsig_b200 import kernels as _k
     nb = 50

@@ -376,7 +376,7 @@ static int tens_vs_seq_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, in
   T* xp = reinterpret_cast<T*>(static_cast<char*>(ws) + packed_bytes(TT * Mz, zs, d, sizeof(T)));
   // first-order RBF: coordinates pre-scaled by sqrt(log2 e), the exponent feeds exp2 (tens_kernels.cuh)
   // d > 16 runs the general kernel (runtime loop over d), natural-base exponent
-  const double cscale = (d <= 16 && desc->order == 1 && desc->base == GPSIG_BASE_RBF) ? 1.2011224087864498 : 1.0;
+  const double cscale = (d <= 16 && !tens_lift_dims(d, sizeof(T)) && desc->order == 1 && desc->base == GPSIG_BASE_RBF) ? 1.2011224087864498 : 1.0;
   if (int rc = pack<T>(Z, TT * Mz, zs, d, ls, zp, s, 0, cscale)) return rc;
   if (int rc = pack<T>(X, N, L, d, ls, xp, s, 0, cscale)) return rc;
   TensSeqParams P;
@@ -392,7 +392,8 @@ static int tens_vs_seq_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, in
   P.sp.p = desc->spectral; P.sp.q = desc->spectral_q; P.sp.family = desc->spectral_family; P.d = d;
   // d > 16, first order: the lifted form (GEMM of all tensor points against blocks of sequences + time recursion,
   // tens_lifted_kernels.cuh); higher order / spectral: the general kernel
-  if (d > 16 && desc->order == 1 && desc->base != GPSIG_BASE_SPECTRAL && getenv("GPSIG_TENS_NO_LIFT") == nullptr) {
+  // (also float64 at d = 9..16, where the tensor's coordinates no longer fit the register tile of tens_vs_seq_kernel2)
+  if (tens_lift_dims(d, sizeof(T)) && desc->order == 1 && desc->base != GPSIG_BASE_SPECTRAL && getenv("GPSIG_TENS_NO_LIFT") == nullptr) {
     const size_t off = packed_bytes(TT * Mz, zs, d, sizeof(T)) + packed_bytes(N, L, d, sizeof(T));
     return launch_tens_seq_lifted<T>(P, padded_dim(d), static_cast<char*>(ws) + off, ws_bytes - off, s);
   }
@@ -697,7 +698,7 @@ size_t gpsig_trunc_diag_workspace_bytes(int N, int L, int d, int elem) {
 }
 size_t gpsig_tens_vs_seq_workspace_bytes(int Mz, int increments, int N, int L, int d, int m, int elem) {
   size_t b = packed_bytes(m * (m + 1) / 2 * Mz, increments ? 2 : 1, d, elem) + packed_bytes(N, L, d, elem);
-  if (d > 16) b += gpsig::tens_lift_bytes(Mz, increments ? 2 : 1, m, L, N, elem);      // lifted Kzx values of a block of sequences
+  if (gpsig::tens_lift_dims(d, elem)) b += gpsig::tens_lift_bytes(Mz, increments ? 2 : 1, m, L, N, elem);      // lifted Kzx values of a block of sequences
   return b;
 }
 

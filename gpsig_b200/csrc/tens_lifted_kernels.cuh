@@ -22,6 +22,9 @@
 namespace gpsig {
 
 constexpr size_t kTensLiftCap = (size_t)1 << 30;       // bytes of lifted values in flight
+// state dimensions that take the lifted form: above 16, and float64 from 9 (the register tile of tens_vs_seq_kernel2 holds
+// m zs (DP + 1) doubles: it stops fitting at DP = 16)
+inline bool tens_lift_dims(int d, int elem) { return d > 16 || (d > 8 && elem == 8); }
 // sequences per block (a multiple of 32 when there are that many) and the scratch it takes
 inline int tens_lift_block(int Mz, int zs, int m, int L, int ncols, int elem) {
   const size_t per_seq = (size_t)(m * (m + 1) / 2) * zs * Mz * L * elem;

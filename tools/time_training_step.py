@@ -33,15 +33,15 @@ def ev_time(fn, reps=5):
     return best
 
 
-L, d, m, Mz = 100, 8, 4, 500
+L, d, m, Mz = 100, int(os.environ.get('GPSIG_TIME_D', '8')), 4, 500      # GPSIG_TIME_D=28: the reference's ArabicDigits shape
 TT = m * (m + 1) // 2
-Zn = np.random.default_rng(2).standard_normal((TT, Mz, 2, d)) * 0.5
+Zn = np.random.default_rng(2).standard_normal((TT, Mz, 2, d)) * 0.5 / np.sqrt(d / 8.0)
 DTYPES = [getattr(torch, a) for a in sys.argv[1:] if a.startswith('float')] or [torch.float64, torch.float32]
 BATCHES = [int(a) for a in sys.argv[1:] if a.isdigit()] or [50, 1000]
 for dt in DTYPES:
     name = str(dt)[6:]
     for nb in BATCHES:
-        X = torch.as_tensor(brownian(nb, L, d, 0), dtype=dt, device='cuda').requires_grad_(True)
+        X = torch.as_tensor(brownian(nb, L, d, 0) / np.sqrt(d / 8.0), dtype=dt, device='cuda').requires_grad_(True)
         Z = torch.as_tensor(Zn, dtype=dt, device='cuda').requires_grad_(True)
 
         def diag_step():
@@ -71,7 +71,7 @@ for dt in DTYPES:
         print("%s minibatch %d: K_tens_n_seq_covs fwd+bwd %.3f ms" % (name, nb, ev_time(full_step)), flush=True)
 
 # Gram-sized backward (inducing sequences: K_seq_n_seq_covs): K(X, X2) raw levels, forward + backward
-for dt in DTYPES:
+for dt in (DTYPES if 'GPSIG_TIME_D' not in os.environ else []):
     for n in (64, 256):
         X = torch.as_tensor(brownian(n, L, d, 0), dtype=dt, device='cuda').requires_grad_(True)
         Y = torch.as_tensor(brownian(n, L, d, 1), dtype=dt, device='cuda').requires_grad_(True)
