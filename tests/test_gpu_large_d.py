@@ -21,7 +21,7 @@ def _dev(a, dtype):
 
 @pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
 @pytest.mark.parametrize("d,L,L2,m", [(28, 40, 33, 4), (46, 70, 100, 5), (126, 50, 50, 4), (17, 130, 200, 3), (64, 9, 257, 2),
-                                      (20, 300, 30, 6)])
+                                      (20, 300, 30, 6), (24, 210, 205, 3)])
 def test_gram_raw_levels_large_d(dtype, d, L, L2, m):
     from gpsig_b200 import ops
     from oracle import c_oracle
