@@ -1033,7 +1033,7 @@ int launch_skew_inst(TruncParams P, cudaStream_t stream) {
       const long ctas = (long)grid.x * ny;
       const double waves = (double)((ctas + sms - 1) / sms);
       const double cost = waves * ((double)ch + 0.32) * (ctas < sms ? (double)sms / ctas : 1.0);   // fewer CTAs than SMs: idle SMs
-      if (cost < best * (1.0 - 1e-9)) { best = cost; best_y = y; }
+      if (cost < best * 0.99) { best = cost; best_y = y; }      // a finer split only for a real gain: every row chunk re-streams its x rows past L2
     }
     if (best_y > 0) ichunk = (rows + best_y - 1) / best_y;
   }
