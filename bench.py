@@ -159,11 +159,11 @@ def measured_peaks():
 
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the headline kernel at the bench shape (c2), from the
 # committed ncu --set full captures (algorithmic bytes: 83.2 MB f64 / 41.6 MB f32 per launch)
-NCU_TRAFFIC_BYTES = {"f64": 79.60e6 + 21.56e6, "f32": 41.73e6 + 1.15e6}
+NCU_TRAFFIC_BYTES = {"f64": 77.79e6 + 17.83e6, "f32": 70.71e6 + 7.09e6}
 # the slab launch of the headline step (rank 0's 2000 rows x 20000 columns, float64): dram read + write of that one launch
 NCU_TRAFFIC_SLAB_F64 = 598322176 + 312179456
 NCU_TRAFFIC_SLAB_SOURCE = "profiles/r02zc_slab_traffic.csv (ncu dram__bytes_read.sum + dram__bytes_write.sum of the slab launch at N=1, final round-2 kernel: 0.60 GB read, 0.31 GB written, against 0.60 GB algorithmic; the x rows are re-streamed from L2 by every CTA)"
-NCU_TRAFFIC_SOURCE = "profiles/r02k_ncu_trunc_skew_f64.txt, profiles/r02k_ncu_trunc_skew_f32.txt (ncu --set full, N=N2=2000 = c2; per launch of the slab step multiply by 10: 20000 columns; the 16-32 MB output still sits in L2 when the kernel ends)"
+NCU_TRAFFIC_SOURCE = "profiles/r02zc_c2_traffic.csv (ncu dram__bytes_read.sum + dram__bytes_write.sum per launch, mean of 4, N=N2=2000 = c2, final round-2 kernels; part of the 16-32 MB output still sits in L2 when the kernel ends; float32 reads rows stored with every coordinate twice for the packed contraction: 1.7x its algorithmic input bytes)"
 
 
 def fma_peak_tflops(torch, lib, esz):
