@@ -71,6 +71,8 @@ def _load():
     lib.gpsig_trunc_vjp_workspace_bytes_order.argtypes = [i] * 7
     lib.gpsig_tens_vs_seq_vjp_workspace_bytes.restype = sz
     lib.gpsig_tens_vs_seq_vjp_workspace_bytes.argtypes = [i] * 5
+    lib.gpsig_tens_vs_seq_lifted_gd_workspace_bytes.restype = sz
+    lib.gpsig_tens_vs_seq_lifted_gd_workspace_bytes.argtypes = [i] * 7
     for sfx in ('f32', 'f64'):
         f = getattr(lib, 'gpsig_trunc_vjp_' + sfx)
         f.restype = i
@@ -78,6 +80,9 @@ def _load():
         f = getattr(lib, 'gpsig_tens_vs_seq_vjp_' + sfx)
         f.restype = i
         f.argtypes = [ctypes.POINTER(TruncDesc), vp, i, i, vp, i, i, i, i, i, vp, vp, vp, vp, sz, vp]
+        f = getattr(lib, 'gpsig_tens_vs_seq_lifted_gd_' + sfx)
+        f.restype = i
+        f.argtypes = [ctypes.POINTER(TruncDesc), vp, i, i, vp, i, i, i, i, i, vp, vp, vp, sz, vp]
         f = getattr(lib, 'gpsig_tens_tens_vjp_' + sfx)
         f.restype = i
         f.argtypes = [ctypes.POINTER(TruncDesc), vp, i, i, i, vp, vp, vp]

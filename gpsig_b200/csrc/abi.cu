@@ -73,6 +73,8 @@ extern template int launch_lift<float>(LiftParams, void*, size_t, const LiftMmaO
 extern template int launch_lift<double>(LiftParams, void*, size_t, const LiftMmaOperands*, cudaStream_t);
 extern template int launch_tens_seq_lifted<float>(const TensSeqParams&, int, void*, size_t, cudaStream_t);
 extern template int launch_tens_seq_lifted<double>(const TensSeqParams&, int, void*, size_t, cudaStream_t);
+extern template int launch_tens_seq_lifted_gd<float>(const TensSeqParams&, int, float*, const float*, cudaStream_t);
+extern template int launch_tens_seq_lifted_gd<double>(const TensSeqParams&, int, double*, const double*, cudaStream_t);
 
 // K(X, X) computed on and above the diagonal only: out[l, i, j] = out[l, j, i] for i > j (32 x 32 tiles through
 // shared memory, both sides coalesced).  Every i > j entry is overwritten, so the result is exactly symmetric.
@@ -634,6 +636,39 @@ static int tens_seq_vjp_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, i
   return GPSIG_OK;
 }
 
+// Reverse mode of Kzx on the lifted form (tens_lifted_kernels.cuh): Gd[r, e] = dL/dkappa (x kappa for RBF) for ALL tensor points
+// r = (c zs + s) Mz + z against the points e = l C + n of the columns [col_begin, col_end), C = col_end - col_begin.
+template <typename T>
+static int tens_seq_lifted_gd_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, int increments, const T* X, int N, int L, int d,
+                                   int col_begin, int col_end, const T* grad_levels, T* Gd, void* ws, size_t ws_bytes, void* stream) {
+  if (int rc = check_desc(desc)) return rc;
+  if (desc->order != 1 || (desc->base != GPSIG_BASE_RBF && desc->base != GPSIG_BASE_LINEAR))
+    GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "the lifted reverse mode takes the first-order linear and RBF kernels");
+  if (!Z || !X || !grad_levels || !Gd) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "Z/X/grad_levels/Gd must not be NULL");
+  if (d < 9) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "the lifted reverse mode is for state dimensions above 8 (d=%d)", d);
+  if (L < (desc->difference ? 2 : 1)) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "sequences too short (L=%d)", L);
+  if (col_begin < 0 || col_end > N || col_begin > col_end) GPSIG_FAIL(GPSIG_ERR_INVALID_ARGUMENT, "bad column range [%d, %d) for N=%d", col_begin, col_end, N);
+  if (col_begin == col_end || Mz == 0) return GPSIG_OK;
+  const int m = desc->num_levels, TT = m * (m + 1) / 2, zs = increments ? 2 : 1;
+  if (m > 8) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "reverse mode supports num_levels <= 8");
+  const size_t need = packed_bytes(TT * Mz, zs, d, sizeof(T)) + packed_bytes(N, L, d, sizeof(T));
+  if (!ws || ws_bytes < need || (reinterpret_cast<uintptr_t>(ws) & 15))
+    GPSIG_FAIL(GPSIG_ERR_WORKSPACE, "workspace too small or misaligned: need %zu bytes, got %zu", need, ws_bytes);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  T* zp = static_cast<T*>(ws);
+  T* xp = reinterpret_cast<T*>(static_cast<char*>(ws) + packed_bytes(TT * Mz, zs, d, sizeof(T)));
+  if (int rc = pack<T>(Z, TT * Mz, zs, d, nullptr, zp, s, 0, 1.0)) return rc;
+  if (int rc = pack<T>(X, N, L, d, nullptr, xp, s, 0, 1.0)) return rc;
+  TensSeqParams P;
+  memset(&P, 0, sizeof(P));
+  P.zp = zp; P.xp = xp;
+  P.zblk = seq_block_elems(zs, d, sizeof(T)); P.xblk = seq_block_elems(L, d, sizeof(T));
+  P.Mz = Mz; P.zs = zs; P.N = N; P.L = L; P.m = m; P.col_begin = col_begin; P.col_end = col_end;
+  P.difference = desc->difference;
+  P.p0 = desc->base_params[0]; P.p1 = desc->base_params[1]; P.base = desc->base; P.d = d; P.return_levels = 1;
+  return launch_tens_seq_lifted_gd<T>(P, padded_dim(d), Gd, grad_levels, s);
+}
+
 template <typename T>
 static int tens_tens_vjp_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, int increments, int d, const T* grad_levels,
                               T* gradZ, void* stream) {
@@ -736,6 +771,17 @@ size_t gpsig_trunc_vjp_workspace_bytes(int npairs, int L, int L2, int m, int dif
 }
 size_t gpsig_trunc_vjp_workspace_bytes_order(int npairs, int L, int L2, int m, int order, int difference, int elem) {
   return trunc_vjp_ws((size_t)npairs, L, L2, m, difference, elem, order);
+}
+size_t gpsig_tens_vs_seq_lifted_gd_workspace_bytes(int Mz, int increments, int N, int L, int d, int m, int elem) {
+  return packed_bytes(m * (m + 1) / 2 * Mz, increments ? 2 : 1, d, elem) + packed_bytes(N, L, d, elem);
+}
+int gpsig_tens_vs_seq_lifted_gd_f64(const gpsig_trunc_desc* desc, const double* Z, int Mz, int inc, const double* X, int N, int L, int d,
+                                    int cb, int ce, const double* g, double* Gd, void* ws, size_t wsb, void* stream) {
+  return gpsig::tens_seq_lifted_gd_impl<double>(desc, Z, Mz, inc, X, N, L, d, cb, ce, g, Gd, ws, wsb, stream);
+}
+int gpsig_tens_vs_seq_lifted_gd_f32(const gpsig_trunc_desc* desc, const float* Z, int Mz, int inc, const float* X, int N, int L, int d,
+                                    int cb, int ce, const float* g, float* Gd, void* ws, size_t wsb, void* stream) {
+  return gpsig::tens_seq_lifted_gd_impl<float>(desc, Z, Mz, inc, X, N, L, d, cb, ce, g, Gd, ws, wsb, stream);
 }
 size_t gpsig_tens_vs_seq_vjp_workspace_bytes(int Mz, int ncols, int L, int m, int elem) {
   return align_up((size_t)Mz * ncols * (m * (m + 1) / 2) * L * elem, 128);

@@ -168,6 +168,27 @@ int launch_tens_seq_lifted(const TensSeqParams& P, int DP, void* scratch, size_t
   prof_end(s);
   return GPSIG_OK;
 }
+template <typename T>
+int launch_tens_seq_lifted_gd(const TensSeqParams& P, int DP, T* C, const T* g, cudaStream_t s) {
+  const int ncols = P.col_end - P.col_begin;
+  if (ncols <= 0 || P.Mz <= 0) return GPSIG_OK;
+  if (P.m < 1 || P.m > 8) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "num_levels=%d is not supported (1..8)", P.m);
+  prof_begin(s);
+  if (int rc = tens_lift_gemm<T, 7, 7>(P, DP, 0, ncols, C, s)) return rc;
+  if (g) {
+    const int by_value = P.base == GPSIG_BASE_RBF ? 1 : 0;
+    dim3 grid((unsigned)((ncols + 127) / 128), (unsigned)P.Mz);
+    if (P.m <= 2) tens_lift_reverse_kernel<T, 2><<<grid, 128, 0, s>>>(P, ncols, C, g, by_value);
+    else if (P.m <= 4) tens_lift_reverse_kernel<T, 4><<<grid, 128, 0, s>>>(P, ncols, C, g, by_value);
+    else if (P.m <= 6) tens_lift_reverse_kernel<T, 6><<<grid, 128, 0, s>>>(P, ncols, C, g, by_value);
+    else tens_lift_reverse_kernel<T, 8><<<grid, 128, 0, s>>>(P, ncols, C, g, by_value);
+    GPSIG_LAUNCH_CHECK("tens_lift_reverse_kernel");
+  }
+  prof_end(s);
+  return GPSIG_OK;
+}
+template int launch_tens_seq_lifted_gd<float>(const TensSeqParams&, int, float*, const float*, cudaStream_t);
+template int launch_tens_seq_lifted_gd<double>(const TensSeqParams&, int, double*, const double*, cudaStream_t);
 template int launch_tens_seq_lifted<float>(const TensSeqParams&, int, void*, size_t, cudaStream_t);
 template int launch_tens_seq_lifted<double>(const TensSeqParams&, int, void*, size_t, cudaStream_t);
 

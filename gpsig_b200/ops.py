@@ -6,6 +6,8 @@ pointers plus the current CUDA stream through ctypes and return the output
 tensor.  Nothing here computes: if the CUDA library is missing the import of
 ``_lib`` has already failed.
 """
+import os
+
 import torch
 
 from . import _lib
@@ -205,6 +207,8 @@ def tens_vs_seq_vjp(Z, X, grad_levels, num_levels, increments=False, base='linea
     gradZ, gradX = torch.zeros_like(Z), torch.zeros_like(X)
     desc = make_desc(base, m, max(1, min(int(order), m)), difference, base_params)
     esz = X.element_size()
+    if (d > 16 or (d > 8 and esz == 8)) and int(order) == 1 and base in ('rbf', 'linear') and not os.environ.get('GPSIG_TENS_VJP_NO_LIFT'):
+        return _tens_vs_seq_vjp_lifted(Z, X, grad_levels, m, increments, base, desc)
     fn = getattr(lib, 'gpsig_tens_vs_seq_vjp_' + sfx(X.dtype))
     cols_per_call = max(1, int(_VJP_WS_BYTES // max(1, lib.gpsig_tens_vs_seq_vjp_workspace_bytes(Mz, 1, L, m, esz))))
     with torch.cuda.device(X.device):
@@ -215,6 +219,51 @@ def tens_vs_seq_vjp(Z, X, grad_levels, num_levels, increments=False, base='linea
             ws = workspace(wsb, X.device)
             check(fn(desc, ptr(Z), Mz, int(increments), ptr(X), N, L, d, cb, ce, ptr(g), ptr(gradZ), ptr(gradX),
                      ptr(ws), wsb, stream_handle(X.device)))
+    return gradZ, gradX
+
+
+_LIFT_GD_BYTES = 1 << 30     # lifted adjoint values of one block of sequences
+
+
+def _tens_vs_seq_vjp_lifted(Z, X, grad_levels, m, increments, base, desc):
+    """Reverse mode of ``tens_vs_seq`` at state dimensions above 16 (float64: above 8), lifted form: the library returns
+    ``Gd[r, e] = dL/dkappa(z point r, x point e)`` (times kappa for RBF) for a block of sequences
+    (``gpsig_tens_vs_seq_lifted_gd_*``: GEMM + reverse time recursion, csrc/tens_lifted_kernels.cuh); the two remaining
+    contractions are plain GEMMs, ``dL/dZ = Gd X - rowsum(Gd) Z`` and ``dL/dX = Gd^T Z - colsum(Gd) X`` (linear: without
+    the sums), done with ``torch.matmul``."""
+    N, L, d = X.shape
+    T, Mz = Z.shape[0], Z.shape[1]
+    zs = 2 if increments else 1
+    R = T * zs * Mz
+    esz = X.element_size()
+    gradZ, gradX = torch.zeros_like(Z), torch.zeros_like(X)
+    Zr = (Z.permute(0, 2, 1, 3) if increments else Z).reshape(R, d).contiguous()          # row r = (c zs + s) Mz + z
+    gZr = torch.zeros_like(Zr)
+    fn = getattr(lib, 'gpsig_tens_vs_seq_lifted_gd_' + sfx(X.dtype))
+    cols_per_call = max(1, int(_LIFT_GD_BYTES // max(1, R * L * esz)))
+    if cols_per_call >= 32:
+        cols_per_call = cols_per_call // 32 * 32
+    wsb = lib.gpsig_tens_vs_seq_lifted_gd_workspace_bytes(Mz, int(increments), N, L, d, m, esz)
+    rbf = base == 'rbf'
+    with torch.cuda.device(X.device):
+        ws = workspace(wsb, X.device)
+        for cb in range(0, N, cols_per_call):
+            ce = min(N, cb + cols_per_call)
+            C = ce - cb
+            g = grad_levels[:, :, cb:ce].contiguous()
+            Gd = torch.empty((R, L * C), dtype=X.dtype, device=X.device)
+            check(fn(desc, ptr(Z), Mz, int(increments), ptr(X), N, L, d, cb, ce, ptr(g), ptr(Gd), ptr(ws), wsb,
+                     stream_handle(X.device)))
+            Xe = X[cb:ce].permute(1, 0, 2).reshape(L * C, d)                              # column e = l C + n
+            dZ = Gd @ Xe
+            dX = Gd.t() @ Zr
+            if rbf:
+                dZ -= Gd.sum(dim=1, keepdim=True) * Zr
+                dX -= Gd.sum(dim=0)[:, None] * Xe
+            gZr += dZ
+            gradX[cb:ce] = dX.reshape(L, C, d).permute(1, 0, 2)
+            del Gd
+    gradZ.copy_(gZr.reshape(T, zs, Mz, d).permute(0, 2, 1, 3) if increments else gZr.reshape(T, Mz, d))
     return gradZ, gradX
 
 

@@ -185,6 +185,19 @@ int gpsig_tens_vs_seq_vjp_f64(const gpsig_trunc_desc* desc, const double* Z, int
 int gpsig_tens_vs_seq_vjp_f32(const gpsig_trunc_desc* desc, const float* Z, int Mz, int increments, const float* X,
                               int N, int L, int d, int col_begin, int col_end, const float* grad_levels,
                               float* gradZ, float* gradX, void* workspace, size_t workspace_bytes, void* stream);
+/* Reverse mode of gpsig_tens_vs_seq_* at state dimensions above 8, lifted form (csrc/tens_lifted_kernels.cuh; the reference gets
+ * this gradient from TensorFlow autodiff of gpsig/signature_algs.py:101-127 + kernels.py:322-341).  First-order linear / RBF.
+ * Gd [m(m+1)/2 * zs * Mz, L * C], C = col_end - col_begin: row r = (c zs + s) Mz + z (component c, increment half s, tensor z),
+ * column e = l C + n; entry = dL/dkappa(z point r, x point e), times kappa for the RBF kernel.  The caller finishes with two
+ * plain GEMMs: dL/dZ = Gd X - rowsum(Gd) Z, dL/dX = Gd^T Z - colsum(Gd) X (linear: without the sums).  Z, X as for
+ * gpsig_tens_vs_seq_vjp_* (already scaled by the lengthscales); grad_levels [m+1, Mz, C] w.r.t. the raw levels. */
+size_t gpsig_tens_vs_seq_lifted_gd_workspace_bytes(int Mz, int increments, int N, int L, int d, int num_levels, int elem);
+int gpsig_tens_vs_seq_lifted_gd_f64(const gpsig_trunc_desc* desc, const double* Z, int Mz, int increments, const double* X,
+                                    int N, int L, int d, int col_begin, int col_end, const double* grad_levels,
+                                    double* Gd, void* workspace, size_t workspace_bytes, void* stream);
+int gpsig_tens_vs_seq_lifted_gd_f32(const gpsig_trunc_desc* desc, const float* Z, int Mz, int increments, const float* X,
+                                    int N, int L, int d, int col_begin, int col_end, const float* grad_levels,
+                                    float* Gd, void* workspace, size_t workspace_bytes, void* stream);
 int gpsig_tens_tens_vjp_f64(const gpsig_trunc_desc* desc, const double* Z, int Mz, int increments, int d,
                             const double* grad_levels, double* gradZ, void* stream);
 int gpsig_tens_tens_vjp_f32(const gpsig_trunc_desc* desc, const float* Z, int Mz, int increments, int d,

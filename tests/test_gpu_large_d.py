@@ -199,3 +199,27 @@ def test_kzx_lifted_blocks_and_column_ranges(dtype, base, increments, monkeypatc
     assert np.max(np.abs(Gc - R[:, :, 10:61]) / scale) < tol
     Gs = ops.tens_vs_seq(_dev(Z, dtype), _dev(X, dtype), m, increments=increments, base=base, return_levels=False).cpu().numpy()
     assert np.max(np.abs(Gs - R.sum(axis=0))) / np.abs(R.sum(axis=0)).max() < tol
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("base", ['rbf', 'linear'])
+@pytest.mark.parametrize("increments,difference", [(True, True), (False, True), (True, False)])
+def test_kzx_lifted_adjoint_matches_thread_per_pair_adjoint(dtype, base, increments, difference, monkeypatch):
+    """Reverse mode of Kzx at d > 16: the lifted form (library: GEMM + reverse time recursion -> dL/dkappa; two plain GEMMs
+    for dL/dZ, dL/dX) against the thread-per-pair adjoint kernel (GPSIG_TENS_VJP_NO_LIFT=1), element by element, with
+    several blocks of sequences."""
+    from gpsig_b200 import ops
+    N, L, d, m, Mz = 70, 9, 20, 3, 5
+    rng = np.random.default_rng(41)
+    X = brownian(N, L, d, 42) / np.sqrt(d / 8.0)
+    Z = inducing_tensors(X, m, Mz, increments, 43)
+    G = rng.standard_normal((m + 1, Mz, N))
+    args = (_dev(Z, dtype), _dev(X, dtype), _dev(G, dtype), m)
+    kw = dict(increments=increments, base=base, difference=difference)
+    monkeypatch.setattr(ops, '_LIFT_GD_BYTES', (m * (m + 1) // 2) * (2 if increments else 1) * Mz * L * 8 * 32)      # 32 sequences per block
+    gZ, gX = ops.tens_vs_seq_vjp(*args, **kw)
+    monkeypatch.setenv('GPSIG_TENS_VJP_NO_LIFT', '1')
+    rZ, rX = ops.tens_vs_seq_vjp(*args, **kw)
+    tol = 1e-9 if dtype == torch.float64 else 2e-4
+    assert rel_err(gZ.cpu().numpy(), rZ.cpu().numpy()) < tol
+    assert rel_err(gX.cpu().numpy(), rX.cpu().numpy()) < tol
