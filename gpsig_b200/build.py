@@ -68,7 +68,8 @@ def _units(fast):
     units = [('abi', os.path.join(CSRC, 'abi.cu'), extra),
              ('pde_vjp', os.path.join(CSRC, 'pde_vjp.cu'), extra),
              ('static_scratch', os.path.join(CSRC, 'static_scratch.cu'), extra),
-             ('lifted', os.path.join(CSRC, 'lifted.cu'), extra)]
+             ('lifted', os.path.join(CSRC, 'lifted.cu'), extra),
+             ('tens_tens', os.path.join(CSRC, 'tens_tens.cu'), extra)]
     for t in ('float', 'double'):
         for op in (0, 1, 2):
             for dp in (4, 8, 16):

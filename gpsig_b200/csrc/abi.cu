@@ -71,6 +71,13 @@ GPSIG_DECL_T(double)
 
 extern template int launch_lift<float>(LiftParams, void*, size_t, const LiftMmaOperands*, cudaStream_t);
 extern template int launch_lift<double>(LiftParams, void*, size_t, const LiftMmaOperands*, cudaStream_t);
+// tens_tens.cu (tens_tens_tile_kernels.cuh): Kzz and its adjoint on 16 x 16 tiles of tensor pairs; false = shape not covered
+template <typename T> bool launch_tens_tens_tile(const TensTensParams&, cudaStream_t);
+template <typename T> bool launch_tens_tens_tile_vjp(const TensTensVjpParams&, cudaStream_t);
+extern template bool launch_tens_tens_tile<float>(const TensTensParams&, cudaStream_t);
+extern template bool launch_tens_tens_tile<double>(const TensTensParams&, cudaStream_t);
+extern template bool launch_tens_tens_tile_vjp<float>(const TensTensVjpParams&, cudaStream_t);
+extern template bool launch_tens_tens_tile_vjp<double>(const TensTensVjpParams&, cudaStream_t);
 extern template int launch_tens_seq_lifted<float>(const TensSeqParams&, int, void*, size_t, cudaStream_t);
 extern template int launch_tens_seq_lifted<double>(const TensSeqParams&, int, void*, size_t, cudaStream_t);
 extern template int launch_tens_seq_lifted_gd<float>(const TensSeqParams&, int, float*, const float*, cudaStream_t);
@@ -417,6 +424,10 @@ static int tens_tens_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, int 
   if (d > 16 && desc->base == GPSIG_BASE_SPECTRAL) GPSIG_FAIL(GPSIG_ERR_UNSUPPORTED, "spectral Kzz supports d <= 16 (got %d)", d);
   if (epi) { P.level_scale = epi->level_scale; P.return_levels = epi->return_levels; } else P.return_levels = 1;
   P.out = out;
+  if (!getenv("GPSIG_TENS_TENS_OLD") && launch_tens_tens_tile<T>(P, static_cast<cudaStream_t>(stream))) {
+    GPSIG_LAUNCH_CHECK("tens_tens_tile_kernel");
+    return GPSIG_OK;
+  }
   dim3 grid((Mz + 127) / 128, Mz);
   if (P.d > 16) tens_tens_big_kernel<T><<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(P);
   else if (P.d <= 8) tens_tens_kernel<T, 8><<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(P);
@@ -683,6 +694,10 @@ static int tens_tens_vjp_impl(const gpsig_trunc_desc* desc, const T* Z, int Mz, 
   P.p0 = desc->base_params[0]; P.p1 = desc->base_params[1]; P.base = desc->base;
   P.g = grad_levels; P.gradZ = gradZ;
   const int TT = P.m * (P.m + 1) / 2;
+  if (!getenv("GPSIG_TENS_TENS_OLD") && launch_tens_tens_tile_vjp<T>(P, static_cast<cudaStream_t>(stream))) {
+    GPSIG_LAUNCH_CHECK("tens_tens_tile_vjp_kernel");
+    return GPSIG_OK;
+  }
   dim3 grid((Mz + 3) / 4, TT);                                       // 4 warps per CTA, one warp per (component, row)
   if (d > 16) tens_tens_vjp_big_kernel<T><<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(P);
   else if (d <= 8) tens_tens_vjp_kernel<T, 8><<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(P);

@@ -223,3 +223,36 @@ def test_kzx_lifted_adjoint_matches_thread_per_pair_adjoint(dtype, base, increme
     tol = 1e-9 if dtype == torch.float64 else 2e-4
     assert rel_err(gZ.cpu().numpy(), rZ.cpu().numpy()) < tol
     assert rel_err(gX.cpu().numpy(), rX.cpu().numpy()) < tol
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("base", ['rbf', 'linear', 'matern32'])
+@pytest.mark.parametrize("d,Mz,increments", [(3, 37, True), (8, 50, True), (8, 16, False), (13, 33, False), (28, 45, True),
+                                             (70, 21, True), (126, 19, False), (200, 18, True)])
+def test_kzz_tiles_match_the_first_kernels(dtype, base, d, Mz, increments, monkeypatch):
+    """Kzz and its adjoint on 16 x 16 tiles of tensor pairs (tens_tens_tile_kernels.cuh: any d, ragged tiles; the adjoint up to
+    d = 128, above that the first kernel) against the first kernels (GPSIG_TENS_TENS_OLD=1): levels, summed with level scales
+    and lengthscales, and dL/dZ."""
+    from gpsig_b200 import ops
+    m = 3
+    rng = np.random.default_rng(d * 100 + Mz)
+    X = brownian(6, 12, d, 1) / np.sqrt(d / 8.0)
+    # points (not increments) shrunk: with far-apart points dL/dZ is the rounding noise of the cancelling diagonal terms
+    Z = _dev(inducing_tensors(X, m, Mz, increments, 2) * (1.0 if increments else 0.3), dtype)
+    len_ = _dev(rng.uniform(0.7, 1.4, d), dtype)
+    lsc = _dev(rng.uniform(0.5, 1.5, m + 1), dtype)
+    G = _dev(rng.standard_normal((m + 1, Mz, Mz)), dtype)
+
+    def run():
+        lev = ops.tens_tens(Z, m, increments=increments, base=base)
+        tot = ops.tens_tens(Z, m, increments=increments, base=base, lengthscales=len_, level_scale=lsc, return_levels=False)
+        gz = ops.tens_tens_vjp(Z, G, m, increments=increments, base=base)
+        return [t.cpu().numpy() for t in (lev, tot, gz)]
+    new = run()
+    monkeypatch.setenv('GPSIG_TENS_TENS_OLD', '1')
+    old = run()
+    # adjoint: sums of cancelling terms in another order; float32: differences of nearby exp values (kernels.py:278)
+    tols = (1e-11, 1e-11, 1e-8) if dtype == torch.float64 else (1e-4, 1e-4, 2e-3)
+    for a, b, tol in zip(new, old, tols):
+        assert np.isfinite(a).all()
+        assert rel_err(a, b) < tol
