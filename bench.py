@@ -298,8 +298,36 @@ def other_configs(torch, ops, lib):
             e1.synchronize()
             best = min(best, e0.elapsed_time(e1))
         out["c4_svgp_step_" + nm] = {"workload": "K_tens_n_seq_covs forward + backward (grads of Z and X), minibatch 50, Mz=500, L=100, d=8, m=4",
-                                     "kernels": "tens_tens(+vjp), trunc_gram diag (+vjp tables/grad), tens_vs_seq_kernel2 + tens_seq_vjp_warp_kernel",
+                                     "kernels": "tens_tens_tile(+vjp), trunc_gram diag (+vjp tables/grad), tens_vs_seq_kernel2 + tens_seq_vjp_warp_kernel",
                                      "ms": best}
+        # the same step captured into a CUDA graph (fixed minibatch shape) and replayed: no host-side launch cost
+        try:
+            import warnings
+            warnings.filterwarnings('ignore', message="The AccumulateGrad node's stream")
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                step()
+            torch.cuda.current_stream().wait_stream(side)
+            graph = torch.cuda.CUDAGraph()
+            Xb.grad = None
+            Zb.grad = None
+            with torch.cuda.graph(graph):
+                Kzz, Kzx, Kxx = kern.K_tens_n_seq_covs(Zb, Xb, full_X_cov=False, increments=True)
+                (Kzz.sum() + Kzx.sum() + Kxx.sum()).backward()
+            graph.replay()
+            best = 1e30
+            for _ in range(10):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                graph.replay()
+                e1.record()
+                e1.synchronize()
+                best = min(best, e0.elapsed_time(e1))
+            out["c4_svgp_step_" + nm]["ms_cuda_graph"] = best
+            del graph
+        except Exception as e:       # noqa: BLE001
+            out["c4_svgp_step_" + nm]["ms_cuda_graph"] = "capture failed: %r" % (e,)
     return out
 
 

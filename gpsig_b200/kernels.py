@@ -186,7 +186,17 @@ class SignatureKernel:
             return None
         if torch.is_tensor(value):                      # a trainable parameter used on the non-differentiable path
             return value.detach().to(dtype=like.dtype, device=like.device).contiguous()
-        return torch.as_tensor(np.asarray(value, dtype=np.float64), dtype=like.dtype, device=like.device).contiguous()
+        # numpy / scalar hyper-parameters: one host -> device copy per VALUE, not per call (a pageable cudaMemcpy costs
+        # 0.3 ms of host time: three of them were half of the SVGP covariance step, which is launch bound at minibatch 50)
+        arr = np.ascontiguousarray(np.asarray(value, dtype=np.float64))
+        cache = self.__dict__.setdefault('_param_cache', {})
+        key = (arr.tobytes(), arr.shape, like.dtype, like.device)
+        hit = cache.get(key)
+        if hit is None:
+            if len(cache) >= 64:
+                cache.clear()
+            hit = cache[key] = torch.as_tensor(arr, dtype=like.dtype, device=like.device).contiguous()
+        return hit
 
     def _level_scale(self, like):
         """sigma * variances  (kernels.py:472)."""

@@ -7,8 +7,12 @@ Usage: python tools/time_training_step.py [float64|float32 ...] [minibatch ...]
 import os
 import sys
 
+import warnings
+
 import numpy as np
 import torch
+
+warnings.filterwarnings('ignore', message="The AccumulateGrad node's stream")
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import gpsig_b200  # noqa: E402
@@ -69,6 +73,32 @@ for dt in DTYPES:
             (Kzz.sum() + Kzx.sum() + Kxx.sum()).backward()
 
         print("%s minibatch %d: K_tens_n_seq_covs fwd+bwd %.3f ms" % (name, nb, ev_time(full_step)), flush=True)
+
+        # the same step captured once into a CUDA graph and replayed (static shapes: what a training loop with a fixed
+        # minibatch does): removes the host-side launch cost of its ~45 kernels
+        try:
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                for _ in range(3):
+                    full_step()
+            torch.cuda.current_stream().wait_stream(side)
+            graph = torch.cuda.CUDAGraph()
+            X2.grad = None; Zt.grad = None
+            with torch.cuda.graph(graph):
+                Kzz, Kzx, Kxx = k.K_tens_n_seq_covs(Zt, X2, full_X_cov=False, increments=True)
+                (Kzz.sum() + Kzx.sum() + Kxx.sum()).backward()
+            cX, cZ = X2.grad, Zt.grad             # the buffers the captured backward writes
+            full_step()                           # eager, into fresh .grad tensors
+            eX, eZ = X2.grad.clone(), Zt.grad.clone()
+            cX.zero_(); cZ.zero_()
+            graph.replay()
+            torch.cuda.synchronize()
+            err = max(float((cX - eX).abs().max() / eX.abs().max()), float((cZ - eZ).abs().max() / eZ.abs().max()))
+            print("%s minibatch %d: K_tens_n_seq_covs fwd+bwd as a CUDA graph %.3f ms (grads against eager: %.1e)" %
+                  (name, nb, ev_time(graph.replay, reps=20), err), flush=True)
+        except Exception as e:       # noqa: BLE001
+            print("CUDA graph capture failed: %r" % (e,), flush=True)
 
 # Gram-sized backward (inducing sequences: K_seq_n_seq_covs): K(X, X2) raw levels, forward + backward
 for dt in (DTYPES if 'GPSIG_TIME_D' not in os.environ else []):
