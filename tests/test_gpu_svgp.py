@@ -249,3 +249,61 @@ def test_dlpack_producers_are_ingested_zero_copy():
     assert torch.equal(kp.Kdiag(Xp), kp.Kdiag(Xt))
     with pytest.raises(TypeError):
         k.K(Xn.reshape(N, -1))                                          # numpy goes through compute_*
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+def test_covariance_step_replays_as_a_cuda_graph(dtype):
+    """Forward + backward of K_tens_n_seq_covs (Kzz, Kzx, Kxx_diag on three streams, hand-written adjoints) captures into
+    one CUDA graph: no entry point synchronises or allocates outside torch's pool.  The replay on NEW inputs (copied into
+    the captured buffers) reproduces the eager step."""
+    import warnings
+    from gpsig_b200 import kernels
+    warnings.filterwarnings('ignore', message="The AccumulateGrad node's stream")
+    N, L, d, m, Mz = 10, 20, 3, 3, 6
+    k = kernels.SignatureRBF(L * d, d, m, lengthscales=np.full(d, 1.3))
+    X = _dev(brownian(N, L, d, 70).reshape(N, -1), dtype).requires_grad_(True)
+    Z = _dev(inducing_tensors(brownian(N, L, d, 70), m, Mz, True, 71), dtype).requires_grad_(True)
+
+    def step():
+        Kzz, Kzx, Kxx = k.K_tens_n_seq_covs(Z, X, full_X_cov=False, increments=True)
+        ((Kzz ** 2).sum() + (Kzx ** 2).sum() + Kxx.sum()).backward()
+
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        step()
+    torch.cuda.current_stream().wait_stream(side)
+    X.grad = None
+    Z.grad = None
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        step()
+    cX, cZ = X.grad, Z.grad
+    with torch.no_grad():                                     # new values in the captured input buffers
+        X.copy_(_dev(brownian(N, L, d, 72).reshape(N, -1), dtype))
+        Z.copy_(_dev(inducing_tensors(brownian(N, L, d, 72), m, Mz, True, 73), dtype))
+    cX.zero_()
+    cZ.zero_()
+    graph.replay()
+    torch.cuda.synchronize()
+    gX, gZ = cX.clone(), cZ.clone()
+    X.grad = None
+    Z.grad = None
+    step()
+    tol = 1e-10 if dtype == torch.float64 else 1e-4
+    assert float(gX.abs().max()) > 0 and float(gZ.abs().max()) > 0
+    assert rel_err(gX.cpu().numpy(), X.grad.cpu().numpy()) < tol
+    assert rel_err(gZ.cpu().numpy(), Z.grad.cpu().numpy()) < tol
+
+
+def test_numpy_hyperparameters_are_copied_to_the_device_once_per_value():
+    from gpsig_b200 import kernels
+    d = 3
+    k = kernels.SignatureRBF(10 * d, d, 2, lengthscales=np.full(d, 1.3))
+    like = _dev(np.zeros(1))
+    a, b = k._param(k.lengthscales, like), k._param(k.lengthscales, like)
+    assert a.data_ptr() == b.data_ptr()
+    k.lengthscales = np.full(d, 0.7)                         # a new value is a new copy, the old one is untouched
+    c = k._param(k.lengthscales, like)
+    assert c.data_ptr() != a.data_ptr() and float(c[0]) == 0.7 and float(a[0]) == 1.3
+    assert k._param(k.lengthscales, like.float()).dtype == torch.float32
