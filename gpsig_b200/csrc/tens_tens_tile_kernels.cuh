@@ -27,32 +27,46 @@ constexpr int kTT = 16;       // tensors per tile side
 // stage component k's tensors t0 .. t0 + 15 (both increment ends) into dst[s][t][dp], zero past Mz; optional lengthscales
 template <typename T>
 __device__ __forceinline__ void tt_stage(T* dst, const T* Z, const T* len, int k, int t0, int Mz, int zs, int d, int dp, int tid) {
-  const int per = zs * d;
-  for (int e = tid; e < kTT * per; e += 256) {
-    const int t = e / per, r = e - t * per, s = r / d, q = r - s * d;
+  // 16 threads per tensor walk its zs * d coordinates (consecutive addresses; zs <= 2: no division)
+  const int t = tid >> 4, per = zs * d;
+  const bool live = t0 + t < Mz;
+  const T* src = Z + ((size_t)k * Mz + (live ? t0 + t : 0)) * per;
+  for (int r = tid & 15; r < per; r += 16) {
+    const int s = r >= d ? 1 : 0, q = r - s * d;
     T v = T(0);
-    if (t0 + t < Mz) { v = Z[((size_t)k * Mz + t0 + t) * per + r]; if (len) v = v / len[q]; }
+    if (live) { v = src[r]; if (len) v = v / len[q]; }
     dst[(s * kTT + t) * dp + q] = v;
   }
 }
 
 // the (up to) four base-kernel values of a tensor pair from staged coordinates, combined as in kernels.py:278
 template <typename T>
-__device__ __forceinline__ T tt_entry(const T* A, const T* B, int ty, int tx, int zs, int d, int dp, int base, T p0, T p1) {
+__device__ __forceinline__ T tt_rbf64(T dot, T xs, T ys, double tab) {      // exp(-(|x|^2 + |y|^2 - 2 x.y) / 2) by the table exp2 (convergent warp)
+  constexpr double kLog2e = 1.4426950408889634;
+  return T(exp2_tab32(((double)dot - 0.5 * ((double)xs + (double)ys)) * kLog2e, tab));
+}
+
+template <typename T>
+__device__ __forceinline__ T tt_entry(const T* A, const T* B, int ty, int tx, int zs, int d, int dp, int base, T p0, T p1, double tab) {
   const T* a0 = A + ty * dp; const T* a1 = A + (kTT + ty) * dp;
   const T* b0 = B + tx * dp; const T* b1 = B + (kTT + tx) * dp;
   if (zs == 2) {
     T d00 = T(0), d01 = T(0), d10 = T(0), d11 = T(0), ua0 = T(0), ua1 = T(0), vb0 = T(0), vb1 = T(0);
+#pragma unroll 4
     for (int q = 0; q < d; ++q) {
       const T x0 = a0[q], x1 = a1[q], y0 = b0[q], y1 = b1[q];
       d00 = gfma<T>(x0, y0, d00); d01 = gfma<T>(x0, y1, d01); d10 = gfma<T>(x1, y0, d10); d11 = gfma<T>(x1, y1, d11);
       ua0 = gfma<T>(x0, x0, ua0); ua1 = gfma<T>(x1, x1, ua1); vb0 = gfma<T>(y0, y0, vb0); vb1 = gfma<T>(y1, y1, vb1);
     }
+    if (sizeof(T) == 8 && base == GPSIG_BASE_RBF)      // 9 FP64 instructions per value against ~35 of exp() behind a call
+      return tt_rbf64<T>(d11, ua1, vb1, tab) + tt_rbf64<T>(d00, ua0, vb0, tab) - tt_rbf64<T>(d10, ua1, vb0, tab) - tt_rbf64<T>(d01, ua0, vb1, tab);
     return base_eval_call<T>(base, p0, p1, d11, ua1, vb1) + base_eval_call<T>(base, p0, p1, d00, ua0, vb0)
          - base_eval_call<T>(base, p0, p1, d10, ua1, vb0) - base_eval_call<T>(base, p0, p1, d01, ua0, vb1);
   }
   T d00 = T(0), ua0 = T(0), vb0 = T(0);
+#pragma unroll 4
   for (int q = 0; q < d; ++q) { const T x0 = a0[q], y0 = b0[q]; d00 = gfma<T>(x0, y0, d00); ua0 = gfma<T>(x0, x0, ua0); vb0 = gfma<T>(y0, y0, vb0); }
+  if (sizeof(T) == 8 && base == GPSIG_BASE_RBF) return tt_rbf64<T>(d00, ua0, vb0, tab);
   return base_eval_call<T>(base, p0, p1, d00, ua0, vb0);
 }
 
@@ -76,6 +90,7 @@ __global__ void __launch_bounds__(256) tens_tens_tile_kernel(const TensTensParam
   const T* Z = static_cast<const T*>(P.Z);
   T* out = static_cast<T*>(P.out);
   const bool live = a < Mz && b < Mz;
+  const double tab = sizeof(T) == 8 ? exp2((double)(tid & 31) * (1.0 / 32.0)) : 0.0;
   const size_t MM = (size_t)Mz * Mz, ab = (size_t)a * Mz + b;
   T acc = ls ? ls[0] : T(1);
   if (P.return_levels && live) out[ab] = acc;
@@ -87,7 +102,7 @@ __global__ void __launch_bounds__(256) tens_tens_tile_kernel(const TensTensParam
       tt_stage<T>(A, Z, len, k, a0, Mz, zs, d, dp, tid);
       tt_stage<T>(B, Z, len, k, b0, Mz, zs, d, dp, tid);
       __syncthreads();
-      const T Mt = tt_entry<T>(A, B, ty, tx, zs, d, dp, P.base, p0, p1);
+      const T Mt = tt_entry<T>(A, B, ty, tx, zs, d, dp, P.base, p0, p1, tab);
       R = jj == 0 ? Mt : Mt * R;                                                                     // signature_algs.py:91-96
     }
     if (ls) R *= ls[i];
@@ -100,7 +115,7 @@ __global__ void __launch_bounds__(256) tens_tens_tile_kernel(const TensTensParam
 // once (slots = m per side: the rows' tiles once, the columns' tiles once per column tile: three barriers and one round of
 // global loads per column tile instead of 2 I + 1 and I); otherwise component k's tiles and one other component at a time.
 template <typename T, int NQ, bool ALL>
-__global__ void __launch_bounds__(256) tens_tens_tile_vjp_kernel(const TensTensVjpParams P, const int slots) {
+__global__ void __launch_bounds__(256, NQ <= 2 ? 3 : 2) tens_tens_tile_vjp_kernel(const TensTensVjpParams P, const int slots) {
   extern __shared__ __align__(16) unsigned char tt_smem[];
   const int d = P.d, zs = P.zs, dp = d + 1, Mz = P.Mz;
   const size_t tile = (size_t)zs * kTT * dp;
@@ -121,6 +136,8 @@ __global__ void __launch_bounds__(256) tens_tens_tile_vjp_kernel(const TensTensV
   for (int s = 0; s < 2; ++s)
 #pragma unroll
     for (int c = 0; c < NQ; ++c) acc[s][c] = T(0);
+  const double tab = sizeof(T) == 8 ? exp2((double)(tid & 31) * (1.0 / 32.0)) : 0.0;
+  const bool rbf64 = sizeof(T) == 8 && P.base == GPSIG_BASE_RBF;
   const int kk = ALL ? k - k0 : 0;
   T* Ak = A + kk * tile; T* Bk = B + kk * tile;
   if (ALL) { for (int jj = 0; jj < I; ++jj) tt_stage<T>(A + jj * tile, Z, nullptr, k0 + jj, a0, Mz, zs, d, dp, tid); }
@@ -134,7 +151,7 @@ __global__ void __launch_bounds__(256) tens_tens_tile_vjp_kernel(const TensTensV
       for (int jj = 0; jj < I; ++jj) tt_stage<T>(B + jj * tile, Z, nullptr, k0 + jj, b0, Mz, zs, d, dp, tid);
       __syncthreads();
       for (int jj = 0; jj < I; ++jj)
-        if (jj != kk) w *= tt_entry<T>(A + jj * tile, B + jj * tile, ty, tx, zs, d, dp, P.base, p0, p1);
+        if (jj != kk) w *= tt_entry<T>(A + jj * tile, B + jj * tile, ty, tx, zs, d, dp, P.base, p0, p1, tab);
     } else {
       T* Aj = A + tile; T* Bj = B + tile;
       for (int jj = 0; jj < I; ++jj) {
@@ -143,7 +160,7 @@ __global__ void __launch_bounds__(256) tens_tens_tile_vjp_kernel(const TensTensV
         tt_stage<T>(Aj, Z, nullptr, k0 + jj, a0, Mz, zs, d, dp, tid);
         tt_stage<T>(Bj, Z, nullptr, k0 + jj, b0, Mz, zs, d, dp, tid);
         __syncthreads();
-        w *= tt_entry<T>(Aj, Bj, ty, tx, zs, d, dp, P.base, p0, p1);
+        w *= tt_entry<T>(Aj, Bj, ty, tx, zs, d, dp, P.base, p0, p1, tab);
       }
       __syncthreads();                                                 // the previous tile's accumulation is done with Bk, Wf, Wx
       tt_stage<T>(Bk, Z, nullptr, k, b0, Mz, zs, d, dp, tid);
@@ -155,6 +172,7 @@ __global__ void __launch_bounds__(256) tens_tens_tile_vjp_kernel(const TensTensV
       const T* x0p = Ak + ty * dp; const T* x1p = Ak + (kTT + ty) * dp;
       const T* y0p = Bk + tx * dp; const T* y1p = Bk + (kTT + tx) * dp;
       if (zs == 2) {
+#pragma unroll 4
         for (int q = 0; q < d; ++q) {
           const T x0 = x0p[q], x1 = x1p[q], y0 = y0p[q], y1 = y1p[q];
           dt[0][0] = gfma<T>(x0, y0, dt[0][0]); dt[0][1] = gfma<T>(x0, y1, dt[0][1]);
@@ -169,7 +187,10 @@ __global__ void __launch_bounds__(256) tens_tens_tile_vjp_kernel(const TensTensV
 #pragma unroll
         for (int s2 = 0; s2 < 2; ++s2) {
           T wf = T(0), wx = T(0);
-          if (s < zs && s2 < zs && w != T(0)) {
+          if (rbf64) {                                   // every lane evaluates (table shuffle), f_dot = f, f_|x|^2 = -f / 2
+            const T f = tt_rbf64<T>(dt[s][s2], uq[s], vq[s2], tab);
+            if (s < zs && s2 < zs) { wf = ((zs == 2 && s != s2) ? -w : w) * f; wx = -wf; }
+          } else if (s < zs && s2 < zs && w != T(0)) {
             const T sgn = (zs == 2 && s != s2) ? T(-1) : T(1);
             T fd, fx, fy;
             base_partials_call<T>(P.base, p0, p1, dt[s][s2], uq[s], vq[s2], fd, fx, fy);
@@ -187,14 +208,25 @@ __global__ void __launch_bounds__(256) tens_tens_tile_vjp_kernel(const TensTensV
       const T* wf = Wf + (ty * 2 + s) * kTT * 2;
       const T* wx = Wx + (ty * 2 + s) * kTT * 2;
       T sx = T(0);
-      for (int bb = 0; bb < kTT; ++bb)
-        for (int s2 = 0; s2 < zs; ++s2) {
-          const T f = wf[bb * 2 + s2];
-          sx += wx[bb * 2 + s2];
-          const T* zb = Bk + (s2 * kTT + bb) * dp;
+      if (zs == 2) {
 #pragma unroll
-          for (int c = 0; c < NQ; ++c) { const int q = tx + 16 * c; if (q < d) acc[s][c] = gfma<T>(f, zb[q], acc[s][c]); }
+        for (int bb = 0; bb < kTT; ++bb) {
+          const T f0 = wf[bb * 2], f1 = wf[bb * 2 + 1];
+          sx += wx[bb * 2] + wx[bb * 2 + 1];
+          const T* z0 = Bk + bb * dp; const T* z1 = Bk + (kTT + bb) * dp;
+#pragma unroll
+          for (int c = 0; c < NQ; ++c) { const int q = tx + 16 * c; if (q < d) acc[s][c] = gfma<T>(f1, z1[q], gfma<T>(f0, z0[q], acc[s][c])); }
         }
+      } else {
+#pragma unroll
+        for (int bb = 0; bb < kTT; ++bb) {
+          const T f0 = wf[bb * 2];
+          sx += wx[bb * 2];
+          const T* z0 = Bk + bb * dp;
+#pragma unroll
+          for (int c = 0; c < NQ; ++c) { const int q = tx + 16 * c; if (q < d) acc[s][c] = gfma<T>(f0, z0[q], acc[s][c]); }
+        }
+      }
       axs[s] += sx;
     }
   }
@@ -229,7 +261,7 @@ bool launch_tens_tens_tile_vjp(const TensTensVjpParams& P, cudaStream_t s) {
   const int slots = all ? P.m : 2;
   const size_t smem = tt_tile_smem(P.d, P.zs, sizeof(T), slots, true);
   if (P.d > 128 || smem > kMaxSmem) return false;
-  if (sizeof(T) == 4 && P.d <= 8) return false;      // float32, d <= 8: the register kernel is faster (500 tensors, m = 4: 0.30 against 0.39 ms)
+  if (sizeof(T) == 4 && P.d <= 4) return false;      // float32, d <= 4: the register kernel is faster (500 tensors, m = 4, d = 4: 0.16 against 0.24 ms; d = 8: 0.30 against 0.26)
   const int TT = P.m * (P.m + 1) / 2;
   const dim3 grid((P.Mz + kTT - 1) / kTT, TT);
 #define GPSIG_TTV2(NQ_, ALL_)                                                                                                      \
