@@ -177,7 +177,7 @@ int launch_tens_seq_lifted_gd(const TensSeqParams& P, int DP, T* C, const T* g, 
   if (int rc = tens_lift_gemm<T, 7, 7>(P, DP, 0, ncols, C, s)) return rc;
   if (g) {
     const int by_value = P.base == GPSIG_BASE_RBF ? 1 : 0;
-    dim3 grid((unsigned)((ncols + 127) / 128), (unsigned)P.Mz);
+    dim3 grid((unsigned)((ncols + 127) / 128), (unsigned)P.Mz, (unsigned)P.m);      // one thread per (sequence, tensor, level)
     if (P.m <= 2) tens_lift_reverse_kernel<T, 2><<<grid, 128, 0, s>>>(P, ncols, C, g, by_value);
     else if (P.m <= 4) tens_lift_reverse_kernel<T, 4><<<grid, 128, 0, s>>>(P, ncols, C, g, by_value);
     else if (P.m <= 6) tens_lift_reverse_kernel<T, 6><<<grid, 128, 0, s>>>(P, ncols, C, g, by_value);

@@ -238,105 +238,94 @@ __global__ void __launch_bounds__(128) tens_lift_recur_kernel(const TensSeqParam
   if (!P.return_levels) static_cast<T*>(P.out)[(size_t)z * ncols + nl] = acc;
 }
 
-// (C) reverse mode on the lifted values: one thread per (tensor z, sequence n).  C holds kappa (the forward GEMM) and is
-// overwritten IN PLACE by Gd[r, e] = dL/dkappa(r, e) (times kappa for the RBF kernel, whose partials are kappa (x - z)), from
-// which the caller forms dL/dZ = Gd X - rowsum(Gd) Z and dL/dX = Gd^T Z - colsum(Gd) X (linear: without the sums) as two plain
-// GEMMs.  Forward recursion S_jj(l) = S_jj(l-1) + D_jj(l) S_{jj-1}(l-1); the states are rebuilt backwards from the final ones
+// (C) reverse mode on the lifted values: one thread per (tensor z, sequence n, LEVEL I) - the levels' recursions are
+// independent of each other (level I only touches its own I components), so a thread keeps I <= MMAX values per array instead
+// of m (m + 1) / 2 (the first version, one thread per (z, n), spilled 700 bytes at m = 4 in float64 and had a quarter of the
+// threads: 1.10 ms at minibatch 50, d = 28).  C holds kappa (the forward GEMM) and is overwritten IN PLACE by
+// Gd[r, e] = dL/dkappa(r, e) (times kappa for the RBF kernel, whose partials are kappa (x - z)), from which the caller forms
+// dL/dZ = Gd X - rowsum(Gd) Z and dL/dX = Gd^T Z - colsum(Gd) X (linear: without the sums) as two plain GEMMs.  Forward
+// recursion S_jj(l) = S_jj(l-1) + D_jj(l) S_{jj-1}(l-1); the states are rebuilt backwards from the final ones
 // (S_jj(l-1) = S_jj(l) - D_jj(l) S_{jj-1}(l-1)), so nothing but C is stored; adjoints lam_jj as in vjp_kernels.cuh.
 template <typename T, int MMAX>
 __global__ void __launch_bounds__(128) tens_lift_reverse_kernel(const TensSeqParams P, const int nb, T* __restrict__ C,
                                                                  const T* __restrict__ g, const int scale_by_value) {
   const int n = blockIdx.x * 128 + threadIdx.x, z = blockIdx.y;
+  const int I = P.m - (int)blockIdx.z;                  // the top level (the longest chain) first
   if (n >= nb) return;
-  const int L = P.L, Mz = P.Mz, zs = P.zs, m = P.m;
+  const int L = P.L, Mz = P.Mz, zs = P.zs;
   const size_t E = (size_t)L * nb;
-  constexpr int TT = MMAX * (MMAX + 1) / 2;
   const bool diff = P.difference != 0;
-  T* base = C + n;
-  auto row = [&](int c, int s) -> size_t { return ((size_t)(c * zs + s) * Mz + z) * E; };
-  T S[TT], Mp[TT];
+  const int kb = I * (I - 1) / 2;
+  T* base = C + n + ((size_t)kb * zs * Mz + z) * E;     // component kb + jj, end s: + (jj zs + s) Mz E
+  const size_t rs = (size_t)Mz * E;
+  T S[MMAX], Mp[MMAX];
 #pragma unroll
-  for (int k = 0; k < TT; ++k) { S[k] = T(0); Mp[k] = T(0); }
+  for (int k = 0; k < MMAX; ++k) { S[k] = T(0); Mp[k] = T(0); }
   // pass 1: the final running sums
   for (int l = 0; l < L; ++l) {
-    const size_t col = (size_t)l * nb;
+    const T* col = base + (size_t)l * nb;
     const bool first = diff && l == 0;
 #pragma unroll
-    for (int I = 1; I <= MMAX; ++I) {
-      if (I > m) break;
-      const int k0 = I * (I - 1) / 2;
-#pragma unroll
-      for (int jj = I - 1; jj >= 0; --jj) {
-        const int c = k0 + jj;
-        const T Mt = zs == 2 ? base[row(c, 1) + col] - base[row(c, 0) + col] : base[row(c, 0) + col];
-        T D = Mt;
-        if (diff) { D = Mt - Mp[c]; Mp[c] = Mt; }
-        if (!first) { if (jj > 0) S[c] = gfma<T>(D, S[c - 1], S[c]); else S[c] += D; }
-      }
+    for (int jj = MMAX - 1; jj >= 0; --jj) {
+      if (jj >= I) continue;
+      const T Mt = zs == 2 ? col[(size_t)(jj * 2 + 1) * rs] - col[(size_t)(jj * 2) * rs] : col[(size_t)jj * rs];
+      T D = Mt;
+      if (diff) { D = Mt - Mp[jj]; Mp[jj] = Mt; }
+      if (!first) { if (jj > 0) S[jj] = gfma<T>(D, S[jj - 1], S[jj]); else S[jj] += D; }
     }
   }
-  // pass 2: backwards; Mp holds Mt(L-1) (difference mode)
-  T lam[TT], aDn[TT], k1[TT], k0v[TT];
+  // pass 2: backwards
+  T lam[MMAX], aDn[MMAX], k1[MMAX], k0v[MMAX];
 #pragma unroll
-  for (int k = 0; k < TT; ++k) { lam[k] = T(0); aDn[k] = T(0); }
+  for (int k = 0; k < MMAX; ++k) { lam[k] = T(0); aDn[k] = T(0); k0v[k] = T(0); k1[k] = T(0); }
   const int ncols = P.col_end - P.col_begin;
+  const T gI = g[((size_t)I * Mz + z) * ncols + n];
 #pragma unroll
-  for (int I = 1; I <= MMAX; ++I)
-    if (I <= m) lam[I * (I - 1) / 2 + I - 1] = g[((size_t)I * Mz + z) * ncols + n];
+  for (int jj = 0; jj < MMAX; ++jj) if (jj == I - 1) lam[jj] = gI;
   {                                                     // kappa values of the last time step
-    const size_t col = (size_t)(L - 1) * nb;
+    const T* col = base + (size_t)(L - 1) * nb;
 #pragma unroll
-    for (int c = 0; c < TT; ++c) {
-      if (c < m * (m + 1) / 2) { k0v[c] = base[row(c, 0) + col]; k1[c] = zs == 2 ? base[row(c, 1) + col] : T(0); }
-      else { k0v[c] = T(0); k1[c] = T(0); }
-    }
+    for (int jj = 0; jj < MMAX; ++jj)
+      if (jj < I) { k0v[jj] = col[(size_t)(jj * zs) * rs]; if (zs == 2) k1[jj] = col[(size_t)(jj * zs + 1) * rs]; }
   }
   for (int l = L - 1; l >= 0; --l) {
-    const size_t col = (size_t)l * nb;
+    T* col = base + (size_t)l * nb;
     const bool first = diff && l == 0;
-    T p1[TT], p0[TT];                                   // kappa values of time l - 1
+    T p1[MMAX], p0[MMAX];                               // kappa values of time l - 1, in flight while time l is worked on
+#pragma unroll
+    for (int jj = 0; jj < MMAX; ++jj) { p0[jj] = T(0); p1[jj] = T(0); }
     if (l > 0) {
-      const size_t colp = (size_t)(l - 1) * nb;
+      const T* colp = col - nb;
 #pragma unroll
-      for (int c = 0; c < TT; ++c) {
-        if (c < m * (m + 1) / 2) { p0[c] = base[row(c, 0) + colp]; p1[c] = zs == 2 ? base[row(c, 1) + colp] : T(0); }
-        else { p0[c] = T(0); p1[c] = T(0); }
+      for (int jj = 0; jj < MMAX; ++jj)
+        if (jj < I) { p0[jj] = colp[(size_t)(jj * zs) * rs]; if (zs == 2) p1[jj] = colp[(size_t)(jj * zs + 1) * rs]; }
+    }
+    T Sprev_below = T(1);                               // S_{jj-1}(l-1), S_{-1} = 1
+#pragma unroll
+    for (int jj = 0; jj < MMAX; ++jj) {                 // ascending: lam[jj-1] is used before it is updated
+      if (jj >= I) continue;
+      const T Mt = zs == 2 ? k1[jj] - k0v[jj] : k0v[jj];
+      const T Mtp = zs == 2 ? p1[jj] - p0[jj] : p0[jj];
+      const T D = diff ? Mt - Mtp : Mt;
+      T aD = T(0);
+      T Sprev = S[jj];
+      if (!first) {
+        Sprev = jj > 0 ? gfma<T>(-D, Sprev_below, S[jj]) : S[jj] - D;          // S_jj(l-1)
+        aD = jj > 0 ? lam[jj] * Sprev_below : lam[jj];
+        if (jj > 0) lam[jj - 1] = gfma<T>(lam[jj], D, lam[jj - 1]);
       }
-    } else {
-#pragma unroll
-      for (int c = 0; c < TT; ++c) { p0[c] = T(0); p1[c] = T(0); }
+      // dL/dMt_jj(l) = aD(l) - aD(l+1) in difference mode, aD(l) otherwise
+      const T gM = diff ? aD - aDn[jj] : aD;
+      aDn[jj] = aD;
+      if (zs == 2) {
+        col[(size_t)(jj * 2 + 1) * rs] = scale_by_value ? gM * k1[jj] : gM;
+        col[(size_t)(jj * 2) * rs] = scale_by_value ? -gM * k0v[jj] : -gM;
+      } else col[(size_t)jj * rs] = scale_by_value ? gM * k0v[jj] : gM;
+      Sprev_below = Sprev;                              // becomes S_jj(l-1) for the component above
+      S[jj] = Sprev;
     }
 #pragma unroll
-    for (int I = 1; I <= MMAX; ++I) {
-      if (I > m) break;
-      const int kb = I * (I - 1) / 2;
-      T Sprev_below = T(1);                             // S_{jj-1}(l-1), S_{-1} = 1
-#pragma unroll
-      for (int jj = 0; jj < I; ++jj) {                  // ascending: lam[c-1] is used before it is updated
-        const int c = kb + jj;
-        const T Mt = zs == 2 ? k1[c] - k0v[c] : k0v[c];
-        const T Mtp = zs == 2 ? p1[c] - p0[c] : p0[c];
-        const T D = diff ? Mt - Mtp : Mt;
-        T aD = T(0);
-        T Sprev = S[c];
-        if (!first) {
-          Sprev = jj > 0 ? gfma<T>(-D, Sprev_below, S[c]) : S[c] - D;          // S_c(l-1)
-          aD = jj > 0 ? lam[c] * Sprev_below : lam[c];
-          if (jj > 0) lam[c - 1] = gfma<T>(lam[c], D, lam[c - 1]);
-        }
-        // dL/dMt_c(l) = aD(l) - aD(l+1) in difference mode, aD(l) otherwise
-        const T gM = diff ? aD - aDn[c] : aD;
-        aDn[c] = aD;
-        if (zs == 2) {
-          base[row(c, 1) + col] = scale_by_value ? gM * k1[c] : gM;
-          base[row(c, 0) + col] = scale_by_value ? -gM * k0v[c] : -gM;
-        } else base[row(c, 0) + col] = scale_by_value ? gM * k0v[c] : gM;
-        Sprev_below = Sprev;                            // becomes S_{jj}(l-1) for the component above
-        S[c] = Sprev;
-      }
-    }
-#pragma unroll
-    for (int c = 0; c < TT; ++c) { k0v[c] = p0[c]; k1[c] = p1[c]; }
+    for (int jj = 0; jj < MMAX; ++jj) { k0v[jj] = p0[jj]; k1[jj] = p1[jj]; }
   }
 }
 

@@ -26,4 +26,4 @@ print("20 steps: host issue %.3f ms/step, with sync %.3f ms/step" % ((t1-t0)*50,
 with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
     for _ in range(5): full_step()
     torch.cuda.synchronize()
-print(prof.key_averages().table(sort_by="cpu_time_total", row_limit=40, max_name_column_width=60))
+print(prof.key_averages().table(sort_by=os.environ.get("GPSIG_PROF_SORT", "cuda_time_total"), row_limit=40, max_name_column_width=60))
