@@ -159,6 +159,15 @@ int launch_tens_seq_lifted(const TensSeqParams& P, int DP, void* scratch, size_t
     const int nb = ncols - n0 < nbmax ? ncols - n0 : nbmax;
     if (int rc = tens_lift_gemm<T, 7, 7>(P, DP, n0, nb, C, s)) return rc;
     dim3 grid((unsigned)((nb + 127) / 128), (unsigned)P.Mz);
+    if (P.return_levels && (long)nb * P.Mz < 148L * 2048) {      // raw levels of a small block: one thread per level as well
+      grid.z = (unsigned)P.m;
+      if (P.m <= 2) tens_lift_recur_level_kernel<T, 2><<<grid, 128, 0, s>>>(P, n0, nb, C);
+      else if (P.m <= 4) tens_lift_recur_level_kernel<T, 4><<<grid, 128, 0, s>>>(P, n0, nb, C);
+      else if (P.m <= 6) tens_lift_recur_level_kernel<T, 6><<<grid, 128, 0, s>>>(P, n0, nb, C);
+      else tens_lift_recur_level_kernel<T, 8><<<grid, 128, 0, s>>>(P, n0, nb, C);
+      GPSIG_LAUNCH_CHECK("tens_lift_recur_level_kernel");
+      continue;
+    }
     if (P.m <= 2) tens_lift_recur_kernel<T, 2><<<grid, 128, 0, s>>>(P, n0, nb, C);
     else if (P.m <= 4) tens_lift_recur_kernel<T, 4><<<grid, 128, 0, s>>>(P, n0, nb, C);
     else if (P.m <= 6) tens_lift_recur_kernel<T, 6><<<grid, 128, 0, s>>>(P, n0, nb, C);

@@ -238,6 +238,46 @@ __global__ void __launch_bounds__(128) tens_lift_recur_kernel(const TensSeqParam
   if (!P.return_levels) static_cast<T*>(P.out)[(size_t)z * ncols + nl] = acc;
 }
 
+// (B') per-level output (the differentiable path asks for raw levels): one thread per (tensor z, sequence n, LEVEL I), the
+// levels being independent chains - m times the threads of (B) for the small blocks of a training minibatch
+template <typename T, int MMAX>
+__global__ void __launch_bounds__(128) tens_lift_recur_level_kernel(const TensSeqParams P, const int n0, const int nb, const T* __restrict__ C) {
+  const int n = blockIdx.x * 128 + threadIdx.x, z = blockIdx.y;
+  const int I = P.m - (int)blockIdx.z;
+  if (n >= nb) return;
+  const int L = P.L, Mz = P.Mz, zs = P.zs;
+  const size_t E = (size_t)L * nb, rs = (size_t)Mz * E;
+  const T* base = C + n + ((size_t)(I * (I - 1) / 2) * zs * Mz + z) * E;
+  const bool diff = P.difference != 0;
+  T S[MMAX], Mp[MMAX];
+#pragma unroll
+  for (int k = 0; k < MMAX; ++k) { S[k] = T(0); Mp[k] = T(0); }
+  for (int l = 0; l < L; ++l) {
+    const T* col = base + (size_t)l * nb;
+    const bool first = diff && l == 0;
+#pragma unroll
+    for (int jj = MMAX - 1; jj >= 0; --jj) {
+      if (jj >= I) continue;
+      const T Mt = zs == 2 ? col[(size_t)(jj * 2 + 1) * rs] - col[(size_t)(jj * 2) * rs] : col[(size_t)jj * rs];      // kernels.py:331
+      T D = Mt;
+      if (diff) { D = Mt - Mp[jj]; Mp[jj] = Mt; }                                                                    // signature_algs.py:114
+      if (!first) { if (jj > 0) S[jj] = gfma<T>(D, S[jj - 1], S[jj]); else S[jj] += D; }                             // signature_algs.py:123
+    }
+  }
+  const int ncols = P.col_end - P.col_begin;
+  const int nl = n0 + n, ng = P.col_begin + nl;
+  auto emit = [&](int lvl, T v) {                                                                                    // kernels.py:604-620
+    if (P.norm_x) v = v / gsqrt<T>(static_cast<const T*>(P.norm_x)[(size_t)lvl * P.N + ng]);
+    if (P.level_scale) v *= static_cast<const T*>(P.level_scale)[lvl];
+    static_cast<T*>(P.out)[((size_t)lvl * Mz + z) * ncols + nl] = v;
+  };
+  if (I == 1) emit(0, T(1));
+  T top = T(0);
+#pragma unroll
+  for (int jj = 0; jj < MMAX; ++jj) if (jj == I - 1) top = S[jj];
+  emit(I, top);                                                                                                      // signature_algs.py:125
+}
+
 // (C) reverse mode on the lifted values: one thread per (tensor z, sequence n, LEVEL I) - the levels' recursions are
 // independent of each other (level I only touches its own I components), so a thread keeps I <= MMAX values per array instead
 // of m (m + 1) / 2 (the first version, one thread per (z, n), spilled 700 bytes at m = 4 in float64 and had a quarter of the
