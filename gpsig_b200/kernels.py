@@ -485,6 +485,24 @@ class SignatureKernel:
                                level_scale=self._level_scale(Xs), return_levels=return_levels, cols=cols,
                                **self._kw(Xs))
 
+    def graphed_tens_n_seq_covs(self, Z, X, full_X_cov=False, increments=False):
+        """``K_tens_n_seq_covs`` with its forward and its backward each captured into a CUDA graph
+        (``torch.cuda.make_graphed_callables``) for a training loop with a FIXED minibatch shape: the step is launch
+        bound at the reference's minibatch of 50 (about 45 kernels, 1.9 ms eager against 1.3 ms replayed).
+        ``Z`` [T, Mz, (2,) d] and ``X`` [N, L * d] are sample tensors on the device that require grad (their values may
+        change between calls, their shapes may not); returns ``f(Z, X) -> (Kzz, Kzx, Kxx)``, differentiable.  Tensor
+        hyper-parameters that require grad are not traced by the capture (pass plain numbers / numpy arrays, or use the
+        eager method)."""
+        if any(torch.is_tensor(t) and t.requires_grad for t in (self.variances, self.lengthscales, self.sigma)):
+            raise NotImplementedError('gpsig_b200: graphed covariances take constant hyper-parameters; '
+                                      'use K_tens_n_seq_covs for trainable lengthscales / variances / sigma')
+        if not (Z.requires_grad and X.requires_grad):
+            raise ValueError('graphed_tens_n_seq_covs: the sample Z and X must require grad')
+
+        def covs(Zt, Xt):
+            return self.K_tens_n_seq_covs(Zt, Xt, full_X_cov=full_X_cov, increments=increments)
+        return torch.cuda.make_graphed_callables(covs, (Z, X))
+
     def K_tens_n_seq_covs(self, Z, X, full_X_cov=False, return_levels=False, increments=False, presliced=False):
         """Kzz, Kzx, Kxx in one call (kernels.py:623-704)."""
         Z, X = as_device_tensor(Z, "Z"), as_device_tensor(X, "X")

@@ -307,3 +307,28 @@ def test_numpy_hyperparameters_are_copied_to_the_device_once_per_value():
     c = k._param(k.lengthscales, like)
     assert c.data_ptr() != a.data_ptr() and float(c[0]) == 0.7 and float(a[0]) == 1.3
     assert k._param(k.lengthscales, like.float()).dtype == torch.float32
+
+
+def test_graphed_covariances_match_the_eager_method():
+    """``graphed_tens_n_seq_covs``: forward and backward as CUDA graphs (make_graphed_callables), fed new values."""
+    import warnings
+    from gpsig_b200 import kernels
+    warnings.filterwarnings('ignore', message="The AccumulateGrad node's stream")
+    N, L, d, m, Mz = 9, 16, 3, 3, 5
+    k = kernels.SignatureRBF(L * d, d, m, lengthscales=np.full(d, 1.2))
+    X = _dev(brownian(N, L, d, 80).reshape(N, -1)).requires_grad_(True)
+    Z = _dev(inducing_tensors(brownian(N, L, d, 80), m, Mz, True, 81)).requires_grad_(True)
+    f = k.graphed_tens_n_seq_covs(Z, X, increments=True)
+    X2 = _dev(brownian(N, L, d, 82).reshape(N, -1)).requires_grad_(True)
+    Z2 = _dev(inducing_tensors(brownian(N, L, d, 82), m, Mz, True, 83)).requires_grad_(True)
+    outs = f(Z2, X2)
+    sum((o ** 2).sum() for o in outs).backward()
+    gZ, gX = Z2.grad.clone(), X2.grad.clone()
+    Z2.grad = None
+    X2.grad = None
+    ref = k.K_tens_n_seq_covs(Z2, X2, increments=True)
+    sum((o ** 2).sum() for o in ref).backward()
+    for a, b in zip(outs, ref):
+        assert rel_err(a.detach().cpu().numpy(), b.detach().cpu().numpy()) < 1e-12
+    assert rel_err(gZ.cpu().numpy(), Z2.grad.cpu().numpy()) < 1e-10
+    assert rel_err(gX.cpu().numpy(), X2.grad.cpu().numpy()) < 1e-10

@@ -97,6 +97,14 @@ for dt in DTYPES:
             err = max(float((cX - eX).abs().max() / eX.abs().max()), float((cZ - eZ).abs().max() / eZ.abs().max()))
             print("%s minibatch %d: K_tens_n_seq_covs fwd+bwd as a CUDA graph %.3f ms (grads against eager: %.1e)" %
                   (name, nb, ev_time(graph.replay, reps=20), err), flush=True)
+            del graph
+            fgr = k.graphed_tens_n_seq_covs(Zt, X2, increments=True)       # forward / backward graphs behind autograd
+
+            def graphed_step():
+                X2.grad = None; Zt.grad = None
+                Kzz, Kzx, Kxx = fgr(Zt, X2)
+                (Kzz.sum() + Kzx.sum() + Kxx.sum()).backward()
+            print("%s minibatch %d: kern.graphed_tens_n_seq_covs fwd+bwd %.3f ms" % (name, nb, ev_time(graphed_step, reps=20)), flush=True)
         except Exception as e:       # noqa: BLE001
             print("CUDA graph capture failed: %r" % (e,), flush=True)
 
