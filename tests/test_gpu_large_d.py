@@ -256,3 +256,22 @@ def test_kzz_tiles_match_the_first_kernels(dtype, base, d, Mz, increments, monke
     for a, b, tol in zip(new, old, tols):
         assert np.isfinite(a).all()
         assert rel_err(a, b) < tol
+
+
+@pytest.mark.parametrize("m,d", [(1, 5), (5, 8), (6, 20)])
+def test_kzz_tiles_other_level_counts(m, d, monkeypatch):
+    """The tiled Kzz kernels at m = 1 (no other component), 5 and 6 levels against the first kernels and the oracle."""
+    from gpsig_b200 import ops
+    from oracle import trunc_np
+    Mz = 23
+    X = brownian(5, 10, d, 3) / np.sqrt(d / 8.0)
+    Zn = inducing_tensors(X, m, Mz, True, 4)
+    Z = _dev(Zn, torch.float64)
+    G = _dev(np.random.default_rng(5).standard_normal((m + 1, Mz, Mz)), torch.float64)
+    lev = ops.tens_tens(Z, m, increments=True, base='rbf').cpu().numpy()
+    gz = ops.tens_tens_vjp(Z, G, m, increments=True, base='rbf').cpu().numpy()
+    monkeypatch.setenv('GPSIG_TENS_TENS_OLD', '1')
+    assert rel_err(lev, ops.tens_tens(Z, m, increments=True, base='rbf').cpu().numpy()) < 1e-11
+    assert rel_err(gz, ops.tens_tens_vjp(Z, G, m, increments=True, base='rbf').cpu().numpy()) < 1e-9
+    o = trunc_np.SignatureKernelOracle(10 * d, d, m, base='rbf')
+    assert rel_err(lev, o.K_tens(Zn, return_levels=True, increments=True)) < 1e-11
