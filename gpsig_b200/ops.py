@@ -247,6 +247,9 @@ def _tens_vs_seq_vjp_lifted(Z, X, grad_levels, m, increments, base, desc):
     rbf = base == 'rbf'
     with torch.cuda.device(X.device):
         ws = workspace(wsb, X.device)
+        if rbf:
+            Zr1 = torch.cat([Zr, torch.ones((R, 1), dtype=X.dtype, device=X.device)], dim=1)
+            ones_e = torch.ones((L * min(N, cols_per_call), 1), dtype=X.dtype, device=X.device)
         for cb in range(0, N, cols_per_call):
             ce = min(N, cb + cols_per_call)
             C = ce - cb
@@ -255,11 +258,14 @@ def _tens_vs_seq_vjp_lifted(Z, X, grad_levels, m, increments, base, desc):
             check(fn(desc, ptr(Z), Mz, int(increments), ptr(X), N, L, d, cb, ce, ptr(g), ptr(Gd), ptr(ws), wsb,
                      stream_handle(X.device)))
             Xe = X[cb:ce].permute(1, 0, 2).reshape(L * C, d)                              # column e = l C + n
-            dZ = Gd @ Xe
-            dX = Gd.t() @ Zr
-            if rbf:
-                dZ -= Gd.sum(dim=1, keepdim=True) * Zr
-                dX -= Gd.sum(dim=0)[:, None] * Xe
+            if rbf:                                     # the row / column sums ride along as one more GEMM column of ones
+                P = Gd @ torch.cat([Xe, ones_e[:L * C]], dim=1)
+                Q = Gd.t() @ Zr1
+                dZ = P[:, :d] - P[:, d:] * Zr
+                dX = Q[:, :d] - Q[:, d:] * Xe
+            else:
+                dZ = Gd @ Xe
+                dX = Gd.t() @ Zr
             gZr += dZ
             gradX[cb:ce] = dX.reshape(L, C, d).permute(1, 0, 2)
             del Gd
